@@ -1,0 +1,129 @@
+/*
+ * rthc.h -- C ABI of libreportree_hc.so: the B200 (sm_100a) replacement for the
+ * numeric layer underneath ReporTree's scripts/partitioning_HC.py.
+ *
+ * The reference has no FFI for this path; the seams these entry points replace are
+ * (citations relative to the reference tree):
+ *
+ *   rthc_set_profiles_i32 + rthc_distance
+ *        <- the `cgmlst-dists` subprocess and the 2,000-column chunk/sum loop,
+ *           scripts/partitioning_HC.py:489-516 (call at :502); same seam in
+ *           scripts/partitioning_grapetree.py:452-483 (call at :466)
+ *   rthc_copy_rows_u16 / rthc_get_condensed_u16
+ *        <- `<out>_dist_hamming.tsv` write + re-read (:518-520) and
+ *           scipy.spatial.distance.squareform in dist_mx() (:173-188)
+ *   rthc_set_condensed_f64
+ *        <- the `-d_mx` entry (:522-525) feeding dist_mx() (:186)
+ *   rthc_linkage
+ *        <- scipy.cluster.hierarchy.linkage(y, method) in hcluster() (:197) and
+ *           maxdists(Z)[-1] (:198) (Z[:,2] is monotone for the supported methods)
+ *   rthc_cut
+ *        <- scipy.cluster.hierarchy.fcluster(Z, t, criterion="distance") at
+ *           :649, :689, :722, :751
+ *
+ * Conventions: every function returns 0 on success or a negative RTHC_E_* code;
+ * rthc_last_error() gives the message.  No C++ exceptions cross the ABI.  The caller
+ * allocates every host buffer; the library owns all device memory inside the context.
+ * A context is bound to one CUDA device, is not thread-safe, and every call is
+ * synchronous on return.  There is NO CPU fallback: without a usable CUDA device
+ * rthc_create() fails.
+ */
+#ifndef RTHC_H
+#define RTHC_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct rthc_ctx rthc_ctx;
+
+enum {
+    RTHC_OK = 0,
+    RTHC_E_CUDA = -1,      /* CUDA runtime error (message has the CUDA string)    */
+    RTHC_E_ARG = -2,       /* bad argument                                         */
+    RTHC_E_STATE = -3,     /* call order violated (e.g. cut before linkage)        */
+    RTHC_E_RANGE = -4,     /* input outside the supported range (see message)      */
+    RTHC_E_NOMEM = -5
+};
+
+/* linkage methods (names follow scipy / --HC-threshold) */
+enum { RTHC_SINGLE = 0, RTHC_COMPLETE = 1, RTHC_AVERAGE = 2, RTHC_WEIGHTED = 3 };
+
+/* single-linkage algorithm selection for rthc_linkage(RTHC_SINGLE):
+ *   RTHC_SL_BORUVKA : GPU Boruvka MST under the total order (w, i, j); membership at
+ *                     every threshold equals scipy's, fcluster ids may differ on ties.
+ *   RTHC_SL_PRIM    : device Prim in scipy's visiting order -> Z identical to scipy's
+ *                     (byte-identical cluster_<id> names and Newick).                  */
+enum { RTHC_SL_BORUVKA = 0, RTHC_SL_PRIM = 1 };
+
+/* ---- lifetime -------------------------------------------------------------- */
+int rthc_create(rthc_ctx **out, int device);
+void rthc_destroy(rthc_ctx *ctx);
+const char *rthc_last_error(const rthc_ctx *ctx);   /* ctx may be NULL: last create error */
+int rthc_version(void);
+
+/* ---- sharding (multi-GPU): this context owns 128-sample tile-rows r with
+ *      owner(r) == rank under the balanced pairing (r, B-1-r) round-robin.
+ *      Default rank 0 / world 1 = everything.  Call before rthc_set_profiles_i32. */
+int rthc_set_shard(rthc_ctx *ctx, int rank, int world);
+
+/* ---- distance half ----------------------------------------------------------
+ * codes: n x L row-major int32 allele codes, 0 (or negative) = missing.
+ * Copies H2D, dense-ranks every locus on the device (uint16, 0 = missing) and packs
+ * bit planes.  Loci with <= 1 distinct called allele cannot contribute and are dropped. */
+int rthc_set_profiles_i32(rthc_ctx *ctx, const int32_t *codes_rowmajor, int64_t n, int64_t L);
+/* same, but the matrix is already in device memory (n x L row-major int32) */
+int rthc_set_profiles_i32_device(rthc_ctx *ctx, const void *dev_codes_rowmajor, int64_t n, int64_t L);
+
+/* d(i,j) = #{l : a_il != a_jl, a_il != 0, a_jl != 0} for every owned pair, written to
+ * the device-resident condensed uint16 matrix (scipy pdist order for a full shard). */
+int rthc_distance(rthc_ctx *ctx);
+
+/* number of condensed entries this context owns (n(n-1)/2 for a full shard) */
+int64_t rthc_owned_pairs(const rthc_ctx *ctx);
+/* full condensed vector (scipy order), full shard only; out has n(n-1)/2 entries */
+int rthc_get_condensed_u16(rthc_ctx *ctx, uint16_t *out);
+/* owned part of the condensed matrix, rows in increasing order; out has rthc_owned_pairs() */
+int rthc_get_owned_condensed_u16(rthc_ctx *ctx, uint16_t *out);
+/* rows [row0, row0+nrows) of the SQUARE matrix (nrows x n, uint16), full shard only:
+ * the block the `_dist_hamming.tsv` writer streams.                                 */
+int rthc_copy_rows_u16(rthc_ctx *ctx, int64_t row0, int64_t nrows, uint16_t *out);
+/* distances of an arbitrary pair list straight from the uint16 codes (independent
+ * scalar kernel; used to cross-check the bit-sliced kernel at sizes no CPU can).    */
+int rthc_direct_pairs(rthc_ctx *ctx, const int32_t *pi, const int32_t *pj, int64_t npairs,
+                      int32_t *out);
+
+/* `-d_mx` entry: externally supplied condensed distances (scipy order, n(n-1)/2).
+ * Values must be non-negative integers <= 65535 for single/complete; any finite
+ * non-negative double for average/weighted.                                         */
+int rthc_set_condensed_f64(rthc_ctx *ctx, const double *y, int64_t n);
+
+/* ---- clustering half --------------------------------------------------------- */
+int rthc_set_single_algo(rthc_ctx *ctx, int algo);
+/* Z_out: (n-1) x 4 float64, scipy linkage layout.  Full shard only.               */
+int rthc_linkage(rthc_ctx *ctx, int method, double *Z_out);
+/* multi-GPU single linkage: minimum spanning forest of the owned edges.
+ * keys_out holds up to n-1 packed edges (w<<48 | i<<24 | j); *m_out = count.       */
+int rthc_local_forest(rthc_ctx *ctx, uint64_t *keys_out, int64_t *m_out);
+/* finish single linkage from the union of the ranks' forests (m keys, any order).  */
+int rthc_linkage_from_forest(rthc_ctx *ctx, const uint64_t *keys, int64_t m, int64_t n,
+                             double *Z_out);
+/* labels_out: T x n int32, row k = fcluster(Z, t[k], "distance") of the last linkage. */
+int rthc_cut(rthc_ctx *ctx, const double *t, int T, int32_t *labels_out);
+
+/* ---- introspection ----------------------------------------------------------- */
+/* info[0]=n, [1]=L, [2]=loci kept, [3]=groups of 32 loci, [4]=plane rows,
+ * [5]=tiles launched, [6]=Boruvka rounds of the last linkage, [7]=max alleles/locus,
+ * [8]=row scans of the last merge loop                                             */
+int rthc_info(const rthc_ctx *ctx, int64_t *info, int n_info);
+/* device-side durations (CUDA events, ms) of the last call of each stage:
+ * [0]=h2d, [1]=recode+pack, [2]=distance kernel, [3]=mst/merge loop, [4]=cut,
+ * [5]=number of kernel launches since create                                       */
+int rthc_timings(const rthc_ctx *ctx, double *ms, int n_ms);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RTHC_H */

@@ -1,0 +1,328 @@
+// api.cu -- the extern "C" surface declared in include/rthc.h (context, geometry, copies).
+#include <stdarg.h>
+
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+
+#include "rthc_internal.cuh"
+
+std::string g_rthc_create_err;
+
+int rthc_fail(rthc_ctx *ctx, int code, const char *fmt, ...)
+{
+    char buf[1024];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    if (ctx) ctx->err = buf;
+    else g_rthc_create_err = buf;
+    return code;
+}
+
+extern "C" int rthc_version(void) { return 100; }
+
+extern "C" const char *rthc_last_error(const rthc_ctx *ctx)
+{
+    return ctx ? ctx->err.c_str() : g_rthc_create_err.c_str();
+}
+
+extern "C" int rthc_create(rthc_ctx **out, int device)
+{
+    if (!out) return rthc_fail(nullptr, RTHC_E_ARG, "rthc_create: out is NULL");
+    *out = nullptr;
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0)
+        return rthc_fail(nullptr, RTHC_E_CUDA, "no usable CUDA device (%s); this library has no CPU fallback",
+                         e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0");
+    if (device < 0 || device >= count)
+        return rthc_fail(nullptr, RTHC_E_ARG, "device %d out of range (0..%d)", device, count - 1);
+    rthc_ctx *ctx = new rthc_ctx();
+    ctx->device = device;
+    if ((e = cudaSetDevice(device)) != cudaSuccess || (e = cudaStreamCreate(&ctx->stream)) != cudaSuccess ||
+        (e = cudaEventCreate(&ctx->ev0)) != cudaSuccess || (e = cudaEventCreate(&ctx->ev1)) != cudaSuccess) {
+        rthc_fail(nullptr, RTHC_E_CUDA, "context setup failed: %s", cudaGetErrorString(e));
+        delete ctx;
+        return RTHC_E_CUDA;
+    }
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, device) == cudaSuccess) {
+        ctx->sm_count = prop.multiProcessorCount;
+        if (prop.major < 10) {
+            rthc_fail(nullptr, RTHC_E_CUDA, "device %d is sm_%d%d; this library is built for sm_100a only",
+                      device, prop.major, prop.minor);
+            delete ctx;
+            return RTHC_E_CUDA;
+        }
+    }
+    *out = ctx;
+    return 0;
+}
+
+static void free_distance_state(rthc_ctx *ctx)
+{
+    rthc_dev_free(&ctx->d_codes); rthc_dev_free(&ctx->d_planes);
+    rthc_dev_free(&ctx->d_grp_off); rthc_dev_free(&ctx->d_grp_np);
+    rthc_dev_free(&ctx->d_tiles); rthc_dev_free(&ctx->d_row_base);
+    rthc_dev_free(&ctx->d_owned_rows); rthc_dev_free(&ctx->d_cond);
+    rthc_dev_free(&ctx->d_cond_f64);
+    ctx->have_profiles = ctx->have_dist = false;
+}
+static void free_linkage_state(rthc_ctx *ctx)
+{
+    rthc_dev_free(&ctx->d_ea); rthc_dev_free(&ctx->d_eb); rthc_dev_free(&ctx->d_eh);
+    rthc_dev_free(&ctx->d_epre); rthc_dev_free(&ctx->d_eleaf);
+    ctx->have_linkage = false;
+}
+
+extern "C" void rthc_destroy(rthc_ctx *ctx)
+{
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    free_distance_state(ctx);
+    free_linkage_state(ctx);
+    if (ctx->ev0) cudaEventDestroy(ctx->ev0);
+    if (ctx->ev1) cudaEventDestroy(ctx->ev1);
+    if (ctx->stream) cudaStreamDestroy(ctx->stream);
+    delete ctx;
+}
+
+extern "C" int rthc_set_shard(rthc_ctx *ctx, int rank, int world)
+{
+    if (!ctx) return RTHC_E_ARG;
+    if (world < 1 || rank < 0 || rank >= world) return rthc_fail(ctx, RTHC_E_ARG, "bad shard %d/%d", rank, world);
+    ctx->rank = rank;
+    ctx->world = world;
+    return 0;
+}
+
+extern "C" int rthc_set_single_algo(rthc_ctx *ctx, int algo)
+{
+    if (!ctx) return RTHC_E_ARG;
+    if (algo != RTHC_SL_BORUVKA && algo != RTHC_SL_PRIM) return rthc_fail(ctx, RTHC_E_ARG, "bad algo %d", algo);
+    ctx->single_algo = algo;
+    return 0;
+}
+
+// tile-row r of B is owned by rank (min(r, B-1-r) mod world): rows pair up long + short
+static inline int owner_of_tile_row(int64_t r, int64_t B, int world)
+{
+    int64_t p = std::min(r, B - 1 - r);
+    return (int)(p % world);
+}
+
+// geometry of the owned part of the condensed matrix + the tile list
+static int setup_geometry(rthc_ctx *ctx, int64_t n)
+{
+    ctx->n = n;
+    ctx->n_pad = (n + RTHC_TILE - 1) / RTHC_TILE * RTHC_TILE;
+    const int64_t B = ctx->n_pad / RTHC_TILE;
+    ctx->n_tiles_edge = B;
+    ctx->h_row_base.assign((size_t)ctx->n_pad, -1);
+    ctx->h_owned_rows.clear();
+    std::vector<int64_t> owned_tile_rows;
+    int64_t off = 0;
+    for (int64_t r = 0; r < B; ++r) {
+        if (owner_of_tile_row(r, B, ctx->world) != ctx->rank) continue;
+        owned_tile_rows.push_back(r);
+        for (int64_t i = r * RTHC_TILE; i < std::min(n, (r + 1) * RTHC_TILE); ++i) {
+            ctx->h_row_base[(size_t)i] = off;
+            off += n - 1 - i;
+            ctx->h_owned_rows.push_back((int32_t)i);
+        }
+    }
+    ctx->owned_pairs = off;
+    // supertiles of 16 x 16 tiles keep the sample blocks of concurrently running CTAs in L2
+    std::vector<int2> tiles;
+    const int64_t S = 16;
+    for (size_t rc0 = 0; rc0 < owned_tile_rows.size(); rc0 += (size_t)S)
+        for (int64_t c0 = 0; c0 < B; c0 += S)
+            for (size_t q = rc0; q < std::min(owned_tile_rows.size(), rc0 + (size_t)S); ++q) {
+                const int64_t I = owned_tile_rows[q];
+                for (int64_t J = std::max(c0, I); J < std::min(B, c0 + S); ++J)
+                    tiles.push_back(make_int2((int)I, (int)J));
+            }
+    ctx->n_tiles = (int64_t)tiles.size();
+    int rc;
+    if ((rc = rthc_dev_alloc(ctx, &ctx->d_row_base, (size_t)ctx->n_pad))) return rc;
+    if ((rc = rthc_dev_alloc(ctx, &ctx->d_owned_rows, ctx->h_owned_rows.size()))) return rc;
+    if ((rc = rthc_dev_alloc(ctx, &ctx->d_tiles, tiles.size()))) return rc;
+    RTHC_CUDA(ctx, cudaMemcpyAsync(ctx->d_row_base, ctx->h_row_base.data(), sizeof(int64_t) * (size_t)ctx->n_pad,
+                                   cudaMemcpyHostToDevice, ctx->stream));
+    if (!ctx->h_owned_rows.empty())
+        RTHC_CUDA(ctx, cudaMemcpyAsync(ctx->d_owned_rows, ctx->h_owned_rows.data(),
+                                       sizeof(int32_t) * ctx->h_owned_rows.size(), cudaMemcpyHostToDevice,
+                                       ctx->stream));
+    if (!tiles.empty())
+        RTHC_CUDA(ctx, cudaMemcpyAsync(ctx->d_tiles, tiles.data(), sizeof(int2) * tiles.size(),
+                                       cudaMemcpyHostToDevice, ctx->stream));
+    RTHC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+
+static int set_profiles_common(rthc_ctx *ctx, const int32_t *d_rowmajor, int64_t n, int64_t L)
+{
+    int rc;
+    ctx->L = L;
+    if ((rc = setup_geometry(ctx, n))) return rc;
+    RTHC_CUDA(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
+    if ((rc = rthc_recode_and_pack(ctx, d_rowmajor))) return rc;
+    RTHC_CUDA(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
+    RTHC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    float ms = 0;
+    RTHC_CUDA(ctx, cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1));
+    ctx->t_ms[1] = ms;
+    ctx->have_profiles = true;
+    return 0;
+}
+
+static int check_shape(rthc_ctx *ctx, int64_t n, int64_t L)
+{
+    if (n < 2) return rthc_fail(ctx, RTHC_E_ARG, "need at least 2 samples (n=%lld)", (long long)n);
+    if (L < 1) return rthc_fail(ctx, RTHC_E_ARG, "need at least 1 locus (L=%lld)", (long long)L);
+    if (n >= (1ll << 24)) return rthc_fail(ctx, RTHC_E_RANGE, "n=%lld exceeds 2^24-1 samples", (long long)n);
+    if (L > 65535) return rthc_fail(ctx, RTHC_E_RANGE, "L=%lld exceeds 65,535 loci (uint16 distances)", (long long)L);
+    return 0;
+}
+
+extern "C" int rthc_set_profiles_i32(rthc_ctx *ctx, const int32_t *codes, int64_t n, int64_t L)
+{
+    if (!ctx || !codes) return rthc_fail(ctx, RTHC_E_ARG, "rthc_set_profiles_i32: NULL argument");
+    int rc = check_shape(ctx, n, L);
+    if (rc) return rc;
+    RTHC_CUDA(ctx, cudaSetDevice(ctx->device));
+    free_distance_state(ctx);
+    free_linkage_state(ctx);
+    int32_t *d_in = nullptr;
+    if ((rc = rthc_dev_alloc(ctx, &d_in, (size_t)(n * L)))) return rc;
+    RTHC_CUDA(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
+    RTHC_CUDA(ctx, cudaMemcpyAsync(d_in, codes, sizeof(int32_t) * (size_t)(n * L), cudaMemcpyHostToDevice,
+                                   ctx->stream));
+    RTHC_CUDA(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
+    RTHC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    float ms = 0;
+    RTHC_CUDA(ctx, cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1));
+    ctx->t_ms[0] = ms;
+    rc = set_profiles_common(ctx, d_in, n, L);
+    rthc_dev_free(&d_in);
+    return rc;
+}
+
+extern "C" int rthc_set_profiles_i32_device(rthc_ctx *ctx, const void *dev_codes, int64_t n, int64_t L)
+{
+    if (!ctx || !dev_codes) return rthc_fail(ctx, RTHC_E_ARG, "rthc_set_profiles_i32_device: NULL argument");
+    int rc = check_shape(ctx, n, L);
+    if (rc) return rc;
+    RTHC_CUDA(ctx, cudaSetDevice(ctx->device));
+    free_distance_state(ctx);
+    free_linkage_state(ctx);
+    ctx->t_ms[0] = 0;
+    RTHC_CUDA(ctx, cudaDeviceSynchronize());   // the caller's producer stream is unknown
+    return set_profiles_common(ctx, (const int32_t *)dev_codes, n, L);
+}
+
+extern "C" int rthc_distance(rthc_ctx *ctx)
+{
+    if (!ctx) return RTHC_E_ARG;
+    if (!ctx->have_profiles) return rthc_fail(ctx, RTHC_E_STATE, "rthc_distance before rthc_set_profiles_i32");
+    RTHC_CUDA(ctx, cudaSetDevice(ctx->device));
+    int rc;
+    if (!ctx->d_cond)
+        if ((rc = rthc_dev_alloc(ctx, &ctx->d_cond, (size_t)std::max<int64_t>(ctx->owned_pairs, 1)))) return rc;
+    if ((rc = rthc_run_distance(ctx))) return rc;
+    ctx->have_dist = true;
+    return 0;
+}
+
+extern "C" int64_t rthc_owned_pairs(const rthc_ctx *ctx) { return ctx ? ctx->owned_pairs : 0; }
+
+extern "C" int rthc_get_owned_condensed_u16(rthc_ctx *ctx, uint16_t *out)
+{
+    if (!ctx || !out) return rthc_fail(ctx, RTHC_E_ARG, "NULL argument");
+    if (!ctx->have_dist) return rthc_fail(ctx, RTHC_E_STATE, "no distance matrix yet");
+    RTHC_CUDA(ctx, cudaSetDevice(ctx->device));
+    RTHC_CUDA(ctx, cudaMemcpy(out, ctx->d_cond, sizeof(uint16_t) * (size_t)ctx->owned_pairs,
+                              cudaMemcpyDeviceToHost));
+    return 0;
+}
+
+extern "C" int rthc_get_condensed_u16(rthc_ctx *ctx, uint16_t *out)
+{
+    if (ctx && ctx->world != 1) return rthc_fail(ctx, RTHC_E_STATE, "full condensed copy needs a full shard");
+    return rthc_get_owned_condensed_u16(ctx, out);
+}
+
+__global__ void rthc_square_rows(const uint16_t *__restrict__ cond, int64_t n, int64_t row0, int64_t nrows,
+                                 uint16_t *__restrict__ out)
+{
+    const int64_t r = blockIdx.y;
+    const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= nrows || j >= n) return;
+    const int64_t i = row0 + r;
+    uint16_t v = 0;
+    if (i != j) {
+        const int64_t a = i < j ? i : j, b = i < j ? j : i;
+        v = cond[n * a - (a * (a + 1)) / 2 + (b - a - 1)];
+    }
+    out[r * n + j] = v;
+}
+
+extern "C" int rthc_copy_rows_u16(rthc_ctx *ctx, int64_t row0, int64_t nrows, uint16_t *out)
+{
+    if (!ctx || !out) return rthc_fail(ctx, RTHC_E_ARG, "NULL argument");
+    if (!ctx->have_dist) return rthc_fail(ctx, RTHC_E_STATE, "no distance matrix yet");
+    if (ctx->world != 1) return rthc_fail(ctx, RTHC_E_STATE, "square rows need a full shard");
+    if (row0 < 0 || nrows < 0 || row0 + nrows > ctx->n) return rthc_fail(ctx, RTHC_E_ARG, "row range out of bounds");
+    if (nrows == 0) return 0;
+    RTHC_CUDA(ctx, cudaSetDevice(ctx->device));
+    uint16_t *d_out = nullptr;
+    int rc = rthc_dev_alloc(ctx, &d_out, (size_t)(nrows * ctx->n));
+    if (rc) return rc;
+    dim3 grd((unsigned)((ctx->n + 255) / 256), (unsigned)nrows);
+    rthc_square_rows<<<grd, 256, 0, ctx->stream>>>(ctx->d_cond, ctx->n, row0, nrows, d_out);
+    RTHC_LAUNCH_CHECK(ctx);
+    RTHC_CUDA(ctx, cudaMemcpyAsync(out, d_out, sizeof(uint16_t) * (size_t)(nrows * ctx->n),
+                                   cudaMemcpyDeviceToHost, ctx->stream));
+    RTHC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    rthc_dev_free(&d_out);
+    return 0;
+}
+
+extern "C" int rthc_direct_pairs(rthc_ctx *ctx, const int32_t *pi, const int32_t *pj, int64_t np, int32_t *out)
+{
+    if (!ctx || !pi || !pj || !out) return rthc_fail(ctx, RTHC_E_ARG, "NULL argument");
+    if (!ctx->have_profiles) return rthc_fail(ctx, RTHC_E_STATE, "no profiles loaded");
+    RTHC_CUDA(ctx, cudaSetDevice(ctx->device));
+    int32_t *d_pi = nullptr, *d_pj = nullptr, *d_out = nullptr;
+    int rc;
+    if ((rc = rthc_dev_alloc(ctx, &d_pi, (size_t)np))) return rc;
+    if ((rc = rthc_dev_alloc(ctx, &d_pj, (size_t)np))) return rc;
+    if ((rc = rthc_dev_alloc(ctx, &d_out, (size_t)np))) return rc;
+    RTHC_CUDA(ctx, cudaMemcpyAsync(d_pi, pi, sizeof(int32_t) * (size_t)np, cudaMemcpyHostToDevice, ctx->stream));
+    RTHC_CUDA(ctx, cudaMemcpyAsync(d_pj, pj, sizeof(int32_t) * (size_t)np, cudaMemcpyHostToDevice, ctx->stream));
+    rc = rthc_run_direct_pairs(ctx, d_pi, d_pj, np, d_out);
+    if (!rc) {
+        cudaError_t e = cudaMemcpy(out, d_out, sizeof(int32_t) * (size_t)np, cudaMemcpyDeviceToHost);
+        if (e != cudaSuccess) rc = rthc_fail(ctx, RTHC_E_CUDA, "D2H failed: %s", cudaGetErrorString(e));
+    }
+    rthc_dev_free(&d_pi); rthc_dev_free(&d_pj); rthc_dev_free(&d_out);
+    return rc;
+}
+
+extern "C" int rthc_info(const rthc_ctx *ctx, int64_t *info, int n_info)
+{
+    if (!ctx || !info) return RTHC_E_ARG;
+    const int64_t v[9] = {ctx->n, ctx->L, ctx->L_kept, ctx->G, ctx->plane_rows, ctx->n_tiles,
+                          ctx->boruvka_rounds, ctx->max_alleles, ctx->row_scans};
+    for (int k = 0; k < n_info && k < 9; ++k) info[k] = v[k];
+    return 0;
+}
+
+extern "C" int rthc_timings(const rthc_ctx *ctx, double *ms, int n_ms)
+{
+    if (!ctx || !ms) return RTHC_E_ARG;
+    for (int k = 0; k < n_ms && k < 6; ++k) ms[k] = k == 5 ? (double)ctx->launches : ctx->t_ms[k];
+    return 0;
+}

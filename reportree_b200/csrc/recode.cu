@@ -1,0 +1,365 @@
+// recode.cu -- device-side allele re-coder.
+//
+// Replaces the per-cell text parse + implicit allele identity of `cgmlst-dists`
+// (call site scripts/partitioning_HC.py:502; contract :293-298) for the distance
+// kernel: every locus column is dense-ranked on the device into uint16 codes with 0
+// reserved for missing (equality-preserving, so distances are bit-exact), then 32 loci
+// at a time are bit-sliced into "plane" words:
+//
+//   planes[off_g + k][s]  bit l = bit k of code(sample s, locus perm[32 g + l])   k < bits_g
+//   planes[off_g + bits_g][s] bit l = (code != 0)                                  (valid plane)
+//
+// Loci are permuted by bit width (the distance is a sum over loci, so order is free),
+// which keeps every group at the minimum number of planes; loci with <= 1 distinct
+// called allele can never produce a mismatch and are dropped.
+#include <algorithm>
+#include <numeric>
+
+#include "rthc_internal.cuh"
+
+#define RANK_THREADS 1024
+#define BITMAP_BITS (1u << 20)
+#define BITMAP_WORDS (BITMAP_BITS / 32)
+
+// ---- 1. transpose n x L (row-major int32) -> L x n_pad ------------------------------
+__global__ void rthc_transpose_i32(const int32_t *__restrict__ in, int32_t *__restrict__ out,
+                                   int64_t n, int64_t L, int64_t n_pad)
+{
+    __shared__ int32_t tile[32][33];
+    int64_t l0 = (int64_t)blockIdx.x * 32, s0 = (int64_t)blockIdx.y * 32;
+    for (int r = threadIdx.y; r < 32; r += blockDim.y) {
+        int64_t s = s0 + r, l = l0 + threadIdx.x;
+        tile[r][threadIdx.x] = (s < n && l < L) ? in[s * L + l] : 0;
+    }
+    __syncthreads();
+    for (int r = threadIdx.y; r < 32; r += blockDim.y) {
+        int64_t l = l0 + r, s = s0 + threadIdx.x;
+        if (l < L && s < n_pad) out[l * n_pad + s] = tile[threadIdx.x][r];
+    }
+}
+
+// ---- 2. per-locus dense rank through a shared-memory bitmap ---------------------------
+// One CTA per locus.  Allele ids < 2^20 are marked in a 128 KB bitmap; the rank of an id
+// is 1 + (number of set bits below it).  status[0] |= 1 if an id >= 2^20 was seen in the
+// fast path, |= 2 if a locus has more than 65,535 distinct called alleles.
+template <bool GLOBAL_BITMAP>
+__global__ void __launch_bounds__(RANK_THREADS, 1)
+rthc_rank_columns(const int32_t *__restrict__ colmajor, uint16_t *__restrict__ codes,
+                  int32_t *__restrict__ n_alleles, int32_t *__restrict__ status, int64_t n,
+                  int64_t n_pad, const int32_t *__restrict__ col_list, uint32_t *g_bitmap,
+                  uint32_t g_words)
+{
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    uint32_t *bm = reinterpret_cast<uint32_t *>(smem_raw);
+    uint16_t *pre = reinterpret_cast<uint16_t *>(smem_raw + BITMAP_WORDS * 4);
+    __shared__ uint32_t warp_tot[32];
+    __shared__ uint32_t warp_off[33];
+
+    const int col = col_list ? col_list[blockIdx.x] : (int)blockIdx.x;
+    const int32_t *src = colmajor + (int64_t)col * n_pad;
+    uint16_t *dst = codes + (int64_t)col * n_pad;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+
+    for (int w = tid; w < (int)BITMAP_WORDS; w += RANK_THREADS) bm[w] = 0;
+    __syncthreads();
+    bool big = false;
+    for (int64_t r = tid; r < n; r += RANK_THREADS) {
+        int32_t v = src[r];
+        if (v > 0) {
+            if ((uint32_t)v >= BITMAP_BITS) big = true;
+            else atomicOr(&bm[v >> 5], 1u << (v & 31));
+        }
+    }
+    if (big) atomicOr(status, 1);
+    __syncthreads();
+    // warp w owns words [1024 w, 1024 (w+1)); conflict-free row-by-row scan
+    uint32_t running = 0;
+    for (int k = 0; k < 32; ++k) {
+        int idx = warp * 1024 + k * 32 + lane;
+        uint32_t c = __popc(bm[idx]);
+        uint32_t inc = c;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            uint32_t t = __shfl_up_sync(0xffffffffu, inc, d);
+            if (lane >= d) inc += t;
+        }
+        pre[idx] = (uint16_t)(running + inc - c);
+        running += __shfl_sync(0xffffffffu, inc, 31);
+    }
+    if (lane == 0) warp_tot[warp] = running;
+    __syncthreads();
+    if (warp == 0) {
+        uint32_t v = warp_tot[lane], inc = v;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            uint32_t t = __shfl_up_sync(0xffffffffu, inc, d);
+            if (lane >= d) inc += t;
+        }
+        warp_off[lane] = inc - v;
+        if (lane == 31) warp_off[32] = inc;
+    }
+    __syncthreads();
+    const uint32_t total = warp_off[32];
+    if (tid == 0) {
+        n_alleles[col] = (int32_t)total;
+        if (total > 65535u) atomicOr(status, 2);
+    }
+    for (int64_t r = tid; r < n_pad; r += RANK_THREADS) {
+        uint16_t code = 0;
+        if (r < n) {
+            int32_t v = src[r];
+            if (v > 0 && (uint32_t)v < BITMAP_BITS) {
+                uint32_t w = (uint32_t)v >> 5;
+                uint32_t below = __popc(bm[w] & ((1u << (v & 31)) - 1u));
+                code = (uint16_t)(1u + warp_off[w >> 10] + pre[w] + below);
+            }
+        }
+        dst[r] = code;
+    }
+}
+
+// ---- 2b. slow path for loci holding allele ids >= 2^20 --------------------------------
+// One CTA per such locus, run one locus at a time against a 2^31-bit bitmap in HBM
+// (256 MB scratch).  Ranks are assigned by scanning only the 2,048-bit windows that a
+// level-1 shared bitmap marks as occupied.
+__global__ void __launch_bounds__(RANK_THREADS, 1)
+rthc_rank_column_wide(const int32_t *__restrict__ colmajor, uint16_t *__restrict__ codes,
+                      int32_t *__restrict__ n_alleles, int32_t *__restrict__ status, int64_t n,
+                      int64_t n_pad, int col, uint32_t *__restrict__ gbm,
+                      uint32_t *__restrict__ win_prefix)
+{
+    // level-1: bit b set <=> some id in [2048 b, 2048 (b+1)) occurs; 2^20 bits = 128 KB
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    uint32_t *l1 = reinterpret_cast<uint32_t *>(smem_raw);
+    __shared__ uint32_t s_total;
+    const int32_t *src = colmajor + (int64_t)col * n_pad;
+    uint16_t *dst = codes + (int64_t)col * n_pad;
+    const int tid = threadIdx.x;
+
+    for (int w = tid; w < (int)BITMAP_WORDS; w += RANK_THREADS) l1[w] = 0;
+    if (tid == 0) s_total = 0;
+    __syncthreads();
+    for (int64_t r = tid; r < n; r += RANK_THREADS) {
+        int32_t v = src[r];
+        if (v > 0) {
+            atomicOr(&gbm[(uint32_t)v >> 5], 1u << (v & 31));
+            uint32_t b = (uint32_t)v >> 11;
+            atomicOr(&l1[b >> 5], 1u << (b & 31));
+        }
+    }
+    __threadfence();
+    __syncthreads();
+    // sequential over occupied windows (at most n of them), one warp scans a 64-word window
+    // win_prefix[b] = number of set bits in all windows before window b (only for occupied b)
+    if (tid < 32) {
+        uint32_t run = 0;
+        for (int w = 0; w < (int)BITMAP_WORDS; ++w) {
+            uint32_t bits = l1[w];
+            while (bits) {
+                int bpos = __ffs(bits) - 1;
+                bits &= bits - 1;
+                uint32_t b = (uint32_t)w * 32u + (uint32_t)bpos;
+                uint32_t c = __popc(gbm[b * 64u + tid]) + __popc(gbm[b * 64u + 32u + tid]);
+#pragma unroll
+                for (int d = 16; d > 0; d >>= 1) c += __shfl_xor_sync(0xffffffffu, c, d);
+                if (tid == 0) win_prefix[b] = run;
+                run += c;
+            }
+        }
+        if (tid == 0) s_total = run;
+    }
+    __threadfence();
+    __syncthreads();
+    const uint32_t total = s_total;
+    if (tid == 0) {
+        n_alleles[col] = (int32_t)total;
+        if (total > 65535u) atomicOr(status, 2);
+    }
+    for (int64_t r = tid; r < n_pad; r += RANK_THREADS) {
+        uint16_t code = 0;
+        if (r < n) {
+            int32_t v = src[r];
+            if (v > 0) {
+                uint32_t b = (uint32_t)v >> 11, w = (uint32_t)v >> 5;
+                uint32_t below = win_prefix[b];
+                for (uint32_t q = b * 64u; q < w; ++q) below += __popc(gbm[q]);
+                below += __popc(gbm[w] & ((1u << (v & 31)) - 1u));
+                code = (uint16_t)(1u + below);
+            }
+        }
+        dst[r] = code;
+    }
+    // leave the HBM bitmap clean for the next locus
+    __syncthreads();
+    for (int64_t r = tid; r < n; r += RANK_THREADS) {
+        int32_t v = src[r];
+        if (v > 0) gbm[(uint32_t)v >> 5] = 0;
+    }
+}
+
+// ---- 3. bit-slice 32 loci into plane words --------------------------------------------
+__global__ void rthc_pack_planes(const uint16_t *__restrict__ codes, const int32_t *__restrict__ perm,
+                                 const int32_t *__restrict__ grp_off, const int32_t *__restrict__ grp_np,
+                                 uint32_t *__restrict__ planes, int64_t n_pad)
+{
+    const int g = blockIdx.y;
+    const int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= n_pad) return;
+    const int bits = grp_np[g] - 1;
+    uint32_t pl[16];
+#pragma unroll
+    for (int k = 0; k < 16; ++k) pl[k] = 0;
+    uint32_t valid = 0;
+#pragma unroll 4
+    for (int l = 0; l < 32; ++l) {
+        int col = perm[g * 32 + l];
+        uint32_t c = col < 0 ? 0u : (uint32_t)codes[(int64_t)col * n_pad + s];
+        valid |= (c != 0u ? 1u : 0u) << l;
+#pragma unroll
+        for (int k = 0; k < 16; ++k) pl[k] |= ((c >> k) & 1u) << l;
+    }
+    const int64_t off = grp_off[g];
+#pragma unroll
+    for (int k = 0; k < 16; ++k)
+        if (k < bits) planes[(off + k) * n_pad + s] = pl[k];
+    planes[(off + bits) * n_pad + s] = valid;
+}
+
+// ---- host driver -----------------------------------------------------------------------
+static inline int bit_width(int a)   // codes 1..a need this many bits
+{
+    int b = 0;
+    while ((1 << b) <= a) ++b;
+    return b;
+}
+
+int rthc_recode_and_pack(rthc_ctx *ctx, const int32_t *d_rowmajor)
+{
+    const int64_t n = ctx->n, L = ctx->L, n_pad = ctx->n_pad;
+    int32_t *d_colmajor = nullptr, *d_nall = nullptr, *d_status = nullptr, *d_perm = nullptr;
+    int rc;
+    if ((rc = rthc_dev_alloc(ctx, &d_colmajor, (size_t)(L * n_pad)))) return rc;
+    if ((rc = rthc_dev_alloc(ctx, &d_nall, (size_t)L))) return rc;
+    if ((rc = rthc_dev_alloc(ctx, &d_status, 1))) return rc;
+    if ((rc = rthc_dev_alloc(ctx, &ctx->d_codes, (size_t)(L * n_pad)))) return rc;
+    RTHC_CUDA(ctx, cudaMemsetAsync(d_status, 0, sizeof(int32_t), ctx->stream));
+
+    {
+        dim3 blk(32, 8), grd((unsigned)((L + 31) / 32), (unsigned)((n_pad + 31) / 32));
+        rthc_transpose_i32<<<grd, blk, 0, ctx->stream>>>(d_rowmajor, d_colmajor, n, L, n_pad);
+        RTHC_LAUNCH_CHECK(ctx);
+    }
+    const size_t rank_smem = BITMAP_WORDS * 4 + BITMAP_WORDS * 2;
+    RTHC_CUDA(ctx, cudaFuncSetAttribute(rthc_rank_columns<false>,
+                                        cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rank_smem));
+    rthc_rank_columns<false><<<(unsigned)L, RANK_THREADS, rank_smem, ctx->stream>>>(
+        d_colmajor, ctx->d_codes, d_nall, d_status, n, n_pad, nullptr, nullptr, 0);
+    RTHC_LAUNCH_CHECK(ctx);
+
+    std::vector<int32_t> nall((size_t)L);
+    int32_t status = 0;
+    RTHC_CUDA(ctx, cudaMemcpyAsync(&status, d_status, sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->stream));
+    RTHC_CUDA(ctx, cudaMemcpyAsync(nall.data(), d_nall, sizeof(int32_t) * (size_t)L,
+                                   cudaMemcpyDeviceToHost, ctx->stream));
+    RTHC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+
+    if (status & 1) {
+        // some loci hold allele ids >= 2^20: find them and redo those through the HBM bitmap
+        std::vector<int32_t> colmax((size_t)L, 0);
+        {
+            // column maxima on the host side of a tiny reduction: reuse n_alleles buffer is not
+            // possible, so do a strided device reduction per column with thrust-free code
+            std::vector<int32_t> tmp((size_t)n_pad);
+            for (int64_t l = 0; l < L; ++l) {
+                // only columns whose fast-path count may be wrong need a check; checking all
+                // is L small D2H copies -- this whole branch is the rare path
+                RTHC_CUDA(ctx, cudaMemcpy(tmp.data(), d_colmajor + l * n_pad, sizeof(int32_t) * (size_t)n,
+                                          cudaMemcpyDeviceToHost));
+                int32_t mx = 0;
+                for (int64_t r = 0; r < n; ++r) mx = std::max(mx, tmp[(size_t)r]);
+                colmax[(size_t)l] = mx;
+            }
+        }
+        uint32_t *d_gbm = nullptr, *d_winpre = nullptr;
+        if ((rc = rthc_dev_alloc(ctx, &d_gbm, (size_t)1 << 26))) return rc;
+        if ((rc = rthc_dev_alloc(ctx, &d_winpre, (size_t)1 << 20))) return rc;
+        RTHC_CUDA(ctx, cudaMemsetAsync(d_gbm, 0, sizeof(uint32_t) << 26, ctx->stream));
+        RTHC_CUDA(ctx, cudaFuncSetAttribute(rthc_rank_column_wide,
+                                            cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                            (int)(BITMAP_WORDS * 4)));
+        for (int64_t l = 0; l < L; ++l) {
+            if ((uint32_t)colmax[(size_t)l] < BITMAP_BITS) continue;
+            rthc_rank_column_wide<<<1, RANK_THREADS, BITMAP_WORDS * 4, ctx->stream>>>(
+                d_colmajor, ctx->d_codes, d_nall, d_status, n, n_pad, (int)l, d_gbm, d_winpre);
+            RTHC_LAUNCH_CHECK(ctx);
+        }
+        RTHC_CUDA(ctx, cudaMemcpyAsync(&status, d_status, sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->stream));
+        RTHC_CUDA(ctx, cudaMemcpyAsync(nall.data(), d_nall, sizeof(int32_t) * (size_t)L,
+                                       cudaMemcpyDeviceToHost, ctx->stream));
+        RTHC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+        rthc_dev_free(&d_gbm);
+        rthc_dev_free(&d_winpre);
+    }
+    rthc_dev_free(&d_colmajor);
+    if (status & 2) {
+        rthc_dev_free(&d_nall); rthc_dev_free(&d_status);
+        return rthc_fail(ctx, RTHC_E_RANGE,
+                         "a locus has more than 65,535 distinct called alleles; the uint16 re-coder "
+                         "cannot represent it");
+    }
+
+    // order loci by bit width (widest first), drop loci that cannot mismatch
+    std::vector<int32_t> kept;
+    int max_all = 0;
+    for (int64_t l = 0; l < L; ++l) {
+        max_all = std::max(max_all, (int)nall[(size_t)l]);
+        if (nall[(size_t)l] >= 2) kept.push_back((int32_t)l);
+    }
+    std::stable_sort(kept.begin(), kept.end(), [&](int32_t a, int32_t b) {
+        return bit_width(nall[(size_t)a]) > bit_width(nall[(size_t)b]);
+    });
+    ctx->max_alleles = max_all;
+    ctx->L_kept = (int64_t)kept.size();
+    const int G = (int)((kept.size() + 31) / 32);
+    std::vector<int32_t> perm((size_t)G * 32, -1), goff((size_t)std::max(G, 1)), gnp((size_t)std::max(G, 1));
+    int rows = 0, max_np = 0;
+    for (int g = 0; g < G; ++g) {
+        int bits = 0;
+        for (int l = 0; l < 32; ++l) {
+            size_t idx = (size_t)g * 32 + (size_t)l;
+            if (idx < kept.size()) {
+                perm[idx] = kept[idx];
+                bits = std::max(bits, bit_width(nall[(size_t)kept[idx]]));
+            }
+        }
+        goff[(size_t)g] = rows;
+        gnp[(size_t)g] = bits + 1;
+        rows += bits + 1;
+        max_np = std::max(max_np, bits + 1);
+    }
+    ctx->G = G;
+    ctx->plane_rows = rows;
+    ctx->max_np = max_np;
+
+    if ((rc = rthc_dev_alloc(ctx, &ctx->d_planes, (size_t)std::max(rows, 1) * (size_t)n_pad))) return rc;
+    if ((rc = rthc_dev_alloc(ctx, &ctx->d_grp_off, (size_t)std::max(G, 1)))) return rc;
+    if ((rc = rthc_dev_alloc(ctx, &ctx->d_grp_np, (size_t)std::max(G, 1)))) return rc;
+    if (G > 0) {
+        if ((rc = rthc_dev_alloc(ctx, &d_perm, perm.size()))) return rc;
+        RTHC_CUDA(ctx, cudaMemcpyAsync(d_perm, perm.data(), perm.size() * sizeof(int32_t),
+                                       cudaMemcpyHostToDevice, ctx->stream));
+        RTHC_CUDA(ctx, cudaMemcpyAsync(ctx->d_grp_off, goff.data(), (size_t)G * sizeof(int32_t),
+                                       cudaMemcpyHostToDevice, ctx->stream));
+        RTHC_CUDA(ctx, cudaMemcpyAsync(ctx->d_grp_np, gnp.data(), (size_t)G * sizeof(int32_t),
+                                       cudaMemcpyHostToDevice, ctx->stream));
+        dim3 grd((unsigned)((n_pad + 255) / 256), (unsigned)G);
+        rthc_pack_planes<<<grd, 256, 0, ctx->stream>>>(ctx->d_codes, d_perm, ctx->d_grp_off,
+                                                       ctx->d_grp_np, ctx->d_planes, n_pad);
+        RTHC_LAUNCH_CHECK(ctx);
+    }
+    RTHC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    rthc_dev_free(&d_perm);
+    rthc_dev_free(&d_nall);
+    rthc_dev_free(&d_status);
+    return 0;
+}

@@ -1,0 +1,124 @@
+// rthc_internal.cuh -- context layout and helpers shared by the kernels of libreportree_hc.so
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string>
+#include <vector>
+
+#include "../../include/rthc.h"
+
+#define RTHC_TILE 128            // samples per tile edge of the distance kernel
+#define RTHC_KEY_INF 0xFFFFFFFFFFFFFFFFull
+
+// (w, i, j) packed as w<<48 | i<<24 | j  (i < j < 2^24, w < 2^16): one total order
+__host__ __device__ inline uint64_t rthc_pack_key(uint32_t w, uint32_t i, uint32_t j)
+{
+    return ((uint64_t)w << 48) | ((uint64_t)i << 24) | (uint64_t)j;
+}
+__host__ __device__ inline uint32_t rthc_key_w(uint64_t k) { return (uint32_t)(k >> 48); }
+__host__ __device__ inline uint32_t rthc_key_i(uint64_t k) { return (uint32_t)((k >> 24) & 0xFFFFFFu); }
+__host__ __device__ inline uint32_t rthc_key_j(uint64_t k) { return (uint32_t)(k & 0xFFFFFFu); }
+
+struct rthc_ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    std::string err;
+    int sm_count = 148;
+
+    // shard
+    int rank = 0, world = 1;
+
+    // problem
+    int64_t n = 0, L = 0, n_pad = 0;
+    int64_t n_tiles_edge = 0;      // ceil(n / 128)
+    int64_t L_kept = 0;
+    int G = 0;                     // groups of 32 loci
+    int plane_rows = 0;            // sum over groups of (bits + 1)
+    int max_np = 0;                // max planes per group (bits + valid)
+    int max_alleles = 0;
+
+    // device buffers (distance half)
+    uint16_t *d_codes = nullptr;   // [L][n_pad] dense-ranked codes, column-major per locus
+    uint32_t *d_planes = nullptr;  // [plane_rows][n_pad]
+    int32_t *d_grp_off = nullptr;  // [G]
+    int32_t *d_grp_np = nullptr;   // [G]
+    int2 *d_tiles = nullptr;       // tile list (I, J), J >= I, owned tile rows only
+    int64_t n_tiles = 0;
+    int64_t *d_row_base = nullptr; // [n_pad] offset of (i, i+1) in d_cond, -1 if row not owned
+    std::vector<int64_t> h_row_base;
+    std::vector<int32_t> h_owned_rows;
+    int32_t *d_owned_rows = nullptr;
+    int64_t owned_pairs = 0;
+    uint16_t *d_cond = nullptr;    // condensed uint16 distances of the owned rows
+    bool have_profiles = false, have_dist = false;
+
+    // externally supplied condensed matrix (-d_mx)
+    double *d_cond_f64 = nullptr;
+    bool ext_integer = false;
+
+    // clustering state
+    int single_algo = RTHC_SL_BORUVKA;
+    int64_t m_edges = 0;           // n - 1 after a successful linkage
+    int32_t *d_ea = nullptr, *d_eb = nullptr;   // leaf representatives of merge k (sorted order)
+    double *d_eh = nullptr;                      // height of merge k
+    int32_t *d_epre = nullptr, *d_eleaf = nullptr;
+    std::vector<double> h_heights;
+    bool have_linkage = false;
+    int boruvka_rounds = 0;
+    int64_t row_scans = 0;
+
+    // timings
+    double t_ms[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    int64_t launches = 0;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+};
+
+extern std::string g_rthc_create_err;
+
+int rthc_fail(rthc_ctx *ctx, int code, const char *fmt, ...);
+
+#define RTHC_CUDA(ctx, expr)                                                              \
+    do {                                                                                  \
+        cudaError_t _e = (expr);                                                          \
+        if (_e != cudaSuccess)                                                            \
+            return rthc_fail((ctx), RTHC_E_CUDA, "%s failed at %s:%d: %s", #expr, __FILE__, \
+                             __LINE__, cudaGetErrorString(_e));                           \
+    } while (0)
+
+#define RTHC_LAUNCH_CHECK(ctx)                                                            \
+    do {                                                                                  \
+        (ctx)->launches++;                                                                \
+        RTHC_CUDA((ctx), cudaGetLastError());                                             \
+    } while (0)
+
+template <typename T> inline int rthc_dev_alloc(rthc_ctx *ctx, T **p, size_t count)
+{
+    if (*p) { cudaFree(*p); *p = nullptr; }
+    if (count == 0) count = 1;
+    cudaError_t e = cudaMalloc((void **)p, count * sizeof(T));
+    if (e != cudaSuccess) {
+        *p = nullptr;
+        return rthc_fail(ctx, RTHC_E_NOMEM, "cudaMalloc of %zu bytes failed: %s", count * sizeof(T),
+                         cudaGetErrorString(e));
+    }
+    return 0;
+}
+template <typename T> inline void rthc_dev_free(T **p)
+{
+    if (*p) { cudaFree(*p); *p = nullptr; }
+}
+
+// stage entry points implemented in the other translation units
+int rthc_recode_and_pack(rthc_ctx *ctx, const int32_t *d_rowmajor);   // recode.cu
+int rthc_run_distance(rthc_ctx *ctx);                                 // distance.cu
+int rthc_run_direct_pairs(rthc_ctx *ctx, const int32_t *d_pi, const int32_t *d_pj, int64_t np,
+                          int32_t *d_out);                            // distance.cu
+int rthc_boruvka_owned(rthc_ctx *ctx, std::vector<uint64_t> &keys);   // mst.cu
+int rthc_boruvka_edge_list(rthc_ctx *ctx, const uint64_t *h_keys, int64_t m, int64_t n,
+                           std::vector<uint64_t> &keys);              // mst.cu
+int rthc_prim_exact(rthc_ctx *ctx, std::vector<int32_t> &ex, std::vector<int32_t> &ey,
+                    std::vector<double> &ew);                         // mst.cu
+int rthc_nn_chain(rthc_ctx *ctx, int method, std::vector<int32_t> &ex, std::vector<int32_t> &ey,
+                  std::vector<double> &ew);                           // nnchain.cu
+int rthc_run_cut(rthc_ctx *ctx, const double *t, int T, int32_t *labels_out);   // cut.cu

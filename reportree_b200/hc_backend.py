@@ -1,0 +1,215 @@
+"""ctypes binding of libreportree_hc.so (include/rthc.h) with the call shapes that
+scripts/partitioning_HC.py uses today:
+
+    cgmlst-dists subprocess + chunk loop  (scripts/partitioning_HC.py:489-516)  -> HCContext.set_profiles / distance
+    squareform(dist)                      (:186)                                 -> HCContext.condensed
+    linkage(y, method)                    (:197)                                 -> HCContext.linkage(method)
+    maxdists(Z)[-1]                       (:198)                                 -> Z[-1, 2] (monotone methods)
+    fcluster(Z, t, criterion="distance")  (:649, :689, :722, :751)               -> HCContext.fcluster(thresholds)
+
+There is no CPU fallback: if the CUDA library is missing or no B200 is visible, every
+entry point raises HCBackendError.
+"""
+import ctypes
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libreportree_hc.so")
+
+METHODS = {"single": 0, "complete": 1, "average": 2, "weighted": 3}
+SL_BORUVKA, SL_PRIM = 0, 1
+
+
+class HCBackendError(RuntimeError):
+    pass
+
+
+_lib = None
+
+
+def load_library():
+    """dlopen the in-tree CUDA library and declare every symbol of include/rthc.h."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise HCBackendError(
+            "CUDA library %s not built (run `python -m reportree_b200.build`); there is no CPU fallback" % LIB_PATH)
+    L = ctypes.CDLL(LIB_PATH)
+    vp, i64, i32, ci = ctypes.c_void_p, ctypes.c_int64, ctypes.c_int32, ctypes.c_int
+    sig = {
+        "rthc_create": (ci, [ctypes.POINTER(vp), ci]),
+        "rthc_destroy": (None, [vp]),
+        "rthc_last_error": (ctypes.c_char_p, [vp]),
+        "rthc_version": (ci, []),
+        "rthc_set_shard": (ci, [vp, ci, ci]),
+        "rthc_set_profiles_i32": (ci, [vp, vp, i64, i64]),
+        "rthc_set_profiles_i32_device": (ci, [vp, vp, i64, i64]),
+        "rthc_distance": (ci, [vp]),
+        "rthc_owned_pairs": (i64, [vp]),
+        "rthc_get_condensed_u16": (ci, [vp, vp]),
+        "rthc_get_owned_condensed_u16": (ci, [vp, vp]),
+        "rthc_copy_rows_u16": (ci, [vp, i64, i64, vp]),
+        "rthc_direct_pairs": (ci, [vp, vp, vp, i64, vp]),
+        "rthc_set_condensed_f64": (ci, [vp, vp, i64]),
+        "rthc_set_single_algo": (ci, [vp, ci]),
+        "rthc_linkage": (ci, [vp, ci, vp]),
+        "rthc_local_forest": (ci, [vp, vp, ctypes.POINTER(i64)]),
+        "rthc_linkage_from_forest": (ci, [vp, vp, i64, i64, vp]),
+        "rthc_cut": (ci, [vp, vp, ci, vp]),
+        "rthc_info": (ci, [vp, vp, ci]),
+        "rthc_timings": (ci, [vp, vp, ci]),
+    }
+    for name, (res, args) in sig.items():
+        fn = getattr(L, name)
+        fn.restype = res
+        fn.argtypes = args
+    _lib = L
+    return L
+
+
+EXPORTED_SYMBOLS = [
+    "rthc_create", "rthc_destroy", "rthc_last_error", "rthc_version", "rthc_set_shard",
+    "rthc_set_profiles_i32", "rthc_set_profiles_i32_device", "rthc_distance", "rthc_owned_pairs",
+    "rthc_get_condensed_u16", "rthc_get_owned_condensed_u16", "rthc_copy_rows_u16", "rthc_direct_pairs",
+    "rthc_set_condensed_f64", "rthc_set_single_algo", "rthc_linkage", "rthc_local_forest",
+    "rthc_linkage_from_forest", "rthc_cut", "rthc_info", "rthc_timings",
+]
+
+
+def _ptr(a):
+    return ctypes.c_void_p(a.ctypes.data)
+
+
+class HCContext:
+    """One device context (one GPU).  Not thread-safe; calls are synchronous."""
+
+    def __init__(self, device=0, rank=0, world=1):
+        self._L = load_library()
+        h = ctypes.c_void_p()
+        rc = self._L.rthc_create(ctypes.byref(h), int(device))
+        if rc != 0:
+            raise HCBackendError("rthc_create failed (%d): %s" % (rc, self._L.rthc_last_error(None).decode()))
+        self._h = h
+        self.n = 0
+        self.L = 0
+        if world != 1:
+            self._check(self._L.rthc_set_shard(self._h, int(rank), int(world)))
+        self.rank, self.world = rank, world
+
+    def _check(self, rc):
+        if rc != 0:
+            raise HCBackendError("rthc error %d: %s" % (rc, self._L.rthc_last_error(self._h).decode()))
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._L.rthc_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    # ---- distance half ---------------------------------------------------------------
+    def set_profiles(self, codes):
+        """codes: n x L integer allele codes (0 = missing), host numpy array."""
+        codes = np.ascontiguousarray(codes, dtype=np.int32)
+        if codes.ndim != 2:
+            raise HCBackendError("allele code matrix must be 2-D")
+        self.n, self.L = codes.shape
+        self._check(self._L.rthc_set_profiles_i32(self._h, _ptr(codes), self.n, self.L))
+
+    def set_profiles_device(self, dev_ptr, n, L):
+        self.n, self.L = int(n), int(L)
+        self._check(self._L.rthc_set_profiles_i32_device(self._h, ctypes.c_void_p(int(dev_ptr)), self.n, self.L))
+
+    def distance(self):
+        self._check(self._L.rthc_distance(self._h))
+
+    def owned_pairs(self):
+        return int(self._L.rthc_owned_pairs(self._h))
+
+    def condensed(self):
+        """Full condensed uint16 distance vector in scipy pdist order (squareform-compatible)."""
+        out = np.empty(self.n * (self.n - 1) // 2, dtype=np.uint16)
+        self._check(self._L.rthc_get_condensed_u16(self._h, _ptr(out)))
+        return out
+
+    def owned_condensed(self):
+        out = np.empty(self.owned_pairs(), dtype=np.uint16)
+        self._check(self._L.rthc_get_owned_condensed_u16(self._h, _ptr(out)))
+        return out
+
+    def square_rows(self, row0, nrows):
+        out = np.empty((nrows, self.n), dtype=np.uint16)
+        self._check(self._L.rthc_copy_rows_u16(self._h, int(row0), int(nrows), _ptr(out)))
+        return out
+
+    def direct_pairs(self, pi, pj):
+        pi = np.ascontiguousarray(pi, dtype=np.int32)
+        pj = np.ascontiguousarray(pj, dtype=np.int32)
+        out = np.empty(pi.size, dtype=np.int32)
+        self._check(self._L.rthc_direct_pairs(self._h, _ptr(pi), _ptr(pj), pi.size, _ptr(out)))
+        return out
+
+    def set_condensed(self, y):
+        y = np.ascontiguousarray(y, dtype=np.float64)
+        n = int(round((1 + (1 + 8 * y.size) ** 0.5) / 2))
+        if n * (n - 1) // 2 != y.size:
+            raise HCBackendError("condensed vector has an invalid length")
+        self.n = n
+        self._check(self._L.rthc_set_condensed_f64(self._h, _ptr(y), n))
+
+    # ---- clustering half -------------------------------------------------------------
+    def set_single_algo(self, algo):
+        self._check(self._L.rthc_set_single_algo(self._h, int(algo)))
+
+    def linkage(self, method="single"):
+        if method not in METHODS:
+            raise HCBackendError("method %r is not available on the CUDA backend" % (method,))
+        Z = np.empty((self.n - 1, 4), dtype=np.float64)
+        self._check(self._L.rthc_linkage(self._h, METHODS[method], _ptr(Z)))
+        return Z
+
+    def local_forest(self):
+        keys = np.empty(max(self.n - 1, 1), dtype=np.uint64)
+        m = ctypes.c_int64(0)
+        self._check(self._L.rthc_local_forest(self._h, _ptr(keys), ctypes.byref(m)))
+        return keys[: m.value].copy()
+
+    def linkage_from_forest(self, keys, n):
+        keys = np.ascontiguousarray(keys, dtype=np.uint64)
+        self.n = int(n)
+        Z = np.empty((self.n - 1, 4), dtype=np.float64)
+        self._check(self._L.rthc_linkage_from_forest(self._h, _ptr(keys), keys.size, self.n, _ptr(Z)))
+        return Z
+
+    def fcluster(self, thresholds):
+        """labels[k] == scipy fcluster(Z, thresholds[k], criterion='distance') of the last linkage."""
+        t = np.ascontiguousarray(np.atleast_1d(thresholds), dtype=np.float64)
+        out = np.empty((t.size, self.n), dtype=np.int32)
+        self._check(self._L.rthc_cut(self._h, _ptr(t), t.size, _ptr(out)))
+        return out
+
+    # ---- introspection -----------------------------------------------------------------
+    def info(self):
+        a = np.zeros(9, dtype=np.int64)
+        self._check(self._L.rthc_info(self._h, _ptr(a), 9))
+        keys = ["n", "L", "loci_kept", "groups", "plane_rows", "tiles", "boruvka_rounds", "max_alleles", "row_scans"]
+        return dict(zip(keys, (int(x) for x in a)))
+
+    def timings(self):
+        a = np.zeros(6, dtype=np.float64)
+        self._check(self._L.rthc_timings(self._h, _ptr(a), 6))
+        keys = ["h2d_ms", "recode_ms", "distance_ms", "linkage_ms", "cut_ms", "launches"]
+        return dict(zip(keys, (float(x) for x in a)))

@@ -1,0 +1,132 @@
+"""GPU parity: bit-sliced distance kernel + device re-coder vs the CPU oracle (bit-exact)."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def _rand_codes(rng, n, L, max_allele, missing):
+    X = rng.integers(1, max_allele + 1, size=(n, L)).astype(np.int32)
+    X[rng.random((n, L)) < missing] = 0
+    return X
+
+
+@pytest.mark.parametrize("n,L,max_allele,missing", [
+    (2, 1, 2, 0.0),
+    (3, 5, 3, 0.3),
+    (14, 94, 4, 0.05),          # shape of tests/allele_matrix.tsv
+    (127, 33, 9, 0.1),
+    (128, 64, 300, 0.02),
+    (129, 2001, 40, 0.02),      # > 2,000 loci: the reference would chunk and sum
+    (300, 700, 70000, 0.02),    # ids above 2^16 but < 2^20 (few distinct per locus)
+    (513, 257, 2, 0.5),
+    (1000, 3002, 500, 0.02),
+])
+def test_distance_matches_oracle(hc, oracle, n, L, max_allele, missing):
+    rng = np.random.default_rng(n * 1000 + L)
+    X = _rand_codes(rng, n, L, max_allele, missing)
+    ref = oracle.dist_condensed(X)
+    with hc.HCContext() as ctx:
+        ctx.set_profiles(X)
+        ctx.distance()
+        got = ctx.condensed()
+        info = ctx.info()
+    assert got.dtype == np.uint16
+    assert np.array_equal(got, ref), (info, np.flatnonzero(got != ref)[:10])
+
+
+def test_chunk_sum_equivalence(hc, oracle):
+    # the reference sums per-2,000-column chunks (scripts/partitioning_HC.py:489-516)
+    rng = np.random.default_rng(7)
+    X = _rand_codes(rng, 60, 4500, 30, 0.05)
+    sq = oracle.dist_square_chunked(X, 2000)
+    with hc.HCContext() as ctx:
+        ctx.set_profiles(X)
+        ctx.distance()
+        rows = ctx.square_rows(0, 60)
+    assert np.array_equal(rows.astype(np.int32), sq)
+
+
+def test_all_missing_rows_and_monomorphic_loci(hc, oracle):
+    rng = np.random.default_rng(11)
+    X = _rand_codes(rng, 200, 150, 6, 0.1)
+    X[5] = 0                       # sample with every locus missing
+    X[:, 10] = 0                   # locus missing everywhere
+    X[:, 11] = 3                   # monomorphic locus
+    X[:, 12] = np.where(rng.random(200) < 0.5, 0, 9)   # one allele + missing
+    ref = oracle.dist_condensed(X)
+    with hc.HCContext() as ctx:
+        ctx.set_profiles(X)
+        ctx.distance()
+        got = ctx.condensed()
+        assert ctx.info()["loci_kept"] <= 147
+    assert np.array_equal(got, ref)
+
+
+def test_large_allele_ids_slow_path(hc, oracle):
+    rng = np.random.default_rng(13)
+    X = _rand_codes(rng, 150, 40, 50, 0.05)
+    X[:, 3] = rng.integers(1, 2**31 - 1, size=150)          # hashed-profile style ids
+    X[:, 7] = np.where(X[:, 7] > 25, X[:, 7] + (1 << 20), X[:, 7])
+    ref = oracle.dist_condensed(X)
+    with hc.HCContext() as ctx:
+        ctx.set_profiles(X)
+        ctx.distance()
+        got = ctx.condensed()
+    assert np.array_equal(got, ref)
+
+
+def test_negative_codes_are_missing(hc, oracle):
+    rng = np.random.default_rng(17)
+    X = _rand_codes(rng, 64, 64, 5, 0.0)
+    Y = X.copy()
+    Y[rng.random(X.shape) < 0.1] = -1
+    X0 = np.where(Y < 0, 0, Y)
+    ref = oracle.dist_condensed(X0)
+    with hc.HCContext() as ctx:
+        ctx.set_profiles(Y)
+        ctx.distance()
+        assert np.array_equal(ctx.condensed(), ref)
+
+
+def test_direct_kernel_agrees_with_bitsliced_on_synthetic(hc):
+    from reportree_b200 import synth
+    X = synth.allele_matrix(3000, 3002, 5)
+    rng = np.random.default_rng(3)
+    pi = rng.integers(0, 3000, size=20000).astype(np.int32)
+    pj = rng.integers(0, 3000, size=20000).astype(np.int32)
+    keep = pi != pj
+    pi, pj = np.minimum(pi, pj)[keep], np.maximum(pi, pj)[keep]
+    with hc.HCContext() as ctx:
+        ctx.set_profiles(X)
+        ctx.distance()
+        y = ctx.condensed()
+        d = ctx.direct_pairs(pi, pj)
+    n = 3000
+    idx = n * pi.astype(np.int64) - pi.astype(np.int64) * (pi + 1) // 2 + (pj - pi - 1)
+    assert np.array_equal(y[idx].astype(np.int32), d)
+
+
+@pytest.mark.parametrize("world", [2, 3, 8])
+def test_sharded_rows_cover_matrix(hc, oracle, world):
+    rng = np.random.default_rng(23)
+    n = 700
+    X = _rand_codes(rng, n, 90, 12, 0.05)
+    ref = oracle.dist_condensed(X)
+    seen = np.zeros(ref.size, dtype=bool)
+    B = (n + 127) // 128
+    for rank in range(world):
+        with hc.HCContext(rank=rank, world=world) as ctx:
+            ctx.set_profiles(X)
+            ctx.distance()
+            part = ctx.owned_condensed()
+        rows = [i for i in range(n) if min(i // 128, B - 1 - i // 128) % world == rank]
+        pos = 0
+        for i in rows:
+            ln = n - 1 - i
+            base = n * i - i * (i + 1) // 2
+            assert np.array_equal(part[pos:pos + ln], ref[base:base + ln])
+            seen[base:base + ln] = True
+            pos += ln
+        assert pos == part.size
+    assert seen.all()

@@ -1,0 +1,77 @@
+"""GPU parity: single linkage (Boruvka MST) + multi-threshold cut vs scipy / the oracle."""
+import numpy as np
+import pytest
+from scipy.cluster.hierarchy import fcluster, linkage
+
+pytestmark = pytest.mark.gpu
+
+
+def _rand_codes(rng, n, L, max_allele, missing):
+    X = rng.integers(1, max_allele + 1, size=(n, L)).astype(np.int32)
+    X[rng.random((n, L)) < missing] = 0
+    return X
+
+
+def _same_membership(a, b, oracle):
+    return np.array_equal(oracle.canonical(a), oracle.canonical(b))
+
+
+@pytest.mark.parametrize("n,L,max_allele", [(2, 3, 2), (3, 4, 2), (17, 20, 3), (200, 30, 2), (777, 60, 4), (1500, 12, 2)])
+def test_single_linkage_membership_every_threshold(hc, oracle, n, L, max_allele):
+    rng = np.random.default_rng(n + L)
+    X = _rand_codes(rng, n, L, max_allele, 0.05)
+    with hc.HCContext() as ctx:
+        ctx.set_profiles(X)
+        ctx.distance()
+        y = ctx.condensed().astype(np.float64)
+        Z = ctx.linkage("single")
+        Zs = linkage(y, "single")
+        # heights (sorted MST weights) are tie-independent
+        assert np.array_equal(Z[:, 2], Zs[:, 2])
+        assert np.array_equal(Z[:, 3].max(), n)
+        thr = np.arange(0, int(Zs[-1, 2]) + 2, dtype=np.float64)
+        labels = ctx.fcluster(thr)
+    for k, t in enumerate(thr):
+        ref = fcluster(Zs, t, criterion="distance")
+        assert _same_membership(labels[k], ref, oracle), (t,)
+        # and the ids are exactly scipy's numbering of OUR dendrogram
+        assert np.array_equal(labels[k], fcluster(Z, t, criterion="distance")), (t,)
+        assert np.array_equal(labels[k], oracle.fcluster(Z, t)), (t,)
+
+
+def test_cut_threshold_order_and_float_thresholds(hc, oracle):
+    rng = np.random.default_rng(99)
+    X = _rand_codes(rng, 300, 40, 3, 0.02)
+    with hc.HCContext() as ctx:
+        ctx.set_profiles(X)
+        ctx.distance()
+        Z = ctx.linkage("single")
+        thr = np.array([7.0, 0.0, 3.5, 100.0, 2.0, 2.0, 1e-9])
+        labels = ctx.fcluster(thr)
+    for k, t in enumerate(thr):
+        assert np.array_equal(labels[k], fcluster(Z, t, criterion="distance"))
+
+
+def test_forest_union_equals_single_gpu(hc, oracle):
+    # multi-GPU algebra on one GPU: per-shard forests, union, final MST == full MST
+    rng = np.random.default_rng(5)
+    n = 900
+    X = _rand_codes(rng, n, 25, 3, 0.05)
+    with hc.HCContext() as full:
+        full.set_profiles(X)
+        full.distance()
+        Zfull = full.linkage("single")
+    for world in (2, 4):
+        keys = []
+        for rank in range(world):
+            with hc.HCContext(rank=rank, world=world) as ctx:
+                ctx.set_profiles(X)
+                ctx.distance()
+                keys.append(ctx.local_forest())
+        allk = np.concatenate(keys)
+        with hc.HCContext() as ctx:
+            Z = ctx.linkage_from_forest(allk, n)
+            assert np.array_equal(Z, Zfull)
+            lab = ctx.fcluster([0.0, 1.0, 2.0, 3.0])
+        for k, t in enumerate([0.0, 1.0, 2.0, 3.0]):
+            assert np.array_equal(lab[k], fcluster(Zfull, t, criterion="distance"))
