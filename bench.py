@@ -1,0 +1,322 @@
+#!/usr/bin/env python3
+"""bench.py -- allele comparisons/s of the partitioning hot path (BASELINE.json metric).
+
+One "step" = one full pass of the hot path over the synthetic 100,000 x 3,000 cgMLST matrix
+(BASELINE.json configs[3]; fits one GPU): device re-coder -> bit-sliced distance kernel ->
+condensed uint16 matrix -> Boruvka MST (single linkage) -> cut at thresholds 0..50.
+
+  value : P*L / step time with the int32 code matrix already resident in HBM
+  e2e   : same, through the host C-ABI call with PINNED HOST buffers: H2D of the codes and
+          D2H of Z + labels inside the timed region
+  N > 1 : strong scaling -- 128-sample tile-rows of the upper triangle sharded over the ranks,
+          per-rank Boruvka forest, one NCCL all_gather of <= n-1 packed edges per rank, final
+          MST + cut on rank 0 (launched by torchrun, one process per GPU)
+
+  --impl reference : the reference's CPU path (oracle/ C port of cgmlst-dists + scipy
+          linkage/fcluster) on a bounded sample of the same workload, all host threads.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+WORKLOAD = dict(name="C4 synthetic cgMLST 100000x3000, 2% missing, single linkage, cut 0..50",
+                cfg="C4", thresholds=51)
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--n", type=int, default=0, help="override sample count (debug only; invalidates the metric)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+def make_workload(args):
+    from reportree_b200 import synth
+    cfg = synth.config(WORKLOAD["cfg"])
+    if args.n:
+        cfg["n"] = args.n
+    X = synth.allele_matrix(**cfg)
+    return X, cfg
+
+
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons during the timed region (B200_PROFILING.md)."""
+
+    def __init__(self, index):
+        self.index = index
+        self.rows = []
+        self._stop = threading.Event()
+        self._thr = None
+
+    def _run(self):
+        q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+             "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+             "clocks_event_reasons.sw_power_cap")
+        while not self._stop.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + q,
+                                      "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
+                parts = [p.strip() for p in out.strip().split(",")]
+                if len(parts) >= 7:
+                    self.rows.append(parts)
+            except Exception:
+                pass
+            self._stop.wait(0.2)
+
+    def start(self):
+        self._thr = threading.Thread(target=self._run, daemon=True)
+        self._thr.start()
+
+    def stop(self):
+        self._stop.set()
+        if self._thr:
+            self._thr.join(timeout=6)
+        sm = [float(r[0]) for r in self.rows if r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({names[k] for r in self.rows for k in range(4) if r[3 + k].lower().startswith("active")})
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(self.rows)}
+
+
+# ------------------------------------------------------------------------------------------
+# reference arm / cpu baseline: the oracle port of the reference's CPU path
+# ------------------------------------------------------------------------------------------
+
+def cpu_reference_step(X, n_sample, threads, thresholds):
+    """cgmlst-dists rule (C port) + scipy linkage/fcluster on the first n_sample rows."""
+    from concurrent.futures import ThreadPoolExecutor
+    from scipy.cluster.hierarchy import fcluster, linkage
+    from oracle import oracle_lib as O
+    Xs = np.ascontiguousarray(X[:n_sample])
+    n, L = Xs.shape
+    t0 = time.perf_counter()
+    # balanced row ranges (row i costs n-1-i pairs)
+    cost = np.cumsum((n - 1 - np.arange(n)).astype(np.float64))
+    cuts = [0] + [int(np.searchsorted(cost, cost[-1] * k / threads)) for k in range(1, threads)] + [n]
+    cuts = sorted(set(cuts))
+    with ThreadPoolExecutor(max_workers=threads) as ex:
+        parts = list(ex.map(lambda ab: O.dist_condensed_rows(Xs, ab[0], ab[1]), zip(cuts[:-1], cuts[1:])))
+    y = np.concatenate(parts).astype(np.float64)
+    t_dist = time.perf_counter() - t0
+    Z = linkage(y, "single")
+    for t in range(thresholds):
+        fcluster(Z, t, criterion="distance")
+    t_all = time.perf_counter() - t0
+    P = n * (n - 1) // 2
+    return P * L, t_all, t_dist
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    X, cfg = make_workload(args)
+    threads = os.cpu_count() or 1
+    n_sample = 4000
+    vals = []
+    for k in range(args.warmup + args.steps):
+        work, t_all, t_dist = cpu_reference_step(X, n_sample, threads, WORKLOAD["thresholds"])
+        if k >= args.warmup:
+            vals.append((work, t_all))
+    tot_work = sum(v[0] for v in vals)
+    tot_t = sum(v[1] for v in vals)
+    value = tot_work / tot_t
+    sample = "first %d of %d samples x %d loci per step (%.2e comparisons), distance + scipy single linkage + %d cuts" % (
+        n_sample, cfg["n"], cfg["L"], vals[0][0], WORKLOAD["thresholds"])
+    line = {"impl": "reference", "metric": "allele comparisons/sec (pairs x loci / s), whole hot path",
+            "value": value, "unit": "comparisons/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": 1e3 * tot_t / len(vals), "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "int32", "data": "synthetic",
+            "config": {"workload": WORKLOAD["name"], "n": cfg["n"], "L": cfg["L"], "sample": sample},
+            "cpu_baseline": {"value": value, "unit": "comparisons/s", "cores": threads, "kind": "port", "sample": sample},
+            "e2e": {"value": value, "unit": "comparisons/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line))
+
+
+# ------------------------------------------------------------------------------------------
+# our arm
+# ------------------------------------------------------------------------------------------
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    from reportree_b200 import hc_backend as hc
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device; the product path has no CPU fallback")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    X, cfg = make_workload(args)
+    n, L = X.shape
+    P = n * (n - 1) // 2
+    pinned = torch.empty((n, L), dtype=torch.int32, pin_memory=True)
+    pinned.numpy()[:] = X
+    host_codes = pinned.numpy()
+    dX = pinned.cuda(non_blocking=False)
+    thr = np.arange(WORKLOAD["thresholds"], dtype=np.float64)
+    ctx = hc.HCContext(device=local, rank=rank, world=world)
+    INF = np.uint64(0xFFFFFFFFFFFFFFFF)
+    state = {"dist_ms": [], "link_ms": [], "cut_ms": [], "recode_ms": [], "h2d_ms": [], "d2h_bytes": 0}
+
+    def step(resident):
+        if resident:
+            ctx.set_profiles_device(dX.data_ptr(), n, L)
+        else:
+            ctx.set_profiles(host_codes)
+        ctx.distance()
+        d2h = 0
+        if world == 1:
+            Z = ctx.linkage("single")
+            labels = ctx.fcluster(thr)
+            d2h = Z.nbytes + labels.nbytes + (n - 1) * 8
+        else:
+            keys = ctx.local_forest()
+            buf = torch.full((n - 1,), -1, dtype=torch.int64, device="cuda")
+            if keys.size:
+                buf[: keys.size] = torch.from_numpy(keys.view(np.int64)).cuda()
+            gathered = [torch.empty_like(buf) for _ in range(world)]
+            dist.all_gather(gathered, buf)
+            d2h = keys.nbytes
+            labels = None
+            if rank == 0:
+                allk = torch.cat(gathered).cpu().numpy().view(np.uint64)
+                allk = allk[allk != INF]
+                Z = ctx.linkage_from_forest(allk, n)
+                labels = ctx.fcluster(thr)
+                d2h += allk.nbytes + Z.nbytes + labels.nbytes
+        tm = ctx.timings()
+        state["dist_ms"].append(tm["distance_ms"]); state["link_ms"].append(tm["linkage_ms"])
+        state["cut_ms"].append(tm["cut_ms"]); state["recode_ms"].append(tm["recode_ms"])
+        state["h2d_ms"].append(tm["h2d_ms"]); state["d2h_bytes"] = d2h
+        return labels
+
+    def sync():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    def timed(resident, steps, warmup):
+        for _ in range(warmup):
+            step(resident)
+        for k in state:
+            if isinstance(state[k], list):
+                state[k].clear()
+        l0 = ctx.timings()["launches"]
+        sync()
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            labels = step(resident)
+        sync()
+        dt = time.perf_counter() - t0
+        launches = ctx.timings()["launches"] - l0
+        if world > 1:
+            t = torch.tensor([dt, launches], dtype=torch.float64, device="cuda")
+            tmax = t.clone()
+            dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+            tsum = t.clone()
+            dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
+            dt, launches = float(tmax[0]), float(tsum[1])
+        return dt, launches, labels
+
+    alu_peak = ctx.alu_peak()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    dt, launches, labels = timed(True, args.steps, args.warmup)
+    kern = {k: float(np.mean(v)) for k, v in state.items() if isinstance(v, list) and v}
+    info = ctx.info()
+    owned_pairs = ctx.owned_pairs()
+    clocks = sampler.stop() if rank == 0 else None
+    dt_e2e, _, labels_e2e = timed(False, args.steps, 1)
+    d2h_bytes = state["d2h_bytes"]
+
+    if rank == 0:
+        work = float(P) * L
+        value = work * args.steps / dt
+        e2e_value = work * args.steps / dt_e2e
+        t_k = kern["dist_ms"] * 1e-3
+        cmp_rate = owned_pairs * float(L) / t_k
+        lop3_rate = owned_pairs * float(info["plane_rows"]) / t_k
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except Exception:
+            pass
+        hbm_peak = peaks.get("hbm_gbs", 6650.0)
+        alg_bytes = 2.0 * n * L + 2.0 * owned_pairs
+        roofline = {
+            "kernel": "rthc_distance_bitsliced",
+            "bound": "int_alu",
+            "achieved": cmp_rate / 1e12, "peak": alu_peak / 2 / 1e12, "unit": "Tcmp/s",
+            "frac": cmp_rate / (alu_peak / 2),
+            "note": "peak = measured LOP3 lane-ops/s / 2 (SURVEY 8d: 2 lane-ops per comparison for a direct "
+                    "compare+accumulate); the bit-sliced kernel issues plane_rows/L_kept*... LOP3 per 32 loci, "
+                    "so frac can exceed 1; alu_pipe_frac is the true pipe utilisation",
+            "alu_pipe_frac": lop3_rate / alu_peak,
+            "alu_peak_lane_ops_per_s": alu_peak, "alu_peak_source": "measured live (rthc_alu_peak LOP3 stream)",
+            "lop3_per_32_loci": info["plane_rows"] / max(info["groups"], 1),
+            "kernel_ms": kern["dist_ms"],
+            "traffic": None,
+            "hbm": {"achieved": alg_bytes / t_k / 1e9, "peak": hbm_peak, "unit": "GB/s",
+                    "frac": alg_bytes / t_k / 1e9 / hbm_peak,
+                    "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback"},
+        }
+        line = {
+            "metric": "allele comparisons/sec (pairs x loci / s), whole hot path",
+            "value": value, "unit": "comparisons/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "u16 codes / u32 bit planes (integer)", "data": "synthetic",
+            "config": {"workload": WORKLOAD["name"], "n": n, "L": L, "pairs": P, "thresholds": WORKLOAD["thresholds"],
+                       "l2": "inputs larger than L2 (bit planes %.0f MB + condensed output %.1f GB per step)" % (
+                           info["plane_rows"] * ctx_npad(n) * 4 / 1e6, 2.0 * owned_pairs / 1e9),
+                       "sharding": "tile-rows of the upper triangle over %d rank(s)" % world},
+            "stage_ms": kern,
+            "roofline": roofline,
+            "e2e": {"value": e2e_value, "unit": "comparisons/s", "ms_per_step": 1e3 * dt_e2e / args.steps,
+                    "h2d_bytes_per_step": int(n) * int(L) * 4, "d2h_bytes_per_step": int(d2h_bytes)},
+            "gpu_launches": int(launches),
+            "clocks": clocks,
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            ns = 3000
+            work_s, t_all, t_dist = cpu_reference_step(X, ns, 1, WORKLOAD["thresholds"])
+            line["cpu_baseline"] = {"value": work_s / t_all, "unit": "comparisons/s", "cores": 1, "kind": "port",
+                                    "sample": "first %d samples x %d loci, C port of the cgmlst-dists rule + scipy "
+                                              "single linkage + %d cuts (%.1f s)" % (ns, L, WORKLOAD["thresholds"], t_all)}
+        print(json.dumps(line))
+    ctx.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def ctx_npad(n):
+    return (n + 127) // 128 * 128
+
+
+if __name__ == "__main__":
+    a = parse_args()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_ours(a)

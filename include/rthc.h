@@ -122,6 +122,8 @@ int rthc_info(const rthc_ctx *ctx, int64_t *info, int n_info);
  * [0]=h2d, [1]=recode+pack, [2]=distance kernel, [3]=mst/merge loop, [4]=cut,
  * [5]=number of kernel launches since create                                       */
 int rthc_timings(const rthc_ctx *ctx, double *ms, int n_ms);
+/* integer-ALU roofline probe: independent LOP3 streams at full occupancy, lane-ops per second */
+int rthc_alu_peak(rthc_ctx *ctx, double *lane_ops_per_s);
 
 #ifdef __cplusplus
 }

@@ -61,6 +61,7 @@ def load_library():
         "rthc_cut": (ci, [vp, vp, ci, vp]),
         "rthc_info": (ci, [vp, vp, ci]),
         "rthc_timings": (ci, [vp, vp, ci]),
+        "rthc_alu_peak": (ci, [vp, ctypes.POINTER(ctypes.c_double)]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(L, name)
@@ -75,7 +76,7 @@ EXPORTED_SYMBOLS = [
     "rthc_set_profiles_i32", "rthc_set_profiles_i32_device", "rthc_distance", "rthc_owned_pairs",
     "rthc_get_condensed_u16", "rthc_get_owned_condensed_u16", "rthc_copy_rows_u16", "rthc_direct_pairs",
     "rthc_set_condensed_f64", "rthc_set_single_algo", "rthc_linkage", "rthc_local_forest",
-    "rthc_linkage_from_forest", "rthc_cut", "rthc_info", "rthc_timings",
+    "rthc_linkage_from_forest", "rthc_cut", "rthc_info", "rthc_timings", "rthc_alu_peak",
 ]
 
 
@@ -213,3 +214,9 @@ class HCContext:
         self._check(self._L.rthc_timings(self._h, _ptr(a), 6))
         keys = ["h2d_ms", "recode_ms", "distance_ms", "linkage_ms", "cut_ms", "launches"]
         return dict(zip(keys, (float(x) for x in a)))
+
+    def alu_peak(self):
+        """Measured int32 ALU lane-ops/s of this GPU (LOP3 stream microbenchmark)."""
+        v = ctypes.c_double(0)
+        self._check(self._L.rthc_alu_peak(self._h, ctypes.byref(v)))
+        return v.value
