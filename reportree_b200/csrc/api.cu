@@ -4,6 +4,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstring>
+#include <cstdlib>
 
 #include "rthc_internal.cuh"
 
@@ -66,7 +67,7 @@ static void free_distance_state(rthc_ctx *ctx)
     rthc_dev_free(&ctx->d_codes); rthc_dev_free(&ctx->d_planes);
     rthc_dev_free(&ctx->d_grp_off); rthc_dev_free(&ctx->d_grp_np);
     rthc_dev_free(&ctx->d_tiles); rthc_dev_free(&ctx->d_row_base);
-    rthc_dev_free(&ctx->d_owned_rows); rthc_dev_free(&ctx->d_cond);
+    rthc_dev_free(&ctx->d_owned_rows);
     rthc_dev_free(&ctx->d_cond_f64);
     ctx->have_profiles = ctx->have_dist = false;
 }
@@ -82,6 +83,7 @@ extern "C" void rthc_destroy(rthc_ctx *ctx)
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     free_distance_state(ctx);
+    rthc_dev_free(&ctx->d_cond);
     free_linkage_state(ctx);
     if (ctx->ev0) cudaEventDestroy(ctx->ev0);
     if (ctx->ev1) cudaEventDestroy(ctx->ev1);
@@ -117,6 +119,7 @@ static inline int owner_of_tile_row(int64_t r, int64_t B, int world)
 static int setup_geometry(rthc_ctx *ctx, int64_t n)
 {
     ctx->n = n;
+    if (const char *e = getenv("RTHC_DIST_NJ")) ctx->dist_nj = atoi(e) == 1 ? 1 : 2;
     ctx->n_pad = (n + RTHC_TILE - 1) / RTHC_TILE * RTHC_TILE;
     const int64_t B = ctx->n_pad / RTHC_TILE;
     ctx->n_tiles_edge = B;
@@ -134,14 +137,15 @@ static int setup_geometry(rthc_ctx *ctx, int64_t n)
         }
     }
     ctx->owned_pairs = off;
-    // supertiles of 16 x 16 tiles keep the sample blocks of concurrently running CTAs in L2
+    // tiles are (128-sample row block I, first 64-sample column block J); supertiles of
+    // 16 row blocks x 32 column blocks keep the blocks of concurrently running CTAs in L2
     std::vector<int2> tiles;
-    const int64_t S = 16;
+    const int64_t S = 16, nj = ctx->dist_nj, B64 = 2 * B;
     for (size_t rc0 = 0; rc0 < owned_tile_rows.size(); rc0 += (size_t)S)
-        for (int64_t c0 = 0; c0 < B; c0 += S)
+        for (int64_t c0 = 0; c0 < B64; c0 += 2 * S)
             for (size_t q = rc0; q < std::min(owned_tile_rows.size(), rc0 + (size_t)S); ++q) {
                 const int64_t I = owned_tile_rows[q];
-                for (int64_t J = std::max(c0, I); J < std::min(B, c0 + S); ++J)
+                for (int64_t J = std::max(c0, 2 * I); J < std::min(B64, c0 + 2 * S); J += nj)
                     tiles.push_back(make_int2((int)I, (int)J));
             }
     ctx->n_tiles = (int64_t)tiles.size();
@@ -229,8 +233,11 @@ extern "C" int rthc_distance(rthc_ctx *ctx)
     if (!ctx->have_profiles) return rthc_fail(ctx, RTHC_E_STATE, "rthc_distance before rthc_set_profiles_i32");
     RTHC_CUDA(ctx, cudaSetDevice(ctx->device));
     int rc;
-    if (!ctx->d_cond)
+    if (!ctx->d_cond || ctx->cond_cap < ctx->owned_pairs) {
+        ctx->cond_cap = 0;
         if ((rc = rthc_dev_alloc(ctx, &ctx->d_cond, (size_t)std::max<int64_t>(ctx->owned_pairs, 1)))) return rc;
+        ctx->cond_cap = std::max<int64_t>(ctx->owned_pairs, 1);
+    }
     if ((rc = rthc_run_distance(ctx))) return rc;
     ctx->have_dist = true;
     return 0;

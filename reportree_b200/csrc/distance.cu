@@ -14,13 +14,14 @@
 // Tiling: one CTA computes a 128 x 128 sample tile of the upper triangle with 256
 // threads, each holding an 8 x 8 block of pairs in registers (64 accumulators + 64
 // running mismatch words).  The plane rows of the 128 + 128 samples of one locus group
-// form one pipeline stage; stages are filled by TMA bulk copies (cp.async.bulk, 512 B
-// per plane row) completing on mbarriers, RTHC_STAGES deep, so loads of groups g+1..g+3
-// overlap the LOP3 stream of group g.  Results go straight to the condensed uint16
+// form one pipeline stage; a stage is filled by two TMA bulk copies (cp.async.bulk, one per
+// sample block, planes are stored tile-blocked so each is one contiguous run) completing on
+// an mbarrier, RTHC_STAGES deep, so loads of groups g+1..g+3 overlap the LOP3 stream of
+// group g; operand words of plane k+1 are fetched from shared memory while plane k is combined.  Results go straight to the condensed uint16
 // upper triangle (scipy pdist order) -- the square matrix is never materialised.
 #include "rthc_internal.cuh"
 
-#define RTHC_STAGES 4
+#define RTHC_STAGES 6
 #define DIST_THREADS 256
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p)
@@ -67,23 +68,56 @@ __device__ __forceinline__ void tma_bulk_g2s(void *dst_smem, const void *src_gme
         : "memory");
 }
 
-// stage layout in shared memory: [max_np][128] words of the I block, then the same for J
-__global__ void __launch_bounds__(DIST_THREADS, 1)
+// Plane layout in HBM is blocked by 64 samples: planes[((s / 64) * plane_rows + row) * 64 + s % 64],
+// so the np plane rows of one locus group of one 64-sample block are one contiguous run of
+// np * 256 bytes = ONE bulk copy.  A stage in shared memory holds 2 + NJ such blocks
+// ([max_np][64] words each): the two halves of the 128-sample I block, then NJ J blocks.
+//
+// NJ = 2: 128 x 128 tile, 8 x 8 pairs per thread, 1 CTA (8 warps) per SM.
+// NJ = 1: 128 x  64 tile, 8 x 4 pairs per thread, <= 128 registers, 2 CTAs (16 warps) per SM:
+//         the second CTA's LOP3 stream covers the POPC tail and barrier waits of the first.
+template <int NJ> struct PlaneOps {
+    uint32_t a[8], b[4 * NJ];
+};
+template <int NJ>
+__device__ __forceinline__ PlaneOps<NJ> load_ops(const uint32_t *st, int blk_words, int ty, int tx, int k)
+{
+    PlaneOps<NJ> o;
+    const uint4 a0 = *reinterpret_cast<const uint4 *>(st + k * RTHC_BLK + 4 * ty);
+    const uint4 a1 = *reinterpret_cast<const uint4 *>(st + blk_words + k * RTHC_BLK + 4 * ty);
+    o.a[0] = a0.x; o.a[1] = a0.y; o.a[2] = a0.z; o.a[3] = a0.w;
+    o.a[4] = a1.x; o.a[5] = a1.y; o.a[6] = a1.z; o.a[7] = a1.w;
+#pragma unroll
+    for (int h = 0; h < NJ; ++h) {
+        const uint4 b0 = *reinterpret_cast<const uint4 *>(st + (2 + h) * blk_words + k * RTHC_BLK + 4 * tx);
+        o.b[4 * h + 0] = b0.x; o.b[4 * h + 1] = b0.y; o.b[4 * h + 2] = b0.z; o.b[4 * h + 3] = b0.w;
+    }
+    return o;
+}
+
+template <int NJ>
+__global__ void __launch_bounds__(DIST_THREADS, NJ == 1 ? 2 : 1)
 rthc_distance_bitsliced(const uint32_t *__restrict__ planes, const int32_t *__restrict__ grp_off,
-                        const int32_t *__restrict__ grp_np, int G, int max_np, int64_t n_pad,
+                        const int32_t *__restrict__ grp_np, int G, int max_np, int plane_rows,
                         const int2 *__restrict__ tiles, const int64_t *__restrict__ row_base,
                         int64_t n, uint16_t *__restrict__ cond)
 {
+    constexpr int NB = 2 + NJ;          // 64-sample blocks per stage
+    constexpr int TJ = 4 * NJ;          // pairs per thread along j
     extern __shared__ __align__(128) unsigned char smem_raw[];
     __shared__ __align__(8) uint64_t full_bar[RTHC_STAGES];
     __shared__ __align__(8) uint64_t empty_bar[RTHC_STAGES];
 
     const int tid = threadIdx.x;
     const int tx = tid & 15, ty = tid >> 4;
-    const int2 tile = tiles[blockIdx.x];
-    const int64_t i0 = (int64_t)tile.x * RTHC_TILE, j0 = (int64_t)tile.y * RTHC_TILE;
-    const uint32_t stage_words = (uint32_t)max_np * 2u * RTHC_TILE;
+    const int2 tile = tiles[blockIdx.x];          // x: 128-sample row block, y: first 64-sample column block
+    const int64_t i0 = (int64_t)tile.x * RTHC_TILE, j0 = (int64_t)tile.y * RTHC_BLK;
+    const int blk_words = max_np * RTHC_BLK;
+    const uint32_t stage_words = (uint32_t)blk_words * NB;
     uint32_t *stage_base = reinterpret_cast<uint32_t *>(smem_raw);
+    // group table (offset << 8 | np) behind the stages
+    uint32_t *gtab = stage_base + (size_t)RTHC_STAGES * stage_words;
+    for (int g = tid; g < G; g += DIST_THREADS) gtab[g] = ((uint32_t)grp_off[g] << 8) | (uint32_t)grp_np[g];
 
     if (tid == 0) {
 #pragma unroll
@@ -95,18 +129,21 @@ rthc_distance_bitsliced(const uint32_t *__restrict__ planes, const int32_t *__re
     }
     __syncthreads();
 
-    auto issue = [&](int g) {   // called by thread 0 only
+    const size_t blk_stride = (size_t)plane_rows * RTHC_BLK;      // words per 64-sample block in HBM
+    auto issue = [&](int g) {   // thread 0 only: one bulk copy per 64-sample block
         const int s = g % RTHC_STAGES;
-        const int np = grp_np[g];
-        const int64_t off = grp_off[g];
-        uint32_t *dstA = stage_base + (size_t)s * stage_words;
-        uint32_t *dstB = dstA + (size_t)max_np * RTHC_TILE;
-        mbar_expect_tx(&full_bar[s], (uint32_t)np * 2u * RTHC_TILE * 4u);
-        for (int k = 0; k < np; ++k) {
-            const uint32_t *row = planes + (off + k) * n_pad;
-            tma_bulk_g2s(dstA + k * RTHC_TILE, row + i0, RTHC_TILE * 4, &full_bar[s]);
-            tma_bulk_g2s(dstB + k * RTHC_TILE, row + j0, RTHC_TILE * 4, &full_bar[s]);
-        }
+        const uint32_t e = gtab[g];
+        const uint32_t np = e & 0xFFu, off = e >> 8;
+        const uint32_t bytes = np * RTHC_BLK * 4u;
+        uint32_t *dst = stage_base + (size_t)s * stage_words;
+        mbar_expect_tx(&full_bar[s], NB * bytes);
+        tma_bulk_g2s(dst, planes + (size_t)(2 * tile.x) * blk_stride + (size_t)off * RTHC_BLK, bytes, &full_bar[s]);
+        tma_bulk_g2s(dst + blk_words, planes + (size_t)(2 * tile.x + 1) * blk_stride + (size_t)off * RTHC_BLK,
+                     bytes, &full_bar[s]);
+#pragma unroll
+        for (int h = 0; h < NJ; ++h)
+            tma_bulk_g2s(dst + (2 + h) * blk_words,
+                         planes + (size_t)(tile.y + h) * blk_stride + (size_t)off * RTHC_BLK, bytes, &full_bar[s]);
     };
 
     if (tid == 0) {
@@ -114,15 +151,34 @@ rthc_distance_bitsliced(const uint32_t *__restrict__ planes, const int32_t *__re
         for (int g = 0; g < pre; ++g) issue(g);
     }
 
-    uint32_t acc[8][8];
+    // Accumulators are packed two 16-bit counters per register (distances <= L <= 65535 cannot
+    // carry across): pair (a, b) lives in accp[a][b % 4], low half for b < 4, high half otherwise
+    // (NJ = 1 uses the low half only).  mm[][] holds the masked mismatch words of the PREVIOUS
+    // group; their POPCs (XU pipe, 16 lanes/clk/SM) are spread 16 per peeled plane block so that
+    // they overlap the LOP3 stream (ALU pipe) of the current group instead of serialising after it.
+    uint32_t accp[8][4];
+    uint32_t mm[8][TJ];
 #pragma unroll
-    for (int a = 0; a < 8; ++a)
+    for (int a = 0; a < 8; ++a) {
 #pragma unroll
-        for (int b = 0; b < 8; ++b) acc[a][b] = 0;
+        for (int b = 0; b < 4; ++b) accp[a][b] = 0;
+#pragma unroll
+        for (int b = 0; b < TJ; ++b) mm[a][b] = 0;
+    }
+    constexpr int QA = 2;               // rows of mm retired per peeled block (4 blocks x 2 rows = 8)
+#define RTHC_RETIRE(a, b)                                                          \
+    do {                                                                           \
+        const uint32_t pc_ = (uint32_t)__popc(mm[a][b]);                           \
+        accp[a][(b) & 3] += ((b) < 4) ? pc_ : pc_ * 65536u;                        \
+    } while (0)
 
+    PlaneOps<NJ> cur;
+    if (G > 0) {
+        mbar_wait(&full_bar[0], 0);
+        cur = load_ops<NJ>(stage_base, blk_words, ty, tx, 0);
+    }
     for (int g = 0; g < G; ++g) {
         const int s = g % RTHC_STAGES;
-        const uint32_t parity = (uint32_t)(g / RTHC_STAGES) & 1u;
         // refill the stage released one iteration ago (keeps thread 0 off the critical path)
         if (tid == 0 && g >= 1 && g - 1 + RTHC_STAGES < G) {
             const int gp = g - 1;
@@ -130,48 +186,72 @@ rthc_distance_bitsliced(const uint32_t *__restrict__ planes, const int32_t *__re
             issue(gp + RTHC_STAGES);
         }
         __syncwarp();
-        mbar_wait(&full_bar[s], parity);
+        const int np = (int)(gtab[g] & 0xFFu);      // >= RTHC_MIN_BITS + 1
+        const uint32_t *st = stage_base + (size_t)s * stage_words;
 
-        const int np = grp_np[g];
-        const uint32_t *sA = stage_base + (size_t)s * stage_words;
-        const uint32_t *sB = sA + (size_t)max_np * RTHC_TILE;
-        const uint4 *pa = reinterpret_cast<const uint4 *>(sA) + ty;   // samples 4ty.. and 64+4ty..
-        const uint4 *pb = reinterpret_cast<const uint4 *>(sB) + tx;
-
-        uint32_t m[8][8];
-        {
-            uint4 a0 = pa[0], a1 = pa[16], b0 = pb[0], b1 = pb[16];
-            const uint32_t av[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
-            const uint32_t bv[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+        uint32_t m[8][TJ];
+        // block 0: bit plane 0 (XOR) + retire rows 0..1 of the previous group
+        PlaneOps<NJ> nxt = load_ops<NJ>(st, blk_words, ty, tx, 1);
+#pragma unroll
+        for (int a = 0; a < 8; ++a)
+#pragma unroll
+            for (int b = 0; b < TJ; ++b) {
+                m[a][b] = cur.a[a] ^ cur.b[b];
+                if (a < QA) RTHC_RETIRE(a, b);
+            }
+        cur = nxt;
+        // block 1: bit plane 1 + retire rows 2..3
+        nxt = load_ops<NJ>(st, blk_words, ty, tx, 2);
+#pragma unroll
+        for (int a = 0; a < 8; ++a)
+#pragma unroll
+            for (int b = 0; b < TJ; ++b) {
+                m[a][b] |= cur.a[a] ^ cur.b[b];
+                if (a < QA) RTHC_RETIRE(a + QA, b);
+            }
+        cur = nxt;
+        // middle bit planes 2 .. np-3
+        for (int k = 2; k < np - 2; ++k) {
+            nxt = load_ops<NJ>(st, blk_words, ty, tx, k + 1);
 #pragma unroll
             for (int a = 0; a < 8; ++a)
 #pragma unroll
-                for (int b = 0; b < 8; ++b) m[a][b] = av[a] ^ bv[b];
+                for (int b = 0; b < TJ; ++b) m[a][b] |= cur.a[a] ^ cur.b[b];
+            cur = nxt;
         }
-        for (int k = 1; k < np - 1; ++k) {
-            const uint4 *qa = pa + k * (RTHC_TILE / 4), *qb = pb + k * (RTHC_TILE / 4);
-            uint4 a0 = qa[0], a1 = qa[16], b0 = qb[0], b1 = qb[16];
-            const uint32_t av[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
-            const uint32_t bv[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+        // block 2: last bit plane (np-2) + retire rows 4..5
+        nxt = load_ops<NJ>(st, blk_words, ty, tx, np - 1);
 #pragma unroll
-            for (int a = 0; a < 8; ++a)
+        for (int a = 0; a < 8; ++a)
 #pragma unroll
-                for (int b = 0; b < 8; ++b) m[a][b] |= av[a] ^ bv[b];
+            for (int b = 0; b < TJ; ++b) {
+                m[a][b] |= cur.a[a] ^ cur.b[b];
+                if (a < QA) RTHC_RETIRE(a + 2 * QA, b);
+            }
+        cur = nxt;
+        // block 3: valid plane; fetch plane 0 of group g+1 first so its latency hides here
+        if (g + 1 < G) {
+            const int s1 = (g + 1) % RTHC_STAGES;
+            mbar_wait(&full_bar[s1], (uint32_t)((g + 1) / RTHC_STAGES) & 1u);
+            nxt = load_ops<NJ>(stage_base + (size_t)s1 * stage_words, blk_words, ty, tx, 0);
         }
-        {
-            const int k = np - 1;   // valid plane
-            const uint4 *qa = pa + k * (RTHC_TILE / 4), *qb = pb + k * (RTHC_TILE / 4);
-            uint4 a0 = qa[0], a1 = qa[16], b0 = qb[0], b1 = qb[16];
-            const uint32_t av[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
-            const uint32_t bv[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
 #pragma unroll
-            for (int a = 0; a < 8; ++a)
+        for (int a = 0; a < 8; ++a)
 #pragma unroll
-                for (int b = 0; b < 8; ++b) acc[a][b] += __popc(m[a][b] & av[a] & bv[b]);
-        }
+            for (int b = 0; b < TJ; ++b) {
+                if (a >= 3 * QA) RTHC_RETIRE(a, b);          // rows 6..7, before they are overwritten
+                mm[a][b] = m[a][b] & cur.a[a] & cur.b[b];
+            }
+        cur = nxt;
         __syncwarp();
         if ((tid & 31) == 0) mbar_arrive(&empty_bar[s]);
     }
+    // retire the last group
+#pragma unroll
+    for (int a = 0; a < 8; ++a)
+#pragma unroll
+        for (int b = 0; b < TJ; ++b) RTHC_RETIRE(a, b);
+#undef RTHC_RETIRE
 
     // epilogue: condensed upper triangle, scipy order: row_base[i] + (j - i - 1)
 #pragma unroll
@@ -181,9 +261,10 @@ rthc_distance_bitsliced(const uint32_t *__restrict__ planes, const int32_t *__re
         const int64_t base = row_base[i];
         if (base < 0) continue;
 #pragma unroll
-        for (int b = 0; b < 8; ++b) {
+        for (int b = 0; b < TJ; ++b) {
             const int64_t j = j0 + (b < 4 ? 4 * tx + b : 64 + 4 * tx + (b - 4));
-            if (j > i && j < n) cond[base + (j - i - 1)] = (uint16_t)acc[a][b];
+            const uint32_t d = b < 4 ? (accp[a][b] & 0xFFFFu) : (accp[a][b & 3] >> 16);
+            if (j > i && j < n) cond[base + (j - i - 1)] = (uint16_t)d;
         }
     }
 }
@@ -220,21 +301,29 @@ int rthc_run_direct_pairs(rthc_ctx *ctx, const int32_t *d_pi, const int32_t *d_p
     return 0;
 }
 
+template <int NJ> static int launch_distance(rthc_ctx *ctx, int max_np)
+{
+    const size_t smem = (size_t)RTHC_STAGES * (size_t)max_np * (2 + NJ) * RTHC_BLK * sizeof(uint32_t) +
+                        (size_t)(ctx->G + 1) * sizeof(uint32_t);
+    if (smem > (NJ == 1 ? 100u : 200u) * 1024u)
+        return rthc_fail(ctx, RTHC_E_RANGE, "plane stage does not fit shared memory (max_np=%d)", max_np);
+    RTHC_CUDA(ctx, cudaFuncSetAttribute(rthc_distance_bitsliced<NJ>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                        (int)smem));
+    RTHC_CUDA(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
+    rthc_distance_bitsliced<NJ><<<(unsigned)ctx->n_tiles, DIST_THREADS, smem, ctx->stream>>>(
+        ctx->d_planes, ctx->d_grp_off, ctx->d_grp_np, ctx->G, max_np, ctx->plane_rows, ctx->d_tiles,
+        ctx->d_row_base, ctx->n, ctx->d_cond);
+    RTHC_LAUNCH_CHECK(ctx);
+    RTHC_CUDA(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
+    return 0;
+}
+
 int rthc_run_distance(rthc_ctx *ctx)
 {
     if (ctx->n_tiles == 0) return 0;
     const int max_np = ctx->max_np > 0 ? ctx->max_np : 1;
-    const size_t smem = (size_t)RTHC_STAGES * (size_t)max_np * 2 * RTHC_TILE * sizeof(uint32_t);
-    if (smem > 200 * 1024)
-        return rthc_fail(ctx, RTHC_E_RANGE, "plane stage does not fit shared memory (max_np=%d)", max_np);
-    RTHC_CUDA(ctx, cudaFuncSetAttribute(rthc_distance_bitsliced, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                        (int)smem));
-    RTHC_CUDA(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
-    rthc_distance_bitsliced<<<(unsigned)ctx->n_tiles, DIST_THREADS, smem, ctx->stream>>>(
-        ctx->d_planes, ctx->d_grp_off, ctx->d_grp_np, ctx->G, max_np, ctx->n_pad, ctx->d_tiles,
-        ctx->d_row_base, ctx->n, ctx->d_cond);
-    RTHC_LAUNCH_CHECK(ctx);
-    RTHC_CUDA(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
+    int rc = ctx->dist_nj == 1 ? launch_distance<1>(ctx, max_np) : launch_distance<2>(ctx, max_np);
+    if (rc) return rc;
     RTHC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     float ms = 0;
     RTHC_CUDA(ctx, cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1));

@@ -28,18 +28,16 @@ __global__ void rthc_fill_u64(uint64_t *a, int64_t n, uint64_t val)
 }
 
 __device__ __forceinline__ void consider(uint32_t w, uint32_t i, uint32_t j, int32_t ci,
-                                         const int32_t *__restrict__ comp, uint64_t *best, uint64_t &mine)
+                                         const int32_t *__restrict__ comp, uint64_t &mine)
 {
-    const int32_t cj = comp[j];
-    if (cj != ci) {
+    if (comp[j] != ci) {
         const uint64_t key = rthc_pack_key(w, i, j);
         if (key < mine) mine = key;
-        if (key < best[cj]) atomicMin((unsigned long long *)&best[cj], (unsigned long long)key);
     }
 }
 
-// one CTA per owned row i: stream D[i, i+1..n-1], lightest outgoing edge for comp[i] (block
-// reduction, one atomic) and for every comp[j] (filtered atomics)
+// ROW PASS.  One CTA per owned row i: stream D[i, i+1..n-1] (16-byte loads), lightest edge
+// leaving comp[i] through a column j > i; block reduction, one atomic per row.
 __global__ void __launch_bounds__(SCAN_THREADS)
 rthc_boruvka_scan(const uint16_t *__restrict__ cond, const int64_t *__restrict__ row_base,
                   const int32_t *__restrict__ owned_rows, int64_t n, const int32_t *__restrict__ comp,
@@ -55,24 +53,24 @@ rthc_boruvka_scan(const uint16_t *__restrict__ cond, const int64_t *__restrict__
 
     int64_t head = (8 - (base & 7)) & 7;
     if (head > len) head = len;
-    if (tid < head) consider(cond[base + tid], i, i + 1 + (uint32_t)tid, ci, comp, best, mine);
+    if (tid < head) consider(cond[base + tid], i, i + 1 + (uint32_t)tid, ci, comp, mine);
     const int64_t nvec = (len - head) >> 3;
     const uint4 *vec = reinterpret_cast<const uint4 *>(cond + base + head);
     for (int64_t v = tid; v < nvec; v += SCAN_THREADS) {
         const uint4 q = vec[v];
         const uint32_t j = i + 1 + (uint32_t)head + (uint32_t)(v << 3);
-        consider(q.x & 0xFFFFu, i, j + 0, ci, comp, best, mine);
-        consider(q.x >> 16, i, j + 1, ci, comp, best, mine);
-        consider(q.y & 0xFFFFu, i, j + 2, ci, comp, best, mine);
-        consider(q.y >> 16, i, j + 3, ci, comp, best, mine);
-        consider(q.z & 0xFFFFu, i, j + 4, ci, comp, best, mine);
-        consider(q.z >> 16, i, j + 5, ci, comp, best, mine);
-        consider(q.w & 0xFFFFu, i, j + 6, ci, comp, best, mine);
-        consider(q.w >> 16, i, j + 7, ci, comp, best, mine);
+        consider(q.x & 0xFFFFu, i, j + 0, ci, comp, mine);
+        consider(q.x >> 16, i, j + 1, ci, comp, mine);
+        consider(q.y & 0xFFFFu, i, j + 2, ci, comp, mine);
+        consider(q.y >> 16, i, j + 3, ci, comp, mine);
+        consider(q.z & 0xFFFFu, i, j + 4, ci, comp, mine);
+        consider(q.z >> 16, i, j + 5, ci, comp, mine);
+        consider(q.w & 0xFFFFu, i, j + 6, ci, comp, mine);
+        consider(q.w >> 16, i, j + 7, ci, comp, mine);
     }
     const int64_t done = head + (nvec << 3);
     if (done + tid < len)
-        consider(cond[base + done + tid], i, i + 1 + (uint32_t)(done + tid), ci, comp, best, mine);
+        consider(cond[base + done + tid], i, i + 1 + (uint32_t)(done + tid), ci, comp, mine);
 
     // block min
 #pragma unroll
@@ -89,6 +87,41 @@ rthc_boruvka_scan(const uint16_t *__restrict__ cond, const int64_t *__restrict__
         if (mine != RTHC_KEY_INF && mine < best[ci])
             atomicMin((unsigned long long *)&best[ci], (unsigned long long)mine);
     }
+}
+
+// COLUMN PASS.  Edge (i, j), i < j, is also a candidate for comp[j].  A CTA owns 256
+// consecutive columns and a chunk of COL_ROWS rows; thread t walks down column j: for a fixed
+// row the 256 threads read 512 contiguous bytes of the condensed row, comp[i] and row_base[i]
+// are warp-uniform.  One filtered atomic per thread per chunk.
+#define COL_ROWS 512
+__global__ void __launch_bounds__(256)
+rthc_boruvka_scan_cols(const uint16_t *__restrict__ cond, const int64_t *__restrict__ row_base, int64_t n,
+                       const int32_t *__restrict__ comp, uint64_t *best)
+{
+    const int64_t j = (int64_t)blockIdx.x * 256 + threadIdx.x;
+    const int64_t r0 = (int64_t)blockIdx.y * COL_ROWS;
+    const int64_t jmax = (int64_t)blockIdx.x * 256 + 255;
+    if (r0 >= jmax || r0 >= n) return;
+    int64_t r1 = r0 + COL_ROWS;
+    if (r1 > jmax) r1 = jmax;            // rows i < j only
+    if (r1 > n) r1 = n;
+    const bool live = j < n;
+    const int32_t cj = live ? comp[j] : -1;
+    uint64_t mine = RTHC_KEY_INF;
+#pragma unroll 4
+    for (int64_t i = r0; i < r1; ++i) {
+        const int64_t base = row_base[i];
+        if (base < 0) continue;           // row not owned by this shard (uniform)
+        if (live && i < j) {
+            const uint32_t w = cond[base + (j - i - 1)];
+            if (comp[i] != cj) {
+                const uint64_t key = rthc_pack_key(w, (uint32_t)i, (uint32_t)j);
+                if (key < mine) mine = key;
+            }
+        }
+    }
+    if (mine != RTHC_KEY_INF && mine < best[cj])
+        atomicMin((unsigned long long *)&best[cj], (unsigned long long)mine);
 }
 
 // same round step over an explicit edge list (merge of the ranks' forests)
@@ -230,6 +263,9 @@ int rthc_boruvka_owned(rthc_ctx *ctx, std::vector<uint64_t> &keys)
         if (n_owned > 0) {
             rthc_boruvka_scan<<<(unsigned)n_owned, SCAN_THREADS, 0, ctx->stream>>>(
                 ctx->d_cond, ctx->d_row_base, ctx->d_owned_rows, n, d_comp, d_best);
+            RTHC_LAUNCH_CHECK(ctx);
+            dim3 grd((unsigned)((n + 255) / 256), (unsigned)((n + COL_ROWS - 1) / COL_ROWS));
+            rthc_boruvka_scan_cols<<<grd, 256, 0, ctx->stream>>>(ctx->d_cond, ctx->d_row_base, n, d_comp, d_best);
             RTHC_LAUNCH_CHECK(ctx);
         }
         return 0;

@@ -6,8 +6,10 @@
 // reserved for missing (equality-preserving, so distances are bit-exact), then 32 loci
 // at a time are bit-sliced into "plane" words:
 //
-//   planes[off_g + k][s]  bit l = bit k of code(sample s, locus perm[32 g + l])   k < bits_g
-//   planes[off_g + bits_g][s] bit l = (code != 0)                                  (valid plane)
+//   plane row off_g + k      : bit l = bit k of code(sample s, locus perm[32 g + l])   k < bits_g
+//   plane row off_g + bits_g : bit l = (code != 0)                                  (valid plane)
+// stored tile-blocked, planes[(s / 64) * plane_rows + row][s % 64], so that the rows of one
+// group for one 128-sample block are one contiguous run (one TMA bulk copy per stage).
 //
 // Loci are permuted by bit width (the distance is a sum over loci, so order is free),
 // which keeps every group at the minimum number of planes; loci with <= 1 distinct
@@ -200,7 +202,7 @@ rthc_rank_column_wide(const int32_t *__restrict__ colmajor, uint16_t *__restrict
 // ---- 3. bit-slice 32 loci into plane words --------------------------------------------
 __global__ void rthc_pack_planes(const uint16_t *__restrict__ codes, const int32_t *__restrict__ perm,
                                  const int32_t *__restrict__ grp_off, const int32_t *__restrict__ grp_np,
-                                 uint32_t *__restrict__ planes, int64_t n_pad)
+                                 uint32_t *__restrict__ planes, int64_t n_pad, int plane_rows)
 {
     const int g = blockIdx.y;
     const int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -218,11 +220,14 @@ __global__ void rthc_pack_planes(const uint16_t *__restrict__ codes, const int32
 #pragma unroll
         for (int k = 0; k < 16; ++k) pl[k] |= ((c >> k) & 1u) << l;
     }
+    // tile-blocked layout: [s / 64][plane row][s % 64]
     const int64_t off = grp_off[g];
+    const int64_t blk = (s / RTHC_BLK) * (int64_t)plane_rows;
+    const int64_t lane_s = s % RTHC_BLK;
 #pragma unroll
     for (int k = 0; k < 16; ++k)
-        if (k < bits) planes[(off + k) * n_pad + s] = pl[k];
-    planes[(off + bits) * n_pad + s] = valid;
+        if (k < bits) planes[(blk + off + k) * RTHC_BLK + lane_s] = pl[k];
+    planes[(blk + off + bits) * RTHC_BLK + lane_s] = valid;
 }
 
 // ---- host driver -----------------------------------------------------------------------
@@ -324,7 +329,7 @@ int rthc_recode_and_pack(rthc_ctx *ctx, const int32_t *d_rowmajor)
     std::vector<int32_t> perm((size_t)G * 32, -1), goff((size_t)std::max(G, 1)), gnp((size_t)std::max(G, 1));
     int rows = 0, max_np = 0;
     for (int g = 0; g < G; ++g) {
-        int bits = 0;
+        int bits = RTHC_MIN_BITS;      // the distance kernel peels 3 bit planes + the valid plane per group
         for (int l = 0; l < 32; ++l) {
             size_t idx = (size_t)g * 32 + (size_t)l;
             if (idx < kept.size()) {
@@ -354,7 +359,7 @@ int rthc_recode_and_pack(rthc_ctx *ctx, const int32_t *d_rowmajor)
                                        cudaMemcpyHostToDevice, ctx->stream));
         dim3 grd((unsigned)((n_pad + 255) / 256), (unsigned)G);
         rthc_pack_planes<<<grd, 256, 0, ctx->stream>>>(ctx->d_codes, d_perm, ctx->d_grp_off,
-                                                       ctx->d_grp_np, ctx->d_planes, n_pad);
+                                                       ctx->d_grp_np, ctx->d_planes, n_pad, rows);
         RTHC_LAUNCH_CHECK(ctx);
     }
     RTHC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));

@@ -8,7 +8,9 @@
 
 #include "../../include/rthc.h"
 
-#define RTHC_TILE 128            // samples per tile edge of the distance kernel
+#define RTHC_TILE 128            // samples per tile-row (ownership granularity) of the distance kernel
+#define RTHC_BLK 64              // samples per plane block in HBM / per bulk copy
+#define RTHC_MIN_BITS 3          // every locus group carries at least 3 bit planes (zero-padded)
 #define RTHC_KEY_INF 0xFFFFFFFFFFFFFFFFull
 
 // (w, i, j) packed as w<<48 | i<<24 | j  (i < j < 2^24, w < 2^16): one total order
@@ -28,6 +30,7 @@ struct rthc_ctx {
 
     // shard
     int rank = 0, world = 1;
+    int dist_nj = 2;               // 64-sample column blocks per distance tile (1: 128x64, 2: 128x128)
 
     // problem
     int64_t n = 0, L = 0, n_pad = 0;
@@ -51,6 +54,7 @@ struct rthc_ctx {
     int32_t *d_owned_rows = nullptr;
     int64_t owned_pairs = 0;
     uint16_t *d_cond = nullptr;    // condensed uint16 distances of the owned rows
+    int64_t cond_cap = 0;          // allocated entries of d_cond (kept across calls of equal size)
     bool have_profiles = false, have_dist = false;
 
     // externally supplied condensed matrix (-d_mx)

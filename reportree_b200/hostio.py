@@ -110,3 +110,8 @@ def newick(Z, leaf_names):
         else:
             out.append(");" if node == root else "):%.2f" % (ph - height[k]))
     return "".join(out)
+
+
+def write_partitions(path, columns):
+    """<out>_partitions.tsv: same text as DataFrame(columns).to_csv(sep='\\t', index=None) (:779-780)."""
+    pandas.DataFrame(data=columns).to_csv(path, sep="\t", index=None)

@@ -180,3 +180,246 @@ def filter_rows(mx, args, say):
     mx = mx[mx[mx.columns[0]].isin(passing)]
     mx.to_csv(args.out + "_flt_samples_matrix.tsv", index=False, header=True, sep="\t")
     return mx
+
+
+# --------------------------------------------------------------------------------------------
+# threshold planning (scripts/partitioning_HC.py:575-615) -- pure host logic, unit-tested on CPU
+# --------------------------------------------------------------------------------------------
+
+def plan_runs(method_threshold, pct_method_threshold, total_size, say):
+    """Returns (runs: {method: [(threshold_str, kind)]}, pct_correspondence: {thr: [pct_str]})."""
+    runs, pct_corr = {}, {}
+    if pct_method_threshold != "none":
+        say("\n\tCorrespondence between percentage and number of differences:")
+        say("\n\t#METHOD\tPERCENTAGE\tDIFFERENCES")
+        for item in pct_method_threshold.split(","):
+            method = item.split("-")[0]
+            pct = item.split("-", 1)[1]
+            thr = str(int(int(total_size) * float(pct)))
+            runs.setdefault(method, [])
+            if (thr, "pct") not in runs[method]:
+                runs[method].append((thr, "pct"))
+            pct_corr.setdefault(thr, [])
+            if str(pct) not in pct_corr[thr]:
+                pct_corr[thr].append(str(pct))
+                say("\t" + str(float(pct) * 100) + "\t" + thr)
+    for item in method_threshold.split(","):
+        if "-" not in item:
+            runs.setdefault(item, []).append(("all", "general"))
+        else:
+            method = item.split("-")[0]
+            runs.setdefault(method, []).append((str(item.split("-", 1)[1]), "general"))
+    return runs, pct_corr
+
+
+def expand_cuts(method, requests, pct_corr, max_dist, dist_unit, say):
+    """One linkage method -> ordered list of (partition column name, cutoff) following
+    :641-772 literally (range clipping, skip messages, pct cutoffs are not scaled by -d)."""
+    cuts = []
+    for threshold, kind in requests:
+        if threshold == "all":
+            say("\tCalculating clustering in range", str(0), str(max_dist), "with a distance of", str(dist_unit))
+            for thr in range(0, int(max_dist) + 1):
+                cuts.append((method + "-" + str(thr) + "x" + str(dist_unit), int(thr) * dist_unit))
+        elif "-" in threshold:
+            lo = int(threshold.split("-")[0])
+            hi = int(threshold.split("-")[1]) + 1
+            if lo < max_dist and hi > max_dist:
+                hi = int(max_dist) + 1
+            elif lo > max_dist:
+                say("\tThe requested partition, " + str(lo) + ", is higher than the maximum distance. Clustering will not be computed.")
+                continue
+            say("\tCalculating clustering in range", str(lo), str(hi), "with a distance of", str(dist_unit))
+            for thr in range(lo, hi):
+                cuts.append((method + "-" + str(thr) + "x" + str(dist_unit), thr * dist_unit))
+        elif kind == "general":
+            if int(threshold) > max_dist:
+                say("\tThe requested partition, " + str(threshold) + ", is higher than the maximum distance. Clustering will not be computed.")
+                continue
+            say("\tCalculating clustering for threshold", str(threshold), "with a distance of", str(dist_unit))
+            cuts.append((method + "-" + str(threshold) + "x" + str(dist_unit), int(threshold) * dist_unit))
+        elif kind == "pct":
+            for pct in pct_corr[threshold]:
+                say("\tCalculating clustering for threshold " + method + "-" + str(threshold) + ", which corresponds to the pct threshold of: " + str(pct))
+                cuts.append((method + "-" + str(pct), int(threshold)))
+    return cuts
+
+
+def read_distance_matrix(path):
+    """-d_mx entry (:522-525): square TSV with ids in the first column."""
+    return pandas.read_table(path)
+
+
+def square_to_condensed(square):
+    """scipy.spatial.distance.squareform(checks=True) semantics for an n x n array (:186)."""
+    a = np.ascontiguousarray(square, dtype=np.float64)
+    if a.ndim != 2 or a.shape[0] != a.shape[1]:
+        raise ValueError("The matrix argument must be square.")
+    if not np.allclose(a, a.T):
+        raise ValueError("Distance matrix 'X' must be symmetric.")
+    if not (np.diag(a) == 0).all():
+        raise ValueError("Distance matrix 'X' diagonal must be zero.")
+    iu = np.triu_indices(a.shape[0], 1)
+    return a[iu]
+
+
+# --------------------------------------------------------------------------------------------
+# the pipeline
+# --------------------------------------------------------------------------------------------
+
+def _exit(log, code=None):
+    log.close()
+    sys.exit(code)
+
+
+def profile_to_distances(args, say, log, ctx):
+    """`-a` branch: load, clean, filter, encode, distance on the GPU, artefact files.
+    Returns (sample names, total_size)."""
+    say("Profile matrix provided... pairwise distance will be calculated!")
+    mx = load_profile(args.allele_profile, str(args.missing_code), args.out, say)
+
+    if args.metadata != "" and args.filter_column != "":
+        from reportree_b200 import metadata_filter
+        say("Filtering the allele matrix...")
+        meta = pandas.read_table(args.metadata, dtype=str)
+        meta.columns = [c.replace(" ", "_") for c in meta.columns]
+        meta = meta.replace(" ", "_", regex=True)
+        n0 = len(mx)
+        say("\tFiltering metadata for the following parameters: " + " & ".join(args.filter_column.split(";")))
+        keep_ids = metadata_filter.select_samples(meta, args.filter_column)
+        mx = mx[mx[mx.columns[0]].isin(keep_ids)]
+        say("\tFrom the " + str(n0) + " samples, " + str(len(mx)) + " were kept in the matrix...")
+        if len(mx) <= 1:
+            say("\nCannot proceed because " + str(len(mx)) + " samples were kept in the matrix!")
+            _exit(log)
+        mx.to_csv(args.out + "_subset_matrix.tsv", sep="\t", index=None)
+
+    mx, n_loci = filter_columns(mx, args, say)
+    if n_loci <= 1:
+        say("\nCannot proceed because " + str(n_loci) + " sites/loci were kept in the matrix!")
+        _exit(log)
+    with open(args.out + "_loci_used.txt", "w+") as fh:
+        for locus in mx.columns[1:]:
+            print(locus, file=fh)
+    mx.to_csv(args.out + "_clean_missing_matrix.tsv", index=False, header=True, sep="\t")
+
+    mx = filter_rows(mx, args, say)
+    if mx is None:
+        _exit(log)
+
+    say("Getting the pairwise distance matrix with cgmlst-dists (if your profile matrix is too big, this will be done in chunks of 2000 alleles/positions)...")
+    total_size = len(mx.columns) - 1
+    # sample ids travel through TSV text in the reference; NaN ids would print as empty strings
+    names = ["" if not isinstance(s, str) else s for s in mx[mx.columns[0]].tolist()]
+    codes = hostio.encode_cells(mx.iloc[:, 1:])
+    ctx.set_profiles(codes)
+    ctx.distance()
+    if os.environ.get("REPORTREE_HC_SKIP_DIST_TSV", "0") != "1":
+        hostio.write_square_tsv(args.out + "_dist_hamming.tsv", names, ctx.square_rows, len(names))
+    return names, total_size
+
+
+def matrix_to_distances(args, say, log, ctx):
+    """`-d_mx` branch (:522-567): distance matrix supplied."""
+    say("Distance matrix provided... pairwise distance will not be calculated!")
+    dist = read_distance_matrix(args.distance_matrix)
+    if args.metadata != "" and args.filter_column != "":
+        from reportree_b200 import metadata_filter
+        say("Filtering the distance matrix...")
+        meta = pandas.read_table(args.metadata, dtype=str)
+        meta.columns = [c.replace(" ", "_") for c in meta.columns]
+        n0 = len(dist)
+        say("\tFiltering metadata for the following parameters: " + " & ".join(args.filter_column.split(";")))
+        keep_ids = set(metadata_filter.select_samples(meta, args.filter_column))
+        sq = dist.set_index(dist.columns[0], drop=True)
+        cols = [c for c in sq.columns if c in keep_ids]
+        dist = sq.loc[cols, cols].reset_index()
+        say("\tFrom the " + str(n0) + " samples, " + str(len(dist)) + " were kept in the matrix...")
+        if len(dist) <= 1:
+            say("\nCannot proceed because " + str(len(dist)) + " samples were kept in the matrix!")
+            _exit(log)
+        dist.to_csv(args.out + "_flt_dist.tsv", sep="\t", index=None)
+    elif args.metadata != "" and args.filter_column == "":
+        say("Metadata file was provided but no filter was found... I am confused :-(")
+        _exit(log)
+    elif args.metadata == "" and args.filter_column != "":
+        say("Metadata file was not provided but a filter was found... I am confused :-(")
+        _exit(log)
+    sq = dist.set_index(dist.columns[0], drop=True)
+    names = [str(c) for c in sq.columns.tolist()]
+    ctx.set_condensed(square_to_condensed(sq.to_numpy()))
+    return names, None
+
+
+def main(argv=None):
+    args = build_parser().parse_args(argv)
+    log = Tee(args.out + ".log")
+    say = log
+    say("\n-------------------- partitioning_HC.py --------------------\n")
+    say("version", version, "last updated on", last_updated, "\n")
+    say(" ".join(sys.argv), "\n")
+
+    if not args.allele_profile and not args.distance_matrix:
+        say("Could not find a profile or a distance matrix... One of them needs to be specified!!")
+        _exit(log)
+
+    ctx = hc_backend.HCContext(device=int(os.environ.get("REPORTREE_HC_DEVICE", "0")))
+    exact = os.environ.get("REPORTREE_HC_EXACT_NAMES", "1") != "0"
+    ctx.set_single_algo(hc_backend.SL_PRIM if exact else hc_backend.SL_BORUVKA)
+
+    if args.allele_profile:
+        names, total_size = profile_to_distances(args, say, log, ctx)
+    else:
+        names, total_size = matrix_to_distances(args, say, log, ctx)
+
+    say("\tGetting condensed distance matrix...")
+    if args.pct_HCmethod_threshold != "none" and total_size is None:
+        raise NameError("name 'total_size' is not defined")      # same failure as the reference (:586)
+    runs, pct_corr = plan_runs(args.method_threshold, args.pct_HCmethod_threshold, total_size, say)
+
+    columns = {"sequence": names}
+    composition = {}
+    for method, requests in runs.items():
+        say("Hierarchical clustering with method: " + method + "...")
+        if method not in GPU_METHODS:
+            raise hc_backend.HCBackendError(
+                "HC method %r is not implemented on the CUDA backend (available: %s)" % (method, ", ".join(GPU_METHODS)))
+        Z = ctx.linkage(method)
+        max_dist = Z[-1, 2]
+        say("\tMaximum distance " + str(max_dist) + "...")
+        say("\tGenerating newick file...")
+        with open(args.out + "_" + method + "_HC.nwk", "w+") as fh:
+            print(hostio.newick(Z, names), file=fh)
+        say("\tDefining clusters...")
+        cuts = expand_cuts(method, requests, pct_corr, max_dist, args.dist, say)
+        if cuts:
+            labels = ctx.fcluster([c[1] for c in cuts])
+            for k, (partition, _) in enumerate(cuts):
+                col, comp = hostio.name_partition(labels[k], names)
+                columns[partition] = col
+                bucket = composition.setdefault(partition, {})
+                for cname, csize, members in comp:
+                    bucket.setdefault(cname, {}).setdefault(csize, []).extend(members)
+
+    say("Creating sample partitions file...")
+    hostio.write_partitions(args.out + "_partitions.tsv", columns)
+    say("Creating cluster composition file...")
+    with open(args.out + "_clusterComposition.tsv", "w+") as fh:
+        print("#partition\tcluster\tcluster_length\tsamples", file=fh)
+        for partition, clusters in composition.items():
+            for cname, by_size in clusters.items():
+                for csize, members in by_size.items():
+                    print(partition + "\t" + cname + "\t" + str(csize) + "\t" + ",".join(members), file=fh)
+    if len(pct_corr) > 0:
+        with open(args.out + "_parcentage2threshold.tsv", "w+") as fh:
+            print("#percentage\tthreshold", file=fh)
+            for thr, pcts in pct_corr.items():
+                for pct in pcts:
+                    print(str(pct) + "\t" + str(thr), file=fh)
+    say("\npartitioning_HC.py is done!")
+    ctx.close()
+    log.close()
+
+
+if __name__ == "__main__":
+    main()
