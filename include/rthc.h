@@ -96,8 +96,8 @@ int rthc_direct_pairs(rthc_ctx *ctx, const int32_t *pi, const int32_t *pj, int64
                       int32_t *out);
 
 /* `-d_mx` entry: externally supplied condensed distances (scipy order, n(n-1)/2).
- * Values must be non-negative integers <= 65535 for single/complete; any finite
- * non-negative double for average/weighted.                                         */
+ * Any finite non-negative doubles.  Integer-valued matrices <= 65535 take the uint16 paths
+ * (Boruvka / integer complete linkage); others run Prim and the merge loop in float64.  */
 int rthc_set_condensed_f64(rthc_ctx *ctx, const double *y, int64_t n);
 
 /* ---- clustering half --------------------------------------------------------- */

@@ -9,7 +9,7 @@ OUT = os.path.join(HERE, "libreportree_hc.so")
 SOURCES = ["api.cu", "recode.cu", "distance.cu", "mst.cu", "cut.cu", "linkage.cu", "nnchain.cu", "probe.cu"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-O3", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",
-         "-Xcompiler", "-fPIC", "-Xcompiler", "-O3", "--use_fast_math", "-fmad=false"]
+         "-Xcompiler", "-fPIC", "-Xcompiler", "-O3", "-fmad=false"]
 FLAGS += os.environ.get("RTHC_EXTRA_NVCC_FLAGS", "").split()
 
 

@@ -333,3 +333,65 @@ extern "C" int rthc_timings(const rthc_ctx *ctx, double *ms, int n_ms)
     for (int k = 0; k < n_ms && k < 6; ++k) ms[k] = k == 5 ? (double)ctx->launches : ctx->t_ms[k];
     return 0;
 }
+
+// ---- `-d_mx` entry: externally supplied condensed distances --------------------------------
+__global__ void rthc_classify_f64(const double *__restrict__ y, int64_t P, uint16_t *__restrict__ out, int *flags)
+{
+    const int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= P) return;
+    const double v = y[p];
+    int f = 0;
+    if (!(v >= 0.0) || isinf(v)) f |= 1;                       // negative, NaN or infinite
+    else if (v > 65535.0 || v != floor(v)) f |= 2;             // not representable as uint16
+    else out[p] = (uint16_t)v;
+    if (f) atomicOr(flags, f);
+}
+
+extern "C" int rthc_set_condensed_f64(rthc_ctx *ctx, const double *y, int64_t n)
+{
+    if (!ctx || !y) return rthc_fail(ctx, RTHC_E_ARG, "rthc_set_condensed_f64: NULL argument");
+    if (n < 2) return rthc_fail(ctx, RTHC_E_ARG, "need at least 2 samples (n=%lld)", (long long)n);
+    if (n >= (1ll << 24)) return rthc_fail(ctx, RTHC_E_RANGE, "n=%lld exceeds 2^24-1 samples", (long long)n);
+    RTHC_CUDA(ctx, cudaSetDevice(ctx->device));
+    free_distance_state(ctx);
+    free_linkage_state(ctx);
+    const int save_rank = ctx->rank, save_world = ctx->world;
+    ctx->rank = 0; ctx->world = 1;                              // an external matrix is always a full shard
+    int rc = setup_geometry(ctx, n);
+    ctx->rank = save_rank; ctx->world = save_world;
+    if (rc) return rc;
+    ctx->world = 1; ctx->rank = 0;
+    ctx->L = 0; ctx->G = 0; ctx->plane_rows = 0; ctx->L_kept = 0;
+    const int64_t P = n * (n - 1) / 2;
+    int *d_flags = nullptr;
+    if ((rc = rthc_dev_alloc(ctx, &ctx->d_cond_f64, (size_t)P))) return rc;
+    if ((rc = rthc_dev_alloc(ctx, &d_flags, 1))) return rc;
+    if (!ctx->d_cond || ctx->cond_cap < P) {
+        ctx->cond_cap = 0;
+        if ((rc = rthc_dev_alloc(ctx, &ctx->d_cond, (size_t)P))) return rc;
+        ctx->cond_cap = P;
+    }
+    RTHC_CUDA(ctx, cudaMemsetAsync(d_flags, 0, sizeof(int), ctx->stream));
+    RTHC_CUDA(ctx, cudaMemcpyAsync(ctx->d_cond_f64, y, sizeof(double) * (size_t)P, cudaMemcpyHostToDevice, ctx->stream));
+    rthc_classify_f64<<<(unsigned)((P + 255) / 256), 256, 0, ctx->stream>>>(ctx->d_cond_f64, P, ctx->d_cond, d_flags);
+    RTHC_LAUNCH_CHECK(ctx);
+    int flags = 0;
+    RTHC_CUDA(ctx, cudaMemcpyAsync(&flags, d_flags, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+    RTHC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    rthc_dev_free(&d_flags);
+    if (flags & 1) {
+        rthc_dev_free(&ctx->d_cond_f64);
+        return rthc_fail(ctx, RTHC_E_RANGE, "distance matrix holds negative, NaN or infinite entries");
+    }
+    if (flags & 2) {
+        rthc_dev_free(&ctx->d_cond);                             // non-integer distances: float64 path only
+        ctx->cond_cap = 0;
+        ctx->ext_integer = false;
+    } else {
+        rthc_dev_free(&ctx->d_cond_f64);                         // integer distances: uint16 path
+        ctx->ext_integer = true;
+    }
+    ctx->have_dist = true;
+    ctx->have_profiles = false;
+    return 0;
+}

@@ -117,8 +117,7 @@ extern "C" int rthc_linkage(rthc_ctx *ctx, int method, double *Z_out)
     RTHC_CUDA(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
     std::vector<int32_t> ex, ey;
     std::vector<double> ew;
-    if (method == RTHC_SINGLE && ctx->single_algo == RTHC_SL_BORUVKA) {
-        if (!ctx->d_cond) return rthc_fail(ctx, RTHC_E_RANGE, "single linkage needs integer distances <= 65535");
+    if (method == RTHC_SINGLE && ctx->single_algo == RTHC_SL_BORUVKA && ctx->d_cond) {
         std::vector<uint64_t> keys;
         if ((rc = rthc_boruvka_owned(ctx, keys))) return rc;
         ex.resize(keys.size()); ey.resize(keys.size()); ew.resize(keys.size());
