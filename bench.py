@@ -53,28 +53,46 @@ def make_workload(args):
 
 
 class ClockSampler:
-    """nvidia-smi clocks + throttle reasons during the timed region (B200_PROFILING.md)."""
+    """SM clocks + throttle reasons during the timed region (B200_PROFILING.md clocks line), read
+    through NVML in-process (the same counters nvidia-smi prints; spawning nvidia-smi 5x per second
+    was measured to stall the launch-heavy MST stage by up to 8x through driver lock contention)."""
 
-    def __init__(self, index):
-        self.index = index
-        self.rows = []
+    def __init__(self, index, period=0.5):
+        self.index, self.period = index, period
+        self.sm, self.mx, self.reasons = [], [], set()
         self._stop = threading.Event()
         self._thr = None
 
     def _run(self):
-        q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
-             "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
-             "clocks_event_reasons.sw_power_cap")
-        while not self._stop.is_set():
-            try:
-                out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + q,
-                                      "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
-                parts = [p.strip() for p in out.strip().split(",")]
-                if len(parts) >= 7:
-                    self.rows.append(parts)
-            except Exception:
-                pass
-            self._stop.wait(0.2)
+        try:
+            import pynvml as N
+            N.nvmlInit()
+            h = N.nvmlDeviceGetHandleByIndex(self.index)
+            names = {N.nvmlClocksEventReasonHwSlowdown: "hw_slowdown",
+                     N.nvmlClocksEventReasonHwThermalSlowdown: "hw_thermal_slowdown",
+                     N.nvmlClocksEventReasonSwThermalSlowdown: "sw_thermal_slowdown",
+                     N.nvmlClocksEventReasonSwPowerCap: "sw_power_cap"}
+            while not self._stop.is_set():
+                self.sm.append(N.nvmlDeviceGetClockInfo(h, N.NVML_CLOCK_SM))
+                self.mx.append(N.nvmlDeviceGetMaxClockInfo(h, N.NVML_CLOCK_SM))
+                r = N.nvmlDeviceGetCurrentClocksEventReasons(h)
+                self.reasons |= {v for k, v in names.items() if r & k}
+                self._stop.wait(self.period)
+        except Exception as e:                      # no NVML: one nvidia-smi sample per 2 s
+            self.err = repr(e)
+            q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+                 "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+            names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+            while not self._stop.is_set():
+                try:
+                    out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + q,
+                                          "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
+                    parts = [p.strip() for p in out.strip().split(",")]
+                    self.sm.append(float(parts[0])); self.mx.append(float(parts[1]))
+                    self.reasons |= {names[k] for k in range(4) if parts[2 + k].lower().startswith("active")}
+                except Exception:
+                    pass
+                self._stop.wait(2.0)
 
     def start(self):
         self._thr = threading.Thread(target=self._run, daemon=True)
@@ -84,12 +102,8 @@ class ClockSampler:
         self._stop.set()
         if self._thr:
             self._thr.join(timeout=6)
-        sm = [float(r[0]) for r in self.rows if r[0].replace(".", "").isdigit()]
-        mx = [float(r[1]) for r in self.rows if r[1].replace(".", "").isdigit()]
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        reasons = sorted({names[k] for r in self.rows for k in range(4) if r[3 + k].lower().startswith("active")})
-        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": reasons, "samples": len(self.rows)}
+        return {"sm_mhz": float(np.median(self.sm)) if self.sm else None, "sm_max_mhz": max(self.mx) if self.mx else None,
+                "reasons": sorted(self.reasons), "samples": len(self.sm), "source": "nvml" if not hasattr(self, "err") else "nvidia-smi"}
 
 
 # ------------------------------------------------------------------------------------------

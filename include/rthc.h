@@ -124,6 +124,9 @@ int rthc_info(const rthc_ctx *ctx, int64_t *info, int n_info);
 int rthc_timings(const rthc_ctx *ctx, double *ms, int n_ms);
 /* integer-ALU roofline probe: independent LOP3 streams at full occupancy, lane-ops per second */
 int rthc_alu_peak(rthc_ctx *ctx, double *lane_ops_per_s);
+/* same, with the distance kernel's operand pattern (8 x 8 register block, three distinct register
+ * sources per LOP3) at warps_per_sm resident warps: the ceiling of that loop on this chip */
+int rthc_alu_peak_block(rthc_ctx *ctx, int warps_per_sm, double *lane_ops_per_s);
 
 #ifdef __cplusplus
 }

@@ -44,6 +44,9 @@ __device__ __forceinline__ void mbar_arrive(uint64_t *bar)
 }
 __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity)
 {
+#ifdef RTHC_EXPERIMENT_NOWAIT
+    return;
+#endif
     uint32_t done = 0;
     const uint32_t addr = smem_u32(bar);
     while (!done) {
@@ -57,6 +60,23 @@ __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity)
             : "r"(addr), "r"(parity)
             : "memory");
     }
+}
+__device__ __forceinline__ uint32_t mbar_try_wait(uint64_t *bar, uint32_t parity)
+{
+#ifdef RTHC_EXPERIMENT_NOWAIT
+    return 1;
+#endif
+    uint32_t done;
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+        "selp.u32 %0, 1, 0, p;\n"
+        "}\n"
+        : "=r"(done)
+        : "r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+    return done;
 }
 __device__ __forceinline__ void tma_bulk_g2s(void *dst_smem, const void *src_gmem, uint32_t bytes,
                                              uint64_t *bar)
@@ -83,6 +103,15 @@ template <int NJ>
 __device__ __forceinline__ PlaneOps<NJ> load_ops(const uint32_t *st, int blk_words, int ty, int tx, int k)
 {
     PlaneOps<NJ> o;
+#ifdef RTHC_EXPERIMENT_NOLDS
+    {
+#pragma unroll
+        for (int q = 0; q < 8; ++q) o.a[q] = (uint32_t)(k * 7 + ty + q);
+#pragma unroll
+        for (int q = 0; q < 4 * NJ; ++q) o.b[q] = (uint32_t)(k * 13 + tx + q) ^ st[0];
+        return o;
+    }
+#endif
     const uint4 a0 = *reinterpret_cast<const uint4 *>(st + k * RTHC_BLK + 4 * ty);
     const uint4 a1 = *reinterpret_cast<const uint4 *>(st + blk_words + k * RTHC_BLK + 4 * ty);
     o.a[0] = a0.x; o.a[1] = a0.y; o.a[2] = a0.z; o.a[3] = a0.w;
@@ -154,10 +183,13 @@ rthc_distance_bitsliced(const uint32_t *__restrict__ planes, const int32_t *__re
     // Accumulators are packed two 16-bit counters per register (distances <= L <= 65535 cannot
     // carry across): pair (a, b) lives in accp[a][b % 4], low half for b < 4, high half otherwise
     // (NJ = 1 uses the low half only).  mm[][] holds the masked mismatch words of the PREVIOUS
-    // group; their POPCs (XU pipe, 16 lanes/clk/SM) are spread 16 per peeled plane block so that
-    // they overlap the LOP3 stream (ALU pipe) of the current group instead of serialising after it.
+    // group.  Their POPCs run on the XU pipe (16 lanes/clk/SM), so they are issued one slice (two
+    // rows) per peeled plane block to overlap the LOP3 stream (ALU pipe) of the current group, and
+    // each slice's counts pc[] are folded into accp one block LATER (IMAD on the FMA pipe), so no
+    // instruction ever waits on a POPC that was just issued.
     uint32_t accp[8][4];
     uint32_t mm[8][TJ];
+    uint32_t pc[2 * TJ];
 #pragma unroll
     for (int a = 0; a < 8; ++a) {
 #pragma unroll
@@ -165,12 +197,21 @@ rthc_distance_bitsliced(const uint32_t *__restrict__ planes, const int32_t *__re
 #pragma unroll
         for (int b = 0; b < TJ; ++b) mm[a][b] = 0;
     }
-    constexpr int QA = 2;               // rows of mm retired per peeled block (4 blocks x 2 rows = 8)
-#define RTHC_RETIRE(a, b)                                                          \
-    do {                                                                           \
-        const uint32_t pc_ = (uint32_t)__popc(mm[a][b]);                           \
-        accp[a][(b) & 3] += ((b) < 4) ? pc_ : pc_ * 65536u;                        \
-    } while (0)
+#pragma unroll
+    for (int q = 0; q < 2 * TJ; ++q) pc[q] = 0;
+
+#define RTHC_POPC_SLICE(sl)                                                        \
+    _Pragma("unroll") for (int r_ = 0; r_ < 2; ++r_)                               \
+        _Pragma("unroll") for (int b_ = 0; b_ < TJ; ++b_)                          \
+            pc[r_ * TJ + b_] = (uint32_t)__popc(mm[2 * (sl) + r_][b_]);
+#define RTHC_ACC_SLICE(sl)                                                         \
+    _Pragma("unroll") for (int r_ = 0; r_ < 2; ++r_)                               \
+        _Pragma("unroll") for (int b_ = 0; b_ < TJ; ++b_)                          \
+            accp[2 * (sl) + r_][b_ & 3] += (b_ < 4) ? pc[r_ * TJ + b_] : pc[r_ * TJ + b_] * 65536u;
+#define RTHC_COMBINE(op_, P_)                                                      \
+    _Pragma("unroll") for (int a_ = 0; a_ < 8; ++a_)                               \
+        _Pragma("unroll") for (int b_ = 0; b_ < TJ; ++b_)                          \
+            m[a_][b_] op_ (P_).a[a_] ^ (P_).b[b_];
 
     PlaneOps<NJ> cur;
     if (G > 0) {
@@ -190,68 +231,68 @@ rthc_distance_bitsliced(const uint32_t *__restrict__ planes, const int32_t *__re
         const uint32_t *st = stage_base + (size_t)s * stage_words;
 
         uint32_t m[8][TJ];
-        // block 0: bit plane 0 (XOR) + retire rows 0..1 of the previous group
+        // block 0: bit plane 0 (XOR); fold slice 3 (issued in the previous group), issue slice 0
         PlaneOps<NJ> nxt = load_ops<NJ>(st, blk_words, ty, tx, 1);
-#pragma unroll
-        for (int a = 0; a < 8; ++a)
-#pragma unroll
-            for (int b = 0; b < TJ; ++b) {
-                m[a][b] = cur.a[a] ^ cur.b[b];
-                if (a < QA) RTHC_RETIRE(a, b);
-            }
+        RTHC_ACC_SLICE(3)
+        RTHC_POPC_SLICE(0)
+        RTHC_COMBINE(=, cur)
         cur = nxt;
-        // block 1: bit plane 1 + retire rows 2..3
+        // block 1: bit plane 1; fold slice 0, issue slice 1
         nxt = load_ops<NJ>(st, blk_words, ty, tx, 2);
-#pragma unroll
-        for (int a = 0; a < 8; ++a)
-#pragma unroll
-            for (int b = 0; b < TJ; ++b) {
-                m[a][b] |= cur.a[a] ^ cur.b[b];
-                if (a < QA) RTHC_RETIRE(a + QA, b);
-            }
+        RTHC_ACC_SLICE(0)
+        RTHC_POPC_SLICE(1)
+        RTHC_COMBINE(|=, cur)
         cur = nxt;
-        // middle bit planes 2 .. np-3
-        for (int k = 2; k < np - 2; ++k) {
+        // middle bit planes 2 .. np-3, two per iteration with ping-pong operand registers
+        int k = 2;
+        for (; k + 1 < np - 2; k += 2) {
             nxt = load_ops<NJ>(st, blk_words, ty, tx, k + 1);
-#pragma unroll
-            for (int a = 0; a < 8; ++a)
-#pragma unroll
-                for (int b = 0; b < TJ; ++b) m[a][b] |= cur.a[a] ^ cur.b[b];
+            RTHC_COMBINE(|=, cur)
+            cur = load_ops<NJ>(st, blk_words, ty, tx, k + 2);
+            RTHC_COMBINE(|=, nxt)
+        }
+        if (k < np - 2) {
+            nxt = load_ops<NJ>(st, blk_words, ty, tx, k + 1);
+            RTHC_COMBINE(|=, cur)
             cur = nxt;
         }
-        // block 2: last bit plane (np-2) + retire rows 4..5
+        // block 2: last bit plane (np-2); fold slice 1, issue slice 2.  The barrier of the next
+        // stage is polled here, a whole plane block before its result is needed.
         nxt = load_ops<NJ>(st, blk_words, ty, tx, np - 1);
-#pragma unroll
-        for (int a = 0; a < 8; ++a)
-#pragma unroll
-            for (int b = 0; b < TJ; ++b) {
-                m[a][b] |= cur.a[a] ^ cur.b[b];
-                if (a < QA) RTHC_RETIRE(a + 2 * QA, b);
-            }
+        const int s1 = (g + 1) % RTHC_STAGES;
+        const uint32_t par1 = (uint32_t)((g + 1) / RTHC_STAGES) & 1u;
+        uint32_t ready = 1;
+        if (g + 1 < G) ready = mbar_try_wait(&full_bar[s1], par1);
+        RTHC_ACC_SLICE(1)
+        RTHC_POPC_SLICE(2)
+        RTHC_COMBINE(|=, cur)
         cur = nxt;
-        // block 3: valid plane; fetch plane 0 of group g+1 first so its latency hides here
+        // block 3: valid plane; fold slice 2, issue slice 3 (rows 6..7) before mm is overwritten;
+        // plane 0 of group g+1 is fetched first so that its latency hides here
         if (g + 1 < G) {
-            const int s1 = (g + 1) % RTHC_STAGES;
-            mbar_wait(&full_bar[s1], (uint32_t)((g + 1) / RTHC_STAGES) & 1u);
+            if (!ready) mbar_wait(&full_bar[s1], par1);
             nxt = load_ops<NJ>(stage_base + (size_t)s1 * stage_words, blk_words, ty, tx, 0);
         }
+        RTHC_ACC_SLICE(2)
+        RTHC_POPC_SLICE(3)
 #pragma unroll
         for (int a = 0; a < 8; ++a)
 #pragma unroll
-            for (int b = 0; b < TJ; ++b) {
-                if (a >= 3 * QA) RTHC_RETIRE(a, b);          // rows 6..7, before they are overwritten
-                mm[a][b] = m[a][b] & cur.a[a] & cur.b[b];
-            }
+            for (int b = 0; b < TJ; ++b) mm[a][b] = m[a][b] & cur.a[a] & cur.b[b];
         cur = nxt;
         __syncwarp();
         if ((tid & 31) == 0) mbar_arrive(&empty_bar[s]);
     }
-    // retire the last group
+    // drain: slice 3 of the second-to-last group is pending in pc[], mm holds the last group
+    RTHC_ACC_SLICE(3)
 #pragma unroll
-    for (int a = 0; a < 8; ++a)
-#pragma unroll
-        for (int b = 0; b < TJ; ++b) RTHC_RETIRE(a, b);
-#undef RTHC_RETIRE
+    for (int sl = 0; sl < 4; ++sl) {
+        RTHC_POPC_SLICE(sl)
+        RTHC_ACC_SLICE(sl)
+    }
+#undef RTHC_POPC_SLICE
+#undef RTHC_ACC_SLICE
+#undef RTHC_COMBINE
 
     // epilogue: condensed upper triangle, scipy order: row_base[i] + (j - i - 1)
 #pragma unroll

@@ -163,10 +163,20 @@ __global__ void rthc_pointer_jump(int32_t *parent, int64_t n)
     const int32_t pp = parent[p];
     if (pp != p) parent[c] = pp;
 }
+// comp[v] = root of v in the hooked forest.  Every thread chases its own chain (read-only, so no
+// ordering issues); chains are short because each round at least halves the components and a
+// hooked root points straight at a previous root.
 __global__ void rthc_relabel(int32_t *comp, const int32_t *__restrict__ parent, int64_t n)
 {
     int64_t v = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (v < n) comp[v] = parent[v];
+    if (v >= n) return;
+    int32_t r = parent[v];
+    for (;;) {
+        const int32_t p = parent[r];
+        if (p == r) break;
+        r = p;
+    }
+    comp[v] = r;
 }
 
 __global__ void rthc_bitonic_step(uint64_t *a, uint32_t j, uint32_t k, uint32_t N)
@@ -233,8 +243,7 @@ static int boruvka_rounds(rthc_ctx *ctx, int64_t n, ScanFn scan, std::vector<uin
         ++rounds;
         if (now == total) break;   // forest of a disconnected (sharded) edge set is complete
         total = now;
-        int64_t roots = n;          // conservative depth bound
-        for (int it = 0; (1ll << it) < 2 * roots; ++it) {
+        for (int it = 0; it < 4; ++it) {      // 16x path compression bounds the chase below on adversarial chains
             rthc_pointer_jump<<<nb, 256, 0, ctx->stream>>>(d_parent, n);
             RTHC_LAUNCH_CHECK(ctx);
         }

@@ -62,6 +62,7 @@ def load_library():
         "rthc_info": (ci, [vp, vp, ci]),
         "rthc_timings": (ci, [vp, vp, ci]),
         "rthc_alu_peak": (ci, [vp, ctypes.POINTER(ctypes.c_double)]),
+        "rthc_alu_peak_block": (ci, [vp, ci, ctypes.POINTER(ctypes.c_double)]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(L, name)
@@ -77,6 +78,7 @@ EXPORTED_SYMBOLS = [
     "rthc_get_condensed_u16", "rthc_get_owned_condensed_u16", "rthc_copy_rows_u16", "rthc_direct_pairs",
     "rthc_set_condensed_f64", "rthc_set_single_algo", "rthc_linkage", "rthc_local_forest",
     "rthc_linkage_from_forest", "rthc_cut", "rthc_info", "rthc_timings", "rthc_alu_peak",
+    "rthc_alu_peak_block",
 ]
 
 
@@ -219,4 +221,10 @@ class HCContext:
         """Measured int32 ALU lane-ops/s of this GPU (LOP3 stream microbenchmark)."""
         v = ctypes.c_double(0)
         self._check(self._L.rthc_alu_peak(self._h, ctypes.byref(v)))
+        return v.value
+
+    def alu_peak_block(self, warps_per_sm=8):
+        """LOP3 lane-ops/s with the distance kernel's 8x8 register-block operand pattern."""
+        v = ctypes.c_double(0)
+        self._check(self._L.rthc_alu_peak_block(self._h, int(warps_per_sm), ctypes.byref(v)))
         return v.value
