@@ -238,11 +238,15 @@ def run_ours(args):
                 state[k].clear()
         l0 = ctx.timings()["launches"]
         sync()
+        ctx.mark(0)                       # CUDA events on the library's own stream
         t0 = time.perf_counter()
         for _ in range(steps):
             labels = step(resident)
+        ctx.mark(1)
         sync()
-        dt = time.perf_counter() - t0
+        wall = time.perf_counter() - t0
+        dt = ctx.mark_elapsed_ms() * 1e-3
+        state["wall_over_device"] = wall / dt if dt > 0 else None
         launches = ctx.timings()["launches"] - l0
         if world > 1:
             t = torch.tensor([dt, launches], dtype=torch.float64, device="cuda")
@@ -259,6 +263,7 @@ def run_ours(args):
         sampler.start()
     dt, launches, labels = timed(True, args.steps, args.warmup)
     kern = {k: float(np.mean(v)) for k, v in state.items() if isinstance(v, list) and v}
+    kern_steps = {k: [round(float(x), 3) for x in v] for k, v in state.items() if isinstance(v, list) and v}
     info = ctx.info()
     owned_pairs = ctx.owned_pairs()
     clocks = sampler.stop() if rank == 0 else None
@@ -291,7 +296,10 @@ def run_ours(args):
             "alu_peak_lane_ops_per_s": alu_peak, "alu_peak_source": "measured live (rthc_alu_peak LOP3 stream)",
             "lop3_per_32_loci": info["plane_rows"] / max(info["groups"], 1),
             "kernel_ms": kern["dist_ms"],
-            "traffic": None,
+            # dram__bytes_read.sum + dram__bytes_write.sum of this kernel at C4 from the committed
+            # `ncu --set full` capture (profiles/r01_ncu_v4_distance_C4.txt): 9.37 GB + 9.96 GB
+            "traffic": 19.335e9 if (n == 100000 and world == 1) else None,
+            "algorithmic_bytes": alg_bytes,
             "hbm": {"achieved": alg_bytes / t_k / 1e9, "peak": hbm_peak, "unit": "GB/s",
                     "frac": alg_bytes / t_k / 1e9 / hbm_peak,
                     "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback"},
@@ -306,14 +314,18 @@ def run_ours(args):
                            info["plane_rows"] * ctx_npad(n) * 4 / 1e6, 2.0 * owned_pairs / 1e9),
                        "sharding": "tile-rows of the upper triangle over %d rank(s)" % world},
             "stage_ms": kern,
+            "stage_ms_per_step": kern_steps,
+            "e2e_stage_ms_per_step": {k: [round(float(x), 3) for x in v] for k, v in state.items() if isinstance(v, list) and v},
             "roofline": roofline,
             "e2e": {"value": e2e_value, "unit": "comparisons/s", "ms_per_step": 1e3 * dt_e2e / args.steps,
                     "h2d_bytes_per_step": int(n) * int(L) * 4, "d2h_bytes_per_step": int(d2h_bytes)},
             "gpu_launches": int(launches),
+            "timing": "CUDA events on the library stream around the K steps (max over ranks); wall/device = %.3f" % (
+                state.get("wall_over_device") or 0.0),
             "clocks": clocks,
         }
         if world == 1 and not args.no_cpu_baseline:
-            ns = 3000
+            ns = 8000
             work_s, t_all, t_dist = cpu_reference_step(X, ns, 1, WORKLOAD["thresholds"])
             line["cpu_baseline"] = {"value": work_s / t_all, "unit": "comparisons/s", "cores": 1, "kind": "port",
                                     "sample": "first %d samples x %d loci, C port of the cgmlst-dists rule + scipy "

@@ -122,6 +122,10 @@ int rthc_info(const rthc_ctx *ctx, int64_t *info, int n_info);
  * [0]=h2d, [1]=recode+pack, [2]=distance kernel, [3]=mst/merge loop, [4]=cut,
  * [5]=number of kernel launches since create                                       */
 int rthc_timings(const rthc_ctx *ctx, double *ms, int n_ms);
+/* caller-placed CUDA events on the library's own stream (slot 0 / 1): bench.py brackets its timed
+ * region with them, so the step time is measured on the device, on the stream the kernels run on */
+int rthc_mark(rthc_ctx *ctx, int slot);
+int rthc_mark_elapsed_ms(rthc_ctx *ctx, double *ms);   /* waits for slot 1, returns t(1) - t(0) */
 /* integer-ALU roofline probe: independent LOP3 streams at full occupancy, lane-ops per second */
 int rthc_alu_peak(rthc_ctx *ctx, double *lane_ops_per_s);
 /* same, with the distance kernel's operand pattern (8 x 8 register block, three distinct register

@@ -58,23 +58,61 @@ extern "C" int rthc_create(rthc_ctx **out, int device)
             return RTHC_E_CUDA;
         }
     }
+    {
+        cudaMemPoolProps props = {};
+        props.allocType = cudaMemAllocationTypePinned;
+        props.handleTypes = cudaMemHandleTypeNone;
+        props.location.type = cudaMemLocationTypeDevice;
+        props.location.id = device;
+        unsigned long long keep = ~0ull;
+        if ((e = cudaMemPoolCreate(&ctx->pool, &props)) != cudaSuccess ||
+            (e = cudaMemPoolSetAttribute(ctx->pool, cudaMemPoolAttrReleaseThreshold, &keep)) != cudaSuccess) {
+            rthc_fail(nullptr, RTHC_E_CUDA, "memory pool setup failed: %s", cudaGetErrorString(e));
+            delete ctx;
+            return RTHC_E_CUDA;
+        }
+    }
+    if ((e = cudaEventCreate(&ctx->ev_mark[0])) != cudaSuccess || (e = cudaEventCreate(&ctx->ev_mark[1])) != cudaSuccess) {
+        rthc_fail(nullptr, RTHC_E_CUDA, "context setup failed: %s", cudaGetErrorString(e));
+        delete ctx;
+        return RTHC_E_CUDA;
+    }
     *out = ctx;
+    return 0;
+}
+
+extern "C" int rthc_mark(rthc_ctx *ctx, int slot)
+{
+    if (!ctx || slot < 0 || slot > 1) return rthc_fail(ctx, RTHC_E_ARG, "rthc_mark: bad argument");
+    RTHC_CUDA(ctx, cudaSetDevice(ctx->device));
+    RTHC_CUDA(ctx, cudaEventRecord(ctx->ev_mark[slot], ctx->stream));
+    return 0;
+}
+
+extern "C" int rthc_mark_elapsed_ms(rthc_ctx *ctx, double *ms)
+{
+    if (!ctx || !ms) return rthc_fail(ctx, RTHC_E_ARG, "rthc_mark_elapsed_ms: NULL argument");
+    RTHC_CUDA(ctx, cudaSetDevice(ctx->device));
+    RTHC_CUDA(ctx, cudaEventSynchronize(ctx->ev_mark[1]));
+    float f = 0;
+    RTHC_CUDA(ctx, cudaEventElapsedTime(&f, ctx->ev_mark[0], ctx->ev_mark[1]));
+    *ms = f;
     return 0;
 }
 
 static void free_distance_state(rthc_ctx *ctx)
 {
-    rthc_dev_free(&ctx->d_codes); rthc_dev_free(&ctx->d_planes);
-    rthc_dev_free(&ctx->d_grp_off); rthc_dev_free(&ctx->d_grp_np);
-    rthc_dev_free(&ctx->d_tiles); rthc_dev_free(&ctx->d_row_base);
-    rthc_dev_free(&ctx->d_owned_rows);
-    rthc_dev_free(&ctx->d_cond_f64);
+    rthc_dev_free(ctx, &ctx->d_codes); rthc_dev_free(ctx, &ctx->d_planes);
+    rthc_dev_free(ctx, &ctx->d_grp_off); rthc_dev_free(ctx, &ctx->d_grp_np);
+    rthc_dev_free(ctx, &ctx->d_tiles); rthc_dev_free(ctx, &ctx->d_row_base);
+    rthc_dev_free(ctx, &ctx->d_owned_rows);
+    rthc_dev_free(ctx, &ctx->d_cond_f64);
     ctx->have_profiles = ctx->have_dist = false;
 }
 static void free_linkage_state(rthc_ctx *ctx)
 {
-    rthc_dev_free(&ctx->d_ea); rthc_dev_free(&ctx->d_eb); rthc_dev_free(&ctx->d_eh);
-    rthc_dev_free(&ctx->d_epre); rthc_dev_free(&ctx->d_eleaf);
+    rthc_dev_free(ctx, &ctx->d_ea); rthc_dev_free(ctx, &ctx->d_eb); rthc_dev_free(ctx, &ctx->d_eh);
+    rthc_dev_free(ctx, &ctx->d_epre); rthc_dev_free(ctx, &ctx->d_eleaf);
     ctx->have_linkage = false;
 }
 
@@ -83,10 +121,14 @@ extern "C" void rthc_destroy(rthc_ctx *ctx)
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     free_distance_state(ctx);
-    rthc_dev_free(&ctx->d_cond);
+    rthc_dev_free(ctx, &ctx->d_cond);
     free_linkage_state(ctx);
     if (ctx->ev0) cudaEventDestroy(ctx->ev0);
     if (ctx->ev1) cudaEventDestroy(ctx->ev1);
+    for (int k = 0; k < 2; ++k)
+        if (ctx->ev_mark[k]) cudaEventDestroy(ctx->ev_mark[k]);
+    if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+    if (ctx->pool) cudaMemPoolDestroy(ctx->pool);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
 }
@@ -210,7 +252,7 @@ extern "C" int rthc_set_profiles_i32(rthc_ctx *ctx, const int32_t *codes, int64_
     RTHC_CUDA(ctx, cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1));
     ctx->t_ms[0] = ms;
     rc = set_profiles_common(ctx, d_in, n, L);
-    rthc_dev_free(&d_in);
+    rthc_dev_free(ctx, &d_in);
     return rc;
 }
 
@@ -293,7 +335,7 @@ extern "C" int rthc_copy_rows_u16(rthc_ctx *ctx, int64_t row0, int64_t nrows, ui
     RTHC_CUDA(ctx, cudaMemcpyAsync(out, d_out, sizeof(uint16_t) * (size_t)(nrows * ctx->n),
                                    cudaMemcpyDeviceToHost, ctx->stream));
     RTHC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-    rthc_dev_free(&d_out);
+    rthc_dev_free(ctx, &d_out);
     return 0;
 }
 
@@ -314,7 +356,7 @@ extern "C" int rthc_direct_pairs(rthc_ctx *ctx, const int32_t *pi, const int32_t
         cudaError_t e = cudaMemcpy(out, d_out, sizeof(int32_t) * (size_t)np, cudaMemcpyDeviceToHost);
         if (e != cudaSuccess) rc = rthc_fail(ctx, RTHC_E_CUDA, "D2H failed: %s", cudaGetErrorString(e));
     }
-    rthc_dev_free(&d_pi); rthc_dev_free(&d_pj); rthc_dev_free(&d_out);
+    rthc_dev_free(ctx, &d_pi); rthc_dev_free(ctx, &d_pj); rthc_dev_free(ctx, &d_out);
     return rc;
 }
 
@@ -378,17 +420,17 @@ extern "C" int rthc_set_condensed_f64(rthc_ctx *ctx, const double *y, int64_t n)
     int flags = 0;
     RTHC_CUDA(ctx, cudaMemcpyAsync(&flags, d_flags, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
     RTHC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-    rthc_dev_free(&d_flags);
+    rthc_dev_free(ctx, &d_flags);
     if (flags & 1) {
-        rthc_dev_free(&ctx->d_cond_f64);
+        rthc_dev_free(ctx, &ctx->d_cond_f64);
         return rthc_fail(ctx, RTHC_E_RANGE, "distance matrix holds negative, NaN or infinite entries");
     }
     if (flags & 2) {
-        rthc_dev_free(&ctx->d_cond);                             // non-integer distances: float64 path only
+        rthc_dev_free(ctx, &ctx->d_cond);                             // non-integer distances: float64 path only
         ctx->cond_cap = 0;
         ctx->ext_integer = false;
     } else {
-        rthc_dev_free(&ctx->d_cond_f64);                         // integer distances: uint16 path
+        rthc_dev_free(ctx, &ctx->d_cond_f64);                         // integer distances: uint16 path
         ctx->ext_integer = true;
     }
     ctx->have_dist = true;

@@ -74,17 +74,64 @@ __global__ void rthc_cut_keys(int32_t *parent, const int32_t *__restrict__ last,
     flags[e] = 1;
 }
 
-// single-CTA inclusive scan of flags[0..m) in place (m = 2n - 1, a few 100k at most)
-__global__ void __launch_bounds__(1024) rthc_cut_scan(int32_t *flags, int64_t m)
+// inclusive scan of flags[0..m) (m = 2n - 1): every CTA scans 4,096 entries in place and
+// publishes its total; one CTA then turns the totals into exclusive offsets, which the label
+// kernel adds back.  (A single-CTA scan of the whole array was 85 % of the cut stage.)
+#define CUT_SCAN_ELEMS 4096
+__global__ void __launch_bounds__(1024) rthc_cut_scan_blocks(int32_t *flags, int64_t m, int32_t *aux)
+{
+    __shared__ int32_t wsum[32];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int64_t idx = (int64_t)blockIdx.x * CUT_SCAN_ELEMS + 4 * tid;
+    int4 v = make_int4(0, 0, 0, 0);
+    if (idx + 3 < m) v = *reinterpret_cast<const int4 *>(flags + idx);
+    else {
+        if (idx < m) v.x = flags[idx];
+        if (idx + 1 < m) v.y = flags[idx + 1];
+        if (idx + 2 < m) v.z = flags[idx + 2];
+    }
+    v.y += v.x; v.z += v.y; v.w += v.z;
+    int32_t inc = v.w;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        int32_t t = __shfl_up_sync(0xffffffffu, inc, d);
+        if (lane >= d) inc += t;
+    }
+    if (lane == 31) wsum[warp] = inc;
+    __syncthreads();
+    if (warp == 0) {
+        int32_t w = wsum[lane], winc = w;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            int32_t t = __shfl_up_sync(0xffffffffu, winc, d);
+            if (lane >= d) winc += t;
+        }
+        wsum[lane] = winc - w;
+        if (lane == 31) aux[blockIdx.x] = winc;
+    }
+    __syncthreads();
+    const int32_t before = inc - v.w + wsum[warp];
+    v.x += before; v.y += before; v.z += before; v.w += before;
+    if (idx + 3 < m) *reinterpret_cast<int4 *>(flags + idx) = v;
+    else {
+        if (idx < m) flags[idx] = v.x;
+        if (idx + 1 < m) flags[idx + 1] = v.y;
+        if (idx + 2 < m) flags[idx + 2] = v.z;
+    }
+}
+
+// exclusive scan of the per-CTA totals in place (one CTA; nb is a few hundred)
+__global__ void __launch_bounds__(1024) rthc_cut_scan_aux(int32_t *aux, int nb)
 {
     __shared__ int32_t wsum[32];
     __shared__ int32_t carry;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     if (tid == 0) carry = 0;
     __syncthreads();
-    for (int64_t base = 0; base < m; base += 1024) {
-        int64_t idx = base + tid;
-        int32_t v = idx < m ? flags[idx] : 0, inc = v;
+    for (int base = 0; base < nb; base += 1024) {
+        const int idx = base + tid;
+        const int32_t v = idx < nb ? aux[idx] : 0;
+        int32_t inc = v;
 #pragma unroll
         for (int d = 1; d < 32; d <<= 1) {
             int32_t t = __shfl_up_sync(0xffffffffu, inc, d);
@@ -104,7 +151,7 @@ __global__ void __launch_bounds__(1024) rthc_cut_scan(int32_t *flags, int64_t m)
         __syncthreads();
         const int32_t c = carry;
         inc += wsum[warp] + c;
-        if (idx < m) flags[idx] = inc;
+        if (idx < nb) aux[idx] = inc - v;
         __syncthreads();
         if (tid == 1023) carry = inc;
         __syncthreads();
@@ -112,10 +159,13 @@ __global__ void __launch_bounds__(1024) rthc_cut_scan(int32_t *flags, int64_t m)
 }
 
 __global__ void rthc_cut_labels(const int32_t *__restrict__ key, const int32_t *__restrict__ scanned,
-                                int32_t *__restrict__ labels, int64_t n)
+                                const int32_t *__restrict__ aux, int32_t *__restrict__ labels, int64_t n)
 {
     int64_t v = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (v < n) labels[v] = scanned[key[v]];
+    if (v < n) {
+        const int32_t e = key[v];
+        labels[v] = scanned[e] + aux[e / CUT_SCAN_ELEMS];
+    }
 }
 
 int rthc_run_cut(rthc_ctx *ctx, const double *t, int T, int32_t *labels_out)
@@ -126,12 +176,14 @@ int rthc_run_cut(rthc_ctx *ctx, const double *t, int T, int32_t *labels_out)
     std::iota(order.begin(), order.end(), 0);
     std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return t[a] < t[b]; });
 
-    int32_t *d_parent = nullptr, *d_last = nullptr, *d_key = nullptr, *d_flags = nullptr, *d_labels = nullptr;
+    int32_t *d_parent = nullptr, *d_last = nullptr, *d_key = nullptr, *d_flags = nullptr, *d_labels = nullptr, *d_aux = nullptr;
     int rc;
     if ((rc = rthc_dev_alloc(ctx, &d_parent, (size_t)n))) return rc;
     if ((rc = rthc_dev_alloc(ctx, &d_last, (size_t)n))) return rc;
     if ((rc = rthc_dev_alloc(ctx, &d_key, (size_t)n))) return rc;
-    if ((rc = rthc_dev_alloc(ctx, &d_flags, (size_t)(2 * n)))) return rc;
+    if ((rc = rthc_dev_alloc(ctx, &d_flags, (size_t)(2 * n + 4)))) return rc;
+    const int scan_blocks = (int)((2 * n - 1 + CUT_SCAN_ELEMS - 1) / CUT_SCAN_ELEMS);
+    if ((rc = rthc_dev_alloc(ctx, &d_aux, (size_t)scan_blocks))) return rc;
     // labels are produced in chunks of thresholds to bound device memory
     const int64_t chunkT = std::max<int64_t>(1, std::min<int64_t>(T, (int64_t)(1ll << 28) / std::max<int64_t>(n, 1)));
     if ((rc = rthc_dev_alloc(ctx, &d_labels, (size_t)(chunkT * n)))) return rc;
@@ -172,9 +224,11 @@ int rthc_run_cut(rthc_ctx *ctx, const double *t, int T, int32_t *labels_out)
         RTHC_CUDA(ctx, cudaMemsetAsync(d_flags, 0, sizeof(int32_t) * (size_t)(2 * n), ctx->stream));
         rthc_cut_keys<<<nb, 256, 0, ctx->stream>>>(d_parent, d_last, ctx->d_epre, ctx->d_eleaf, d_key, d_flags, n);
         RTHC_LAUNCH_CHECK(ctx);
-        rthc_cut_scan<<<1, 1024, 0, ctx->stream>>>(d_flags, 2 * n - 1);
+        rthc_cut_scan_blocks<<<scan_blocks, 1024, 0, ctx->stream>>>(d_flags, 2 * n - 1, d_aux);
         RTHC_LAUNCH_CHECK(ctx);
-        rthc_cut_labels<<<nb, 256, 0, ctx->stream>>>(d_key, d_flags, d_labels + in_chunk * n, n);
+        rthc_cut_scan_aux<<<1, 1024, 0, ctx->stream>>>(d_aux, scan_blocks);
+        RTHC_LAUNCH_CHECK(ctx);
+        rthc_cut_labels<<<nb, 256, 0, ctx->stream>>>(d_key, d_flags, d_aux, d_labels + in_chunk * n, n);
         RTHC_LAUNCH_CHECK(ctx);
         if (++in_chunk == chunkT)
             if ((rc = flush())) return rc;
@@ -184,7 +238,7 @@ int rthc_run_cut(rthc_ctx *ctx, const double *t, int T, int32_t *labels_out)
     float ms = 0;
     RTHC_CUDA(ctx, cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1));
     ctx->t_ms[4] = ms;
-    rthc_dev_free(&d_parent); rthc_dev_free(&d_last); rthc_dev_free(&d_key);
-    rthc_dev_free(&d_flags); rthc_dev_free(&d_labels);
+    rthc_dev_free(ctx, &d_parent); rthc_dev_free(ctx, &d_last); rthc_dev_free(ctx, &d_key);
+    rthc_dev_free(ctx, &d_flags); rthc_dev_free(ctx, &d_labels); rthc_dev_free(ctx, &d_aux);
     return 0;
 }

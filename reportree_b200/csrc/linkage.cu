@@ -111,7 +111,7 @@ extern "C" int rthc_linkage(rthc_ctx *ctx, int method, double *Z_out)
         return rthc_fail(ctx, RTHC_E_STATE, "rthc_linkage needs a full shard; use rthc_local_forest + "
                                             "rthc_linkage_from_forest for sharded single linkage");
     RTHC_CUDA(ctx, cudaSetDevice(ctx->device));
-    rthc_dev_free(&ctx->d_ea); rthc_dev_free(&ctx->d_eb); rthc_dev_free(&ctx->d_epre); rthc_dev_free(&ctx->d_eleaf);
+    rthc_dev_free(ctx, &ctx->d_ea); rthc_dev_free(ctx, &ctx->d_eb); rthc_dev_free(ctx, &ctx->d_epre); rthc_dev_free(ctx, &ctx->d_eleaf);
     ctx->have_linkage = false;
     int rc;
     RTHC_CUDA(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
@@ -166,7 +166,7 @@ extern "C" int rthc_linkage_from_forest(rthc_ctx *ctx, const uint64_t *keys, int
     if (!ctx || !keys || !Z_out) return rthc_fail(ctx, RTHC_E_ARG, "NULL argument");
     if (n < 2 || m < n - 1) return rthc_fail(ctx, RTHC_E_ARG, "forest union has %lld edges for n=%lld", (long long)m, (long long)n);
     RTHC_CUDA(ctx, cudaSetDevice(ctx->device));
-    rthc_dev_free(&ctx->d_ea); rthc_dev_free(&ctx->d_eb); rthc_dev_free(&ctx->d_epre); rthc_dev_free(&ctx->d_eleaf);
+    rthc_dev_free(ctx, &ctx->d_ea); rthc_dev_free(ctx, &ctx->d_eb); rthc_dev_free(ctx, &ctx->d_epre); rthc_dev_free(ctx, &ctx->d_eleaf);
     ctx->have_linkage = false;
     std::vector<uint64_t> mst;
     int rc = rthc_boruvka_edge_list(ctx, keys, m, n, mst);

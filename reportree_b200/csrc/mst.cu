@@ -11,6 +11,7 @@
 // (3) Device Prim in scipy's visiting order (first strictly-smaller key wins) for the
 //     mode that reproduces scipy's Z byte for byte.
 #include <algorithm>
+#include <cstdlib>
 
 #include "rthc_internal.cuh"
 
@@ -122,6 +123,149 @@ rthc_boruvka_scan_cols(const uint16_t *__restrict__ cond, const int64_t *__restr
     }
     if (mine != RTHC_KEY_INF && mine < best[cj])
         atomicMin((unsigned long long *)&best[cj], (unsigned long long)mine);
+}
+
+// TILE PASS (row and column candidates in ONE sweep over the matrix).  A CTA owns TS_ROWS
+// consecutive rows x TS_COLS columns of the square view; thread t owns the 8 strided columns
+// c0 + t + 256 k, so for a fixed row a warp reads 64 contiguous bytes of the condensed row and
+// keeps 8 loads in flight.  comp[] of the thread's columns and the running column minima live
+// in registers, comp[] / base of the rows in shared memory -- no gathers in the inner loop.
+// Candidates are compared as 32-bit local keys (w << 16 | local index): for a fixed row the
+// order (w, j) and for a fixed column the order (w, i) are exactly the global (w, i, j) order.
+// Row minima: warp REDUX + one shared atomic per warp per row; per tile at most one filtered
+// 64-bit atomicMin per row and per column.
+#define TS_ROWS 64
+#define TS_COLS 2048
+#define TS_KEY_INF 0xFFFFFFFFu
+
+// Same-address pressure on best[] is what limits the late rounds (one giant component: every
+// column of every tile holds a candidate for the same entry), so candidates are merged first
+// inside the warp (match_any groups + REDUX), then inside the CTA (direct-mapped shared table),
+// and the filter reads best[] through L2 (ld.global.cg; an L1-stale +inf would let every
+// candidate through to the atomic unit).
+#define TS_TAB 512
+__device__ __forceinline__ void best_push(uint64_t *best, int32_t c, uint64_t key)
+{
+    if (key < __ldcg(reinterpret_cast<const unsigned long long *>(&best[c])))
+        atomicMin((unsigned long long *)&best[c], (unsigned long long)key);
+}
+// must be called by all 32 lanes of a warp
+__device__ __forceinline__ void tile_push(bool has, int32_t c, uint64_t key, int32_t *tab_c,
+                                          unsigned long long *tab_k, uint64_t *best)
+{
+    const unsigned act = __ballot_sync(0xffffffffu, has);
+    if (!has) return;
+    const unsigned grp = __match_any_sync(act, c);
+    const uint32_t hi = (uint32_t)(key >> 32), lo = (uint32_t)key;
+    const uint32_t mh = __reduce_min_sync(grp, hi);
+    const uint32_t ml = __reduce_min_sync(grp, hi == mh ? lo : 0xFFFFFFFFu);
+    if (hi != mh || lo != ml) return;                      // keys are distinct: one lane per group survives
+    const uint32_t slot = ((uint32_t)c * 2654435761u) >> 23;
+    const int32_t old = atomicCAS(&tab_c[slot], -1, c);
+    if (old == -1 || old == c) atomicMin(&tab_k[slot], (unsigned long long)key);
+    else best_push(best, c, key);
+}
+
+template <bool CHECK>
+__device__ __forceinline__ void scan_tile_body(const uint16_t *__restrict__ cond, const int64_t *s_off,
+                                               const int32_t *s_ci, uint32_t *s_rowmin, int64_t r0,
+                                               int64_t c0, int64_t n, const int32_t (&cj)[8],
+                                               uint32_t (&colmin)[8])
+{
+    const int tid = threadIdx.x;
+    const int64_t jt = c0 + tid;
+#pragma unroll 2
+    for (int r = 0; r < TS_ROWS; ++r) {
+        const int64_t off = s_off[r];               // row_base[i] - i - 1, or < -n if the row is absent
+        if (off < -n) continue;                     // uniform
+        const int32_t ci = s_ci[r];
+        const int64_t i = r0 + r;
+        const uint16_t *row = cond + off + jt;
+        uint32_t w[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            const int64_t j = jt + 256 * k;
+            w[k] = 0;
+            if (!CHECK || (j > i && j < n)) w[k] = row[256 * k];
+        }
+        uint32_t rowmin = TS_KEY_INF;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            const int64_t j = jt + 256 * k;
+            if ((!CHECK || (j > i && j < n)) && cj[k] != ci) {
+                const uint32_t hi = w[k] << 16;
+                colmin[k] = min(colmin[k], hi | (uint32_t)r);
+                rowmin = min(rowmin, hi | (uint32_t)(tid + 256 * k));
+            }
+        }
+        rowmin = __reduce_min_sync(0xffffffffu, rowmin);
+        if ((tid & 31) == 0 && rowmin != TS_KEY_INF) atomicMin(&s_rowmin[r], rowmin);
+    }
+}
+
+__global__ void __launch_bounds__(256)
+rthc_boruvka_scan_tile(const uint16_t *__restrict__ cond, const int64_t *__restrict__ row_base, int64_t n,
+                       const int32_t *__restrict__ comp, uint64_t *best)
+{
+    const int64_t r0 = (int64_t)blockIdx.y * TS_ROWS, c0 = (int64_t)blockIdx.x * TS_COLS;
+    if (c0 + TS_COLS - 1 <= r0) return;                     // no column j > i in this tile
+    __shared__ int64_t s_off[TS_ROWS];
+    __shared__ int32_t s_ci[TS_ROWS];
+    __shared__ uint32_t s_rowmin[TS_ROWS];
+    __shared__ int32_t tab_c[TS_TAB];
+    __shared__ unsigned long long tab_k[TS_TAB];
+    const int tid = threadIdx.x;
+    for (int q = tid; q < TS_TAB; q += 256) { tab_c[q] = -1; tab_k[q] = RTHC_KEY_INF; }
+    if (tid < TS_ROWS) {
+        const int64_t i = r0 + tid;
+        int64_t off = -n - 1;
+        int32_t ci = -1;
+        if (i < n - 1) {
+            const int64_t base = row_base[i];
+            if (base >= 0) { off = base - i - 1; ci = comp[i]; }
+        }
+        s_off[tid] = off; s_ci[tid] = ci; s_rowmin[tid] = TS_KEY_INF;
+    }
+    int32_t cj[8];
+    uint32_t colmin[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        const int64_t j = c0 + tid + 256 * k;
+        cj[k] = j < n ? comp[j] : -2;
+        colmin[k] = TS_KEY_INF;
+    }
+    __syncthreads();
+    const bool edge = (c0 <= r0 + TS_ROWS - 1) || (c0 + TS_COLS > n);
+    if (edge) scan_tile_body<true>(cond, s_off, s_ci, s_rowmin, r0, c0, n, cj, colmin);
+    else scan_tile_body<false>(cond, s_off, s_ci, s_rowmin, r0, c0, n, cj, colmin);
+    __syncthreads();
+    // candidates of this tile -> at most one global operation per distinct component
+    {
+        bool has = false;
+        int32_t c = -1;
+        uint64_t key = RTHC_KEY_INF;
+        if (tid < TS_ROWS) {                                   // warps 0 and 1, convergent
+            const uint32_t rm = s_rowmin[tid];
+            if (rm != TS_KEY_INF) {
+                has = true;
+                c = s_ci[tid];
+                key = rthc_pack_key(rm >> 16, (uint32_t)(r0 + tid), (uint32_t)(c0 + (rm & 0xFFFFu)));
+            }
+            tile_push(has, c, key, tab_c, tab_k, best);
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        const uint32_t cm = colmin[k];
+        const bool has = cm != TS_KEY_INF;
+        const uint64_t key = rthc_pack_key(cm >> 16, (uint32_t)(r0 + (cm & 0xFFFFu)), (uint32_t)(c0 + tid + 256 * k));
+        tile_push(has, cj[k], key, tab_c, tab_k, best);
+    }
+    __syncthreads();
+    for (int slot = tid; slot < TS_TAB; slot += 256) {
+        const int32_t c = tab_c[slot];
+        if (c != -1) best_push(best, c, tab_k[slot]);
+    }
 }
 
 // same round step over an explicit edge list (merge of the ranks' forests)
@@ -258,9 +402,9 @@ static int boruvka_rounds(rthc_ctx *ctx, int64_t n, ScanFn scan, std::vector<uin
                                        cudaMemcpyDeviceToHost, ctx->stream));
     }
     RTHC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-    rthc_dev_free(&d_sorted);
-    rthc_dev_free(&d_comp); rthc_dev_free(&d_parent); rthc_dev_free(&d_best);
-    rthc_dev_free(&d_keys); rthc_dev_free(&d_count);
+    rthc_dev_free(ctx, &d_sorted);
+    rthc_dev_free(ctx, &d_comp); rthc_dev_free(ctx, &d_parent); rthc_dev_free(ctx, &d_best);
+    rthc_dev_free(ctx, &d_keys); rthc_dev_free(ctx, &d_count);
     return 0;
 }
 
@@ -268,8 +412,13 @@ int rthc_boruvka_owned(rthc_ctx *ctx, std::vector<uint64_t> &keys)
 {
     const int64_t n = ctx->n;
     const int64_t n_owned = (int64_t)ctx->h_owned_rows.size();
+    static const bool two_pass = getenv("RTHC_BORUVKA_TWO_PASS") != nullptr;     // A/B switch (older kernels)
     auto scan = [&](int32_t *d_comp, uint64_t *d_best) -> int {
-        if (n_owned > 0) {
+        if (n_owned > 0 && !two_pass) {
+            dim3 grd((unsigned)((n + TS_COLS - 1) / TS_COLS), (unsigned)((n + TS_ROWS - 1) / TS_ROWS));
+            rthc_boruvka_scan_tile<<<grd, 256, 0, ctx->stream>>>(ctx->d_cond, ctx->d_row_base, n, d_comp, d_best);
+            RTHC_LAUNCH_CHECK(ctx);
+        } else if (n_owned > 0) {
             rthc_boruvka_scan<<<(unsigned)n_owned, SCAN_THREADS, 0, ctx->stream>>>(
                 ctx->d_cond, ctx->d_row_base, ctx->d_owned_rows, n, d_comp, d_best);
             RTHC_LAUNCH_CHECK(ctx);
@@ -298,6 +447,6 @@ int rthc_boruvka_edge_list(rthc_ctx *ctx, const uint64_t *h_keys, int64_t m, int
         return 0;
     };
     rc = boruvka_rounds(ctx, n, scan, keys);
-    rthc_dev_free(&d_in);
+    rthc_dev_free(ctx, &d_in);
     return rc;
 }

@@ -166,7 +166,7 @@ static int run_prim(rthc_ctx *ctx, const T *d_cond, std::vector<int32_t> &ex, st
     RTHC_CUDA(ctx, cudaMemcpyAsync(ey.data(), d_ey, sizeof(int32_t) * (size_t)m, cudaMemcpyDeviceToHost, ctx->stream));
     RTHC_CUDA(ctx, cudaMemcpyAsync(ew.data(), d_ew, sizeof(double) * (size_t)m, cudaMemcpyDeviceToHost, ctx->stream));
     RTHC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-    rthc_dev_free(&d_slots); rthc_dev_free(&d_ex); rthc_dev_free(&d_ey); rthc_dev_free(&d_ew);
+    rthc_dev_free(ctx, &d_slots); rthc_dev_free(ctx, &d_ex); rthc_dev_free(ctx, &d_ey); rthc_dev_free(ctx, &d_ew);
     return 0;
 }
 
@@ -333,8 +333,8 @@ static int run_nn_chain(rthc_ctx *ctx, const S *d_cond, int method, std::vector<
     RTHC_CUDA(ctx, cudaMemcpyAsync(&ctl, d_ctl, sizeof(ChainCtl), cudaMemcpyDeviceToHost, ctx->stream));
     RTHC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     ctx->row_scans = ctl.scans;
-    rthc_dev_free(&d_W); rthc_dev_free(&d_size); rthc_dev_free(&d_chain); rthc_dev_free(&d_slots);
-    rthc_dev_free(&d_ex); rthc_dev_free(&d_ey); rthc_dev_free(&d_ew); rthc_dev_free(&d_ctl);
+    rthc_dev_free(ctx, &d_W); rthc_dev_free(ctx, &d_size); rthc_dev_free(ctx, &d_chain); rthc_dev_free(ctx, &d_slots);
+    rthc_dev_free(ctx, &d_ex); rthc_dev_free(ctx, &d_ey); rthc_dev_free(ctx, &d_ew); rthc_dev_free(ctx, &d_ctl);
     return 0;
 }
 

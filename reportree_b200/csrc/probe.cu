@@ -40,7 +40,7 @@ extern "C" int rthc_alu_peak(rthc_ctx *ctx, double *lane_ops_per_s)
         double rate = (double)blocks * threads * (double)iters * 16.0 / (ms * 1e-3);
         if (rep > 0 && rate > best) best = rate;
     }
-    rthc_dev_free(&d_out);
+    rthc_dev_free(ctx, &d_out);
     *lane_ops_per_s = best;
     return 0;
 }
@@ -100,7 +100,7 @@ extern "C" int rthc_alu_peak_block(rthc_ctx *ctx, int warps_per_sm, double *lane
         double rate = (double)blocks * threads * (double)iters * 80.0 / (ms * 1e-3);
         if (rep > 0 && rate > best) best = rate;
     }
-    rthc_dev_free(&d_out);
+    rthc_dev_free(ctx, &d_out);
     *lane_ops_per_s = best;
     return 0;
 }

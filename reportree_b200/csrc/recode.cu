@@ -302,12 +302,12 @@ int rthc_recode_and_pack(rthc_ctx *ctx, const int32_t *d_rowmajor)
         RTHC_CUDA(ctx, cudaMemcpyAsync(nall.data(), d_nall, sizeof(int32_t) * (size_t)L,
                                        cudaMemcpyDeviceToHost, ctx->stream));
         RTHC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-        rthc_dev_free(&d_gbm);
-        rthc_dev_free(&d_winpre);
+        rthc_dev_free(ctx, &d_gbm);
+        rthc_dev_free(ctx, &d_winpre);
     }
-    rthc_dev_free(&d_colmajor);
+    rthc_dev_free(ctx, &d_colmajor);
     if (status & 2) {
-        rthc_dev_free(&d_nall); rthc_dev_free(&d_status);
+        rthc_dev_free(ctx, &d_nall); rthc_dev_free(ctx, &d_status);
         return rthc_fail(ctx, RTHC_E_RANGE,
                          "a locus has more than 65,535 distinct called alleles; the uint16 re-coder "
                          "cannot represent it");
@@ -363,8 +363,8 @@ int rthc_recode_and_pack(rthc_ctx *ctx, const int32_t *d_rowmajor)
         RTHC_LAUNCH_CHECK(ctx);
     }
     RTHC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-    rthc_dev_free(&d_perm);
-    rthc_dev_free(&d_nall);
-    rthc_dev_free(&d_status);
+    rthc_dev_free(ctx, &d_perm);
+    rthc_dev_free(ctx, &d_nall);
+    rthc_dev_free(ctx, &d_status);
     return 0;
 }

@@ -25,6 +25,7 @@ __host__ __device__ inline uint32_t rthc_key_j(uint64_t k) { return (uint32_t)(k
 struct rthc_ctx {
     int device = 0;
     cudaStream_t stream = nullptr;
+    cudaMemPool_t pool = nullptr;   // stream-ordered allocation pool of this context
     std::string err;
     int sm_count = 148;
 
@@ -76,6 +77,7 @@ struct rthc_ctx {
     double t_ms[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     int64_t launches = 0;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    cudaEvent_t ev_mark[2] = {nullptr, nullptr};   // rthc_mark(): caller-placed events on the library stream
 };
 
 extern std::string g_rthc_create_err;
@@ -96,21 +98,32 @@ int rthc_fail(rthc_ctx *ctx, int code, const char *fmt, ...);
         RTHC_CUDA((ctx), cudaGetLastError());                                             \
     } while (0)
 
+// Device memory comes from a per-context stream-ordered pool (cudaMallocFromPoolAsync) whose
+// release threshold is unlimited: after the first pass over a workload no call reaches the
+// driver's allocator again (cudaMalloc / cudaFree of GB-sized buffers cost tens of ms and
+// synchronise the device).  Everything is allocated, used and freed on ctx->stream.
+template <typename T> inline void rthc_dev_free(rthc_ctx *ctx, T **p)
+{
+    if (*p) { cudaFreeAsync((void *)*p, ctx->stream); *p = nullptr; }
+}
 template <typename T> inline int rthc_dev_alloc(rthc_ctx *ctx, T **p, size_t count)
 {
-    if (*p) { cudaFree(*p); *p = nullptr; }
+    rthc_dev_free(ctx, p);
     if (count == 0) count = 1;
-    cudaError_t e = cudaMalloc((void **)p, count * sizeof(T));
+    cudaError_t e = cudaMallocFromPoolAsync((void **)p, count * sizeof(T), ctx->pool, ctx->stream);
+    if (e != cudaSuccess) {                 // give cached blocks back to the driver and retry once
+        cudaGetLastError();
+        cudaStreamSynchronize(ctx->stream);
+        cudaMemPoolTrimTo(ctx->pool, 0);
+        e = cudaMallocFromPoolAsync((void **)p, count * sizeof(T), ctx->pool, ctx->stream);
+    }
     if (e != cudaSuccess) {
         *p = nullptr;
-        return rthc_fail(ctx, RTHC_E_NOMEM, "cudaMalloc of %zu bytes failed: %s", count * sizeof(T),
+        cudaGetLastError();
+        return rthc_fail(ctx, RTHC_E_NOMEM, "device allocation of %zu bytes failed: %s", count * sizeof(T),
                          cudaGetErrorString(e));
     }
     return 0;
-}
-template <typename T> inline void rthc_dev_free(T **p)
-{
-    if (*p) { cudaFree(*p); *p = nullptr; }
 }
 
 // stage entry points implemented in the other translation units

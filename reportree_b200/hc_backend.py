@@ -61,6 +61,8 @@ def load_library():
         "rthc_cut": (ci, [vp, vp, ci, vp]),
         "rthc_info": (ci, [vp, vp, ci]),
         "rthc_timings": (ci, [vp, vp, ci]),
+        "rthc_mark": (ci, [vp, ci]),
+        "rthc_mark_elapsed_ms": (ci, [vp, ctypes.POINTER(ctypes.c_double)]),
         "rthc_alu_peak": (ci, [vp, ctypes.POINTER(ctypes.c_double)]),
         "rthc_alu_peak_block": (ci, [vp, ci, ctypes.POINTER(ctypes.c_double)]),
     }
@@ -77,7 +79,7 @@ EXPORTED_SYMBOLS = [
     "rthc_set_profiles_i32", "rthc_set_profiles_i32_device", "rthc_distance", "rthc_owned_pairs",
     "rthc_get_condensed_u16", "rthc_get_owned_condensed_u16", "rthc_copy_rows_u16", "rthc_direct_pairs",
     "rthc_set_condensed_f64", "rthc_set_single_algo", "rthc_linkage", "rthc_local_forest",
-    "rthc_linkage_from_forest", "rthc_cut", "rthc_info", "rthc_timings", "rthc_alu_peak",
+    "rthc_linkage_from_forest", "rthc_cut", "rthc_info", "rthc_timings", "rthc_mark", "rthc_mark_elapsed_ms", "rthc_alu_peak",
     "rthc_alu_peak_block",
 ]
 
@@ -216,6 +218,15 @@ class HCContext:
         self._check(self._L.rthc_timings(self._h, _ptr(a), 6))
         keys = ["h2d_ms", "recode_ms", "distance_ms", "linkage_ms", "cut_ms", "launches"]
         return dict(zip(keys, (float(x) for x in a)))
+
+    def mark(self, slot):
+        """Record CUDA event `slot` (0 or 1) on the library stream."""
+        self._check(self._L.rthc_mark(self._h, int(slot)))
+
+    def mark_elapsed_ms(self):
+        v = ctypes.c_double(0)
+        self._check(self._L.rthc_mark_elapsed_ms(self._h, ctypes.byref(v)))
+        return v.value
 
     def alu_peak(self):
         """Measured int32 ALU lane-ops/s of this GPU (LOP3 stream microbenchmark)."""
