@@ -200,10 +200,15 @@ rthc_distance_bitsliced(const uint32_t *__restrict__ planes, const int32_t *__re
 #pragma unroll
     for (int q = 0; q < 2 * TJ; ++q) pc[q] = 0;
 
+#ifdef RTHC_EXPERIMENT_NOPOPC
+#define RTHC_POPC(x) (x)
+#else
+#define RTHC_POPC(x) ((uint32_t)__popc(x))
+#endif
 #define RTHC_POPC_SLICE(sl)                                                        \
     _Pragma("unroll") for (int r_ = 0; r_ < 2; ++r_)                               \
         _Pragma("unroll") for (int b_ = 0; b_ < TJ; ++b_)                          \
-            pc[r_ * TJ + b_] = (uint32_t)__popc(mm[2 * (sl) + r_][b_]);
+            pc[r_ * TJ + b_] = RTHC_POPC(mm[2 * (sl) + r_][b_]);
 #define RTHC_ACC_SLICE(sl)                                                         \
     _Pragma("unroll") for (int r_ = 0; r_ < 2; ++r_)                               \
         _Pragma("unroll") for (int b_ = 0; b_ < TJ; ++b_)                          \
