@@ -19,74 +19,12 @@
 // an mbarrier, RTHC_STAGES deep, so loads of groups g+1..g+3 overlap the LOP3 stream of
 // group g; operand words of plane k+1 are fetched from shared memory while plane k is combined.  Results go straight to the condensed uint16
 // upper triangle (scipy pdist order) -- the square matrix is never materialised.
-#include "rthc_internal.cuh"
+#include <cstdlib>
+#include <cstring>
 
-#define RTHC_STAGES 6
+#include "dist_common.cuh"
+
 #define DIST_THREADS 256
-
-__device__ __forceinline__ uint32_t smem_u32(const void *p)
-{
-    return (uint32_t)__cvta_generic_to_shared(p);
-}
-__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count)
-{
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
-}
-__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes)
-{
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)),
-                 "r"(bytes)
-                 : "memory");
-}
-__device__ __forceinline__ void mbar_arrive(uint64_t *bar)
-{
-    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity)
-{
-#ifdef RTHC_EXPERIMENT_NOWAIT
-    return;
-#endif
-    uint32_t done = 0;
-    const uint32_t addr = smem_u32(bar);
-    while (!done) {
-        asm volatile(
-            "{\n"
-            ".reg .pred p;\n"
-            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
-            "selp.u32 %0, 1, 0, p;\n"
-            "}\n"
-            : "=r"(done)
-            : "r"(addr), "r"(parity)
-            : "memory");
-    }
-}
-__device__ __forceinline__ uint32_t mbar_try_wait(uint64_t *bar, uint32_t parity)
-{
-#ifdef RTHC_EXPERIMENT_NOWAIT
-    return 1;
-#endif
-    uint32_t done;
-    asm volatile(
-        "{\n"
-        ".reg .pred p;\n"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
-        "selp.u32 %0, 1, 0, p;\n"
-        "}\n"
-        : "=r"(done)
-        : "r"(smem_u32(bar)), "r"(parity)
-        : "memory");
-    return done;
-}
-__device__ __forceinline__ void tma_bulk_g2s(void *dst_smem, const void *src_gmem, uint32_t bytes,
-                                             uint64_t *bar)
-{
-    asm volatile(
-        "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
-            smem_u32(dst_smem)),
-        "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar))
-        : "memory");
-}
 
 // Plane layout in HBM is blocked by 64 samples: planes[((s / 64) * plane_rows + row) * 64 + s % 64],
 // so the np plane rows of one locus group of one 64-sample block are one contiguous run of
@@ -368,7 +306,17 @@ int rthc_run_distance(rthc_ctx *ctx)
 {
     if (ctx->n_tiles == 0) return 0;
     const int max_np = ctx->max_np > 0 ? ctx->max_np : 1;
-    int rc = ctx->dist_nj == 1 ? launch_distance<1>(ctx, max_np) : launch_distance<2>(ctx, max_np);
+    // default: warp-specialised persistent kernel (distance_ws.cu); RTHC_DIST_KERNEL=v4 selects the
+    // older one-tile-per-CTA kernel of this file (kept for A/B measurements)
+    static const bool use_v4 = getenv("RTHC_DIST_KERNEL") && !strcmp(getenv("RTHC_DIST_KERNEL"), "v4");
+    int rc;
+    if (use_v4 || ctx->dist_nj == 1) {
+        rc = ctx->dist_nj == 1 ? launch_distance<1>(ctx, max_np) : launch_distance<2>(ctx, max_np);
+    } else {
+        RTHC_CUDA(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
+        rc = rthc_launch_distance_ws(ctx, max_np);
+        if (!rc) RTHC_CUDA(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
+    }
     if (rc) return rc;
     RTHC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     float ms = 0;

@@ -129,6 +129,7 @@ template <typename T> inline int rthc_dev_alloc(rthc_ctx *ctx, T **p, size_t cou
 // stage entry points implemented in the other translation units
 int rthc_recode_and_pack(rthc_ctx *ctx, const int32_t *d_rowmajor);   // recode.cu
 int rthc_run_distance(rthc_ctx *ctx);                                 // distance.cu
+int rthc_launch_distance_ws(rthc_ctx *ctx, int max_np);                // distance_ws.cu
 int rthc_run_direct_pairs(rthc_ctx *ctx, const int32_t *d_pi, const int32_t *d_pj, int64_t np,
                           int32_t *d_out);                            // distance.cu
 int rthc_boruvka_owned(rthc_ctx *ctx, std::vector<uint64_t> &keys);   // mst.cu
