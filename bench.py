@@ -285,7 +285,7 @@ def run_ours(args):
         hbm_peak = peaks.get("hbm_gbs", 6650.0)
         alg_bytes = 2.0 * n * L + 2.0 * owned_pairs
         roofline = {
-            "kernel": "rthc_distance_bitsliced",
+            "kernel": "rthc_distance_ws",
             "bound": "int_alu",
             "achieved": cmp_rate / 1e12, "peak": alu_peak / 2 / 1e12, "unit": "Tcmp/s",
             "frac": cmp_rate / (alu_peak / 2),

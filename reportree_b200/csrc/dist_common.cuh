@@ -2,7 +2,9 @@
 #pragma once
 #include "rthc_internal.cuh"
 
+#ifndef RTHC_STAGES
 #define RTHC_STAGES 6
+#endif
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p)
 {

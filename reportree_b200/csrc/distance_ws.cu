@@ -129,7 +129,12 @@ __device__ __forceinline__ void ws_group(WsRing &R, WsAcc &A, WsOps &cur, const 
         for (int r = 0; r < nq; ++r) ws_fold(A, q0 + r, pcs[r]);
         cur = nxt;
     }
-    // last block: valid plane (cur).  Release / acquire of the ring happens here.
+    // last block: valid plane (cur).  Plane 0 of the next group is fetched first so that its
+    // shared-memory latency hides behind this block's 64 LOP3s.
+    // (The producer appends one padding group to the ring, so there always is a next stage.)
+    const uint32_t s1 = (R.it + 1) % RTHC_STAGES;
+    ws_wait(R.full_bar + 8 * s1, ((R.it + 1) / RTHC_STAGES) & 1u);
+    const WsOps nxt = ws_load(R.base_a + s1 * R.stage_bytes, R.base_b + s1 * R.stage_bytes, R.blk_bytes, 0);
     // old row 7 is POPC'd one word per new row 0..6 (two behind row 6), then overwritten last
     uint32_t p7[8];
 #pragma unroll
@@ -145,11 +150,7 @@ __device__ __forceinline__ void ws_group(WsRing &R, WsAcc &A, WsOps &cur, const 
     for (int b = 0; b < 8; ++b) ws_fold(A, 56 + b, p7[b]);
     ws_arrive(R.empty_bar + 8 * s);            // every consumer thread arrives (count = 256)
     R.it += 1;
-    if (R.it < R.total) {
-        const uint32_t s1 = R.it % RTHC_STAGES;
-        ws_wait(R.full_bar + 8 * s1, (R.it / RTHC_STAGES) & 1u);
-        cur = ws_load(R.base_a + s1 * R.stage_bytes, R.base_b + s1 * R.stage_bytes, R.blk_bytes, 0);
-    }
+    cur = nxt;
 }
 
 // Any plane count (loci with more than 2,047 alleles): runtime plane loop, POPCs not overlapped.
@@ -178,11 +179,9 @@ __device__ __forceinline__ void ws_group_generic(WsRing &R, WsAcc &A, WsOps &cur
         for (int b = 0; b < 8; ++b) A.mm[a][b] = m[a][b] & cur.a[a] & cur.b[b];
     ws_arrive(R.empty_bar + 8 * s);
     R.it += 1;
-    if (R.it < R.total) {
-        const uint32_t s1 = R.it % RTHC_STAGES;
-        ws_wait(R.full_bar + 8 * s1, (R.it / RTHC_STAGES) & 1u);
-        cur = ws_load(R.base_a + s1 * R.stage_bytes, R.base_b + s1 * R.stage_bytes, R.blk_bytes, 0);
-    }
+    const uint32_t s1 = R.it % RTHC_STAGES;
+    ws_wait(R.full_bar + 8 * s1, (R.it / RTHC_STAGES) & 1u);
+    cur = ws_load(R.base_a + s1 * R.stage_bytes, R.base_b + s1 * R.stage_bytes, R.blk_bytes, 0);
 }
 
 template <int NP>
@@ -226,13 +225,16 @@ rthc_distance_ws(const uint32_t *__restrict__ planes, const int32_t *__restrict_
         if (tid == WS_CONSUMERS) {
             const size_t blk_stride = (size_t)plane_rows * RTHC_BLK;      // words per 64-sample block in HBM
             uint32_t it = 0;
-            for (int t = 0; t < my_tiles; ++t) {
-                const int2 tile = tiles[blockIdx.x + (size_t)t * gridDim.x];
+            // one padding group (group 0 of the last tile again) closes the ring: consumers fetch
+            // plane 0 of "the next group" unconditionally
+            for (int t = 0; t < my_tiles + (my_tiles > 0 && G > 0 ? 1 : 0); ++t) {
+                const bool pad = t == my_tiles;
+                const int2 tile = tiles[blockIdx.x + (size_t)(pad ? my_tiles - 1 : t) * gridDim.x];
                 const uint32_t *srcs[4] = {planes + (size_t)(2 * tile.x) * blk_stride,
                                            planes + (size_t)(2 * tile.x + 1) * blk_stride,
                                            planes + (size_t)tile.y * blk_stride,
                                            planes + (size_t)(tile.y + 1) * blk_stride};
-                for (int g = 0; g < G; ++g, ++it) {
+                for (int g = 0; g < (pad ? 1 : G); ++g, ++it) {
                     const uint32_t s = it % RTHC_STAGES;
                     if (it >= RTHC_STAGES) mbar_wait(&empty_bar[s], ((it / RTHC_STAGES) - 1u) & 1u);
                     const uint32_t e = gtab[g];
