@@ -169,7 +169,7 @@ def run_reference(args):
 def run_ours(args):
     import torch
     import torch.distributed as dist
-    from reportree_b200 import hc_backend as hc
+    from reportree_b200 import hc_backend as hc, sharded
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -205,16 +205,10 @@ def run_ours(args):
             d2h = Z.nbytes + labels.nbytes + (n - 1) * 8
         else:
             keys = ctx.local_forest()
-            buf = torch.full((n - 1,), -1, dtype=torch.int64, device="cuda")
-            if keys.size:
-                buf[: keys.size] = torch.from_numpy(keys.view(np.int64)).cuda()
-            gathered = [torch.empty_like(buf) for _ in range(world)]
-            dist.all_gather(gathered, buf)
+            allk = sharded.all_gather_forests(keys, n, dist, device="cuda")     # the one NCCL exchange
             d2h = keys.nbytes
             labels = None
             if rank == 0:
-                allk = torch.cat(gathered).cpu().numpy().view(np.uint64)
-                allk = allk[allk != INF]
                 Z = ctx.linkage_from_forest(allk, n)
                 labels = ctx.fcluster(thr)
                 d2h += allk.nbytes + Z.nbytes + labels.nbytes
@@ -297,8 +291,9 @@ def run_ours(args):
             "lop3_per_32_loci": info["plane_rows"] / max(info["groups"], 1),
             "kernel_ms": kern["dist_ms"],
             # dram__bytes_read.sum + dram__bytes_write.sum of this kernel at C4 from the committed
-            # `ncu --set full` capture (profiles/r01_ncu_v4_distance_C4.txt): 9.37 GB + 9.96 GB
-            "traffic": 19.335e9 if (n == 100000 and world == 1) else None,
+            # `ncu --set full` capture (profiles/r01_ncu_v5_distance_C4.txt): 40.78 GB + 10.40 GB
+            # (the 378 MB plane matrix is re-read from HBM when tiles miss L2; 142 GB/s, 2 % of peak)
+            "traffic": 51.17e9 if (n == 100000 and world == 1) else None,
             "algorithmic_bytes": alg_bytes,
             "hbm": {"achieved": alg_bytes / t_k / 1e9, "peak": hbm_peak, "unit": "GB/s",
                     "frac": alg_bytes / t_k / 1e9 / hbm_peak,
@@ -325,7 +320,7 @@ def run_ours(args):
             "clocks": clocks,
         }
         if world == 1 and not args.no_cpu_baseline:
-            ns = 8000
+            ns = 7000
             work_s, t_all, t_dist = cpu_reference_step(X, ns, 1, WORKLOAD["thresholds"])
             line["cpu_baseline"] = {"value": work_s / t_all, "unit": "comparisons/s", "cores": 1, "kind": "port",
                                     "sample": "first %d samples x %d loci, C port of the cgmlst-dists rule + scipy "

@@ -1,0 +1,129 @@
+"""CPU (gloo, world_size 2 and 3) test of the multi-GPU host logic in reportree_b200/sharded.py:
+tile-row ownership, per-rank minimum spanning forests under the (w, i, j) order, the single
+all_gather of padded edge lists, and the final merge -- with the per-rank forest computed by a
+plain Kruskal on distances from the CPU oracle (the GPU kernels are covered by the -m gpu tests,
+tests/test_gpu_linkage.py::test_forest_union_equals_single_gpu)."""
+import os
+import socket
+import sys
+
+import numpy as np
+import pytest
+import torch.multiprocessing as mp
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _kruskal(keys, n):
+    """Minimum spanning forest of the packed edges under the total key order."""
+    parent = list(range(n))
+
+    def find(v):
+        while parent[v] != v:
+            parent[v] = parent[parent[v]]
+            v = parent[v]
+        return v
+
+    out = []
+    for k in np.sort(keys):
+        i = int((k >> np.uint64(24)) & np.uint64(0xFFFFFF))
+        j = int(k & np.uint64(0xFFFFFF))
+        a, b = find(i), find(j)
+        if a != b:
+            parent[a] = b
+            out.append(k)
+    return np.asarray(out, dtype=np.uint64)
+
+
+def _worker(rank, world, port, n, L, seed, q):
+    sys.path.insert(0, ROOT)
+    import torch.distributed as dist
+    from oracle import oracle_lib as O
+    from reportree_b200 import sharded, synth
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    X = synth.allele_matrix(n, L, seed)
+    D = O.dist_square(X)
+    rows = sharded.owned_rows(n, rank, world)
+    ii, jj = [], []
+    for i in rows:
+        j = np.arange(i + 1, n)
+        ii.append(np.full(j.size, i)); jj.append(j)
+    ii = np.concatenate(ii) if ii else np.zeros(0, np.int64)
+    jj = np.concatenate(jj) if jj else np.zeros(0, np.int64)
+    local = _kruskal(sharded.pack_keys(D[ii, jj], ii, jj), n)
+    allk = sharded.all_gather_forests(local, n, dist)
+    if rank == 0:
+        q.put((int(ii.size), allk))
+    else:
+        q.put((int(ii.size), None))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_forest_union_over_gloo_equals_single_rank_mst(world, oracle):
+    from scipy.cluster.hierarchy import fcluster, linkage
+    from reportree_b200 import sharded, synth
+    n, L, seed = 700, 60, 11
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, world, port, n, L, seed, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    got = [q.get(timeout=120) for _ in range(world)]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    # every pair is owned exactly once, and the ranks are balanced to within one tile-row pair
+    owned = [g[0] for g in got]
+    assert sum(owned) == n * (n - 1) // 2
+    allk = next(g[1] for g in got if g[1] is not None)
+    assert allk.size <= world * (n - 1)
+    mst = _kruskal(allk, n)
+    assert mst.size == n - 1
+    # reference: MST of the complete graph on one rank, same total order
+    X = synth.allele_matrix(n, L, seed)
+    D = oracle.dist_square(X)
+    iu = np.triu_indices(n, 1)
+    full = _kruskal(sharded.pack_keys(D[iu], iu[0], iu[1]), n)
+    assert np.array_equal(np.sort(mst), np.sort(full))
+    # and it cuts like scipy's single linkage at every threshold
+    w, i, j = sharded.unpack_keys(np.sort(mst))
+    Z = linkage(D[iu].astype(np.float64), "single")
+    assert np.array_equal(np.sort(w).astype(np.float64), Z[:, 2])
+    for t in (0, 1, 3, 8, 20):
+        parent = list(range(n))
+
+        def find(v):
+            while parent[v] != v:
+                parent[v] = parent[parent[v]]
+                v = parent[v]
+            return v
+        for ww, a, b in zip(w, i, j):
+            if ww <= t:
+                parent[find(int(a))] = find(int(b))
+        mine = oracle.canonical(np.asarray([find(v) for v in range(n)]))
+        assert np.array_equal(mine, oracle.canonical(fcluster(Z, t, criterion="distance")))
+
+
+def test_ownership_is_a_balanced_partition():
+    from reportree_b200 import sharded
+    for n in (1, 127, 128, 129, 1000, 5000):
+        for world in (1, 2, 4, 8):
+            rows = [sharded.owned_rows(n, r, world) for r in range(world)]
+            allr = np.concatenate(rows)
+            assert np.array_equal(np.sort(allr), np.arange(n))
+            if n >= 128 * 2 * world:
+                pairs = [int(np.sum(n - 1 - r)) for r in rows]
+                assert max(pairs) - min(pairs) <= 2 * 128 * n
