@@ -189,7 +189,6 @@ def run_ours(args):
     dX = pinned.cuda(non_blocking=False)
     thr = np.arange(WORKLOAD["thresholds"], dtype=np.float64)
     ctx = hc.HCContext(device=local, rank=rank, world=world)
-    INF = np.uint64(0xFFFFFFFFFFFFFFFF)
     state = {"dist_ms": [], "link_ms": [], "cut_ms": [], "recode_ms": [], "h2d_ms": [], "d2h_bytes": 0}
 
     def step(resident):
