@@ -13,15 +13,30 @@ FLAGS = ["-O3", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-li
 FLAGS += os.environ.get("RTHC_EXTRA_NVCC_FLAGS", "").split()
 
 
+HOSTIO_SRC = os.path.join(CSRC, "hostio.cpp")
+HOSTIO_OUT = os.path.join(HERE, "librthc_hostio.so")
+CXX = os.environ.get("CXX", "g++")
+
+
+def build_hostio(force=False):
+    """librthc_hostio.so: plain C++ host text I/O (include/rthio.h), no CUDA involved."""
+    deps = [HOSTIO_SRC, os.path.join(HERE, "..", "include", "rthio.h")]
+    if not force and os.path.exists(HOSTIO_OUT) and all(os.path.getmtime(d) <= os.path.getmtime(HOSTIO_OUT) for d in deps):
+        return HOSTIO_OUT
+    subprocess.check_call([CXX, "-O3", "-std=c++17", "-fPIC", "-shared", "-pthread", "-Wall", "-o", HOSTIO_OUT, HOSTIO_SRC])
+    return HOSTIO_OUT
+
+
 def needs_build():
     if not os.path.exists(OUT):
         return True
     t = os.path.getmtime(OUT)
-    deps = [os.path.join(CSRC, f) for f in os.listdir(CSRC)] + [os.path.join(HERE, "..", "include", "rthc.h")]
+    deps = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f != "hostio.cpp"] + [os.path.join(HERE, "..", "include", "rthc.h")]
     return any(os.path.getmtime(d) > t for d in deps)
 
 
 def build(force=False, verbose=False):
+    build_hostio(force)
     if not force and not needs_build():
         return OUT
     objs = []

@@ -1,0 +1,579 @@
+// hostio.cpp -- librthc_hostio.so: text ingest and artefact writers of the drop-in CLI (include/rthio.h).
+//
+// Plain C++ (no CUDA).  Every function restates, at the string level, what the reference does with
+// pandas in scripts/partitioning_HC.py; the pandas code path in reportree_b200/partitioning_HC.py
+// stays the specification and the fallback for irregular files (RTHIO_IRREGULAR).
+#include <fcntl.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <string.h>
+#include <sys/mman.h>
+#include <sys/stat.h>
+#include <unistd.h>
+
+#include <algorithm>
+#include <atomic>
+#include <string>
+#include <thread>
+#include <unordered_set>
+#include <vector>
+
+#include "../../include/rthio.h"
+
+static thread_local std::string g_err;
+static int fail(int code, const char *fmt, ...)
+{
+    char buf[1024];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    g_err = buf;
+    return code;
+}
+extern "C" const char *rthio_last_error(void) { return g_err.c_str(); }
+extern "C" int rthio_version(void) { return 100; }
+
+static int pick_threads(int n_threads)
+{
+    if (n_threads > 0) return n_threads;
+    unsigned hc = std::thread::hardware_concurrency();
+    return hc ? (int)hc : 1;
+}
+
+// run fn(t, lo, hi) over [0, count) split into contiguous ranges, one per thread
+template <typename F> static void parallel_ranges(int64_t count, int n_threads, F fn)
+{
+    int T = (int)std::min<int64_t>(std::max<int64_t>(count, 1), n_threads);
+    if (T <= 1) { fn(0, (int64_t)0, count); return; }
+    std::vector<std::thread> th;
+    for (int t = 0; t < T; ++t) {
+        const int64_t lo = count * t / T, hi = count * (t + 1) / T;
+        th.emplace_back([=]() { fn(t, lo, hi); });
+    }
+    for (auto &x : th) x.join();
+}
+
+// ---- pandas' default NA tokens (read_table, keep_default_na=True; they apply with dtype=str too)
+static bool is_na_token(const char *s, size_t n)
+{
+    switch (n) {
+    case 0: return true;
+    case 2: return !memcmp(s, "NA", 2);
+    case 3: return !memcmp(s, "N/A", 3) || !memcmp(s, "NaN", 3) || !memcmp(s, "nan", 3) || !memcmp(s, "n/a", 3) ||
+                   !memcmp(s, "#NA", 3);
+    case 4: return !memcmp(s, "NULL", 4) || !memcmp(s, "null", 4) || !memcmp(s, "None", 4) || !memcmp(s, "#N/A", 4) ||
+                   !memcmp(s, "-NaN", 4) || !memcmp(s, "-nan", 4) || !memcmp(s, "<NA>", 4);
+    case 6: return !memcmp(s, "1.#IND", 6);
+    case 7: return !memcmp(s, "-1.#IND", 7) || !memcmp(s, "1.#QNAN", 7);
+    case 8: return !memcmp(s, "-1.#QNAN", 8) || !memcmp(s, "#N/A N/A", 8);
+    default: return false;
+    }
+}
+
+// The reference's cleaning (scripts/partitioning_HC.py:363-364): one regex pass removing every
+// "INF-", then one removing every "*".  Returns the cleaned token (view into `tmp` if changed).
+struct Tok {
+    const char *s;
+    size_t n;
+};
+static inline Tok clean_token(const char *s, size_t n, std::string &tmp)
+{
+    const bool has_star = memchr(s, '*', n) != nullptr;
+    bool has_inf = false;
+    if (n >= 4) {
+        const char *p = s, *end = s + n - 3;
+        while (p < end && (p = (const char *)memchr(p, 'I', (size_t)(end - p)))) {
+            if (p[1] == 'N' && p[2] == 'F' && p[3] == '-') { has_inf = true; break; }
+            ++p;
+        }
+    }
+    if (!has_star && !has_inf) return Tok{s, n};
+    tmp.clear();
+    size_t i = 0;
+    while (i < n) {
+        if (has_inf && i + 4 <= n && s[i] == 'I' && s[i + 1] == 'N' && s[i + 2] == 'F' && s[i + 3] == '-') { i += 4; continue; }
+        tmp.push_back(s[i++]);
+    }
+    if (has_star) tmp.erase(std::remove(tmp.begin(), tmp.end(), '*'), tmp.end());
+    return Tok{tmp.data(), tmp.size()};
+}
+
+enum { MISS_NONE = 0, MISS_EMPTY = 1, MISS_STRING = 2 };
+
+struct rthio_profile {
+    const char *buf = nullptr;       // mmap of the file
+    size_t size = 0;
+    int fd = -1;
+    int miss_mode = MISS_NONE;
+    std::string miss_code;
+    int n_threads = 1;
+    int64_t n = 0, L = 0;
+    std::vector<std::string> header;            // L + 1 cells
+    std::vector<size_t> row_begin, row_end;     // data rows (blank lines skipped)
+    std::vector<std::string> ids;               // cleaned sample ids
+    std::vector<char> id_nan;
+    std::vector<int32_t> codes;                 // n x L
+};
+
+// final text of a DATA cell (not the id column): cleaning + --missing-code replacement.
+// *nan_out = the cell is NaN in the DataFrame (prints as the empty string).
+static inline Tok final_cell(const rthio_profile *p, const char *s, size_t n, std::string &tmp, bool *nan_out)
+{
+    static const char ZERO[] = "0";
+    if (is_na_token(s, n)) {
+        if (p->miss_mode == MISS_EMPTY) { *nan_out = false; return Tok{ZERO, 1}; }
+        *nan_out = true;
+        return Tok{s, 0};
+    }
+    *nan_out = false;
+    Tok t = clean_token(s, n, tmp);
+    if (p->miss_mode == MISS_STRING && t.n == p->miss_code.size() && !memcmp(t.s, p->miss_code.data(), t.n))
+        return Tok{ZERO, 1};
+    return t;
+}
+
+// conv_nucl + the cgmlst-dists cell contract, see rthio.h
+static inline int32_t cell_code(Tok t, bool nan)
+{
+    if (nan || t.n == 0) return -1;
+    const unsigned char c0 = (unsigned char)t.s[0];
+    if (t.n == 1) {
+        if (c0 >= 'a' && c0 <= 'z') return c0 - 'a' + 1;
+        if (c0 >= 'A' && c0 <= 'Z') return c0 - 'A' + 27;
+    }
+    if (t.n > 9) return -1;
+    int32_t v = 0;
+    for (size_t i = 0; i < t.n; ++i) {
+        const unsigned d = (unsigned char)t.s[i] - '0';
+        if (d > 9) return -1;
+        v = v * 10 + (int32_t)d;
+    }
+    if (v == 0) return t.n == 1 ? 0 : -1;      // "0" is the literal missing code; "00" is not
+    return v;
+}
+
+// ---------------------------------------------------------------------------------------------
+// profile ingest
+// ---------------------------------------------------------------------------------------------
+extern "C" void rthio_profile_close(rthio_profile *p)
+{
+    if (!p) return;
+    if (p->buf && p->size) munmap((void *)p->buf, p->size);
+    if (p->fd >= 0) close(p->fd);
+    delete p;
+}
+
+extern "C" int rthio_profile_open(const char *path, const char *missing_code, int n_threads, rthio_profile **out)
+{
+    if (!path || !out) return fail(RTHIO_E_ARG, "rthio_profile_open: NULL argument");
+    *out = nullptr;
+    rthio_profile *p = new rthio_profile();
+    p->n_threads = pick_threads(n_threads);
+    const std::string mc = missing_code ? missing_code : "0";
+    if (mc == "0") p->miss_mode = MISS_NONE;
+    else if (mc == "empty") p->miss_mode = MISS_EMPTY;
+    else { p->miss_mode = MISS_STRING; p->miss_code = mc; }
+    p->fd = open(path, O_RDONLY);
+    if (p->fd < 0) { rthio_profile_close(p); return fail(RTHIO_E_IO, "cannot open %s", path); }
+    struct stat st;
+    if (fstat(p->fd, &st) != 0 || st.st_size <= 0) { rthio_profile_close(p); return fail(RTHIO_IRREGULAR, "empty or unreadable file"); }
+    p->size = (size_t)st.st_size;
+    void *m = mmap(nullptr, p->size, PROT_READ, MAP_PRIVATE, p->fd, 0);
+    if (m == MAP_FAILED) { p->size = 0; rthio_profile_close(p); return fail(RTHIO_E_IO, "mmap of %s failed", path); }
+    p->buf = (const char *)m;
+    madvise(m, p->size, MADV_SEQUENTIAL);
+    const char *buf = p->buf;
+    const size_t size = p->size;
+    // anything pandas' C parser would treat specially -> the caller takes the pandas path
+    if (size >= 3 && (unsigned char)buf[0] == 0xEF && (unsigned char)buf[1] == 0xBB && (unsigned char)buf[2] == 0xBF) {
+        rthio_profile_close(p); return fail(RTHIO_IRREGULAR, "byte-order mark");
+    }
+    {
+        std::atomic<int> odd(0);
+        parallel_ranges((int64_t)size, p->n_threads, [&](int, int64_t lo, int64_t hi) {
+            if (memchr(buf + lo, '"', (size_t)(hi - lo)) || memchr(buf + lo, '\r', (size_t)(hi - lo)) ||
+                memchr(buf + lo, '\0', (size_t)(hi - lo)))
+                odd.store(1);
+        });
+        if (odd.load()) { rthio_profile_close(p); return fail(RTHIO_IRREGULAR, "quote, CR or NUL in the file"); }
+    }
+    // lines (blank lines are skipped like skip_blank_lines=True)
+    std::vector<size_t> lb, le;
+    {
+        size_t pos = 0;
+        while (pos < size) {
+            const char *nl = (const char *)memchr(buf + pos, '\n', size - pos);
+            const size_t end = nl ? (size_t)(nl - buf) : size;
+            if (end > pos) { lb.push_back(pos); le.push_back(end); }
+            pos = end + 1;
+        }
+    }
+    if (lb.size() < 1) { rthio_profile_close(p); return fail(RTHIO_IRREGULAR, "no header line"); }
+    // header
+    {
+        std::unordered_set<std::string> seen;
+        size_t a = lb[0];
+        const size_t e = le[0];
+        for (;;) {
+            const char *tab = (const char *)memchr(buf + a, '\t', e - a);
+            const size_t b = tab ? (size_t)(tab - buf) : e;
+            std::string cell(buf + a, b - a);
+            if (cell.empty() || !seen.insert(cell).second) {
+                rthio_profile_close(p); return fail(RTHIO_IRREGULAR, "empty or duplicated header cell");
+            }
+            p->header.push_back(cell);
+            if (!tab) break;
+            a = b + 1;
+        }
+    }
+    if (p->header.size() < 2) { rthio_profile_close(p); return fail(RTHIO_IRREGULAR, "fewer than two columns"); }
+    p->L = (int64_t)p->header.size() - 1;
+    p->n = (int64_t)lb.size() - 1;
+    p->row_begin.assign(lb.begin() + 1, lb.end());
+    p->row_end.assign(le.begin() + 1, le.end());
+    try {
+        p->codes.resize((size_t)(p->n * p->L));
+        p->ids.resize((size_t)p->n);
+        p->id_nan.assign((size_t)p->n, 0);
+    } catch (...) { rthio_profile_close(p); return fail(RTHIO_E_NOMEM, "out of host memory for %lld x %lld codes", (long long)p->n, (long long)p->L); }
+    std::atomic<int> ragged(0);
+    const int64_t L = p->L;
+    parallel_ranges(p->n, p->n_threads, [&](int, int64_t lo, int64_t hi) {
+        std::string tmp;
+        for (int64_t r = lo; r < hi && !ragged.load(std::memory_order_relaxed); ++r) {
+            const char *a = buf + p->row_begin[(size_t)r], *e = buf + p->row_end[(size_t)r];
+            int32_t *dst = p->codes.data() + (size_t)(r * L);
+            // id cell
+            const char *tab = (const char *)memchr(a, '\t', (size_t)(e - a));
+            const char *b = tab ? tab : e;
+            if (is_na_token(a, (size_t)(b - a))) p->id_nan[(size_t)r] = 1;
+            else { Tok t = clean_token(a, (size_t)(b - a), tmp); p->ids[(size_t)r].assign(t.s, t.n); }
+            int64_t c = 0;
+            while (tab) {
+                a = tab + 1;
+                tab = (const char *)memchr(a, '\t', (size_t)(e - a));
+                b = tab ? tab : e;
+                if (c >= L) { c = L + 1; break; }
+                bool nan;
+                const size_t len = (size_t)(b - a);
+                // fast path: short all-digit token (the overwhelmingly common cell)
+                if (len >= 1 && len <= 9 && p->miss_mode != MISS_STRING) {
+                    int32_t v = 0; bool digits = true;
+                    for (size_t i = 0; i < len; ++i) { const unsigned d = (unsigned char)a[i] - '0'; if (d > 9) { digits = false; break; } v = v * 10 + (int32_t)d; }
+                    if (digits) { dst[c++] = v ? v : (len == 1 ? 0 : -1); continue; }
+                }
+                Tok t = final_cell(p, a, len, tmp, &nan);
+                dst[c++] = cell_code(t, nan);
+            }
+            if (c != L) ragged.store(1);
+        }
+    });
+    if (ragged.load()) { rthio_profile_close(p); return fail(RTHIO_IRREGULAR, "a row does not have %lld cells", (long long)(L + 1)); }
+    *out = p;
+    return RTHIO_OK;
+}
+
+extern "C" int64_t rthio_profile_rows(const rthio_profile *p) { return p ? p->n : 0; }
+extern "C" int64_t rthio_profile_cols(const rthio_profile *p) { return p ? p->L : 0; }
+extern "C" const int32_t *rthio_profile_codes(const rthio_profile *p) { return p ? p->codes.data() : nullptr; }
+
+extern "C" int rthio_profile_header(const rthio_profile *p, int64_t col, const char **s, int64_t *len)
+{
+    if (!p || !s || !len || col < 0 || col > p->L) return fail(RTHIO_E_ARG, "rthio_profile_header: bad argument");
+    *s = p->header[(size_t)col].data();
+    *len = (int64_t)p->header[(size_t)col].size();
+    return RTHIO_OK;
+}
+
+extern "C" int rthio_profile_sample(const rthio_profile *p, int64_t row, const char **s, int64_t *len, int *is_nan)
+{
+    if (!p || !s || !len || !is_nan || row < 0 || row >= p->n) return fail(RTHIO_E_ARG, "rthio_profile_sample: bad argument");
+    *s = p->ids[(size_t)row].data();
+    *len = (int64_t)p->ids[(size_t)row].size();
+    *is_nan = p->id_nan[(size_t)row];
+    return RTHIO_OK;
+}
+
+extern "C" int rthio_profile_gather(const rthio_profile *p, const int64_t *rows, int64_t nrows, const int64_t *cols,
+                                    int64_t ncols, int32_t *out)
+{
+    if (!p || !rows || !cols || !out) return fail(RTHIO_E_ARG, "rthio_profile_gather: NULL argument");
+    for (int64_t r = 0; r < nrows; ++r) if (rows[r] < 0 || rows[r] >= p->n) return fail(RTHIO_E_ARG, "row index out of range");
+    for (int64_t c = 0; c < ncols; ++c) if (cols[c] < 0 || cols[c] >= p->L) return fail(RTHIO_E_ARG, "column index out of range");
+    parallel_ranges(nrows, p->n_threads, [&](int, int64_t lo, int64_t hi) {
+        for (int64_t r = lo; r < hi; ++r) {
+            const int32_t *src = p->codes.data() + (size_t)(rows[r] * p->L);
+            int32_t *dst = out + (size_t)(r * ncols);
+            for (int64_t c = 0; c < ncols; ++c) dst[c] = src[cols[c]];
+        }
+    });
+    return RTHIO_OK;
+}
+
+static int write_all(int fd, const char *s, size_t n)
+{
+    while (n) {
+        ssize_t w = write(fd, s, n);
+        if (w <= 0) return -1;
+        s += w; n -= (size_t)w;
+    }
+    return 0;
+}
+
+extern "C" int rthio_profile_write(const rthio_profile *p, const char *path, const int64_t *rows, int64_t nrows,
+                                   const int64_t *cols, int64_t ncols)
+{
+    if (!p || !path || (!rows && nrows) || (!cols && ncols)) return fail(RTHIO_E_ARG, "rthio_profile_write: NULL argument");
+    for (int64_t c = 0; c < ncols; ++c)
+        if (cols[c] < 0 || cols[c] >= p->L || (c && cols[c] <= cols[c - 1])) return fail(RTHIO_E_ARG, "columns must be ascending and in range");
+    for (int64_t r = 0; r < nrows; ++r) if (rows[r] < 0 || rows[r] >= p->n) return fail(RTHIO_E_ARG, "row index out of range");
+    const int fd = open(path, O_WRONLY | O_CREAT | O_TRUNC, 0644);
+    if (fd < 0) return fail(RTHIO_E_IO, "cannot create %s", path);
+    std::string head = p->header[0];
+    for (int64_t c = 0; c < ncols; ++c) { head.push_back('\t'); head += p->header[(size_t)cols[c] + 1]; }
+    head.push_back('\n');
+    int rc = write_all(fd, head.data(), head.size());
+    const int T = p->n_threads;
+    const int64_t wave = (int64_t)T * 512;
+    std::vector<std::string> outb((size_t)T);
+    for (int64_t w0 = 0; w0 < nrows && !rc; w0 += wave) {
+        const int64_t w1 = std::min(nrows, w0 + wave);
+        for (auto &s : outb) s.clear();
+        parallel_ranges(w1 - w0, T, [&](int t, int64_t lo, int64_t hi) {
+            std::string &ob = outb[(size_t)t];
+            std::string tmp;
+            for (int64_t q = w0 + lo; q < w0 + hi; ++q) {
+                const int64_t r = rows[q];
+                if (!p->id_nan[(size_t)r]) ob += p->ids[(size_t)r];
+                const char *a = p->buf + p->row_begin[(size_t)r], *e = p->buf + p->row_end[(size_t)r];
+                const char *tab = (const char *)memchr(a, '\t', (size_t)(e - a));
+                int64_t c = 0, want = 0;
+                while (tab && want < ncols) {
+                    a = tab + 1;
+                    tab = (const char *)memchr(a, '\t', (size_t)(e - a));
+                    if (c == cols[want]) {
+                        const char *b = tab ? tab : e;
+                        bool nan;
+                        Tok t = final_cell(p, a, (size_t)(b - a), tmp, &nan);
+                        ob.push_back('\t');
+                        if (!nan) ob.append(t.s, t.n);
+                        ++want;
+                    }
+                    ++c;
+                }
+                ob.push_back('\n');
+            }
+        });
+        for (int t = 0; t < T && !rc; ++t)
+            if (!outb[(size_t)t].empty()) rc = write_all(fd, outb[(size_t)t].data(), outb[(size_t)t].size());
+    }
+    if (close(fd) != 0) rc = -1;
+    return rc ? fail(RTHIO_E_IO, "write to %s failed", path) : RTHIO_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// square distance matrix -> <out>_dist_hamming.tsv
+// ---------------------------------------------------------------------------------------------
+struct rthio_file {
+    int fd = -1;
+    int n_threads = 1;
+    int64_t n = 0;
+    std::vector<std::string> names;
+    std::string path;
+};
+
+static inline char *put_u32(char *o, uint32_t v)
+{
+    char tmp[10];
+    int k = 0;
+    do { tmp[k++] = (char)('0' + v % 10); v /= 10; } while (v);
+    while (k) *o++ = tmp[--k];
+    return o;
+}
+
+extern "C" int rthio_square_open(const char *path, const char *corner, const char *blob, const int64_t *offs, int64_t n,
+                                 int n_threads, rthio_file **out)
+{
+    if (!path || !corner || !blob || !offs || !out || n < 0) return fail(RTHIO_E_ARG, "rthio_square_open: bad argument");
+    rthio_file *f = new rthio_file();
+    f->n_threads = pick_threads(n_threads);
+    f->n = n;
+    f->path = path;
+    f->names.resize((size_t)n);
+    std::string head = corner;
+    for (int64_t k = 0; k < n; ++k) {
+        f->names[(size_t)k].assign(blob + offs[k], (size_t)(offs[k + 1] - offs[k]));
+        head.push_back('\t');
+        head += f->names[(size_t)k];
+    }
+    head.push_back('\n');
+    f->fd = open(path, O_WRONLY | O_CREAT | O_TRUNC, 0644);
+    if (f->fd < 0 || write_all(f->fd, head.data(), head.size())) {
+        if (f->fd >= 0) close(f->fd);
+        delete f;
+        return fail(RTHIO_E_IO, "cannot write %s", path);
+    }
+    *out = f;
+    return RTHIO_OK;
+}
+
+extern "C" int rthio_square_append_u16(rthio_file *f, int64_t row0, int64_t nrows, const uint16_t *block)
+{
+    if (!f || !block || row0 < 0 || nrows < 0 || row0 + nrows > f->n) return fail(RTHIO_E_ARG, "rthio_square_append_u16: bad argument");
+    const int64_t n = f->n;
+    const int T = f->n_threads;
+    std::vector<std::vector<char>> outb((size_t)T);
+    std::vector<size_t> used((size_t)T, 0);
+    parallel_ranges(nrows, T, [&](int t, int64_t lo, int64_t hi) {
+        size_t cap = 0;
+        for (int64_t r = lo; r < hi; ++r) cap += f->names[(size_t)(row0 + r)].size() + (size_t)n * 6 + 2;
+        std::vector<char> &ob = outb[(size_t)t];
+        ob.resize(cap);
+        char *o = ob.data();
+        for (int64_t r = lo; r < hi; ++r) {
+            const std::string &nm = f->names[(size_t)(row0 + r)];
+            memcpy(o, nm.data(), nm.size());
+            o += nm.size();
+            const uint16_t *src = block + (size_t)(r * n);
+            for (int64_t j = 0; j < n; ++j) {
+                *o++ = '\t';
+                const uint32_t v = src[j];
+                if (v < 10) *o++ = (char)('0' + v);
+                else o = put_u32(o, v);
+            }
+            *o++ = '\n';
+        }
+        used[(size_t)t] = (size_t)(o - ob.data());
+    });
+    for (int t = 0; t < T; ++t)
+        if (used[(size_t)t] && write_all(f->fd, outb[(size_t)t].data(), used[(size_t)t]))
+            return fail(RTHIO_E_IO, "write to %s failed", f->path.c_str());
+    return RTHIO_OK;
+}
+
+extern "C" int rthio_square_close(rthio_file *f)
+{
+    if (!f) return RTHIO_OK;
+    int rc = close(f->fd);
+    std::string path = f->path;
+    delete f;
+    return rc ? fail(RTHIO_E_IO, "close of %s failed", path.c_str()) : RTHIO_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// partitions.tsv + clusterComposition.tsv
+// ---------------------------------------------------------------------------------------------
+// Naming rule (scripts/partitioning_HC.py:651-670): walking the samples in matrix order, a
+// cluster of size 1 becomes singleton_<running count>, any other cluster_<fcluster id>.
+// code[t][i] > 0: cluster_<code>;  < 0: singleton_<-code>.
+static inline char *put_name(char *o, int32_t code)
+{
+    if (code > 0) { memcpy(o, "cluster_", 8); return put_u32(o + 8, (uint32_t)code); }
+    memcpy(o, "singleton_", 10);
+    return put_u32(o + 10, (uint32_t)(-(int64_t)code));
+}
+
+extern "C" int rthio_write_partitions(const char *path_partitions, const char *path_composition, const char *names_blob,
+                                      const int64_t *names_offs, int64_t n, const int32_t *labels, int64_t T,
+                                      const char *col_blob, const int64_t *col_offs, int n_threads)
+{
+    if (!path_partitions || !path_composition || !names_blob || !names_offs || (!labels && T) || !col_blob || !col_offs || n < 1 || T < 0)
+        return fail(RTHIO_E_ARG, "rthio_write_partitions: bad argument");
+    const int NT = pick_threads(n_threads);
+    std::vector<int32_t> code;
+    try { code.resize((size_t)(T * n)); } catch (...) { return fail(RTHIO_E_NOMEM, "out of host memory for %lld x %lld names", (long long)T, (long long)n); }
+    const int fdc = open(path_composition, O_WRONLY | O_CREAT | O_TRUNC, 0644);
+    if (fdc < 0) return fail(RTHIO_E_IO, "cannot create %s", path_composition);
+    static const char CHEAD[] = "#partition\tcluster\tcluster_length\tsamples\n";
+    int rc = write_all(fdc, CHEAD, sizeof CHEAD - 1);
+    std::atomic<int> bad(0);
+    // thresholds in waves of NT: names + composition text per threshold in parallel, written in order
+    for (int64_t t0 = 0; t0 < T && !rc; t0 += NT) {
+        const int64_t t1 = std::min(T, t0 + NT);
+        std::vector<std::string> comp((size_t)(t1 - t0));
+        parallel_ranges(t1 - t0, NT, [&](int, int64_t lo, int64_t hi) {
+            std::vector<int32_t> count, start, fill, first, order;
+            for (int64_t t = t0 + lo; t < t0 + hi; ++t) {
+                const int32_t *lab = labels + (size_t)(t * n);
+                int32_t *cd = code.data() + (size_t)(t * n);
+                int32_t k = 0;
+                for (int64_t i = 0; i < n; ++i) { if (lab[i] < 1) bad.store(1); k = std::max(k, lab[i]); }
+                if (bad.load()) return;
+                count.assign((size_t)k + 1, 0);
+                for (int64_t i = 0; i < n; ++i) count[(size_t)lab[i]]++;
+                int32_t singles = 0;
+                for (int64_t i = 0; i < n; ++i) cd[i] = count[(size_t)lab[i]] == 1 ? -(++singles) : lab[i];
+                // members of every cluster in row order (counting sort), clusters by first appearance
+                start.assign((size_t)k + 2, 0);
+                for (int32_t c = 1; c <= k; ++c) start[(size_t)c + 1] = start[(size_t)c] + count[(size_t)c];
+                fill.assign(start.begin(), start.end());
+                order.resize((size_t)n);
+                first.clear();
+                for (int64_t i = 0; i < n; ++i) {
+                    const int32_t c = lab[i];
+                    if (fill[(size_t)c] == start[(size_t)c]) first.push_back(c);
+                    order[(size_t)fill[(size_t)c]++] = (int32_t)i;
+                }
+                std::string &out = comp[(size_t)(t - t0)];
+                const std::string part(col_blob + col_offs[t], (size_t)(col_offs[t + 1] - col_offs[t]));
+                char num[32];
+                for (int32_t c : first) {
+                    const int32_t sz = count[(size_t)c];
+                    out += part;
+                    out.push_back('\t');
+                    char *e = put_name(num, cd[order[(size_t)start[(size_t)c]]]);
+                    out.append(num, (size_t)(e - num));
+                    out.push_back('\t');
+                    e = put_u32(num, (uint32_t)sz);
+                    out.append(num, (size_t)(e - num));
+                    out.push_back('\t');
+                    for (int32_t q = 0; q < sz; ++q) {
+                        const int32_t i = order[(size_t)(start[(size_t)c] + q)];
+                        if (q) out.push_back(',');
+                        out.append(names_blob + names_offs[i], (size_t)(names_offs[i + 1] - names_offs[i]));
+                    }
+                    out.push_back('\n');
+                }
+            }
+        });
+        if (bad.load()) { close(fdc); return fail(RTHIO_E_ARG, "cluster ids must be >= 1"); }
+        for (auto &s : comp)
+            if (!rc && !s.empty()) rc = write_all(fdc, s.data(), s.size());
+    }
+    if (close(fdc) != 0) rc = -1;
+    if (rc) return fail(RTHIO_E_IO, "write to %s failed", path_composition);
+    // partitions.tsv: one row per sample, one column per threshold
+    const int fdp = open(path_partitions, O_WRONLY | O_CREAT | O_TRUNC, 0644);
+    if (fdp < 0) return fail(RTHIO_E_IO, "cannot create %s", path_partitions);
+    std::string head = "sequence";
+    for (int64_t t = 0; t < T; ++t) { head.push_back('\t'); head.append(col_blob + col_offs[t], (size_t)(col_offs[t + 1] - col_offs[t])); }
+    head.push_back('\n');
+    rc = write_all(fdp, head.data(), head.size());
+    const int64_t wave = std::max<int64_t>(1, (int64_t)NT * std::max<int64_t>(1, (int64_t)(1 << 22) / std::max<int64_t>(T * 16, 1)));
+    std::vector<std::vector<char>> outb((size_t)NT);
+    std::vector<size_t> used((size_t)NT);
+    for (int64_t r0 = 0; r0 < n && !rc; r0 += wave) {
+        const int64_t r1 = std::min(n, r0 + wave);
+        std::fill(used.begin(), used.end(), 0);
+        parallel_ranges(r1 - r0, NT, [&](int th, int64_t lo, int64_t hi) {
+            size_t cap = 0;
+            for (int64_t i = r0 + lo; i < r0 + hi; ++i) cap += (size_t)(names_offs[i + 1] - names_offs[i]) + (size_t)T * 22 + 2;
+            std::vector<char> &ob = outb[(size_t)th];
+            if (ob.size() < cap) ob.resize(cap);
+            char *o = ob.data();
+            for (int64_t i = r0 + lo; i < r0 + hi; ++i) {
+                const size_t ln = (size_t)(names_offs[i + 1] - names_offs[i]);
+                memcpy(o, names_blob + names_offs[i], ln);
+                o += ln;
+                for (int64_t t = 0; t < T; ++t) { *o++ = '\t'; o = put_name(o, code[(size_t)(t * n + i)]); }
+                *o++ = '\n';
+            }
+            used[(size_t)th] = (size_t)(o - ob.data());
+        });
+        for (int th = 0; th < NT && !rc; ++th)
+            if (used[(size_t)th]) rc = write_all(fdp, outb[(size_t)th].data(), used[(size_t)th]);
+    }
+    if (close(fdp) != 0) rc = -1;
+    return rc ? fail(RTHIO_E_IO, "write to %s failed", path_partitions) : RTHIO_OK;
+}

@@ -33,6 +33,33 @@ last_updated = "2025-10-21"
 GPU_METHODS = ("single", "complete", "average", "weighted")
 
 
+class Phases:
+    """REPORTREE_HC_TIMING=1: wall time of every phase of the run, printed to stderr at the end
+    (stdout and <out>.log stay byte-identical to the reference's messages)."""
+
+    def __init__(self):
+        import time
+        self.clock = time.perf_counter
+        self.on = os.environ.get("REPORTREE_HC_TIMING", "0") == "1"
+        self.t0 = self.last = self.clock()
+        self.rows = []
+
+    def mark(self, name):
+        now = self.clock()
+        self.rows.append((name, now - self.last))
+        self.last = now
+
+    def report(self):
+        if self.on:
+            total = self.clock() - self.t0
+            for name, dt in self.rows:
+                sys.stderr.write("[hc-timing] %-28s %9.3f s\n" % (name, dt))
+            sys.stderr.write("[hc-timing] %-28s %9.3f s\n" % ("TOTAL (main)", total))
+
+
+PH = Phases()
+
+
 class Tee:
     """Every message goes to stdout and to <out>.log (scripts/partitioning_HC.py:340-348)."""
 
@@ -276,7 +303,13 @@ def profile_to_distances(args, say, log, ctx):
     """`-a` branch: load, clean, filter, encode, distance on the GPU, artefact files.
     Returns (sample names, total_size)."""
     say("Profile matrix provided... pairwise distance will be calculated!")
+    from reportree_b200 import fastio
+    if fastio.enabled():
+        prof = fastio.open_profile(args.allele_profile, str(args.missing_code))
+        if prof is not None:                      # None: irregular text, pandas decides what it means
+            return profile_to_distances_fast(args, say, log, ctx, prof)
     mx = load_profile(args.allele_profile, str(args.missing_code), args.out, say)
+    PH.mark("load + clean profile")
 
     if args.metadata != "" and args.filter_column != "":
         from reportree_b200 import metadata_filter
@@ -301,22 +334,151 @@ def profile_to_distances(args, say, log, ctx):
     with open(args.out + "_loci_used.txt", "w+") as fh:
         for locus in mx.columns[1:]:
             print(locus, file=fh)
+    PH.mark("column filter")
     mx.to_csv(args.out + "_clean_missing_matrix.tsv", index=False, header=True, sep="\t")
+    PH.mark("write clean_missing_matrix")
 
     mx = filter_rows(mx, args, say)
     if mx is None:
         _exit(log)
+    PH.mark("row filter + flt_samples")
 
     say("Getting the pairwise distance matrix with cgmlst-dists (if your profile matrix is too big, this will be done in chunks of 2000 alleles/positions)...")
     total_size = len(mx.columns) - 1
     # sample ids travel through TSV text in the reference; NaN ids would print as empty strings
     names = ["" if not isinstance(s, str) else s for s in mx[mx.columns[0]].tolist()]
     codes = hostio.encode_cells(mx.iloc[:, 1:])
+    PH.mark("encode cells")
     ctx.set_profiles(codes)
     ctx.distance()
+    PH.mark("GPU recode + distance")
     if os.environ.get("REPORTREE_HC_SKIP_DIST_TSV", "0") != "1":
-        hostio.write_square_tsv(args.out + "_dist_hamming.tsv", names, ctx.square_rows, len(names))
+        write_dist_tsv(args.out + "_dist_hamming.tsv", names, ctx)
+        PH.mark("write dist_hamming.tsv")
     return names, total_size
+
+
+def _loci_selection_fast(prof, rows, args, say):
+    """filter_columns() on a fastio.Profile: returns the kept locus indices (ascending)."""
+    loci = prof.header[1:]
+    n_before = len(loci)
+    site = float(args.samples_called)
+    keep = np.arange(n_before)
+
+    def called_fraction(cols):
+        if len(cols) == 0:
+            return np.zeros(0)
+        sub = prof.codes[np.ix_(rows, cols)] if len(rows) != prof.n else prof.codes[:, cols]
+        return (sub != 0).sum(axis=0) / len(rows)           # (col != "0").sum() / n, float64 (:414-415)
+
+    if args.loci != "none":
+        wanted = set(read_loci_list(args.loci, _Columns(prof.header)))
+        in_list = np.fromiter((c in wanted for c in loci), dtype=bool, count=n_before)
+        if site == 0.0:
+            say("Keeping the sites/loci present in the loci list.")
+            keep = np.flatnonzero(in_list)
+        else:
+            say("Keeping the sites/loci present in the loci list and those with information in >= " + str(site * 100) + "%% of the samples...")
+            others = np.flatnonzero(~in_list)
+            extra = np.zeros(n_before, dtype=bool)
+            extra[others[called_fraction(others) >= site]] = True
+            keep = np.flatnonzero(in_list | extra)
+        say("\tFrom the " + str(n_before) + " loci/positions, " + str(len(keep)) + " were kept in the matrix.")
+    elif site > 0.0:
+        say("Keeping the sites/loci with information in >= " + str(site * 100) + "%% of the samples...")
+        keep = np.flatnonzero(called_fraction(np.arange(n_before)) >= site)
+        say("\tFrom the " + str(n_before) + " loci/positions, " + str(len(keep)) + " were kept in the matrix.")
+    return keep
+
+
+class _Columns:
+    """Just enough of a DataFrame for read_loci_list(): `.columns`."""
+
+    def __init__(self, header):
+        self.columns = header
+
+
+def profile_to_distances_fast(args, say, log, ctx, prof):
+    """`-a` branch on a profile parsed by librthc_hostio.so: same filters, messages and artefact
+    files as profile_to_distances(), without a string DataFrame."""
+    out = args.out
+    all_cols = np.arange(prof.n_loci)
+    rows = np.arange(prof.n)
+    if str(args.missing_code) != "0":
+        prof.write(out + "_missing0.tsv", rows, all_cols)
+    PH.mark("load + clean profile")
+
+    if args.metadata != "" and args.filter_column != "":
+        from reportree_b200 import metadata_filter
+        say("Filtering the allele matrix...")
+        meta = pandas.read_table(args.metadata, dtype=str)
+        meta.columns = [c.replace(" ", "_") for c in meta.columns]
+        meta = meta.replace(" ", "_", regex=True)
+        say("\tFiltering metadata for the following parameters: " + " & ".join(args.filter_column.split(";")))
+        keep_ids = set(metadata_filter.select_samples(meta, args.filter_column))
+        rows = np.asarray([i for i, s in enumerate(prof.ids) if s is not None and s in keep_ids], dtype=np.int64)
+        say("\tFrom the " + str(prof.n) + " samples, " + str(len(rows)) + " were kept in the matrix...")
+        if len(rows) <= 1:
+            say("\nCannot proceed because " + str(len(rows)) + " samples were kept in the matrix!")
+            _exit(log)
+        prof.write(out + "_subset_matrix.tsv", rows, all_cols)
+
+    cols = _loci_selection_fast(prof, rows, args, say)
+    if len(cols) <= 1:
+        say("\nCannot proceed because " + str(len(cols)) + " sites/loci were kept in the matrix!")
+        _exit(log)
+    with open(out + "_loci_used.txt", "w+") as fh:
+        fh.write("".join(prof.header[c + 1] + "\n" for c in cols.tolist()))
+    PH.mark("column filter")
+    prof.write(out + "_clean_missing_matrix.tsv", rows, cols)
+    PH.mark("write clean_missing_matrix")
+
+    thr = float(args.loci_called)
+    if thr >= 0.0:
+        say("Cleaning the profile matrix using a threshold of >" + str(args.loci_called) + " alleles/positions called per sample...")
+        len_schema = len(cols)
+        codes = prof.gather(rows, cols)
+        id_is_zero = np.fromiter((prof.ids[i] == "0" for i in rows.tolist()), dtype=bool, count=len(rows))
+        missing = (codes == 0).sum(axis=1) + id_is_zero       # isin(["0"]) over every column incl. the id (:451)
+        called = len_schema - missing
+        ids = [prof.ids[i] if prof.ids[i] is not None else np.nan for i in rows.tolist()]
+        report = pandas.DataFrame({"samples": pandas.Series(ids, dtype=object), "missing": missing, "called": called,
+                                   "pct_called": called / len_schema})
+        passed = (report["pct_called"] >= thr).to_numpy()
+        report.to_csv(out + "_loci_report.tsv", index=False, header=True, sep="\t")
+        say("\tFrom the " + str(len(rows)) + " samples, " + str(int(passed.sum())) + " were kept in the profile matrix.")
+        if int(passed.sum()) <= 1:
+            say("\nCannot proceed because " + str(int(passed.sum())) + " samples were kept in the matrix!")
+            _exit(log)
+        # isin(passing): every row whose id equals the id of a passing row stays (duplicated ids)
+        passing_ids = {prof.ids[i] for i, ok in zip(rows.tolist(), passed.tolist()) if ok}
+        sel = np.fromiter((prof.ids[i] in passing_ids for i in rows.tolist()), dtype=bool, count=len(rows))
+        rows, codes = rows[sel], codes[sel]
+        prof.write(out + "_flt_samples_matrix.tsv", rows, cols)
+    else:
+        codes = prof.gather(rows, cols)
+    PH.mark("row filter + flt_samples")
+
+    say("Getting the pairwise distance matrix with cgmlst-dists (if your profile matrix is too big, this will be done in chunks of 2000 alleles/positions)...")
+    total_size = len(cols)
+    names = ["" if prof.ids[i] is None else prof.ids[i] for i in rows.tolist()]
+    prof.close()
+    PH.mark("encode cells")
+    ctx.set_profiles(np.ascontiguousarray(codes))
+    ctx.distance()
+    PH.mark("GPU recode + distance")
+    if os.environ.get("REPORTREE_HC_SKIP_DIST_TSV", "0") != "1":
+        write_dist_tsv(out + "_dist_hamming.tsv", names, ctx)
+        PH.mark("write dist_hamming.tsv")
+    return names, total_size
+
+
+def write_dist_tsv(path, names, ctx):
+    from reportree_b200 import fastio
+    if fastio.enabled() and fastio.plain_text(names):
+        fastio.write_square_tsv(path, names, ctx.square_rows, len(names))
+    else:
+        hostio.write_square_tsv(path, names, ctx.square_rows, len(names))
 
 
 def matrix_to_distances(args, say, log, ctx):
@@ -363,7 +525,9 @@ def main(argv=None):
         say("Could not find a profile or a distance matrix... One of them needs to be specified!!")
         _exit(log)
 
+    PH.__init__()
     ctx = hc_backend.HCContext(device=int(os.environ.get("REPORTREE_HC_DEVICE", "0")))
+    PH.mark("create GPU context")
     exact = os.environ.get("REPORTREE_HC_EXACT_NAMES", "1") != "0"
     ctx.set_single_algo(hc_backend.SL_PRIM if exact else hc_backend.SL_BORUVKA)
 
@@ -377,39 +541,65 @@ def main(argv=None):
         raise NameError("name 'total_size' is not defined")      # same failure as the reference (:586)
     runs, pct_corr = plan_runs(args.method_threshold, args.pct_HCmethod_threshold, total_size, say)
 
-    columns = {"sequence": names}
-    composition = {}
+    from reportree_b200 import fastio
+    cut_names, cut_labels = [], []              # every partition column in output order
     for method, requests in runs.items():
         say("Hierarchical clustering with method: " + method + "...")
         if method not in GPU_METHODS:
             raise hc_backend.HCBackendError(
                 "HC method %r is not implemented on the CUDA backend (available: %s)" % (method, ", ".join(GPU_METHODS)))
+        PH.mark("plan")
         Z = ctx.linkage(method)
+        PH.mark("GPU linkage " + method)
         max_dist = Z[-1, 2]
         say("\tMaximum distance " + str(max_dist) + "...")
         say("\tGenerating newick file...")
         with open(args.out + "_" + method + "_HC.nwk", "w+") as fh:
             print(hostio.newick(Z, names), file=fh)
+        PH.mark("newick " + method)
         say("\tDefining clusters...")
         cuts = expand_cuts(method, requests, pct_corr, max_dist, args.dist, say)
         if cuts:
             labels = ctx.fcluster([c[1] for c in cuts])
-            for k, (partition, _) in enumerate(cuts):
-                col, comp = hostio.name_partition(labels[k], names)
+            PH.mark("GPU cut " + method)
+            cut_names.extend(c[0] for c in cuts)
+            cut_labels.append(labels)
+
+    # The C++ writer needs distinct partition names (a repeated name makes the reference extend the
+    # composition of the first one, :217-230) and text that needs no CSV quoting; else the Python path.
+    fast = (fastio.enabled() and len(set(cut_names)) == len(cut_names) and fastio.plain_text(names)
+            and fastio.plain_text(cut_names))
+    if fast:
+        say("Creating sample partitions file...")
+        say("Creating cluster composition file...")
+        all_labels = np.concatenate(cut_labels, axis=0) if cut_labels else np.zeros((0, len(names)), dtype=np.int32)
+        fastio.write_partitions(args.out + "_partitions.tsv", args.out + "_clusterComposition.tsv", names, all_labels, cut_names)
+        PH.mark("write partitions + composition")
+    else:
+        columns = {"sequence": names}
+        composition = {}
+        k = 0
+        for labels in cut_labels:
+            for row in labels:
+                partition = cut_names[k]
+                k += 1
+                col, comp = hostio.name_partition(row, names)
                 columns[partition] = col
                 bucket = composition.setdefault(partition, {})
                 for cname, csize, members in comp:
                     bucket.setdefault(cname, {}).setdefault(csize, []).extend(members)
-
-    say("Creating sample partitions file...")
-    hostio.write_partitions(args.out + "_partitions.tsv", columns)
-    say("Creating cluster composition file...")
-    with open(args.out + "_clusterComposition.tsv", "w+") as fh:
-        print("#partition\tcluster\tcluster_length\tsamples", file=fh)
-        for partition, clusters in composition.items():
-            for cname, by_size in clusters.items():
-                for csize, members in by_size.items():
-                    print(partition + "\t" + cname + "\t" + str(csize) + "\t" + ",".join(members), file=fh)
+        PH.mark("name partitions")
+        say("Creating sample partitions file...")
+        hostio.write_partitions(args.out + "_partitions.tsv", columns)
+        PH.mark("write partitions.tsv")
+        say("Creating cluster composition file...")
+        with open(args.out + "_clusterComposition.tsv", "w+") as fh:
+            print("#partition\tcluster\tcluster_length\tsamples", file=fh)
+            for partition, clusters in composition.items():
+                for cname, by_size in clusters.items():
+                    for csize, members in by_size.items():
+                        print(partition + "\t" + cname + "\t" + str(csize) + "\t" + ",".join(members), file=fh)
+        PH.mark("write clusterComposition")
     if len(pct_corr) > 0:
         with open(args.out + "_parcentage2threshold.tsv", "w+") as fh:
             print("#percentage\tthreshold", file=fh)
@@ -419,6 +609,7 @@ def main(argv=None):
     say("\npartitioning_HC.py is done!")
     ctx.close()
     log.close()
+    PH.report()
 
 
 if __name__ == "__main__":

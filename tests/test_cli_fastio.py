@@ -1,0 +1,155 @@
+"""CPU tests of the drop-in CLI's host side through a fake numeric backend (oracle + scipy):
+ (1) the C++ text I/O path (librthc_hostio.so) writes byte-identical files and messages to the
+     pandas path on regular inputs, incl. INF-/'*' cleaning, NA tokens, letters, --missing-code,
+     --loci / --site-inclusion / --loci-called filters, duplicated sample ids;
+ (2) irregular inputs (quotes, CRLF, ragged rows) fall back to the pandas path;
+ (3) both paths reproduce the golden outputs of the unmodified reference script."""
+import gzip
+import os
+import shutil
+import sys
+
+import numpy as np
+import pytest
+
+G = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+def _run(monkeypatch, capsys, argv, fast):
+    from reportree_b200 import hc_backend, partitioning_HC as phc
+    from tests.fake_backend import FakeContext
+    monkeypatch.setattr(hc_backend, "HCContext", FakeContext)
+    monkeypatch.setenv("REPORTREE_HC_FASTIO", "1" if fast else "0")
+    monkeypatch.setattr(sys, "argv", ["partitioning_HC.py"] + argv)
+    try:
+        phc.main(argv)
+    except SystemExit:
+        pass
+    return capsys.readouterr().out
+
+
+def _files(tag):
+    d, base = os.path.dirname(tag), os.path.basename(tag)
+    return {f[len(base):]: open(os.path.join(d, f), "rb").read() for f in sorted(os.listdir(d))
+            if f.startswith(base + "_") or f == base + ".log"}
+
+
+def _messy_matrix(path, n=60, L=40, seed=3, dup_ids=False):
+    rng = np.random.default_rng(seed)
+    toks = ["0", "1", "2", "3", "17", "INF-5", "*8", "INF-*12", "LNF", "NA", "", "nan", "a", "C", "T", "00", "007", "-", "N/A",
+            "ININF-F-3", "4*", "PLOT5", "123456789", "1234567890", "NIPH"]
+    p = np.array([8, 20, 20, 15, 10, 3, 3, 1, 2, 1, 1, 1, 1, 1, 1, 1, 1, 2, 1, 1, 1, 1, 1, 1, 1], dtype=float)
+    cells = rng.choice(len(toks), size=(n, L), p=p / p.sum())
+    with open(path, "w") as fh:
+        fh.write("FILE\t" + "\t".join("loc%d" % k for k in range(L)) + "\n")
+        for i in range(n):
+            name = "s%03d" % (i if not (dup_ids and i % 17 == 5) else 3)
+            if i == 7:
+                name = "INF-x*7"
+            if i == 11:
+                name = "0"
+            fh.write(name + "\t" + "\t".join(toks[c] for c in cells[i]) + "\n")
+            if i == 20:
+                fh.write("\n")                       # blank line: skipped by both parsers
+    return path
+
+
+CASES = [
+    ["--HC-threshold", "single-1-6,complete-3"],
+    ["--HC-threshold", "single-2", "--loci-called", "0.6", "--site-inclusion", "0.7"],
+    ["--HC-threshold", "average-1-4", "--missing-code", "-", "--loci-called", "0.5"],
+    ["--HC-threshold", "single-3", "--missing-code", "empty", "--site-inclusion", "0.8"],
+    ["--HC-threshold", "single-1,single-1", "--pct-HC-threshold", "single-0.1"],
+]
+
+
+@pytest.mark.parametrize("case", range(len(CASES)))
+def test_fast_text_path_equals_pandas_path(case, tmp_path, monkeypatch, capsys):
+    inp = _messy_matrix(str(tmp_path / "in.tsv"), dup_ids=(case == 1))
+    outs = {}
+    for fast in (False, True):
+        d = tmp_path / ("fast" if fast else "slow")
+        d.mkdir()
+        argv = ["-a", inp, "-o", str(d / "run")] + CASES[case]
+        msgs = _run(monkeypatch, capsys, argv, fast)
+        outs[fast] = (_files(str(d / "run")), [l for l in msgs.split("\n") if str(tmp_path) not in l])
+    files_slow, msg_slow = outs[False]
+    files_fast, msg_fast = outs[True]
+    assert msg_fast == msg_slow
+    assert sorted(files_fast) == sorted(files_slow)
+    for k in files_slow:
+        if k == ".log":
+            continue
+        assert files_fast[k] == files_slow[k], k
+    assert "_partitions.tsv" in files_fast and "_dist_hamming.tsv" in files_fast
+
+
+def test_loci_list_and_metadata_free_paths(tmp_path, monkeypatch, capsys):
+    inp = _messy_matrix(str(tmp_path / "in.tsv"), seed=5)
+    loci = tmp_path / "loci.txt"
+    loci.write_text("".join("loc%d\n" % k for k in range(0, 40, 3)))
+    outs = {}
+    for fast in (False, True):
+        d = tmp_path / ("f" if fast else "s")
+        d.mkdir()
+        argv = ["-a", inp, "-o", str(d / "run"), "--HC-threshold", "single-1-3", "-l", str(loci), "--site-inclusion", "0.9"]
+        msgs = _run(monkeypatch, capsys, argv, fast)
+        outs[fast] = (_files(str(d / "run")), [l for l in msgs.split("\n") if str(tmp_path) not in l])
+    assert outs[True][1] == outs[False][1]
+    for k in outs[False][0]:
+        if k != ".log":
+            assert outs[True][0][k] == outs[False][0][k], k
+
+
+@pytest.mark.parametrize("kind", ["quote", "crlf", "ragged", "dup_header"])
+def test_irregular_text_takes_the_pandas_path(kind, tmp_path):
+    from reportree_b200 import fastio
+    p = tmp_path / "x.tsv"
+    rows = ["FILE\tA\tB", "s1\t1\t2", "s2\t1\t3"]
+    if kind == "quote":
+        rows[1] = 's1\t"1"\t2'
+    if kind == "ragged":
+        rows[2] = "s2\t1"
+    if kind == "dup_header":
+        rows[0] = "FILE\tA\tA"
+    p.write_bytes((("\r\n" if kind == "crlf" else "\n").join(rows) + "\n").encode())
+    assert fastio.open_profile(str(p)) is None
+
+
+def test_hostio_library_exports_every_declared_symbol():
+    import re
+    from reportree_b200 import fastio
+    lib = fastio.load_library()
+    txt = open(os.path.join(os.path.dirname(G), "..", "include", "rthio.h")).read()
+    declared = sorted(set(re.findall(r"\b(rthio_[a-z0-9_]+)\s*\(", txt)))
+    assert declared == sorted(fastio.EXPORTED_SYMBOLS)
+    for name in declared:
+        getattr(lib, name)
+    assert lib.rthio_version() >= 100
+
+
+GOLD = {
+    "C1": ("allele_matrix.tsv.gz", ["--HC-threshold", "single-1-10"]),
+    "C1b": ("allele_matrix.tsv.gz", ["--HC-threshold", "single,complete,average,weighted", "--loci-called", "0.9"]),
+    "C2b": ("Listeria_alleles.tsv.gz", ["--HC-threshold", "complete-1-30,average-5", "--pct-HC-threshold", "single-0.004",
+                                         "--loci-called", "0.95", "--site-inclusion", "0.99"]),
+}
+
+
+@pytest.mark.parametrize("case", list(GOLD))
+@pytest.mark.parametrize("fast", [False, True])
+def test_cli_host_side_reproduces_reference_goldens(case, fast, tmp_path, monkeypatch, capsys):
+    inp_gz, extra = GOLD[case]
+    inp = str(tmp_path / inp_gz[:-3])
+    with gzip.open(os.path.join(G, "inputs", inp_gz), "rb") as fi, open(inp, "wb") as fo:
+        shutil.copyfileobj(fi, fo)
+    tag = str(tmp_path / case)
+    out = _run(monkeypatch, capsys, ["-a", inp, "-o", tag] + extra, fast)
+    gdir = os.path.join(G, case)
+    for f in sorted(os.listdir(gdir)):
+        if f.endswith(".gz"):
+            produced = tag + f[len(case):-3]
+            assert os.path.exists(produced), f
+            assert open(produced, "rb").read() == gzip.open(os.path.join(gdir, f), "rb").read(), f
+    gold = open(os.path.join(gdir, case + "_stdout.txt")).read().split("\n")
+    assert [l for l in out.split("\n") if str(tmp_path) not in l] == gold
