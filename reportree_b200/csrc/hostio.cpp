@@ -113,6 +113,7 @@ struct rthio_profile {
     std::vector<size_t> row_begin, row_end;     // data rows (blank lines skipped)
     std::vector<std::string> ids;               // cleaned sample ids
     std::vector<char> id_nan;
+    std::vector<char> row_plain;                // 1: the final text of every cell of the row is its raw text
     std::vector<int32_t> codes;                 // n x L
 };
 
@@ -236,6 +237,7 @@ extern "C" int rthio_profile_open(const char *path, const char *missing_code, in
         p->codes.resize((size_t)(p->n * p->L));
         p->ids.resize((size_t)p->n);
         p->id_nan.assign((size_t)p->n, 0);
+        p->row_plain.assign((size_t)p->n, 0);
     } catch (...) { rthio_profile_close(p); return fail(RTHIO_E_NOMEM, "out of host memory for %lld x %lld codes", (long long)p->n, (long long)p->L); }
     std::atomic<int> ragged(0);
     const int64_t L = p->L;
@@ -247,8 +249,9 @@ extern "C" int rthio_profile_open(const char *path, const char *missing_code, in
             // id cell
             const char *tab = (const char *)memchr(a, '\t', (size_t)(e - a));
             const char *b = tab ? tab : e;
-            if (is_na_token(a, (size_t)(b - a))) p->id_nan[(size_t)r] = 1;
-            else { Tok t = clean_token(a, (size_t)(b - a), tmp); p->ids[(size_t)r].assign(t.s, t.n); }
+            bool plain = true;
+            if (is_na_token(a, (size_t)(b - a))) { p->id_nan[(size_t)r] = 1; plain = false; }
+            else { Tok t = clean_token(a, (size_t)(b - a), tmp); p->ids[(size_t)r].assign(t.s, t.n); plain = t.s == a; }
             int64_t c = 0;
             while (tab) {
                 a = tab + 1;
@@ -264,9 +267,11 @@ extern "C" int rthio_profile_open(const char *path, const char *missing_code, in
                     if (digits) { dst[c++] = v ? v : (len == 1 ? 0 : -1); continue; }
                 }
                 Tok t = final_cell(p, a, len, tmp, &nan);
+                if (nan || t.s != a || t.n != len) plain = false;
                 dst[c++] = cell_code(t, nan);
             }
             if (c != L) ragged.store(1);
+            p->row_plain[(size_t)r] = plain ? 1 : 0;
         }
     });
     if (ragged.load()) { rthio_profile_close(p); return fail(RTHIO_IRREGULAR, "a row does not have %lld cells", (long long)(L + 1)); }
@@ -336,17 +341,25 @@ extern "C" int rthio_profile_write(const rthio_profile *p, const char *path, con
     int rc = write_all(fd, head.data(), head.size());
     const int T = p->n_threads;
     const int64_t wave = (int64_t)T * 512;
-    std::vector<std::string> outb((size_t)T);
-    for (int64_t w0 = 0; w0 < nrows && !rc; w0 += wave) {
+    const bool all_cols = ncols == p->L;
+    // two buffer sets: wave w is written by a helper thread while wave w + 1 is formatted
+    std::vector<std::string> outb[2] = {std::vector<std::string>((size_t)T), std::vector<std::string>((size_t)T)};
+    std::thread writer;
+    std::atomic<int> wrc(0);
+    int flip = 0;
+    for (int64_t w0 = 0; w0 < nrows && !rc && !wrc.load(); w0 += wave, flip ^= 1) {
         const int64_t w1 = std::min(nrows, w0 + wave);
-        for (auto &s : outb) s.clear();
+        std::vector<std::string> &set = outb[flip];
+        for (auto &s : set) s.clear();
         parallel_ranges(w1 - w0, T, [&](int t, int64_t lo, int64_t hi) {
-            std::string &ob = outb[(size_t)t];
+            std::string &ob = set[(size_t)t];
             std::string tmp;
             for (int64_t q = w0 + lo; q < w0 + hi; ++q) {
                 const int64_t r = rows[q];
-                if (!p->id_nan[(size_t)r]) ob += p->ids[(size_t)r];
                 const char *a = p->buf + p->row_begin[(size_t)r], *e = p->buf + p->row_end[(size_t)r];
+                const bool plain = p->row_plain[(size_t)r] != 0;
+                if (plain && all_cols) { ob.append(a, (size_t)(e - a)); ob.push_back('\n'); continue; }
+                if (!p->id_nan[(size_t)r]) ob += p->ids[(size_t)r];
                 const char *tab = (const char *)memchr(a, '\t', (size_t)(e - a));
                 int64_t c = 0, want = 0;
                 while (tab && want < ncols) {
@@ -354,10 +367,13 @@ extern "C" int rthio_profile_write(const rthio_profile *p, const char *path, con
                     tab = (const char *)memchr(a, '\t', (size_t)(e - a));
                     if (c == cols[want]) {
                         const char *b = tab ? tab : e;
-                        bool nan;
-                        Tok t = final_cell(p, a, (size_t)(b - a), tmp, &nan);
                         ob.push_back('\t');
-                        if (!nan) ob.append(t.s, t.n);
+                        if (plain) ob.append(a, (size_t)(b - a));
+                        else {
+                            bool nan;
+                            Tok t = final_cell(p, a, (size_t)(b - a), tmp, &nan);
+                            if (!nan) ob.append(t.s, t.n);
+                        }
                         ++want;
                     }
                     ++c;
@@ -365,9 +381,14 @@ extern "C" int rthio_profile_write(const rthio_profile *p, const char *path, con
                 ob.push_back('\n');
             }
         });
-        for (int t = 0; t < T && !rc; ++t)
-            if (!outb[(size_t)t].empty()) rc = write_all(fd, outb[(size_t)t].data(), outb[(size_t)t].size());
+        if (writer.joinable()) writer.join();
+        writer = std::thread([&set, &wrc, fd, T]() {
+            for (int t = 0; t < T; ++t)
+                if (!set[(size_t)t].empty() && write_all(fd, set[(size_t)t].data(), set[(size_t)t].size())) { wrc.store(1); return; }
+        });
     }
+    if (writer.joinable()) writer.join();
+    if (wrc.load()) rc = -1;
     if (close(fd) != 0) rc = -1;
     return rc ? fail(RTHIO_E_IO, "write to %s failed", path) : RTHIO_OK;
 }
