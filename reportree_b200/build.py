@@ -27,17 +27,33 @@ def build_hostio(force=False):
     return HOSTIO_OUT
 
 
+CGMLST_SRC = os.path.join(CSRC, "cgmlst_dists_main.cpp")
+CGMLST_OUT = os.path.join(HERE, "bin", "cgmlst-dists")
+
+
+def build_cgmlst_dists(force=False):
+    """bin/cgmlst-dists: the external program's CLI (seam B2) on top of libreportree_hc.so."""
+    deps = [CGMLST_SRC, OUT]
+    if not force and os.path.exists(CGMLST_OUT) and all(os.path.getmtime(d) <= os.path.getmtime(CGMLST_OUT) for d in deps):
+        return CGMLST_OUT
+    os.makedirs(os.path.dirname(CGMLST_OUT), exist_ok=True)
+    subprocess.check_call([CXX, "-O3", "-std=c++17", "-pthread", "-Wall", "-o", CGMLST_OUT, CGMLST_SRC,
+                           "-L" + HERE, "-lreportree_hc", "-Wl,-rpath,$ORIGIN/..", "-ldl", "-lrt"])
+    return CGMLST_OUT
+
+
 def needs_build():
     if not os.path.exists(OUT):
         return True
     t = os.path.getmtime(OUT)
-    deps = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f != "hostio.cpp"] + [os.path.join(HERE, "..", "include", "rthc.h")]
+    deps = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f not in ("hostio.cpp", "cgmlst_dists_main.cpp")] + [os.path.join(HERE, "..", "include", "rthc.h")]
     return any(os.path.getmtime(d) > t for d in deps)
 
 
 def build(force=False, verbose=False):
     build_hostio(force)
     if not force and not needs_build():
+        build_cgmlst_dists(force)
         return OUT
     objs = []
     os.makedirs(os.path.join(HERE, "build"), exist_ok=True)
@@ -55,6 +71,7 @@ def build(force=False, verbose=False):
             raise RuntimeError("nvcc failed on " + src)
     subprocess.check_call([NVCC, "-shared", "-o", OUT] + objs + ["-gencode", "arch=compute_100a,code=sm_100a",
                                                                     "-cudart", "static"])
+    build_cgmlst_dists(True)
     return OUT
 
 

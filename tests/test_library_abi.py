@@ -40,3 +40,18 @@ def test_product_package_never_imports_the_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".h")):
                 src = open(os.path.join(dirpath, f)).read()
                 assert "oracle" not in src.replace("oracle/", "").lower() or f == "partitioning_HC.py" and False, f
+
+
+def test_cgmlst_dists_binary_is_built_and_refuses_to_run_without_a_gpu(tmp_path):
+    """Seam B2 executable: present after build(); no CPU fallback (exit 1 + message) on a GPU-less host."""
+    import subprocess
+    import torch
+    exe = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "reportree_b200", "bin", "cgmlst-dists")
+    assert os.path.exists(exe)
+    p = tmp_path / "m.tsv"
+    p.write_text("FILE\ta\tb\ns1\t1\t2\ns2\t1\t3\n")
+    r = subprocess.run([exe, str(p)], capture_output=True, text=True)
+    if torch.cuda.is_available():
+        assert r.returncode == 0 and r.stdout.split("\n")[1] == "s1\t0\t1"
+    else:
+        assert r.returncode == 1 and "no CPU fallback" in r.stderr and r.stdout == ""
