@@ -60,6 +60,44 @@ class Phases:
 PH = Phases()
 
 
+class Background:
+    """Run fn(*args) on a helper thread (the C++ writers and the CUDA context set-up release the GIL);
+    join() re-raises whatever it raised."""
+
+    def __init__(self, fn, *args):
+        import threading
+        self.exc = None
+        self.result = None
+
+        def run():
+            try:
+                self.result = fn(*args)
+            except BaseException as e:          # noqa: BLE001 -- re-raised in join()
+                self.exc = e
+        self.thread = threading.Thread(target=run, daemon=True)
+        self.thread.start()
+
+    def join(self):
+        self.thread.join()
+        if self.exc is not None:
+            raise self.exc
+        return self.result
+
+
+class LazyContext:
+    """The GPU context is created on a helper thread while the profile is being read (CUDA
+    start-up is ~1.3 s); the first use waits for it.  A failure surfaces at that first use."""
+
+    def __init__(self, device):
+        self._bg = Background(lambda: hc_backend.HCContext(device=device))
+        self._ctx = None
+
+    def __getattr__(self, name):
+        if self._ctx is None:
+            self._ctx = self._bg.join()
+        return getattr(self._ctx, name)
+
+
 class Tee:
     """Every message goes to stdout and to <out>.log (scripts/partitioning_HC.py:340-348)."""
 
@@ -430,8 +468,7 @@ def profile_to_distances_fast(args, say, log, ctx, prof):
     with open(out + "_loci_used.txt", "w+") as fh:
         fh.write("".join(prof.header[c + 1] + "\n" for c in cols.tolist()))
     PH.mark("column filter")
-    prof.write(out + "_clean_missing_matrix.tsv", rows, cols)
-    PH.mark("write clean_missing_matrix")
+    writers = [Background(prof.write, out + "_clean_missing_matrix.tsv", rows, cols)]     # overlaps the row filter
 
     thr = float(args.loci_called)
     if thr >= 0.0:
@@ -449,24 +486,31 @@ def profile_to_distances_fast(args, say, log, ctx, prof):
         say("\tFrom the " + str(len(rows)) + " samples, " + str(int(passed.sum())) + " were kept in the profile matrix.")
         if int(passed.sum()) <= 1:
             say("\nCannot proceed because " + str(int(passed.sum())) + " samples were kept in the matrix!")
+            for w in writers:
+                w.join()
             _exit(log)
         # isin(passing): every row whose id equals the id of a passing row stays (duplicated ids)
         passing_ids = {prof.ids[i] for i, ok in zip(rows.tolist(), passed.tolist()) if ok}
         sel = np.fromiter((prof.ids[i] in passing_ids for i in rows.tolist()), dtype=bool, count=len(rows))
         rows, codes = rows[sel], codes[sel]
-        prof.write(out + "_flt_samples_matrix.tsv", rows, cols)
+        writers.append(Background(prof.write, out + "_flt_samples_matrix.tsv", rows, cols))   # overlaps the GPU stages
     else:
         codes = prof.gather(rows, cols)
-    PH.mark("row filter + flt_samples")
+    PH.mark("row filter")
 
     say("Getting the pairwise distance matrix with cgmlst-dists (if your profile matrix is too big, this will be done in chunks of 2000 alleles/positions)...")
     total_size = len(cols)
     names = ["" if prof.ids[i] is None else prof.ids[i] for i in rows.tolist()]
-    prof.close()
     PH.mark("encode cells")
-    ctx.set_profiles(np.ascontiguousarray(codes))
-    ctx.distance()
-    PH.mark("GPU recode + distance")
+    try:
+        ctx.set_profiles(np.ascontiguousarray(codes))
+        ctx.distance()
+        PH.mark("GPU context + recode + distance")
+    finally:
+        for w in writers:
+            w.join()
+        prof.close()
+    PH.mark("wait for matrix artefacts")
     if os.environ.get("REPORTREE_HC_SKIP_DIST_TSV", "0") != "1":
         write_dist_tsv(out + "_dist_hamming.tsv", names, ctx)
         PH.mark("write dist_hamming.tsv")
@@ -526,8 +570,7 @@ def main(argv=None):
         _exit(log)
 
     PH.__init__()
-    ctx = hc_backend.HCContext(device=int(os.environ.get("REPORTREE_HC_DEVICE", "0")))
-    PH.mark("create GPU context")
+    ctx = LazyContext(int(os.environ.get("REPORTREE_HC_DEVICE", "0")))
     exact = os.environ.get("REPORTREE_HC_EXACT_NAMES", "1") != "0"
     ctx.set_single_algo(hc_backend.SL_PRIM if exact else hc_backend.SL_BORUVKA)
 
