@@ -69,6 +69,14 @@ int rthc_version(void);
  *      Default rank 0 / world 1 = everything.  Call before rthc_set_profiles_i32. */
 int rthc_set_shard(rthc_ctx *ctx, int rank, int world);
 
+/* single-process multi-device (the reference spawns ONE partitioning_HC.py process, reportree.py:1796):
+ * the context computes only the tiles of shard rank/world but stores them in the FULL condensed
+ * vector; rthc_import_shard copies another context's owned rows (any device of the box, peer copy)
+ * into it, rthc_finish_import turns it into an ordinary full shard (linkage, cut, row copies).  */
+int rthc_set_shard_full_storage(rthc_ctx *ctx, int rank, int world);
+int rthc_import_shard(rthc_ctx *dst, rthc_ctx *src);
+int rthc_finish_import(rthc_ctx *ctx);
+
 /* ---- distance half ----------------------------------------------------------
  * codes: n x L row-major int32 allele codes, 0 (or negative) = missing.
  * Copies H2D, dense-ranks every locus on the device (uint16, 0 = missing) and packs

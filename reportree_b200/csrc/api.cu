@@ -133,12 +133,66 @@ extern "C" void rthc_destroy(rthc_ctx *ctx)
     delete ctx;
 }
 
+// tile-row r of B is owned by rank (min(r, B-1-r) mod world): rows pair up long + short
+static inline int owner_of_tile_row(int64_t r, int64_t B, int world)
+{
+    int64_t p = std::min(r, B - 1 - r);
+    return (int)(p % world);
+}
+
 extern "C" int rthc_set_shard(rthc_ctx *ctx, int rank, int world)
 {
     if (!ctx) return RTHC_E_ARG;
     if (world < 1 || rank < 0 || rank >= world) return rthc_fail(ctx, RTHC_E_ARG, "bad shard %d/%d", rank, world);
     ctx->rank = rank;
     ctx->world = world;
+    ctx->full_storage = false;
+    return 0;
+}
+
+// ---- single-process multi-device (the CLI is ONE process, SURVEY 8b seam B0) -------------------
+extern "C" int rthc_set_shard_full_storage(rthc_ctx *ctx, int rank, int world)
+{
+    int rc = rthc_set_shard(ctx, rank, world);
+    if (rc) return rc;
+    ctx->full_storage = true;
+    return 0;
+}
+
+extern "C" int rthc_import_shard(rthc_ctx *dst, rthc_ctx *src)
+{
+    if (!dst || !src) return rthc_fail(dst, RTHC_E_ARG, "rthc_import_shard: NULL argument");
+    if (!dst->full_storage || !dst->have_dist) return rthc_fail(dst, RTHC_E_STATE, "destination needs full storage and its own distances");
+    if (!src->have_dist || !src->d_cond || src->n != dst->n || src->full_storage)
+        return rthc_fail(dst, RTHC_E_STATE, "source shard has no distances of the same matrix");
+    RTHC_CUDA(dst, cudaSetDevice(dst->device));
+    const int64_t n = dst->n, B = dst->n_tiles_edge;
+    for (int64_t r = 0; r < B; ++r) {
+        if (owner_of_tile_row(r, B, src->world) != src->rank) continue;
+        const int64_t i0 = r * RTHC_TILE, i1 = std::min(n, (r + 1) * RTHC_TILE);
+        int64_t len = 0;
+        for (int64_t i = i0; i < i1; ++i) len += n - 1 - i;
+        if (len == 0) continue;
+        RTHC_CUDA(dst, cudaMemcpyPeerAsync(dst->d_cond + dst->h_row_base[(size_t)i0], dst->device,
+                                           src->d_cond + src->h_row_base[(size_t)i0], src->device,
+                                           sizeof(uint16_t) * (size_t)len, dst->stream));
+    }
+    RTHC_CUDA(dst, cudaStreamSynchronize(dst->stream));
+    return 0;
+}
+
+extern "C" int rthc_finish_import(rthc_ctx *ctx)
+{
+    if (!ctx || !ctx->full_storage || !ctx->have_dist) return rthc_fail(ctx, RTHC_E_STATE, "rthc_finish_import: nothing to finish");
+    RTHC_CUDA(ctx, cudaSetDevice(ctx->device));
+    ctx->rank = 0; ctx->world = 1; ctx->full_storage = false;      // from here on: an ordinary full shard
+    ctx->h_owned_rows.resize((size_t)ctx->n);
+    for (int64_t i = 0; i < ctx->n; ++i) ctx->h_owned_rows[(size_t)i] = (int32_t)i;
+    int rc = rthc_dev_alloc(ctx, &ctx->d_owned_rows, (size_t)ctx->n);
+    if (rc) return rc;
+    RTHC_CUDA(ctx, cudaMemcpyAsync(ctx->d_owned_rows, ctx->h_owned_rows.data(), sizeof(int32_t) * (size_t)ctx->n,
+                                   cudaMemcpyHostToDevice, ctx->stream));
+    RTHC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     return 0;
 }
 
@@ -150,12 +204,6 @@ extern "C" int rthc_set_single_algo(rthc_ctx *ctx, int algo)
     return 0;
 }
 
-// tile-row r of B is owned by rank (min(r, B-1-r) mod world): rows pair up long + short
-static inline int owner_of_tile_row(int64_t r, int64_t B, int world)
-{
-    int64_t p = std::min(r, B - 1 - r);
-    return (int)(p % world);
-}
 
 // geometry of the owned part of the condensed matrix + the tile list
 static int setup_geometry(rthc_ctx *ctx, int64_t n)
@@ -170,12 +218,13 @@ static int setup_geometry(rthc_ctx *ctx, int64_t n)
     std::vector<int64_t> owned_tile_rows;
     int64_t off = 0;
     for (int64_t r = 0; r < B; ++r) {
-        if (owner_of_tile_row(r, B, ctx->world) != ctx->rank) continue;
-        owned_tile_rows.push_back(r);
+        const bool owned = owner_of_tile_row(r, B, ctx->world) == ctx->rank;
+        if (owned) owned_tile_rows.push_back(r);
+        if (!owned && !ctx->full_storage) continue;
         for (int64_t i = r * RTHC_TILE; i < std::min(n, (r + 1) * RTHC_TILE); ++i) {
-            ctx->h_row_base[(size_t)i] = off;
+            ctx->h_row_base[(size_t)i] = off;          // full storage: the global scipy offset of row i
             off += n - 1 - i;
-            ctx->h_owned_rows.push_back((int32_t)i);
+            if (owned) ctx->h_owned_rows.push_back((int32_t)i);
         }
     }
     ctx->owned_pairs = off;

@@ -31,6 +31,7 @@ struct rthc_ctx {
 
     // shard
     int rank = 0, world = 1;
+    bool full_storage = false;     // sharded tiles, but d_cond is the FULL condensed vector (single-process multi-device)
     int dist_nj = 2;               // 64-sample column blocks per distance tile (1: 128x64, 2: 128x128)
 
     // problem

@@ -45,6 +45,9 @@ def load_library():
         "rthc_last_error": (ctypes.c_char_p, [vp]),
         "rthc_version": (ci, []),
         "rthc_set_shard": (ci, [vp, ci, ci]),
+        "rthc_set_shard_full_storage": (ci, [vp, ci, ci]),
+        "rthc_import_shard": (ci, [vp, vp]),
+        "rthc_finish_import": (ci, [vp]),
         "rthc_set_profiles_i32": (ci, [vp, vp, i64, i64]),
         "rthc_set_profiles_i32_device": (ci, [vp, vp, i64, i64]),
         "rthc_distance": (ci, [vp]),
@@ -76,6 +79,7 @@ def load_library():
 
 EXPORTED_SYMBOLS = [
     "rthc_create", "rthc_destroy", "rthc_last_error", "rthc_version", "rthc_set_shard",
+    "rthc_set_shard_full_storage", "rthc_import_shard", "rthc_finish_import",
     "rthc_set_profiles_i32", "rthc_set_profiles_i32_device", "rthc_distance", "rthc_owned_pairs",
     "rthc_get_condensed_u16", "rthc_get_owned_condensed_u16", "rthc_copy_rows_u16", "rthc_direct_pairs",
     "rthc_set_condensed_f64", "rthc_set_single_algo", "rthc_linkage", "rthc_local_forest",
@@ -91,7 +95,7 @@ def _ptr(a):
 class HCContext:
     """One device context (one GPU).  Not thread-safe; calls are synchronous."""
 
-    def __init__(self, device=0, rank=0, world=1):
+    def __init__(self, device=0, rank=0, world=1, full_storage=False):
         self._L = load_library()
         h = ctypes.c_void_p()
         rc = self._L.rthc_create(ctypes.byref(h), int(device))
@@ -100,7 +104,9 @@ class HCContext:
         self._h = h
         self.n = 0
         self.L = 0
-        if world != 1:
+        if full_storage:
+            self._check(self._L.rthc_set_shard_full_storage(self._h, int(rank), int(world)))
+        elif world != 1:
             self._check(self._L.rthc_set_shard(self._h, int(rank), int(world)))
         self.rank, self.world = rank, world
 
@@ -140,6 +146,14 @@ class HCContext:
 
     def distance(self):
         self._check(self._L.rthc_distance(self._h))
+
+    def import_shard(self, other):
+        """Copy another context's owned rows (same matrix, any device) into this full-storage context."""
+        self._check(self._L.rthc_import_shard(self._h, other._h))
+
+    def finish_import(self):
+        self._check(self._L.rthc_finish_import(self._h))
+        self.rank, self.world = 0, 1
 
     def owned_pairs(self):
         return int(self._L.rthc_owned_pairs(self._h))
@@ -239,3 +253,68 @@ class HCContext:
         v = ctypes.c_double(0)
         self._check(self._L.rthc_alu_peak_block(self._h, int(warps_per_sm), ctypes.byref(v)))
         return v.value
+
+
+class MultiDeviceContext:
+    """One process, several GPUs (SURVEY.md 8b seam B0: reportree.py spawns exactly one
+    partitioning_HC.py): the distance tiles are sharded over `devices` (one context and one host
+    thread per device, tile-rows paired long + short), the shards are copied device-to-device into
+    the full condensed matrix of devices[0], and everything after the distance stage (any linkage,
+    cut, row blocks for the TSV writer) runs there exactly as on one GPU."""
+
+    def __init__(self, devices):
+        if len(devices) < 2:
+            raise HCBackendError("MultiDeviceContext needs at least two devices")
+        w = len(devices)
+        self._ctx = [HCContext(device=devices[0], rank=0, world=w, full_storage=True)]
+        self._ctx += [HCContext(device=d, rank=k, world=w) for k, d in enumerate(devices) if k > 0]
+        self._algo = None
+
+    def _each(self, fn):
+        import threading
+        errs = []
+
+        def run(c):
+            try:
+                fn(c)
+            except BaseException as e:      # noqa: BLE001 -- re-raised below
+                errs.append(e)
+        th = [threading.Thread(target=run, args=(c,)) for c in self._ctx]
+        for t in th:
+            t.start()
+        for t in th:
+            t.join()
+        if errs:
+            raise errs[0]
+
+    def set_profiles(self, codes):
+        codes = np.ascontiguousarray(codes, dtype=np.int32)
+        self._each(lambda c: c.set_profiles(codes))
+
+    def distance(self):
+        self._each(lambda c: c.distance())
+        head = self._ctx[0]
+        for c in self._ctx[1:]:
+            head.import_shard(c)
+            c.close()
+        head.finish_import()
+        self._ctx = [head]
+
+    def set_condensed(self, y):
+        for c in self._ctx[1:]:
+            c.close()
+        self._ctx = self._ctx[:1]
+        self._ctx[0].set_condensed(y)
+
+    def close(self):
+        for c in self._ctx:
+            c.close()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    def __getattr__(self, name):            # linkage, fcluster, square_rows, condensed, info, ... of the full context
+        return getattr(self._ctx[0], name)

@@ -12,6 +12,8 @@ the GPU through reportree_b200.hc_backend.  There is no CPU fallback for that la
 
 Environment switches (argv stays frozen so reportree.py can call this unchanged):
   REPORTREE_HC_DEVICE=<int>          CUDA device (default 0)
+  REPORTREE_HC_DEVICES=0,1,..        several GPUs from this ONE process: distance tiles sharded, shards
+                                     copied device-to-device into the first GPU, which does the rest
   REPORTREE_HC_EXACT_NAMES=0|1       1 (default): scipy-order Prim, cluster_<id> names and Newick
                                      byte-identical to scipy; 0: Boruvka MST (same membership)
   REPORTREE_HC_SKIP_DIST_TSV=1       do not write <out>_dist_hamming.tsv (benchmark runs)
@@ -88,8 +90,11 @@ class LazyContext:
     """The GPU context is created on a helper thread while the profile is being read (CUDA
     start-up is ~1.3 s); the first use waits for it.  A failure surfaces at that first use."""
 
-    def __init__(self, device):
-        self._bg = Background(lambda: hc_backend.HCContext(device=device))
+    def __init__(self, device, devices=None):
+        if devices and len(devices) > 1:
+            self._bg = Background(lambda: hc_backend.MultiDeviceContext(devices))
+        else:
+            self._bg = Background(lambda: hc_backend.HCContext(device=device))
         self._ctx = None
 
     def __getattr__(self, name):
@@ -570,7 +575,8 @@ def main(argv=None):
         _exit(log)
 
     PH.__init__()
-    ctx = LazyContext(int(os.environ.get("REPORTREE_HC_DEVICE", "0")))
+    devices = [int(d) for d in os.environ.get("REPORTREE_HC_DEVICES", "").split(",") if d.strip() != ""]
+    ctx = LazyContext(int(os.environ.get("REPORTREE_HC_DEVICE", "0")), devices)
     exact = os.environ.get("REPORTREE_HC_EXACT_NAMES", "1") != "0"
     ctx.set_single_algo(hc_backend.SL_PRIM if exact else hc_backend.SL_BORUVKA)
 
