@@ -191,25 +191,41 @@ def run_ours(args):
     ctx = hc.HCContext(device=local, rank=rank, world=world)
     state = {"dist_ms": [], "link_ms": [], "cut_ms": [], "recode_ms": [], "h2d_ms": [], "d2h_bytes": 0}
 
+    seg = {}
+
+    def lap(name, t0):
+        t1 = time.perf_counter()
+        seg.setdefault(name, []).append(1e3 * (t1 - t0))
+        return t1
+
     def step(resident):
+        t = time.perf_counter()
         if resident:
             ctx.set_profiles_device(dX.data_ptr(), n, L)
         else:
             ctx.set_profiles(host_codes)
+        t = lap("set_profiles", t)
         ctx.distance()
+        t = lap("distance", t)
         d2h = 0
         if world == 1:
             Z = ctx.linkage("single")
+            t = lap("linkage", t)
             labels = ctx.fcluster(thr)
+            t = lap("cut", t)
             d2h = Z.nbytes + labels.nbytes + (n - 1) * 8
         else:
             keys = ctx.local_forest()
+            t = lap("local_forest", t)
             allk = sharded.all_gather_forests(keys, n, dist, device="cuda")     # the one NCCL exchange
+            t = lap("all_gather", t)
             d2h = keys.nbytes
             labels = None
             if rank == 0:
                 Z = ctx.linkage_from_forest(allk, n)
+                t = lap("final_merge", t)
                 labels = ctx.fcluster(thr)
+                t = lap("cut", t)
                 d2h += allk.nbytes + Z.nbytes + labels.nbytes
         tm = ctx.timings()
         state["dist_ms"].append(tm["distance_ms"]); state["link_ms"].append(tm["linkage_ms"])
@@ -229,6 +245,7 @@ def run_ours(args):
         for k in state:
             if isinstance(state[k], list):
                 state[k].clear()
+        seg.clear()
         l0 = ctx.timings()["launches"]
         sync()
         ctx.mark(0)                       # CUDA events on the library's own stream
@@ -257,6 +274,7 @@ def run_ours(args):
     dt, launches, labels = timed(True, args.steps, args.warmup)
     kern = {k: float(np.mean(v)) for k, v in state.items() if isinstance(v, list) and v}
     kern_steps = {k: [round(float(x), 3) for x in v] for k, v in state.items() if isinstance(v, list) and v}
+    host_seg = {k: round(float(np.mean(v)), 3) for k, v in seg.items()}
     info = ctx.info()
     owned_pairs = ctx.owned_pairs()
     clocks = sampler.stop() if rank == 0 else None
@@ -309,6 +327,7 @@ def run_ours(args):
                        "sharding": "tile-rows of the upper triangle over %d rank(s)" % world},
             "stage_ms": kern,
             "stage_ms_per_step": kern_steps,
+            "host_wall_ms_rank0": host_seg,
             "e2e_stage_ms_per_step": {k: [round(float(x), 3) for x in v] for k, v in state.items() if isinstance(v, list) and v},
             "roofline": roofline,
             "e2e": {"value": e2e_value, "unit": "comparisons/s", "ms_per_step": 1e3 * dt_e2e / args.steps,

@@ -111,8 +111,8 @@ static void free_distance_state(rthc_ctx *ctx)
 }
 static void free_linkage_state(rthc_ctx *ctx)
 {
-    rthc_dev_free(ctx, &ctx->d_ea); rthc_dev_free(ctx, &ctx->d_eb); rthc_dev_free(ctx, &ctx->d_eh);
-    rthc_dev_free(ctx, &ctx->d_epre); rthc_dev_free(ctx, &ctx->d_eleaf);
+    rthc_dev_free(ctx, &ctx->d_tpar); rthc_dev_free(ctx, &ctx->d_event); rthc_dev_free(ctx, &ctx->d_up);
+    ctx->up_levels = 0;
     ctx->have_linkage = false;
 }
 

@@ -1,86 +1,60 @@
-// cut.cu -- multi-threshold cut with a lock-free union-find on the device.
+// cut.cu -- multi-threshold cut of the dendrogram, all thresholds in one batch.
 //
 // Replaces scipy's `_hierarchy.cluster_dist` behind fcluster(Z, t, criterion="distance")
 // (scripts/partitioning_HC.py:649, :689, :722, :751; scipy _hierarchy_impl.py:2589-2590).
 //
-// Input (uploaded by rthc_linkage): the n-1 merges of the dendrogram in Z order (sorted by
-// height) as (leaf representative a_k, leaf representative b_k, height h_k), plus the
-// position of every dendrogram node in scipy's numbering traversal:
-//     epre[k]  : when internal node k is first visited (where a leader takes its id)
-//     eleaf[v] : when leaf v is numbered (at its parent's final visit, left before right)
-// For a monotone dendrogram the flat clusters at cutoff t are the connected components of
-// merges {k : h_k <= t}; the leader of a component is its last merge.  Thresholds are
-// swept in ascending order, so every merge is united exactly once (atomicCAS hooking,
-// path halving); a cluster's id is the rank of its leader/leaf event among the events of
-// that threshold, which reproduces scipy's fcluster numbering exactly.
+// Input (uploaded by rthc_linkage): the dendrogram as a parent array over its 2n-1 nodes
+// (leaves 0..n-1, merge k = node n+k, merges sorted by height) and the position of every node in
+// scipy's numbering walk (`event`).  For a monotone dendrogram the flat clusters at cutoff t are
+// the subtrees of the merges {k : h_k <= t} = {k < K(t)}; ancestors have increasing ids, so the
+// leader of leaf v is its highest ancestor with id < n + K(t), found by binary lifting in
+// O(log n) independent of every other (threshold, leaf) pair.  A leaf whose parent is already
+// beyond the cutoff is its own cluster.  scipy numbers clusters in the order its walk meets the
+// leader (or the lone leaf), so the id of a cluster is the rank of its leader's event among the
+// events present at that threshold: a flag array per threshold + an inclusive scan.
+// Everything is batched over thresholds (grid.y): ~25 launches per call instead of 7 per threshold.
 #include <algorithm>
 #include <numeric>
 
 #include "rthc_internal.cuh"
 
-__device__ __forceinline__ int32_t uf_find(int32_t *parent, int32_t v)
-{
-    int32_t p = parent[v];
-    while (p != v) {
-        int32_t gp = parent[p];
-        if (gp != p) parent[v] = gp;   // path halving (benign race)
-        v = p;
-        p = gp;
-        if (p == v) break;
-        p = parent[v];
-    }
-    return v;
-}
-
-__global__ void rthc_cut_init(int32_t *parent, int32_t *last, int64_t n)
-{
-    int64_t v = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (v < n) { parent[v] = (int32_t)v; last[v] = -1; }
-}
-
-__global__ void rthc_cut_union(int32_t *parent, const int32_t *__restrict__ ea,
-                               const int32_t *__restrict__ eb, int64_t k0, int64_t k1)
-{
-    int64_t k = k0 + (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (k >= k1) return;
-    int32_t a = ea[k], b = eb[k];
-    for (;;) {
-        a = uf_find(parent, a);
-        b = uf_find(parent, b);
-        if (a == b) return;
-        if (a < b) { int32_t t = a; a = b; b = t; }          // hook larger root under smaller
-        if (atomicCAS(&parent[a], a, b) == a) return;
-    }
-}
-
-__global__ void rthc_cut_last(int32_t *parent, int32_t *last, const int32_t *__restrict__ ea,
-                              int64_t k0, int64_t k1)
-{
-    int64_t k = k0 + (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (k >= k1) return;
-    atomicMax(&last[uf_find(parent, ea[k])], (int32_t)k);
-}
-
-__global__ void rthc_cut_keys(int32_t *parent, const int32_t *__restrict__ last,
-                              const int32_t *__restrict__ epre, const int32_t *__restrict__ eleaf,
-                              int32_t *__restrict__ key, int32_t *__restrict__ flags, int64_t n)
-{
-    int64_t v = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (v >= n) return;
-    const int32_t r = uf_find(parent, (int32_t)v);
-    const int32_t lk = last[r];
-    const int32_t e = lk < 0 ? eleaf[v] : epre[lk];
-    key[v] = e;
-    flags[e] = 1;
-}
-
-// inclusive scan of flags[0..m) (m = 2n - 1): every CTA scans 4,096 entries in place and
-// publishes its total; one CTA then turns the totals into exclusive offsets, which the label
-// kernel adds back.  (A single-CTA scan of the whole array was 85 % of the cut stage.)
 #define CUT_SCAN_ELEMS 4096
-__global__ void __launch_bounds__(1024) rthc_cut_scan_blocks(int32_t *flags, int64_t m, int32_t *aux)
+#define CUT_ROOT_PARENT 0x7FFFFFFF
+
+__global__ void rthc_cut_lift(const int32_t *__restrict__ prev, int32_t *__restrict__ next, int64_t nodes)
+{
+    const int64_t x = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (x >= nodes) return;
+    const int32_t p = prev[x];
+    next[x] = p == CUT_ROOT_PARENT ? CUT_ROOT_PARENT : prev[p];
+}
+
+// key[t][v] = event of the leader of leaf v at threshold t; flags[t][event] = 1
+__global__ void rthc_cut_leaders(const int32_t *__restrict__ up, int levels, int64_t nodes, int64_t n,
+                                 const int32_t *__restrict__ limit, const int32_t *__restrict__ event,
+                                 int32_t *__restrict__ key, int32_t *__restrict__ flags, int64_t flag_stride)
+{
+    const int64_t v = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int t = blockIdx.y;
+    if (v >= n) return;
+    const int32_t lim = limit[t];                  // n + K(t): first node id that is NOT merged at this cutoff
+    int32_t x = (int32_t)v;
+    for (int j = levels - 1; j >= 0; --j) {
+        const int32_t a = up[(int64_t)j * nodes + x];
+        if (a < lim) x = a;
+    }
+    const int32_t e = event[x];
+    key[(int64_t)t * n + v] = e;
+    flags[(int64_t)t * flag_stride + e] = 1;
+}
+
+// inclusive scan of flags[t][0..m): every CTA scans 4,096 entries in place and publishes its total
+__global__ void __launch_bounds__(1024) rthc_cut_scan_blocks(int32_t *flags_all, int64_t m, int64_t flag_stride,
+                                                             int32_t *aux_all, int nb)
 {
     __shared__ int32_t wsum[32];
+    int32_t *flags = flags_all + (int64_t)blockIdx.y * flag_stride;
+    int32_t *aux = aux_all + (int64_t)blockIdx.y * nb;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int64_t idx = (int64_t)blockIdx.x * CUT_SCAN_ELEMS + 4 * tid;
     int4 v = make_int4(0, 0, 0, 0);
@@ -120,11 +94,12 @@ __global__ void __launch_bounds__(1024) rthc_cut_scan_blocks(int32_t *flags, int
     }
 }
 
-// exclusive scan of the per-CTA totals in place (one CTA; nb is a few hundred)
-__global__ void __launch_bounds__(1024) rthc_cut_scan_aux(int32_t *aux, int nb)
+// exclusive scan of the per-CTA totals of threshold blockIdx.x, in place
+__global__ void __launch_bounds__(1024) rthc_cut_scan_aux(int32_t *aux_all, int nb)
 {
     __shared__ int32_t wsum[32];
     __shared__ int32_t carry;
+    int32_t *aux = aux_all + (int64_t)blockIdx.x * nb;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     if (tid == 0) carry = 0;
     __syncthreads();
@@ -158,87 +133,80 @@ __global__ void __launch_bounds__(1024) rthc_cut_scan_aux(int32_t *aux, int nb)
     }
 }
 
-__global__ void rthc_cut_labels(const int32_t *__restrict__ key, const int32_t *__restrict__ scanned,
-                                const int32_t *__restrict__ aux, int32_t *__restrict__ labels, int64_t n)
+__global__ void rthc_cut_labels(const int32_t *__restrict__ key, const int32_t *__restrict__ scanned, int64_t flag_stride,
+                                const int32_t *__restrict__ aux, int nb, int32_t *__restrict__ labels, int64_t n)
 {
-    int64_t v = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (v < n) {
-        const int32_t e = key[v];
-        labels[v] = scanned[e] + aux[e / CUT_SCAN_ELEMS];
+    const int64_t v = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int t = blockIdx.y;
+    if (v >= n) return;
+    const int32_t e = key[(int64_t)t * n + v];
+    labels[(int64_t)t * n + v] = scanned[(int64_t)t * flag_stride + e] + aux[(int64_t)t * nb + e / CUT_SCAN_ELEMS];
+}
+
+static int build_lifting_table(rthc_ctx *ctx)
+{
+    const int64_t nodes = 2 * ctx->n - 1;
+    int levels = 1;
+    while (((int64_t)1 << levels) < nodes) ++levels;          // 2^levels >= any root path length
+    int rc = rthc_dev_alloc(ctx, &ctx->d_up, (size_t)levels * (size_t)nodes);
+    if (rc) return rc;
+    RTHC_CUDA(ctx, cudaMemcpyAsync(ctx->d_up, ctx->d_tpar, sizeof(int32_t) * (size_t)nodes, cudaMemcpyDeviceToDevice, ctx->stream));
+    const unsigned nb = (unsigned)((nodes + 255) / 256);
+    for (int j = 1; j < levels; ++j) {
+        rthc_cut_lift<<<nb, 256, 0, ctx->stream>>>(ctx->d_up + (size_t)(j - 1) * nodes, ctx->d_up + (size_t)j * nodes, nodes);
+        RTHC_LAUNCH_CHECK(ctx);
     }
+    ctx->up_levels = levels;
+    return 0;
 }
 
 int rthc_run_cut(rthc_ctx *ctx, const double *t, int T, int32_t *labels_out)
 {
-    const int64_t n = ctx->n, m = ctx->m_edges;
+    const int64_t n = ctx->n, m = ctx->m_edges, nodes = 2 * n - 1;
     if (T <= 0) return 0;
-    std::vector<int> order((size_t)T);
-    std::iota(order.begin(), order.end(), 0);
-    std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return t[a] < t[b]; });
-
-    int32_t *d_parent = nullptr, *d_last = nullptr, *d_key = nullptr, *d_flags = nullptr, *d_labels = nullptr, *d_aux = nullptr;
-    int rc;
-    if ((rc = rthc_dev_alloc(ctx, &d_parent, (size_t)n))) return rc;
-    if ((rc = rthc_dev_alloc(ctx, &d_last, (size_t)n))) return rc;
-    if ((rc = rthc_dev_alloc(ctx, &d_key, (size_t)n))) return rc;
-    if ((rc = rthc_dev_alloc(ctx, &d_flags, (size_t)(2 * n + 4)))) return rc;
-    const int scan_blocks = (int)((2 * n - 1 + CUT_SCAN_ELEMS - 1) / CUT_SCAN_ELEMS);
-    if ((rc = rthc_dev_alloc(ctx, &d_aux, (size_t)scan_blocks))) return rc;
-    // labels are produced in chunks of thresholds to bound device memory
-    const int64_t chunkT = std::max<int64_t>(1, std::min<int64_t>(T, (int64_t)(1ll << 28) / std::max<int64_t>(n, 1)));
-    if ((rc = rthc_dev_alloc(ctx, &d_labels, (size_t)(chunkT * n)))) return rc;
-
-    const unsigned nb = (unsigned)((n + 255) / 256);
     RTHC_CUDA(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
-    rthc_cut_init<<<nb, 256, 0, ctx->stream>>>(d_parent, d_last, n);
-    RTHC_LAUNCH_CHECK(ctx);
-    int64_t kprev = 0;
-    int64_t in_chunk = 0, chunk_start = 0;
-    auto flush = [&]() -> int {
-        // thresholds order[chunk_start .. chunk_start + in_chunk) are in d_labels rows 0..in_chunk
-        RTHC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-        for (int64_t q = 0; q < in_chunk; ++q) {
-            int dst = order[(size_t)(chunk_start + q)];
-            RTHC_CUDA(ctx, cudaMemcpyAsync(labels_out + (int64_t)dst * n, d_labels + q * n,
-                                           sizeof(int32_t) * (size_t)n, cudaMemcpyDeviceToHost, ctx->stream));
-        }
-        RTHC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-        chunk_start += in_chunk;
-        in_chunk = 0;
-        return 0;
-    };
+    int rc;
+    if (!ctx->d_up && (rc = build_lifting_table(ctx))) return rc;
+    // merges with height <= cutoff (same float64 comparison as scipy's MD <= cutoff)
+    std::vector<int32_t> limit((size_t)T);
     for (int q = 0; q < T; ++q) {
-        const double cutoff = t[order[(size_t)q]];
-        // merges with height <= cutoff (same float64 comparison as scipy's MD <= cutoff)
-        int64_t knew = (int64_t)(std::upper_bound(ctx->h_heights.begin(), ctx->h_heights.end(), cutoff) -
-                                 ctx->h_heights.begin());
-        if (knew > m) knew = m;
-        if (knew > kprev) {
-            const unsigned eb = (unsigned)((knew - kprev + 255) / 256);
-            rthc_cut_union<<<eb, 256, 0, ctx->stream>>>(d_parent, ctx->d_ea, ctx->d_eb, kprev, knew);
-            RTHC_LAUNCH_CHECK(ctx);
-            rthc_cut_last<<<eb, 256, 0, ctx->stream>>>(d_parent, d_last, ctx->d_ea, kprev, knew);
-            RTHC_LAUNCH_CHECK(ctx);
-            kprev = knew;
-        }
-        RTHC_CUDA(ctx, cudaMemsetAsync(d_flags, 0, sizeof(int32_t) * (size_t)(2 * n), ctx->stream));
-        rthc_cut_keys<<<nb, 256, 0, ctx->stream>>>(d_parent, d_last, ctx->d_epre, ctx->d_eleaf, d_key, d_flags, n);
-        RTHC_LAUNCH_CHECK(ctx);
-        rthc_cut_scan_blocks<<<scan_blocks, 1024, 0, ctx->stream>>>(d_flags, 2 * n - 1, d_aux);
-        RTHC_LAUNCH_CHECK(ctx);
-        rthc_cut_scan_aux<<<1, 1024, 0, ctx->stream>>>(d_aux, scan_blocks);
-        RTHC_LAUNCH_CHECK(ctx);
-        rthc_cut_labels<<<nb, 256, 0, ctx->stream>>>(d_key, d_flags, d_aux, d_labels + in_chunk * n, n);
-        RTHC_LAUNCH_CHECK(ctx);
-        if (++in_chunk == chunkT)
-            if ((rc = flush())) return rc;
+        int64_t K = (int64_t)(std::upper_bound(ctx->h_heights.begin(), ctx->h_heights.end(), t[q]) - ctx->h_heights.begin());
+        if (K > m) K = m;
+        limit[(size_t)q] = (int32_t)(n + K);
     }
-    RTHC_CUDA(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
-    if ((rc = flush())) return rc;
+    // thresholds are processed in chunks that bound device memory (labels + keys + flags)
+    const int64_t chunkT = std::max<int64_t>(1, std::min<int64_t>(T, (int64_t)(1ll << 27) / std::max<int64_t>(n, 1)));
+    const int64_t flag_stride = (nodes + 3) / 4 * 4;
+    const int nbs = (int)((nodes + CUT_SCAN_ELEMS - 1) / CUT_SCAN_ELEMS);
+    int32_t *d_limit = nullptr, *d_key = nullptr, *d_flags = nullptr, *d_labels = nullptr, *d_aux = nullptr;
+    if ((rc = rthc_dev_alloc(ctx, &d_limit, (size_t)T))) return rc;
+    if ((rc = rthc_dev_alloc(ctx, &d_key, (size_t)(chunkT * n)))) return rc;
+    if ((rc = rthc_dev_alloc(ctx, &d_labels, (size_t)(chunkT * n)))) return rc;
+    if ((rc = rthc_dev_alloc(ctx, &d_flags, (size_t)(chunkT * flag_stride)))) return rc;
+    if ((rc = rthc_dev_alloc(ctx, &d_aux, (size_t)(chunkT * nbs)))) return rc;
+    RTHC_CUDA(ctx, cudaMemcpyAsync(d_limit, limit.data(), sizeof(int32_t) * (size_t)T, cudaMemcpyHostToDevice, ctx->stream));
+    const unsigned nb = (unsigned)((n + 255) / 256);
+    for (int64_t q0 = 0; q0 < T; q0 += chunkT) {
+        const int64_t tc = std::min<int64_t>(chunkT, T - q0);
+        RTHC_CUDA(ctx, cudaMemsetAsync(d_flags, 0, sizeof(int32_t) * (size_t)(tc * flag_stride), ctx->stream));
+        rthc_cut_leaders<<<dim3(nb, (unsigned)tc), 256, 0, ctx->stream>>>(ctx->d_up, ctx->up_levels, nodes, n, d_limit + q0,
+                                                                          ctx->d_event, d_key, d_flags, flag_stride);
+        RTHC_LAUNCH_CHECK(ctx);
+        rthc_cut_scan_blocks<<<dim3((unsigned)nbs, (unsigned)tc), 1024, 0, ctx->stream>>>(d_flags, nodes, flag_stride, d_aux, nbs);
+        RTHC_LAUNCH_CHECK(ctx);
+        rthc_cut_scan_aux<<<(unsigned)tc, 1024, 0, ctx->stream>>>(d_aux, nbs);
+        RTHC_LAUNCH_CHECK(ctx);
+        rthc_cut_labels<<<dim3(nb, (unsigned)tc), 256, 0, ctx->stream>>>(d_key, d_flags, flag_stride, d_aux, nbs, d_labels, n);
+        RTHC_LAUNCH_CHECK(ctx);
+        if (q0 + tc >= T) RTHC_CUDA(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
+        RTHC_CUDA(ctx, cudaMemcpyAsync(labels_out + q0 * n, d_labels, sizeof(int32_t) * (size_t)(tc * n), cudaMemcpyDeviceToHost,
+                                       ctx->stream));
+        RTHC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    }
     float ms = 0;
     RTHC_CUDA(ctx, cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1));
     ctx->t_ms[4] = ms;
-    rthc_dev_free(ctx, &d_parent); rthc_dev_free(ctx, &d_last); rthc_dev_free(ctx, &d_key);
-    rthc_dev_free(ctx, &d_flags); rthc_dev_free(ctx, &d_labels); rthc_dev_free(ctx, &d_aux);
+    rthc_dev_free(ctx, &d_limit); rthc_dev_free(ctx, &d_key); rthc_dev_free(ctx, &d_flags);
+    rthc_dev_free(ctx, &d_labels); rthc_dev_free(ctx, &d_aux);
     return 0;
 }

@@ -18,9 +18,7 @@ static int finish_linkage(rthc_ctx *ctx, int64_t n, const std::vector<int32_t> &
     const int64_t m = n - 1;
     if ((int64_t)ex.size() != m)
         return rthc_fail(ctx, RTHC_E_STATE, "linkage produced %zu merges, expected %lld", ex.size(), (long long)m);
-    std::vector<int32_t> parent((size_t)(2 * n), -1), size((size_t)(2 * n), 1), rep((size_t)(2 * n));
-    for (int64_t v = 0; v < n; ++v) rep[(size_t)v] = (int32_t)v;
-    std::vector<int32_t> ea((size_t)m), eb((size_t)m);
+    std::vector<int32_t> parent((size_t)(2 * n), -1), size((size_t)(2 * n), 1), tpar((size_t)(2 * n), 0x7FFFFFFF);
     auto find = [&](int32_t v) {
         int32_t r = v;
         while (parent[(size_t)r] != -1) r = parent[(size_t)r];
@@ -35,41 +33,34 @@ static int finish_linkage(rthc_ctx *ctx, int64_t n, const std::vector<int32_t> &
         Z[4 * k + 0] = rx; Z[4 * k + 1] = ry; Z[4 * k + 2] = ew[(size_t)k];
         size[(size_t)id] = size[(size_t)rx] + size[(size_t)ry];
         Z[4 * k + 3] = size[(size_t)id];
-        ea[(size_t)k] = rep[(size_t)rx];
-        eb[(size_t)k] = rep[(size_t)ry];
-        rep[(size_t)id] = rep[(size_t)rx];
-        parent[(size_t)rx] = id;
-        parent[(size_t)ry] = id;
+        parent[(size_t)rx] = id; parent[(size_t)ry] = id;      // union-find (gets path-compressed)
+        tpar[(size_t)rx] = id; tpar[(size_t)ry] = id;          // the dendrogram itself
     }
-    // traversal positions of scipy's cluster_monocrit walk (independent of the cutoff)
-    std::vector<int32_t> epre((size_t)m, -1), eleaf((size_t)n, -1), stack((size_t)n);
-    std::vector<char> pushed((size_t)(2 * n), 0);
-    int32_t ev = 0;
-    int64_t k = 0;
-    stack[0] = (int32_t)(2 * n - 2);
-    while (k >= 0) {
-        const int32_t root = stack[(size_t)k] - (int32_t)n;
-        const int32_t lc = (int32_t)Z[4 * root], rc = (int32_t)Z[4 * root + 1];
-        if (epre[(size_t)root] < 0) epre[(size_t)root] = ev++;
-        if (lc >= n && !pushed[(size_t)lc]) { pushed[(size_t)lc] = 1; stack[(size_t)++k] = lc; continue; }
-        if (rc >= n && !pushed[(size_t)rc]) { pushed[(size_t)rc] = 1; stack[(size_t)++k] = rc; continue; }
-        if (lc < n) eleaf[(size_t)lc] = ev++;
-        if (rc < n) eleaf[(size_t)rc] = ev++;
-        --k;
+    // Position of every node in scipy's numbering walk (cluster_dist / cluster_monocrit): a node is
+    // numbered when first visited, then its left and right internal subtrees, then its leaf
+    // children (left before right).  A subtree of s leaves holds 2 s - 1 events, so the positions
+    // follow top-down (parents have larger ids than children): no stack, no recursion.
+    std::vector<int32_t> event((size_t)(2 * n - 1), 0);
+    event[(size_t)(2 * n - 2)] = 0;
+    for (int64_t k = m - 1; k >= 0; --k) {
+        const int32_t lc = (int32_t)Z[4 * k], rc = (int32_t)Z[4 * k + 1];
+        int32_t cursor = event[(size_t)(n + k)] + 1;
+        if (lc >= n) { event[(size_t)lc] = cursor; cursor += 2 * size[(size_t)lc] - 1; }
+        if (rc >= n) { event[(size_t)rc] = cursor; cursor += 2 * size[(size_t)rc] - 1; }
+        if (lc < n) event[(size_t)lc] = cursor++;
+        if (rc < n) event[(size_t)rc] = cursor++;
     }
     ctx->h_heights = ew;
     for (int64_t q = 1; q < m; ++q)
         if (ctx->h_heights[(size_t)q] < ctx->h_heights[(size_t)q - 1])
             return rthc_fail(ctx, RTHC_E_STATE, "merge heights are not monotone at row %lld", (long long)q);
     int rcode;
-    if ((rcode = rthc_dev_alloc(ctx, &ctx->d_ea, (size_t)m))) return rcode;
-    if ((rcode = rthc_dev_alloc(ctx, &ctx->d_eb, (size_t)m))) return rcode;
-    if ((rcode = rthc_dev_alloc(ctx, &ctx->d_epre, (size_t)m))) return rcode;
-    if ((rcode = rthc_dev_alloc(ctx, &ctx->d_eleaf, (size_t)n))) return rcode;
-    RTHC_CUDA(ctx, cudaMemcpyAsync(ctx->d_ea, ea.data(), sizeof(int32_t) * (size_t)m, cudaMemcpyHostToDevice, ctx->stream));
-    RTHC_CUDA(ctx, cudaMemcpyAsync(ctx->d_eb, eb.data(), sizeof(int32_t) * (size_t)m, cudaMemcpyHostToDevice, ctx->stream));
-    RTHC_CUDA(ctx, cudaMemcpyAsync(ctx->d_epre, epre.data(), sizeof(int32_t) * (size_t)m, cudaMemcpyHostToDevice, ctx->stream));
-    RTHC_CUDA(ctx, cudaMemcpyAsync(ctx->d_eleaf, eleaf.data(), sizeof(int32_t) * (size_t)n, cudaMemcpyHostToDevice, ctx->stream));
+    if ((rcode = rthc_dev_alloc(ctx, &ctx->d_tpar, (size_t)(2 * n - 1)))) return rcode;
+    if ((rcode = rthc_dev_alloc(ctx, &ctx->d_event, (size_t)(2 * n - 1)))) return rcode;
+    rthc_dev_free(ctx, &ctx->d_up);
+    ctx->up_levels = 0;
+    RTHC_CUDA(ctx, cudaMemcpyAsync(ctx->d_tpar, tpar.data(), sizeof(int32_t) * (size_t)(2 * n - 1), cudaMemcpyHostToDevice, ctx->stream));
+    RTHC_CUDA(ctx, cudaMemcpyAsync(ctx->d_event, event.data(), sizeof(int32_t) * (size_t)(2 * n - 1), cudaMemcpyHostToDevice, ctx->stream));
     RTHC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     ctx->m_edges = m;
     ctx->n = n;
@@ -111,7 +102,7 @@ extern "C" int rthc_linkage(rthc_ctx *ctx, int method, double *Z_out)
         return rthc_fail(ctx, RTHC_E_STATE, "rthc_linkage needs a full shard; use rthc_local_forest + "
                                             "rthc_linkage_from_forest for sharded single linkage");
     RTHC_CUDA(ctx, cudaSetDevice(ctx->device));
-    rthc_dev_free(ctx, &ctx->d_ea); rthc_dev_free(ctx, &ctx->d_eb); rthc_dev_free(ctx, &ctx->d_epre); rthc_dev_free(ctx, &ctx->d_eleaf);
+    rthc_dev_free(ctx, &ctx->d_tpar); rthc_dev_free(ctx, &ctx->d_event); rthc_dev_free(ctx, &ctx->d_up);
     ctx->have_linkage = false;
     int rc;
     RTHC_CUDA(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
@@ -166,7 +157,7 @@ extern "C" int rthc_linkage_from_forest(rthc_ctx *ctx, const uint64_t *keys, int
     if (!ctx || !keys || !Z_out) return rthc_fail(ctx, RTHC_E_ARG, "NULL argument");
     if (n < 2 || m < n - 1) return rthc_fail(ctx, RTHC_E_ARG, "forest union has %lld edges for n=%lld", (long long)m, (long long)n);
     RTHC_CUDA(ctx, cudaSetDevice(ctx->device));
-    rthc_dev_free(ctx, &ctx->d_ea); rthc_dev_free(ctx, &ctx->d_eb); rthc_dev_free(ctx, &ctx->d_epre); rthc_dev_free(ctx, &ctx->d_eleaf);
+    rthc_dev_free(ctx, &ctx->d_tpar); rthc_dev_free(ctx, &ctx->d_event); rthc_dev_free(ctx, &ctx->d_up);
     ctx->have_linkage = false;
     std::vector<uint64_t> mst;
     int rc = rthc_boruvka_edge_list(ctx, keys, m, n, mst);

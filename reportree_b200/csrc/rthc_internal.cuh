@@ -66,9 +66,10 @@ struct rthc_ctx {
     // clustering state
     int single_algo = RTHC_SL_BORUVKA;
     int64_t m_edges = 0;           // n - 1 after a successful linkage
-    int32_t *d_ea = nullptr, *d_eb = nullptr;   // leaf representatives of merge k (sorted order)
-    double *d_eh = nullptr;                      // height of merge k
-    int32_t *d_epre = nullptr, *d_eleaf = nullptr;
+    int32_t *d_tpar = nullptr;     // [2n-1] dendrogram parent of every node (leaves 0..n-1, merge k = n+k), root: INT_MAX
+    int32_t *d_event = nullptr;    // [2n-1] position of every node in scipy's fcluster numbering walk
+    int32_t *d_up = nullptr;       // [levels][2n-1] binary-lifting table over d_tpar (built by the first cut)
+    int up_levels = 0;
     std::vector<double> h_heights;
     bool have_linkage = false;
     int boruvka_rounds = 0;
