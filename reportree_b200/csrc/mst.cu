@@ -205,9 +205,10 @@ __device__ __forceinline__ void scan_tile_body(const uint16_t *__restrict__ cond
 
 __global__ void __launch_bounds__(256)
 rthc_boruvka_scan_tile(const uint16_t *__restrict__ cond, const int64_t *__restrict__ row_base, int64_t n,
-                       const int32_t *__restrict__ comp, uint64_t *best)
+                       const int32_t *__restrict__ comp, uint64_t *best, const int32_t *__restrict__ bands)
 {
-    const int64_t r0 = (int64_t)blockIdx.y * TS_ROWS, c0 = (int64_t)blockIdx.x * TS_COLS;
+    // bands: the 64-row bands that hold rows of this shard (a sharded context owns 1/world of them)
+    const int64_t r0 = (int64_t)bands[blockIdx.y] * TS_ROWS, c0 = (int64_t)blockIdx.x * TS_COLS;
     if (c0 + TS_COLS - 1 <= r0) return;                     // no column j > i in this tile
     __shared__ int64_t s_off[TS_ROWS];
     __shared__ int32_t s_ci[TS_ROWS];
@@ -413,10 +414,18 @@ int rthc_boruvka_owned(rthc_ctx *ctx, std::vector<uint64_t> &keys)
     const int64_t n = ctx->n;
     const int64_t n_owned = (int64_t)ctx->h_owned_rows.size();
     static const bool two_pass = getenv("RTHC_BORUVKA_TWO_PASS") != nullptr;     // A/B switch (older kernels)
+    std::vector<int32_t> bands;
+    for (int32_t i : ctx->h_owned_rows)
+        if (bands.empty() || bands.back() != i / TS_ROWS) bands.push_back(i / TS_ROWS);      // rows are ascending
+    int32_t *d_bands = nullptr;
+    int rcb = rthc_dev_alloc(ctx, &d_bands, bands.size());
+    if (rcb) return rcb;
+    if (!bands.empty())
+        RTHC_CUDA(ctx, cudaMemcpyAsync(d_bands, bands.data(), sizeof(int32_t) * bands.size(), cudaMemcpyHostToDevice, ctx->stream));
     auto scan = [&](int32_t *d_comp, uint64_t *d_best) -> int {
         if (n_owned > 0 && !two_pass) {
-            dim3 grd((unsigned)((n + TS_COLS - 1) / TS_COLS), (unsigned)((n + TS_ROWS - 1) / TS_ROWS));
-            rthc_boruvka_scan_tile<<<grd, 256, 0, ctx->stream>>>(ctx->d_cond, ctx->d_row_base, n, d_comp, d_best);
+            dim3 grd((unsigned)((n + TS_COLS - 1) / TS_COLS), (unsigned)bands.size());
+            rthc_boruvka_scan_tile<<<grd, 256, 0, ctx->stream>>>(ctx->d_cond, ctx->d_row_base, n, d_comp, d_best, d_bands);
             RTHC_LAUNCH_CHECK(ctx);
         } else if (n_owned > 0) {
             rthc_boruvka_scan<<<(unsigned)n_owned, SCAN_THREADS, 0, ctx->stream>>>(
@@ -428,7 +437,9 @@ int rthc_boruvka_owned(rthc_ctx *ctx, std::vector<uint64_t> &keys)
         }
         return 0;
     };
-    return boruvka_rounds(ctx, n, scan, keys);
+    const int rc = boruvka_rounds(ctx, n, scan, keys);
+    rthc_dev_free(ctx, &d_bands);
+    return rc;
 }
 
 int rthc_boruvka_edge_list(rthc_ctx *ctx, const uint64_t *h_keys, int64_t m, int64_t n,
