@@ -72,6 +72,11 @@ int rthio_write_partitions(const char *path_partitions, const char *path_composi
                            const int64_t *names_offs, int64_t n, const int32_t *labels, int64_t T,
                            const char *col_blob, const int64_t *col_offs, int n_threads);
 
+/* ---- synthetic inputs (bench / tests): n x L int32 matrix -> profile TSV with header
+ * <corner>\t<col_prefix>00001.. and ids <row_prefix>0000001..                                   */
+int rthio_write_int_matrix(const char *path, const char *corner, const char *row_prefix, const char *col_prefix,
+                           const int32_t *codes, int64_t n, int64_t L, int n_threads);
+
 #ifdef __cplusplus
 }
 #endif

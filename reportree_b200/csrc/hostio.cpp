@@ -598,3 +598,50 @@ extern "C" int rthio_write_partitions(const char *path_partitions, const char *p
     if (close(fdp) != 0) rc = -1;
     return rc ? fail(RTHIO_E_IO, "write to %s failed", path_partitions) : RTHIO_OK;
 }
+
+// ---------------------------------------------------------------------------------------------
+// synthetic-input helper: an int32 allele matrix as a profile TSV (bench / test inputs)
+// ---------------------------------------------------------------------------------------------
+extern "C" int rthio_write_int_matrix(const char *path, const char *corner, const char *row_prefix, const char *col_prefix,
+                                      const int32_t *codes, int64_t n, int64_t L, int n_threads)
+{
+    if (!path || !corner || !row_prefix || !col_prefix || !codes || n < 0 || L < 0) return fail(RTHIO_E_ARG, "rthio_write_int_matrix: bad argument");
+    const int T = pick_threads(n_threads);
+    const int fd = open(path, O_WRONLY | O_CREAT | O_TRUNC, 0644);
+    if (fd < 0) return fail(RTHIO_E_IO, "cannot create %s", path);
+    std::string head = corner;
+    char num[32];
+    for (int64_t c = 0; c < L; ++c) { snprintf(num, sizeof num, "\t%s%05lld", col_prefix, (long long)(c + 1)); head += num; }
+    head.push_back('\n');
+    int rc = write_all(fd, head.data(), head.size());
+    const int64_t wave = (int64_t)T * 256;
+    std::vector<std::vector<char>> ob((size_t)T);
+    std::vector<size_t> used((size_t)T);
+    const size_t plen = strlen(row_prefix);
+    for (int64_t r0 = 0; r0 < n && !rc; r0 += wave) {
+        const int64_t r1 = std::min(n, r0 + wave);
+        std::fill(used.begin(), used.end(), 0);
+        parallel_ranges(r1 - r0, T, [&](int t, int64_t lo, int64_t hi) {
+            const size_t cap = (size_t)(hi - lo) * (plen + 16 + (size_t)L * 12);
+            if (ob[(size_t)t].size() < cap) ob[(size_t)t].resize(cap);
+            char *o = ob[(size_t)t].data();
+            for (int64_t r = r0 + lo; r < r0 + hi; ++r) {
+                memcpy(o, row_prefix, plen); o += plen;
+                o += snprintf(o, 16, "%07lld", (long long)(r + 1));
+                const int32_t *src = codes + (size_t)(r * L);
+                for (int64_t c = 0; c < L; ++c) {
+                    *o++ = '\t';
+                    const int32_t v = src[c];
+                    if (v < 0) { *o++ = '-'; o = put_u32(o, (uint32_t)(-(int64_t)v)); }
+                    else o = put_u32(o, (uint32_t)v);
+                }
+                *o++ = '\n';
+            }
+            used[(size_t)t] = (size_t)(o - ob[(size_t)t].data());
+        });
+        for (int t = 0; t < T && !rc; ++t)
+            if (used[(size_t)t]) rc = write_all(fd, ob[(size_t)t].data(), used[(size_t)t]);
+    }
+    if (close(fd) != 0) rc = -1;
+    return rc ? fail(RTHIO_E_IO, "write to %s failed", path) : RTHIO_OK;
+}

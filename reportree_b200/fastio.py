@@ -18,7 +18,7 @@ EXPORTED_SYMBOLS = [
     "rthio_last_error", "rthio_version", "rthio_profile_open", "rthio_profile_close", "rthio_profile_rows",
     "rthio_profile_cols", "rthio_profile_header", "rthio_profile_sample", "rthio_profile_codes",
     "rthio_profile_gather", "rthio_profile_write", "rthio_square_open", "rthio_square_append_u16",
-    "rthio_square_close", "rthio_write_partitions",
+    "rthio_square_close", "rthio_write_partitions", "rthio_write_int_matrix",
 ]
 _lib = None
 
@@ -56,6 +56,7 @@ def load_library():
         "rthio_square_append_u16": (ci, [vp, i64, i64, vp]),
         "rthio_square_close": (ci, [vp]),
         "rthio_write_partitions": (ci, [cp, cp, vp, vp, i64, vp, i64, vp, vp, ci]),
+        "rthio_write_int_matrix": (ci, [cp, cp, cp, cp, vp, i64, i64, ci]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(L, name)
@@ -181,4 +182,14 @@ def write_partitions(path_partitions, path_composition, names, labels, partition
     cb, co = _blob(partition_names)
     if L.rthio_write_partitions(os.fsencode(path_partitions), os.fsencode(path_composition), nb, _ptr(no), n,
                                 _ptr(labels), T, cb, _ptr(co), int(threads)) != 0:
+        raise FastIOError(_err(L))
+
+
+def write_int_matrix(path, codes, corner="FILE", row_prefix="S", col_prefix="L", threads=0):
+    """Synthetic profile TSV from an int32 matrix (ids S0000001.., loci L00001..)."""
+    L = load_library()
+    codes = np.ascontiguousarray(codes, dtype=np.int32)
+    n, nl = codes.shape
+    if L.rthio_write_int_matrix(os.fsencode(path), corner.encode(), row_prefix.encode(), col_prefix.encode(), _ptr(codes), n, nl,
+                                int(threads)) != 0:
         raise FastIOError(_err(L))

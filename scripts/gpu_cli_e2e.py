@@ -17,16 +17,22 @@ work = os.environ.get("E2E_DIR", "/tmp/rthc_e2e"); os.makedirs(work, exist_ok=Tr
 tsv = os.path.join(work, "%s.tsv" % what)
 t0 = time.perf_counter()
 if not os.path.exists(tsv):
-    with open(tsv, "w") as fh:
-        fh.write("FILE\t" + "\t".join("L%05d" % (k + 1) for k in range(L)) + "\n")
-        for r0 in range(0, n, 2000):
-            S = X[r0:r0 + 2000].astype("U7")
-            fh.write("".join("S%07d\t" % (r0 + i + 1) + "\t".join(S[i].tolist()) + "\n" for i in range(S.shape[0])))
+    from reportree_b200 import fastio
+    fastio.write_int_matrix(tsv, X)
 print("TSV %s: %d x %d, %.1f MB, written in %.1f s" % (tsv, n, L, os.path.getsize(tsv) / 1e6, time.perf_counter() - t0), flush=True)
 env = dict(os.environ, REPORTREE_HC_TIMING="1", PYTHONPATH=ROOT)
 if "--skip-dist" in sys.argv:
     env["REPORTREE_HC_SKIP_DIST_TSV"] = "1"
 args = extra or ["--HC-threshold", "single-1-50"]
+if what == "C3" and not extra:
+    args = ["--HC-threshold", "single-1-50,average-1-50"]                  # configs[2]: single + average
+if what == "C5" and not extra:                                             # configs[4]: --loci subset + --loci-called 0.95, complete
+    loci = os.path.join(work, "C5_loci.txt")
+    rng = np.random.default_rng(1)
+    cols = rng.permutation(L)[:3000]
+    with open(loci, "w") as fh:
+        fh.write("".join("L%05d\n" % (c + 1) for c in cols))
+    args = ["--HC-threshold", "complete-1-50", "-l", loci, "--loci-called", "0.95"]
 t0 = time.perf_counter()
 rc = subprocess.call([sys.executable, "-m", "reportree_b200.partitioning_HC", "-a", tsv, "-o", os.path.join(work, what)] + args,
                      env=env, stdout=subprocess.DEVNULL)
