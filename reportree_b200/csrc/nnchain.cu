@@ -241,6 +241,8 @@ rthc_nn_chain_kernel(T *W, int64_t n, int method, int32_t *size, int32_t *chain,
         unsigned long long bw = ~0ull;
         unsigned int bi = ~0u;
         const T *row = W + (int64_t)x * n;
+        // D[x, prev] is needed right after the reduction: request it with the row, not after it
+        const unsigned long long dprev = len > 1 ? order_bits(__ldcg(&row[prev])) : ~0ull;
         for (int64_t i = gtid; i < n; i += gthreads) {
             if (i == x || i == dead || __ldcg(&size[i]) == 0) continue;
             const unsigned long long d = order_bits(__ldcg(&row[i]));
@@ -256,10 +258,7 @@ rthc_nn_chain_kernel(T *W, int64_t n, int method, int32_t *size, int32_t *chain,
         grid_min(cur, nblocks, bw, bi, sh);
         int32_t y = (int32_t)bi;
         unsigned long long dmin = bw;
-        if (len > 1) {
-            const unsigned long long dprev = order_bits(__ldcg(&row[prev]));
-            if (dprev <= dmin) { y = prev; dmin = dprev; }       // previous chain element wins ties
-        }
+        if (len > 1 && dprev <= dmin) { y = prev; dmin = dprev; }  // previous chain element wins ties
         if (!(len > 1 && y == prev)) {
             // ---- extend the chain ---------------------------------------------------------------
             if (leader) chain[len] = y;
