@@ -75,3 +75,21 @@ def test_forest_union_equals_single_gpu(hc, oracle):
             lab = ctx.fcluster([0.0, 1.0, 2.0, 3.0])
         for k, t in enumerate([0.0, 1.0, 2.0, 3.0]):
             assert np.array_equal(lab[k], fcluster(Zfull, t, criterion="distance"))
+
+
+def test_event_marks_and_stage_timings(hc):
+    """rthc_mark / rthc_mark_elapsed_ms (bench.py's device-side step clock) and rthc_timings."""
+    from reportree_b200 import synth
+    X = synth.allele_matrix(1500, 200, 3)
+    with hc.HCContext() as ctx:
+        ctx.mark(0)
+        ctx.set_profiles(X)
+        ctx.distance()
+        ctx.linkage("single")
+        ctx.fcluster([1.0, 2.0])
+        ctx.mark(1)
+        total = ctx.mark_elapsed_ms()
+        tm = ctx.timings()
+        assert total > 0
+        assert 0 < tm["distance_ms"] < total and 0 < tm["linkage_ms"] < total and tm["launches"] > 5
+        assert tm["recode_ms"] + tm["distance_ms"] + tm["linkage_ms"] + tm["cut_ms"] <= total * 1.05
