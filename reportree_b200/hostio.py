@@ -10,7 +10,7 @@ reference's per-cell pandas / pure-Python loops; outputs are byte-identical).
 import string
 
 import numpy as np
-import pandas
+from reportree_b200.lazy_pandas import pandas
 
 _LETTERS = {c: i + 1 for i, c in enumerate(string.ascii_lowercase + string.ascii_uppercase)}
 

@@ -24,7 +24,7 @@ import sys
 import textwrap
 
 import numpy as np
-import pandas
+from reportree_b200.lazy_pandas import pandas
 
 from reportree_b200 import hc_backend
 from reportree_b200 import hostio
@@ -563,6 +563,8 @@ def matrix_to_distances(args, say, log, ctx):
 
 
 def main(argv=None):
+    from reportree_b200 import lazy_pandas
+    lazy_pandas.preload()                         # ~1 s of import, hidden behind the profile parse
     args = build_parser().parse_args(argv)
     log = Tee(args.out + ".log")
     say = log
