@@ -121,6 +121,21 @@ int rthc_linkage_from_forest(rthc_ctx *ctx, const uint64_t *keys, int64_t m, int
 /* labels_out: T x n int32, row k = fcluster(Z, t[k], "distance") of the last linkage. */
 int rthc_cut(rthc_ctx *ctx, const double *t, int T, int32_t *labels_out);
 
+/* ---- zoom-in on the resident matrix ----------------------------- */
+/* Replaces get_closest_samples (reportree.py:591-617), which re-reads one column of
+ * <out>_dist_hamming.tsv per sample of interest: every sample j with
+ * d(sample, j) <= d_sorted[k], where d_sorted is the ascending row of `sample` including its own 0
+ * (the reference's `max_dist = distances[int(n)]`).  out_idx / out_dist need room for n entries
+ * (ties can select any number), filled in no particular order; *out_count = how many.           */
+int rthc_closest(rthc_ctx *ctx, int64_t sample, int64_t k, int64_t *out_idx, uint16_t *out_dist,
+                 int64_t *out_count, int *out_max_dist);
+/* Replaces the distance half of a zoom-in re-run (reportree.py:1965-2055 re-invokes
+ * partitioning_HC.py with --loci <out>_loci_used.txt on the subset, cgmlst-dists included):
+ * `child` (same device, created by rthc_create) receives the m x m sub-matrix of `parent`'s resident
+ * distances for the samples idx[0..m) (distinct) and is then ready for rthc_linkage / rthc_cut /
+ * rthc_copy_rows_u16.                                                                            */
+int rthc_subset_from(rthc_ctx *child, rthc_ctx *parent, const int64_t *idx, int64_t m);
+
 /* ---- introspection ----------------------------------------------------------- */
 /* info[0]=n, [1]=L, [2]=loci kept, [3]=groups of 32 loci, [4]=plane rows,
  * [5]=tiles launched, [6]=Boruvka rounds of the last linkage, [7]=max alleles/locus,

@@ -100,7 +100,7 @@ extern "C" int rthc_mark_elapsed_ms(rthc_ctx *ctx, double *ms)
     return 0;
 }
 
-static void free_distance_state(rthc_ctx *ctx)
+void rthc_free_distance_state(rthc_ctx *ctx)
 {
     rthc_dev_free(ctx, &ctx->d_codes); rthc_dev_free(ctx, &ctx->d_planes);
     rthc_dev_free(ctx, &ctx->d_grp_off); rthc_dev_free(ctx, &ctx->d_grp_np);
@@ -109,7 +109,7 @@ static void free_distance_state(rthc_ctx *ctx)
     rthc_dev_free(ctx, &ctx->d_cond_f64);
     ctx->have_profiles = ctx->have_dist = false;
 }
-static void free_linkage_state(rthc_ctx *ctx)
+void rthc_free_linkage_state(rthc_ctx *ctx)
 {
     rthc_dev_free(ctx, &ctx->d_tpar); rthc_dev_free(ctx, &ctx->d_event); rthc_dev_free(ctx, &ctx->d_up);
     ctx->up_levels = 0;
@@ -120,9 +120,9 @@ extern "C" void rthc_destroy(rthc_ctx *ctx)
 {
     if (!ctx) return;
     cudaSetDevice(ctx->device);
-    free_distance_state(ctx);
+    rthc_free_distance_state(ctx);
     rthc_dev_free(ctx, &ctx->d_cond);
-    free_linkage_state(ctx);
+    rthc_free_linkage_state(ctx);
     if (ctx->ev0) cudaEventDestroy(ctx->ev0);
     if (ctx->ev1) cudaEventDestroy(ctx->ev1);
     for (int k = 0; k < 2; ++k)
@@ -206,7 +206,7 @@ extern "C" int rthc_set_single_algo(rthc_ctx *ctx, int algo)
 
 
 // geometry of the owned part of the condensed matrix + the tile list
-static int setup_geometry(rthc_ctx *ctx, int64_t n)
+int rthc_setup_geometry(rthc_ctx *ctx, int64_t n)
 {
     ctx->n = n;
     if (const char *e = getenv("RTHC_DIST_NJ")) ctx->dist_nj = atoi(e) == 1 ? 1 : 2;
@@ -261,7 +261,7 @@ static int set_profiles_common(rthc_ctx *ctx, const int32_t *d_rowmajor, int64_t
 {
     int rc;
     ctx->L = L;
-    if ((rc = setup_geometry(ctx, n))) return rc;
+    if ((rc = rthc_setup_geometry(ctx, n))) return rc;
     RTHC_CUDA(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
     if ((rc = rthc_recode_and_pack(ctx, d_rowmajor))) return rc;
     RTHC_CUDA(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
@@ -288,8 +288,8 @@ extern "C" int rthc_set_profiles_i32(rthc_ctx *ctx, const int32_t *codes, int64_
     int rc = check_shape(ctx, n, L);
     if (rc) return rc;
     RTHC_CUDA(ctx, cudaSetDevice(ctx->device));
-    free_distance_state(ctx);
-    free_linkage_state(ctx);
+    rthc_free_distance_state(ctx);
+    rthc_free_linkage_state(ctx);
     int32_t *d_in = nullptr;
     if ((rc = rthc_dev_alloc(ctx, &d_in, (size_t)(n * L)))) return rc;
     RTHC_CUDA(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
@@ -311,8 +311,8 @@ extern "C" int rthc_set_profiles_i32_device(rthc_ctx *ctx, const void *dev_codes
     int rc = check_shape(ctx, n, L);
     if (rc) return rc;
     RTHC_CUDA(ctx, cudaSetDevice(ctx->device));
-    free_distance_state(ctx);
-    free_linkage_state(ctx);
+    rthc_free_distance_state(ctx);
+    rthc_free_linkage_state(ctx);
     ctx->t_ms[0] = 0;
     RTHC_CUDA(ctx, cudaDeviceSynchronize());   // the caller's producer stream is unknown
     return set_profiles_common(ctx, (const int32_t *)dev_codes, n, L);
@@ -444,11 +444,11 @@ extern "C" int rthc_set_condensed_f64(rthc_ctx *ctx, const double *y, int64_t n)
     if (n < 2) return rthc_fail(ctx, RTHC_E_ARG, "need at least 2 samples (n=%lld)", (long long)n);
     if (n >= (1ll << 24)) return rthc_fail(ctx, RTHC_E_RANGE, "n=%lld exceeds 2^24-1 samples", (long long)n);
     RTHC_CUDA(ctx, cudaSetDevice(ctx->device));
-    free_distance_state(ctx);
-    free_linkage_state(ctx);
+    rthc_free_distance_state(ctx);
+    rthc_free_linkage_state(ctx);
     const int save_rank = ctx->rank, save_world = ctx->world;
     ctx->rank = 0; ctx->world = 1;                              // an external matrix is always a full shard
-    int rc = setup_geometry(ctx, n);
+    int rc = rthc_setup_geometry(ctx, n);
     ctx->rank = save_rank; ctx->world = save_world;
     if (rc) return rc;
     ctx->world = 1; ctx->rank = 0;

@@ -128,6 +128,11 @@ template <typename T> inline int rthc_dev_alloc(rthc_ctx *ctx, T **p, size_t cou
     return 0;
 }
 
+// context state helpers (api.cu)
+void rthc_free_distance_state(rthc_ctx *ctx);
+void rthc_free_linkage_state(rthc_ctx *ctx);
+int rthc_setup_geometry(rthc_ctx *ctx, int64_t n);
+
 // stage entry points implemented in the other translation units
 int rthc_recode_and_pack(rthc_ctx *ctx, const int32_t *d_rowmajor);   // recode.cu
 int rthc_run_distance(rthc_ctx *ctx);                                 // distance.cu

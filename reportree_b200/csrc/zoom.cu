@@ -1,0 +1,174 @@
+// zoom.cu -- SURVEY 8(f) N3: zoom-in / subtree queries on the RESIDENT distance matrix.
+//
+// The reference answers both questions from text: get_closest_samples (reportree.py:591-617)
+// re-reads one column of <out>_dist_hamming.tsv per sample of interest, and the zoom-in loop
+// (reportree.py:1965-2055) re-runs the whole HC script (cgmlst-dists included) on the subset with
+// `--loci <out>_loci_used.txt`.  With the same loci the distance of a pair does not depend on the
+// other samples, so the subset's matrix is a sub-matrix of the one already in HBM:
+//
+//   rthc_closest      one row of the condensed matrix -> value at sorted position k (65,536-bin
+//                     histogram) -> every sample with d <= that value
+//   rthc_subset_from  gather of the m(m-1)/2 sub-matrix into a child context that then runs
+//                     rthc_linkage / rthc_cut as usual
+#include <algorithm>
+
+#include "rthc_internal.cuh"
+
+__device__ __forceinline__ int64_t cond_index(int64_t n, int64_t i, int64_t j)
+{
+    const int64_t a = i < j ? i : j, b = i < j ? j : i;
+    return n * a - (a * (a + 1)) / 2 + (b - a - 1);
+}
+
+// ---- closest samples ---------------------------------------------------------------------------
+__global__ void rthc_zoom_row_hist(const uint16_t *__restrict__ cond, int64_t n, int64_t s, uint16_t *__restrict__ row,
+                                   unsigned int *__restrict__ hist)
+{
+    const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n) return;
+    const uint16_t v = j == s ? (uint16_t)0 : cond[cond_index(n, s, j)];
+    row[j] = v;
+    atomicAdd(&hist[v], 1u);
+}
+
+// one CTA of 1024 threads: smallest v with #(d <= v) > k  (= the value at 0-based sorted position k)
+__global__ void rthc_zoom_kth(const unsigned int *__restrict__ hist, int64_t k, int *__restrict__ out_v,
+                              unsigned int *__restrict__ out_count)
+{
+    __shared__ unsigned int part[1024];
+    const int t = threadIdx.x;
+    unsigned int s = 0;
+    for (int b = 0; b < 64; ++b) s += hist[t * 64 + b];
+    part[t] = s;
+    __syncthreads();
+    for (int off = 1; off < 1024; off <<= 1) {                // inclusive scan of the 1024 partial sums
+        unsigned int v = t >= off ? part[t - off] : 0u;
+        __syncthreads();
+        part[t] += v;
+        __syncthreads();
+    }
+    const unsigned int before = t ? part[t - 1] : 0u;
+    if ((int64_t)before <= k && (int64_t)part[t] > k) {       // exactly one thread
+        unsigned int c = before;
+        for (int b = 0; b < 64; ++b) {
+            c += hist[t * 64 + b];
+            if ((int64_t)c > k) { *out_v = t * 64 + b; *out_count = c; break; }
+        }
+    }
+}
+
+__global__ void rthc_zoom_select(const uint16_t *__restrict__ row, int64_t n, const int *__restrict__ vmax,
+                                 int64_t *__restrict__ out_idx, uint16_t *__restrict__ out_d, unsigned int *cursor)
+{
+    const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n) return;
+    const uint16_t v = row[j];
+    if ((int)v <= *vmax) {
+        const unsigned int p = atomicAdd(cursor, 1u);
+        out_idx[p] = j;
+        out_d[p] = v;
+    }
+}
+
+extern "C" int rthc_closest(rthc_ctx *ctx, int64_t sample, int64_t k, int64_t *out_idx, uint16_t *out_dist,
+                            int64_t *out_count, int *out_max_dist)
+{
+    if (!ctx || !out_idx || !out_dist || !out_count) return rthc_fail(ctx, RTHC_E_ARG, "rthc_closest: NULL argument");
+    if (!ctx->have_dist || !ctx->d_cond) return rthc_fail(ctx, RTHC_E_STATE, "rthc_closest needs a resident uint16 distance matrix");
+    if (ctx->world != 1) return rthc_fail(ctx, RTHC_E_STATE, "rthc_closest needs a full shard");
+    const int64_t n = ctx->n;
+    if (sample < 0 || sample >= n || k < 0 || k >= n) return rthc_fail(ctx, RTHC_E_ARG, "rthc_closest: sample / k out of range");
+    RTHC_CUDA(ctx, cudaSetDevice(ctx->device));
+    uint16_t *d_row = nullptr, *d_od = nullptr;
+    unsigned int *d_hist = nullptr;      // 65536 bins + [65536] count<=v + [65537] cursor
+    int *d_v = nullptr;
+    int64_t *d_oi = nullptr;
+    int rc;
+    if ((rc = rthc_dev_alloc(ctx, &d_row, (size_t)n))) return rc;
+    if ((rc = rthc_dev_alloc(ctx, &d_od, (size_t)n))) return rc;
+    if ((rc = rthc_dev_alloc(ctx, &d_oi, (size_t)n))) return rc;
+    if ((rc = rthc_dev_alloc(ctx, &d_hist, (size_t)65536 + 2))) return rc;
+    if ((rc = rthc_dev_alloc(ctx, &d_v, 1))) return rc;
+    RTHC_CUDA(ctx, cudaMemsetAsync(d_hist, 0, sizeof(unsigned int) * (65536 + 2), ctx->stream));
+    const unsigned nb = (unsigned)((n + 255) / 256);
+    rthc_zoom_row_hist<<<nb, 256, 0, ctx->stream>>>(ctx->d_cond, n, sample, d_row, d_hist);
+    RTHC_LAUNCH_CHECK(ctx);
+    rthc_zoom_kth<<<1, 1024, 0, ctx->stream>>>(d_hist, k, d_v, d_hist + 65536);
+    RTHC_LAUNCH_CHECK(ctx);
+    rthc_zoom_select<<<nb, 256, 0, ctx->stream>>>(d_row, n, d_v, d_oi, d_od, d_hist + 65537);
+    RTHC_LAUNCH_CHECK(ctx);
+    unsigned int cnt = 0;
+    int vmax = 0;
+    RTHC_CUDA(ctx, cudaMemcpyAsync(&cnt, d_hist + 65536, sizeof(cnt), cudaMemcpyDeviceToHost, ctx->stream));
+    RTHC_CUDA(ctx, cudaMemcpyAsync(&vmax, d_v, sizeof(vmax), cudaMemcpyDeviceToHost, ctx->stream));
+    RTHC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    RTHC_CUDA(ctx, cudaMemcpyAsync(out_idx, d_oi, sizeof(int64_t) * cnt, cudaMemcpyDeviceToHost, ctx->stream));
+    RTHC_CUDA(ctx, cudaMemcpyAsync(out_dist, d_od, sizeof(uint16_t) * cnt, cudaMemcpyDeviceToHost, ctx->stream));
+    RTHC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    rthc_dev_free(ctx, &d_row); rthc_dev_free(ctx, &d_od); rthc_dev_free(ctx, &d_oi);
+    rthc_dev_free(ctx, &d_hist); rthc_dev_free(ctx, &d_v);
+    *out_count = cnt;
+    if (out_max_dist) *out_max_dist = vmax;
+    return 0;
+}
+
+// ---- sub-matrix ---------------------------------------------------------------------------------
+__global__ void rthc_zoom_gather(const uint16_t *__restrict__ cond, int64_t n, const int64_t *__restrict__ idx, int64_t m,
+                                 uint16_t *__restrict__ out, int *__restrict__ flag)
+{
+    // one CTA row per child row a; threads stride over b > a
+    const int64_t a = blockIdx.x;
+    const int64_t ia = idx[a];
+    const int64_t base = m * a - (a * (a + 1)) / 2 - a - 1;
+    for (int64_t b = a + 1 + threadIdx.x; b < m; b += blockDim.x) {
+        const int64_t ib = idx[b];
+        uint16_t v = 0;
+        if (ia == ib) *flag = 1;
+        else v = cond[cond_index(n, ia, ib)];
+        out[base + b] = v;
+    }
+}
+
+extern "C" int rthc_subset_from(rthc_ctx *child, rthc_ctx *parent, const int64_t *idx, int64_t m)
+{
+    if (!child || !parent || !idx) return rthc_fail(child, RTHC_E_ARG, "rthc_subset_from: NULL argument");
+    if (child == parent) return rthc_fail(child, RTHC_E_ARG, "rthc_subset_from: child and parent must differ");
+    if (child->device != parent->device) return rthc_fail(child, RTHC_E_ARG, "rthc_subset_from: contexts on different devices");
+    if (!parent->have_dist || !parent->d_cond || parent->world != 1)
+        return rthc_fail(child, RTHC_E_STATE, "parent has no resident full uint16 distance matrix");
+    if (m < 2) return rthc_fail(child, RTHC_E_ARG, "need at least 2 samples (m=%lld)", (long long)m);
+    for (int64_t a = 0; a < m; ++a)
+        if (idx[a] < 0 || idx[a] >= parent->n) return rthc_fail(child, RTHC_E_ARG, "subset index %lld out of range", (long long)idx[a]);
+    RTHC_CUDA(child, cudaSetDevice(child->device));
+    RTHC_CUDA(child, cudaStreamSynchronize(parent->stream));
+    rthc_free_distance_state(child);
+    rthc_free_linkage_state(child);
+    child->rank = 0; child->world = 1; child->full_storage = false;
+    int rc = rthc_setup_geometry(child, m);
+    if (rc) return rc;
+    child->L = parent->L; child->L_kept = parent->L_kept;
+    child->G = 0; child->plane_rows = 0;
+    const int64_t P = m * (m - 1) / 2;
+    if (!child->d_cond || child->cond_cap < P) {
+        child->cond_cap = 0;
+        if ((rc = rthc_dev_alloc(child, &child->d_cond, (size_t)P))) return rc;
+        child->cond_cap = P;
+    }
+    int64_t *d_idx = nullptr;
+    int *d_flag = nullptr;
+    if ((rc = rthc_dev_alloc(child, &d_idx, (size_t)m))) return rc;
+    if ((rc = rthc_dev_alloc(child, &d_flag, 1))) return rc;
+    RTHC_CUDA(child, cudaMemsetAsync(d_flag, 0, sizeof(int), child->stream));
+    RTHC_CUDA(child, cudaMemcpyAsync(d_idx, idx, sizeof(int64_t) * (size_t)m, cudaMemcpyHostToDevice, child->stream));
+    rthc_zoom_gather<<<(unsigned)(m - 1), 256, 0, child->stream>>>(parent->d_cond, parent->n, d_idx, m, child->d_cond, d_flag);
+    RTHC_LAUNCH_CHECK(child);
+    int flag = 0;
+    RTHC_CUDA(child, cudaMemcpyAsync(&flag, d_flag, sizeof(int), cudaMemcpyDeviceToHost, child->stream));
+    RTHC_CUDA(child, cudaStreamSynchronize(child->stream));
+    rthc_dev_free(child, &d_idx); rthc_dev_free(child, &d_flag);
+    if (flag) return rthc_fail(child, RTHC_E_ARG, "rthc_subset_from: a sample index is listed twice");
+    child->ext_integer = true;
+    child->have_dist = true;
+    child->have_profiles = false;
+    return 0;
+}

@@ -68,6 +68,8 @@ def load_library():
         "rthc_mark_elapsed_ms": (ci, [vp, ctypes.POINTER(ctypes.c_double)]),
         "rthc_alu_peak": (ci, [vp, ctypes.POINTER(ctypes.c_double)]),
         "rthc_alu_peak_block": (ci, [vp, ci, ctypes.POINTER(ctypes.c_double)]),
+        "rthc_closest": (ci, [vp, i64, i64, vp, vp, ctypes.POINTER(i64), ctypes.POINTER(ci)]),
+        "rthc_subset_from": (ci, [vp, vp, vp, i64]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(L, name)
@@ -84,7 +86,7 @@ EXPORTED_SYMBOLS = [
     "rthc_get_condensed_u16", "rthc_get_owned_condensed_u16", "rthc_copy_rows_u16", "rthc_direct_pairs",
     "rthc_set_condensed_f64", "rthc_set_single_algo", "rthc_linkage", "rthc_local_forest",
     "rthc_linkage_from_forest", "rthc_cut", "rthc_info", "rthc_timings", "rthc_mark", "rthc_mark_elapsed_ms", "rthc_alu_peak",
-    "rthc_alu_peak_block",
+    "rthc_alu_peak_block", "rthc_closest", "rthc_subset_from",
 ]
 
 
@@ -102,6 +104,7 @@ class HCContext:
         if rc != 0:
             raise HCBackendError("rthc_create failed (%d): %s" % (rc, self._L.rthc_last_error(None).decode()))
         self._h = h
+        self.device = int(device)
         self.n = 0
         self.L = 0
         if full_storage:
@@ -219,6 +222,32 @@ class HCContext:
         out = np.empty((t.size, self.n), dtype=np.int32)
         self._check(self._L.rthc_cut(self._h, _ptr(t), t.size, _ptr(out)))
         return out
+
+    # ---- zoom-in on the resident matrix ----------------------------------
+    def closest(self, sample, k):
+        """(indices, distances, max_dist): every sample within the distance found at sorted position
+        k of `sample`'s row (own 0 included), ordered by (distance, index)."""
+        idx = np.empty(self.n, dtype=np.int64)
+        d = np.empty(self.n, dtype=np.uint16)
+        cnt, vmax = ctypes.c_int64(0), ctypes.c_int(0)
+        self._check(self._L.rthc_closest(self._h, int(sample), int(k), _ptr(idx), _ptr(d), ctypes.byref(cnt),
+                                         ctypes.byref(vmax)))
+        idx, d = idx[: cnt.value], d[: cnt.value]
+        order = np.lexsort((idx, d))
+        return idx[order].copy(), d[order].copy(), int(vmax.value)
+
+    def subset(self, indices):
+        """New context on the same device holding the sub-matrix of `indices` (distinct sample
+        positions), ready for linkage() / fcluster() / square_rows()."""
+        indices = np.ascontiguousarray(indices, dtype=np.int64)
+        child = HCContext(device=self.device)
+        try:
+            child._check(self._L.rthc_subset_from(child._h, self._h, _ptr(indices), indices.size))
+        except Exception:
+            child.close()
+            raise
+        child.n, child.L = int(indices.size), self.L
+        return child
 
     # ---- introspection -----------------------------------------------------------------
     def info(self):
