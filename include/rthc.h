@@ -136,6 +136,24 @@ int rthc_closest(rthc_ctx *ctx, int64_t sample, int64_t k, int64_t *out_idx, uin
  * rthc_copy_rows_u16.                                                                            */
 int rthc_subset_from(rthc_ctx *child, rthc_ctx *parent, const int64_t *idx, int64_t m);
 
+/* ---- cluster stability over neighbouring thresholds -------------- */
+/* Replaces getContTable / getContTableTotals / getMismatchMatrix (scripts/ComparingPartitions/
+ * metrics.py:23-91) for the adjacent-column comparisons of metrics4stability
+ * (scripts/ComparingPartitions/comparing_partitions_v2.py:74-113).
+ * codes: T x n int32 (host), row t = cluster id of every sample in partition column t, any
+ * numbering with 0 <= id < n.  For every pair p = (column p, column p+1) the non-empty cells of
+ * the contingency table are returned in the iteration order of the reference's dict of dicts
+ * getContTable(col[p+1], col[p]): rows = clusters of column p+1 by first appearance, cells of a row
+ * by first appearance.  cell_off: T entries (cell_off[0] = 0; pair p owns [cell_off[p], cell_off[p+1]));
+ * cell_row / cell_col / cell_count: room for (T-1) * n entries each.                            */
+int rthc_contingency_adjacent(rthc_ctx *ctx, const int32_t *codes, int T, int64_t n, int64_t *cell_off,
+                              int32_t *cell_row, int32_t *cell_col, int32_t *cell_count);
+/* Host finish of one table (no device work): the two row sums of getAdjustedWallace
+ * (metrics.py:147-165: rSumW1, rSumW2) accumulated in the reference's order with libm pow where the
+ * reference writes `** 2.0` / `** 3.0`, from the cells of one pair as returned above.            */
+int rthc_adjusted_wallace_sums(const int32_t *cell_row, const int32_t *cell_count, int64_t m, double *sum_w1,
+                               double *sum_w2);
+
 /* ---- introspection ----------------------------------------------------------- */
 /* info[0]=n, [1]=L, [2]=loci kept, [3]=groups of 32 loci, [4]=plane rows,
  * [5]=tiles launched, [6]=Boruvka rounds of the last linkage, [7]=max alleles/locus,
@@ -143,7 +161,7 @@ int rthc_subset_from(rthc_ctx *child, rthc_ctx *parent, const int64_t *idx, int6
 int rthc_info(const rthc_ctx *ctx, int64_t *info, int n_info);
 /* device-side durations (CUDA events, ms) of the last call of each stage:
  * [0]=h2d, [1]=recode+pack, [2]=distance kernel, [3]=mst/merge loop, [4]=cut,
- * [5]=number of kernel launches since create                                       */
+ * [5]=number of kernel launches since create, [6]=rthc_contingency_adjacent        */
 int rthc_timings(const rthc_ctx *ctx, double *ms, int n_ms);
 /* caller-placed CUDA events on the library's own stream (slot 0 / 1): bench.py brackets its timed
  * region with them, so the step time is measured on the device, on the stream the kernels run on */

@@ -421,7 +421,7 @@ extern "C" int rthc_info(const rthc_ctx *ctx, int64_t *info, int n_info)
 extern "C" int rthc_timings(const rthc_ctx *ctx, double *ms, int n_ms)
 {
     if (!ctx || !ms) return RTHC_E_ARG;
-    for (int k = 0; k < n_ms && k < 6; ++k) ms[k] = k == 5 ? (double)ctx->launches : ctx->t_ms[k];
+    for (int k = 0; k < n_ms && k < 7; ++k) ms[k] = k == 5 ? (double)ctx->launches : ctx->t_ms[k];
     return 0;
 }
 

@@ -70,6 +70,8 @@ def load_library():
         "rthc_alu_peak_block": (ci, [vp, ci, ctypes.POINTER(ctypes.c_double)]),
         "rthc_closest": (ci, [vp, i64, i64, vp, vp, ctypes.POINTER(i64), ctypes.POINTER(ci)]),
         "rthc_subset_from": (ci, [vp, vp, vp, i64]),
+        "rthc_contingency_adjacent": (ci, [vp, vp, ci, i64, vp, vp, vp, vp]),
+        "rthc_adjusted_wallace_sums": (ci, [vp, vp, i64, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_double)]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(L, name)
@@ -87,6 +89,7 @@ EXPORTED_SYMBOLS = [
     "rthc_set_condensed_f64", "rthc_set_single_algo", "rthc_linkage", "rthc_local_forest",
     "rthc_linkage_from_forest", "rthc_cut", "rthc_info", "rthc_timings", "rthc_mark", "rthc_mark_elapsed_ms", "rthc_alu_peak",
     "rthc_alu_peak_block", "rthc_closest", "rthc_subset_from",
+    "rthc_contingency_adjacent", "rthc_adjusted_wallace_sums",
 ]
 
 
@@ -249,6 +252,29 @@ class HCContext:
         child.n, child.L = int(indices.size), self.L
         return child
 
+    # ---- cluster stability -------------------------------------------------
+    def contingency_adjacent(self, codes):
+        """codes: T x n int32 cluster ids (0 <= id < n).  Returns one (rows, cols, counts) triple per
+        adjacent column pair (p, p+1): the cells of getContTable(col[p+1], col[p]) in the reference's
+        dict iteration order."""
+        codes = np.ascontiguousarray(codes, dtype=np.int32)
+        T, n = codes.shape
+        off = np.zeros(T, dtype=np.int64)
+        cap = max((T - 1) * n, 1)
+        rows, cols, cnts = (np.empty(cap, dtype=np.int32) for _ in range(3))
+        self._check(self._L.rthc_contingency_adjacent(self._h, _ptr(codes), T, n, _ptr(off), _ptr(rows), _ptr(cols), _ptr(cnts)))
+        return [(rows[off[p]:off[p + 1]], cols[off[p]:off[p + 1]], cnts[off[p]:off[p + 1]]) for p in range(T - 1)]
+
+    def adjusted_wallace_sums(self, rows, counts):
+        """(rSumW1, rSumW2) of getAdjustedWallace for one table (host arithmetic, libm pow)."""
+        rows = np.ascontiguousarray(rows, dtype=np.int32)
+        counts = np.ascontiguousarray(counts, dtype=np.int32)
+        a, b = ctypes.c_double(0), ctypes.c_double(0)
+        rc = self._L.rthc_adjusted_wallace_sums(_ptr(rows), _ptr(counts), rows.size, ctypes.byref(a), ctypes.byref(b))
+        if rc != 0:
+            raise HCBackendError("rthc_adjusted_wallace_sums failed (%d)" % rc)
+        return a.value, b.value
+
     # ---- introspection -----------------------------------------------------------------
     def info(self):
         a = np.zeros(9, dtype=np.int64)
@@ -257,9 +283,9 @@ class HCContext:
         return dict(zip(keys, (int(x) for x in a)))
 
     def timings(self):
-        a = np.zeros(6, dtype=np.float64)
-        self._check(self._L.rthc_timings(self._h, _ptr(a), 6))
-        keys = ["h2d_ms", "recode_ms", "distance_ms", "linkage_ms", "cut_ms", "launches"]
+        a = np.zeros(7, dtype=np.float64)
+        self._check(self._L.rthc_timings(self._h, _ptr(a), 7))
+        keys = ["h2d_ms", "recode_ms", "distance_ms", "linkage_ms", "cut_ms", "launches", "stability_ms"]
         return dict(zip(keys, (float(x) for x in a)))
 
     def mark(self, slot):

@@ -40,3 +40,33 @@ class FakeContext:
 
     def close(self):
         pass
+
+    # ---- N3 / N4 stand-ins ------------------------------------------------------------------
+    def closest(self, sample, k):
+        col = self.D[:, sample].astype(np.int64)
+        cut = np.sort(col, kind="stable")[k]
+        idx = np.nonzero(col <= cut)[0]
+        order = np.lexsort((idx, col[idx]))
+        return idx[order], col[idx][order].astype(np.uint16), int(cut)
+
+    def contingency_adjacent(self, codes):
+        out = []
+        for p in range(codes.shape[0] - 1):
+            table = {}
+            for r, c in zip(codes[p + 1].tolist(), codes[p].tolist()):
+                inner = table.setdefault(r, {})
+                inner[c] = inner.get(c, 0) + 1
+            cells = [(r, c, v) for r, inner in table.items() for c, v in inner.items()]
+            out.append(tuple(np.array([x[k] for x in cells], dtype=np.int32) for k in range(3)))
+        return out
+
+    def adjusted_wallace_sums(self, rows, counts):
+        # the real host-side C function: it needs the library, not a GPU
+        import ctypes
+        from reportree_b200 import hc_backend
+        L = hc_backend.load_library()
+        rows = np.ascontiguousarray(rows, dtype=np.int32)
+        counts = np.ascontiguousarray(counts, dtype=np.int32)
+        a, b = ctypes.c_double(0), ctypes.c_double(0)
+        assert L.rthc_adjusted_wallace_sums(rows.ctypes.data, counts.ctypes.data, rows.size, ctypes.byref(a), ctypes.byref(b)) == 0
+        return a.value, b.value
