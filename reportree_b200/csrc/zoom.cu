@@ -32,7 +32,7 @@ __global__ void rthc_zoom_row_hist(const uint16_t *__restrict__ cond, int64_t n,
 }
 
 // one CTA of 1024 threads: smallest v with #(d <= v) > k  (= the value at 0-based sorted position k)
-__global__ void rthc_zoom_kth(const unsigned int *__restrict__ hist, int64_t k, int *__restrict__ out_v,
+__global__ void __launch_bounds__(1024) rthc_zoom_kth(const unsigned int *__restrict__ hist, int64_t k, int *__restrict__ out_v,
                               unsigned int *__restrict__ out_count)
 {
     __shared__ unsigned int part[1024];
