@@ -40,6 +40,9 @@ def parse_args():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--n", type=int, default=0, help="override sample count (debug only; invalidates the metric)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--next", action="store_true",
+                    help="measure the SURVEY 8(f) N3 / N4 components (zoom-in, cluster stability) instead of the hot path")
+    ap.add_argument("--next-workload", default="C4", choices=["C3", "C4"])
     return ap.parse_args()
 
 
@@ -354,9 +357,28 @@ def ctx_npad(n):
     return (n + 127) // 128 * 128
 
 
+def run_next(args):
+    """zoom-in + stability timings (scripts/gpu_next_bench.py) with this file's cpu_baseline ports handed in."""
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("gpu_next_bench", os.path.join(os.path.dirname(os.path.abspath(__file__)),
+                                                                                 "scripts", "gpu_next_bench.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    cpu = None
+    if not args.no_cpu_baseline:
+        from oracle import oracle_lib, partition_metrics
+
+        class cpu:                                # noqa: N801 -- a namespace of the oracle ports
+            stability_lines = staticmethod(partition_metrics.stability_lines)
+            dist_square = staticmethod(oracle_lib.dist_square)
+    print(json.dumps(mod.run(args.next_workload, cpu)))
+
+
 if __name__ == "__main__":
     a = parse_args()
-    if a.impl == "reference":
+    if a.next:
+        run_next(a)
+    elif a.impl == "reference":
         run_reference(a)
     else:
         run_ours(a)

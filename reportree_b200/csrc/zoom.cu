@@ -31,28 +31,42 @@ __global__ void rthc_zoom_row_hist(const uint16_t *__restrict__ cond, int64_t n,
     atomicAdd(&hist[v], 1u);
 }
 
-// one CTA of 1024 threads: smallest v with #(d <= v) > k  (= the value at 0-based sorted position k)
+// one CTA of 1024 threads: smallest v with #(d <= v) > k  (= the value at 0-based sorted position k).
+// Segment s = bins [64 s, 64 s + 64); warp w sums segments 32 w .. 32 w + 31 with coalesced loads.
 __global__ void __launch_bounds__(1024) rthc_zoom_kth(const unsigned int *__restrict__ hist, int64_t k, int *__restrict__ out_v,
-                              unsigned int *__restrict__ out_count)
+                                                      unsigned int *__restrict__ out_count)
 {
     __shared__ unsigned int part[1024];
-    const int t = threadIdx.x;
-    unsigned int s = 0;
-    for (int b = 0; b < 64; ++b) s += hist[t * 64 + b];
-    part[t] = s;
+    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    for (int q = 0; q < 32; ++q) {
+        const int seg = warp * 32 + q;
+        unsigned int s = hist[seg * 64 + lane] + hist[seg * 64 + 32 + lane];
+        for (int off = 16; off > 0; off >>= 1) s += __shfl_xor_sync(0xFFFFFFFFu, s, off);
+        if (lane == 0) part[seg] = s;
+    }
     __syncthreads();
-    for (int off = 1; off < 1024; off <<= 1) {                // inclusive scan of the 1024 partial sums
+    for (int off = 1; off < 1024; off <<= 1) {                // inclusive scan of the 1024 segment sums
         unsigned int v = t >= off ? part[t - off] : 0u;
         __syncthreads();
         part[t] += v;
         __syncthreads();
     }
-    const unsigned int before = t ? part[t - 1] : 0u;
-    if ((int64_t)before <= k && (int64_t)part[t] > k) {       // exactly one thread
-        unsigned int c = before;
-        for (int b = 0; b < 64; ++b) {
-            c += hist[t * 64 + b];
-            if ((int64_t)c > k) { *out_v = t * 64 + b; *out_count = c; break; }
+    // the warp that owns the segment holding position k resolves it: lane l covers bins 2l, 2l+1 of the segment
+    for (int q = 0; q < 32; ++q) {
+        const int seg = warp * 32 + q;
+        const unsigned int before = seg ? part[seg - 1] : 0u;
+        if (!((int64_t)before <= k && (int64_t)part[seg] > k)) continue;      // warp-uniform
+        const unsigned int h0 = hist[seg * 64 + 2 * lane], h1 = hist[seg * 64 + 2 * lane + 1];
+        unsigned int inc = h0 + h1;
+        for (int off = 1; off < 32; off <<= 1) {
+            const unsigned int v = __shfl_up_sync(0xFFFFFFFFu, inc, off);
+            if (lane >= off) inc += v;
+        }
+        const unsigned int c1 = before + inc, c0 = c1 - h1;                    // counts up to and including bin 2l / 2l+1
+        const unsigned int hit = __ballot_sync(0xFFFFFFFFu, (int64_t)c1 > k);
+        if (lane == __ffs(hit) - 1) {
+            if ((int64_t)c0 > k) { *out_v = seg * 64 + 2 * lane; *out_count = c0; }
+            else { *out_v = seg * 64 + 2 * lane + 1; *out_count = c1; }
         }
     }
 }

@@ -239,15 +239,17 @@ class HCContext:
         order = np.lexsort((idx, d))
         return idx[order].copy(), d[order].copy(), int(vmax.value)
 
-    def subset(self, indices):
-        """New context on the same device holding the sub-matrix of `indices` (distinct sample
-        positions), ready for linkage() / fcluster() / square_rows()."""
+    def subset(self, indices, into=None):
+        """Context on the same device holding the sub-matrix of `indices` (distinct sample positions),
+        ready for linkage() / fcluster() / square_rows().  `into`: an earlier child to refill (its
+        memory pool is warm, which is most of the cost of a small zoom-in); default a new context."""
         indices = np.ascontiguousarray(indices, dtype=np.int64)
-        child = HCContext(device=self.device)
+        child = into if into is not None else HCContext(device=self.device)
         try:
             child._check(self._L.rthc_subset_from(child._h, self._h, _ptr(indices), indices.size))
         except Exception:
-            child.close()
+            if into is None:
+                child.close()
             raise
         child.n, child.L = int(indices.size), self.L
         return child

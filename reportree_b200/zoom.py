@@ -25,6 +25,7 @@ class ResidentMatrix:
             raise ValueError("%d names for a %d-sample matrix" % (len(names), ctx.n))
         self.ctx = ctx
         self.names = names
+        self._child = None                    # one child context, refilled by every cluster_subset()
         self._pos = {}
         for k, s in enumerate(names):
             self._pos.setdefault(s, k)        # duplicated ids: the first row wins, as a column look-up by name would
@@ -47,13 +48,15 @@ class ResidentMatrix:
 
     def cluster_subset(self, samples, method, thresholds):
         """linkage + fcluster of the subset without recomputing a distance: (Z, T x m labels)."""
-        child = self.subset_context(samples)
-        try:
-            Z = child.linkage(method)
-            labels = child.fcluster(thresholds)
-        finally:
-            child.close()
-        return Z, labels
+        pos = np.fromiter((self.position(s) for s in samples), dtype=np.int64)
+        self._child = self.ctx.subset(pos, into=self._child)
+        Z = self._child.linkage(method)
+        return Z, self._child.fcluster(thresholds)
+
+    def close(self):
+        if self._child is not None:
+            self._child.close()
+            self._child = None
 
 
 def get_closest_samples(sample, n, resident, samples_in_partitions):

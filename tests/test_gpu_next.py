@@ -122,6 +122,26 @@ def test_subset_argument_errors_and_resident_wrapper():
             assert same_partition(labels[k], fcluster(Zs, t, criterion="distance"))
 
 
+def test_subset_refills_an_existing_child():
+    rng = np.random.default_rng(8)
+    codes = random_profiles(rng, 900, 80)
+    D = O.dist_square(codes)
+    with hc_backend.HCContext() as ctx:
+        ctx.set_profiles(codes)
+        ctx.distance()
+        child = None
+        for m in (50, 700, 2, 300):
+            picks = rng.permutation(900)[:m]
+            child = ctx.subset(picks, into=child)
+            assert child.n == m
+            y = squareform(zoom_oracle.sub_square(D, picks).astype(np.float64), checks=False)
+            for method in ("complete", "single"):
+                child.set_single_algo(hc_backend.SL_PRIM)
+                assert child.linkage(method).tobytes() == linkage(y, method).tobytes()
+            assert np.array_equal(child.fcluster([4.0])[0], fcluster(linkage(y, "single"), 4.0, criterion="distance"))
+        child.close()
+
+
 def same_partition(a, b):
     pairs = {}
     back = {}
