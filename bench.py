@@ -191,6 +191,7 @@ def run_ours(args):
     host_codes = pinned.numpy()
     dX = pinned.cuda(non_blocking=False)
     thr = np.arange(WORKLOAD["thresholds"], dtype=np.float64)
+    labels_host = torch.empty((thr.size, n), dtype=torch.int32, pin_memory=True).numpy()   # result buffer, reused every step
     ctx = hc.HCContext(device=local, rank=rank, world=world)
     state = {"dist_ms": [], "link_ms": [], "cut_ms": [], "recode_ms": [], "h2d_ms": [], "d2h_bytes": 0}
 
@@ -214,7 +215,7 @@ def run_ours(args):
         if world == 1:
             Z = ctx.linkage("single")
             t = lap("linkage", t)
-            labels = ctx.fcluster(thr)
+            labels = ctx.fcluster(thr, out=labels_host)
             t = lap("cut", t)
             d2h = Z.nbytes + labels.nbytes + (n - 1) * 8
         else:
@@ -227,7 +228,7 @@ def run_ours(args):
             if rank == 0:
                 Z = ctx.linkage_from_forest(allk, n)
                 t = lap("final_merge", t)
-                labels = ctx.fcluster(thr)
+                labels = ctx.fcluster(thr, out=labels_host)
                 t = lap("cut", t)
                 d2h += allk.nbytes + Z.nbytes + labels.nbytes
         tm = ctx.timings()

@@ -38,20 +38,29 @@ def say(log, *parts):
     print(*parts, file=log)
 
 
-def rm_redundant(matrix, log):
-    """One sample per cluster of the most discriminatory column (first maximum, columns in file order)."""
-    best, main_col = 0, ""
-    for col in matrix.columns[1:]:
-        size = matrix[col].nunique(dropna=False)
+def encode_columns(matrix):
+    """(names, T x n int32 codes): every partition column as dense cluster ids (first appearance order)."""
+    names = list(matrix.columns[1:])
+    codes = np.empty((len(names), len(matrix)), dtype=np.int32)
+    for k, col in enumerate(names):
+        codes[k] = pandas.factorize(matrix[col].to_numpy(), use_na_sentinel=False)[0]
+    return names, codes
+
+
+def rm_redundant(names, codes, log):
+    """One sample per cluster of the most discriminatory column (first maximum, columns in file order);
+    the surviving rows keep their order.  Codes are made dense again (the device wants ids < n)."""
+    best, main = 0, 0
+    for k in range(len(names)):
+        size = int(codes[k].max()) + 1 if codes.shape[1] else 0
         if size > best:
-            best, main_col = size, col
-    say(log, "\tThe most discriminatory column found was " + main_col)
-    return matrix[~matrix[main_col].duplicated()]
-
-
-def order_columns(matrix):
-    cols = matrix.columns.tolist()
-    return matrix[[cols[0]] + cols[1:][::-1]]
+            best, main = size, k
+    say(log, "\tThe most discriminatory column found was " + (names[main] if names else ""))
+    keep = np.sort(np.unique(codes[main], return_index=True)[1])
+    sub = codes[:, keep]
+    for k in range(sub.shape[0]):
+        sub[k] = np.unique(sub[k], return_inverse=True)[1]
+    return sub
 
 
 class ColumnStats:
@@ -101,11 +110,7 @@ def pair_metrics(ctx, cells, st_i, st_j):
     return rand, wallace, adj
 
 
-def metrics4stability(matrix, tag, log, ctx):
-    names = list(matrix.columns)
-    codes = np.empty((len(names), len(matrix)), dtype=np.int32)
-    for k, col in enumerate(names):
-        codes[k] = pandas.factorize(matrix[col].to_numpy(), use_na_sentinel=False)[0]
+def metrics4stability(names, codes, tag, log, ctx):
     stats = [ColumnStats(row) for row in codes]
     tables = ctx.contingency_adjacent(codes) if len(names) > 1 else []
     with open(tag + "_metrics.tsv", "w+") as out:
@@ -176,28 +181,41 @@ def main(argv=None, ctx=None):
         if args.input2 or args.order2:
             say(log, "Provided options are incompatible! 'stability' analysis only accepts input1 and order1!")
             sys.exit()
+        import threading
+        box = {}
+        if ctx is None:                       # CUDA context creation overlaps the pandas parse
+            def create():
+                try:
+                    import os
+                    from reportree_b200 import hc_backend
+                    box["ctx"] = hc_backend.HCContext(device=int(os.environ.get("REPORTREE_HC_DEVICE", "0")))
+                except BaseException as e:    # noqa: BLE001 -- re-raised on the main thread
+                    box["err"] = e
+            maker = threading.Thread(target=create)
+            maker.start()
         matrix = pandas.read_table(args.input1)
         say(log, "Preparing for stability analysis...")
+        names, codes = encode_columns(matrix)
         if not args.keep_redundants:
             say(log, "Removing redundant samples...")
-            matrix = rm_redundant(matrix, log)
+            codes = rm_redundant(names, codes, log)
         say(log, "Ordering matrix...")
         if int(args.order1) != 0:
             if int(args.order1) == 1:
-                matrix = order_columns(matrix)
+                names, codes = names[::-1], np.ascontiguousarray(codes[::-1])
             else:
                 say(log, "\tInvalid order!")
                 sys.exit()
         say(log, "Cleaning matrix...")
-        clean = matrix.drop(matrix.columns[0], axis=1)
         say(log, "Calculating metrics...")
         own = ctx is None
         if own:
-            import os
-            from reportree_b200 import hc_backend
-            ctx = hc_backend.HCContext(device=int(os.environ.get("REPORTREE_HC_DEVICE", "0")))
+            maker.join()
+            if "err" in box:
+                raise box["err"]
+            ctx = box["ctx"]
         try:
-            metrics4stability(clean, args.tag, log, ctx)
+            metrics4stability(names, codes, args.tag, log, ctx)
         finally:
             if own:
                 ctx.close()

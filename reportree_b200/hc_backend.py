@@ -219,10 +219,14 @@ class HCContext:
         self._check(self._L.rthc_linkage_from_forest(self._h, _ptr(keys), keys.size, self.n, _ptr(Z)))
         return Z
 
-    def fcluster(self, thresholds):
-        """labels[k] == scipy fcluster(Z, thresholds[k], criterion='distance') of the last linkage."""
+    def fcluster(self, thresholds, out=None):
+        """labels[k] == scipy fcluster(Z, thresholds[k], criterion='distance') of the last linkage.
+        out: optional preallocated C-contiguous int32 [T, n] array (e.g. a view of page-locked memory)."""
         t = np.ascontiguousarray(np.atleast_1d(thresholds), dtype=np.float64)
-        out = np.empty((t.size, self.n), dtype=np.int32)
+        if out is None:
+            out = np.empty((t.size, self.n), dtype=np.int32)
+        elif out.dtype != np.int32 or out.shape != (t.size, self.n) or not out.flags.c_contiguous:
+            raise HCBackendError("fcluster: `out` must be a C-contiguous int32 array of shape (%d, %d)" % (t.size, self.n))
         self._check(self._L.rthc_cut(self._h, _ptr(t), t.size, _ptr(out)))
         return out
 
