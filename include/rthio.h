@@ -43,6 +43,10 @@ int64_t rthio_profile_cols(const rthio_profile *p);          /* loci (id column 
 int rthio_profile_header(const rthio_profile *p, int64_t col, const char **s, int64_t *len);
 /* cleaned sample id of `row`; *is_nan = 1 when pandas would have parsed it as NaN */
 int rthio_profile_sample(const rthio_profile *p, int64_t row, const char **s, int64_t *len, int *is_nan);
+/* every name in two calls' worth of data instead of n + L calls: header cells joined by '\t', cleaned sample ids
+ * joined by '\n' (neither can contain its separator), id_is_nan[row] = 1 where pandas has NaN.  Owned by the profile. */
+int rthio_profile_names(const rthio_profile *p, const char **header_blob, int64_t *header_len, const char **ids_blob,
+                        int64_t *ids_len, const char **id_is_nan);
 /* n x L int32 codes, row-major, owned by the profile:
  *    > 0  allele code (integer value, or 1..52 for a single ASCII letter)
  *      0  the cell is the literal string "0" after cleaning / missing-code replacement
@@ -53,6 +57,10 @@ const int32_t *rthio_profile_codes(const rthio_profile *p);
 /* out[r * ncols + c] = codes[rows[r]][cols[c]] (cols are 0-based locus indices) */
 int rthio_profile_gather(const rthio_profile *p, const int64_t *rows, int64_t nrows, const int64_t *cols,
                          int64_t ncols, int32_t *out);
+/* out[r] = #{c : codes[rows[r]][cols[c]] == value}: the per-sample count behind
+ * `isin(["0"]).sum(axis=1)` (scripts/partitioning_HC.py:451) with value = 0, without materialising the sub-matrix */
+int rthio_profile_count_eq(const rthio_profile *p, const int64_t *rows, int64_t nrows, const int64_t *cols,
+                           int64_t ncols, int32_t value, int64_t *out);
 /* TSV of the selected rows / loci with the cleaned cell text, as DataFrame.to_csv writes it */
 int rthio_profile_write(const rthio_profile *p, const char *path, const int64_t *rows, int64_t nrows,
                         const int64_t *cols, int64_t ncols);

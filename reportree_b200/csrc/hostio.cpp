@@ -114,7 +114,9 @@ struct rthio_profile {
     std::vector<std::string> ids;               // cleaned sample ids
     std::vector<char> id_nan;
     std::vector<char> row_plain;                // 1: the final text of every cell of the row is its raw text
-    std::vector<int32_t> codes;                 // n x L
+    int32_t *codes = nullptr;                   // n x L, anonymous mapping: pages are first touched (zero-filled) by the
+    size_t codes_bytes = 0;                     // parser threads, not by one thread clearing 1.2 GB up front
+    std::string ids_blob, header_blob;          // ids joined by '\n' / header cells joined by '\t' (one call instead of n)
 };
 
 // final text of a DATA cell (not the id column): cleaning + --missing-code replacement.
@@ -161,6 +163,7 @@ extern "C" void rthio_profile_close(rthio_profile *p)
 {
     if (!p) return;
     if (p->buf && p->size) munmap((void *)p->buf, p->size);
+    if (p->codes && p->codes_bytes) munmap((void *)p->codes, p->codes_bytes);
     if (p->fd >= 0) close(p->fd);
     delete p;
 }
@@ -234,7 +237,13 @@ extern "C" int rthio_profile_open(const char *path, const char *missing_code, in
     p->row_begin.assign(lb.begin() + 1, lb.end());
     p->row_end.assign(le.begin() + 1, le.end());
     try {
-        p->codes.resize((size_t)(p->n * p->L));
+        p->codes_bytes = std::max<size_t>(sizeof(int32_t) * (size_t)(p->n * p->L), 4096);
+        void *cm = mmap(nullptr, p->codes_bytes, PROT_READ | PROT_WRITE, MAP_PRIVATE | MAP_ANONYMOUS, -1, 0);
+        if (cm == MAP_FAILED) { p->codes_bytes = 0; throw std::bad_alloc(); }
+        p->codes = (int32_t *)cm;
+#ifdef MADV_HUGEPAGE
+        madvise(cm, p->codes_bytes, MADV_HUGEPAGE);
+#endif
         p->ids.resize((size_t)p->n);
         p->id_nan.assign((size_t)p->n, 0);
         p->row_plain.assign((size_t)p->n, 0);
@@ -245,7 +254,7 @@ extern "C" int rthio_profile_open(const char *path, const char *missing_code, in
         std::string tmp;
         for (int64_t r = lo; r < hi && !ragged.load(std::memory_order_relaxed); ++r) {
             const char *a = buf + p->row_begin[(size_t)r], *e = buf + p->row_end[(size_t)r];
-            int32_t *dst = p->codes.data() + (size_t)(r * L);
+            int32_t *dst = p->codes + (size_t)(r * L);
             // id cell
             const char *tab = (const char *)memchr(a, '\t', (size_t)(e - a));
             const char *b = tab ? tab : e;
@@ -275,13 +284,52 @@ extern "C" int rthio_profile_open(const char *path, const char *missing_code, in
         }
     });
     if (ragged.load()) { rthio_profile_close(p); return fail(RTHIO_IRREGULAR, "a row does not have %lld cells", (long long)(L + 1)); }
+    for (int64_t r = 0; r < p->n; ++r) {
+        if (r) p->ids_blob.push_back('\n');
+        p->ids_blob += p->ids[(size_t)r];
+    }
+    for (size_t c = 0; c < p->header.size(); ++c) {
+        if (c) p->header_blob.push_back('\t');
+        p->header_blob += p->header[c];
+    }
     *out = p;
     return RTHIO_OK;
 }
 
 extern "C" int64_t rthio_profile_rows(const rthio_profile *p) { return p ? p->n : 0; }
 extern "C" int64_t rthio_profile_cols(const rthio_profile *p) { return p ? p->L : 0; }
-extern "C" const int32_t *rthio_profile_codes(const rthio_profile *p) { return p ? p->codes.data() : nullptr; }
+extern "C" const int32_t *rthio_profile_codes(const rthio_profile *p) { return p ? p->codes : nullptr; }
+
+extern "C" int rthio_profile_names(const rthio_profile *p, const char **header_blob, int64_t *header_len, const char **ids_blob,
+                                   int64_t *ids_len, const char **id_is_nan)
+{
+    if (!p || !header_blob || !header_len || !ids_blob || !ids_len || !id_is_nan) return fail(RTHIO_E_ARG, "rthio_profile_names: NULL argument");
+    *header_blob = p->header_blob.data(); *header_len = (int64_t)p->header_blob.size();
+    *ids_blob = p->ids_blob.data(); *ids_len = (int64_t)p->ids_blob.size();
+    *id_is_nan = p->id_nan.data();
+    return RTHIO_OK;
+}
+
+extern "C" int rthio_profile_count_eq(const rthio_profile *p, const int64_t *rows, int64_t nrows, const int64_t *cols,
+                                      int64_t ncols, int32_t value, int64_t *out)
+{
+    if (!p || (!rows && nrows) || (!cols && ncols) || !out) return fail(RTHIO_E_ARG, "rthio_profile_count_eq: NULL argument");
+    for (int64_t r = 0; r < nrows; ++r) if (rows[r] < 0 || rows[r] >= p->n) return fail(RTHIO_E_ARG, "row index out of range");
+    for (int64_t c = 0; c < ncols; ++c) if (cols[c] < 0 || cols[c] >= p->L) return fail(RTHIO_E_ARG, "column index out of range");
+    const bool all_cols = ncols == p->L;       // ascending distinct columns are not required here, so test the identity
+    bool identity = all_cols;
+    for (int64_t c = 0; identity && c < ncols; ++c) identity = cols[c] == c;
+    parallel_ranges(nrows, p->n_threads, [&](int, int64_t lo, int64_t hi) {
+        for (int64_t r = lo; r < hi; ++r) {
+            const int32_t *src = p->codes + (size_t)(rows[r] * p->L);
+            int64_t k = 0;
+            if (identity) for (int64_t c = 0; c < ncols; ++c) k += src[c] == value;
+            else for (int64_t c = 0; c < ncols; ++c) k += src[cols[c]] == value;
+            out[r] = k;
+        }
+    });
+    return RTHIO_OK;
+}
 
 extern "C" int rthio_profile_header(const rthio_profile *p, int64_t col, const char **s, int64_t *len)
 {
@@ -308,7 +356,7 @@ extern "C" int rthio_profile_gather(const rthio_profile *p, const int64_t *rows,
     for (int64_t c = 0; c < ncols; ++c) if (cols[c] < 0 || cols[c] >= p->L) return fail(RTHIO_E_ARG, "column index out of range");
     parallel_ranges(nrows, p->n_threads, [&](int, int64_t lo, int64_t hi) {
         for (int64_t r = lo; r < hi; ++r) {
-            const int32_t *src = p->codes.data() + (size_t)(rows[r] * p->L);
+            const int32_t *src = p->codes + (size_t)(rows[r] * p->L);
             int32_t *dst = out + (size_t)(r * ncols);
             for (int64_t c = 0; c < ncols; ++c) dst[c] = src[cols[c]];
         }

@@ -18,7 +18,8 @@ EXPORTED_SYMBOLS = [
     "rthio_last_error", "rthio_version", "rthio_profile_open", "rthio_profile_close", "rthio_profile_rows",
     "rthio_profile_cols", "rthio_profile_header", "rthio_profile_sample", "rthio_profile_codes",
     "rthio_profile_gather", "rthio_profile_write", "rthio_square_open", "rthio_square_append_u16",
-    "rthio_square_close", "rthio_write_partitions", "rthio_write_int_matrix",
+    "rthio_square_close", "rthio_write_partitions", "rthio_write_int_matrix", "rthio_profile_names",
+    "rthio_profile_count_eq",
 ]
 _lib = None
 
@@ -50,6 +51,8 @@ def load_library():
         "rthio_profile_header": (ci, [vp, i64, pp(vp), pp(i64)]),
         "rthio_profile_sample": (ci, [vp, i64, pp(vp), pp(i64), pp(ci)]),
         "rthio_profile_codes": (vp, [vp]),
+        "rthio_profile_names": (ci, [vp, pp(vp), pp(i64), pp(vp), pp(i64), pp(vp)]),
+        "rthio_profile_count_eq": (ci, [vp, vp, i64, vp, i64, ctypes.c_int32, vp]),
         "rthio_profile_gather": (ci, [vp, vp, i64, vp, i64, vp]),
         "rthio_profile_write": (ci, [vp, cp, vp, i64, vp, i64]),
         "rthio_square_open": (ci, [cp, cp, vp, vp, i64, ci, pp(vp)]),
@@ -95,16 +98,17 @@ class Profile:
         self._L, self._h = L, handle
         self.n = int(L.rthio_profile_rows(handle))
         self.n_loci = int(L.rthio_profile_cols(handle))
-        s, ln = ctypes.c_void_p(), ctypes.c_int64()
-        self.header = []
-        for c in range(self.n_loci + 1):
-            L.rthio_profile_header(handle, c, ctypes.byref(s), ctypes.byref(ln))
-            self.header.append(ctypes.string_at(s.value, ln.value).decode("utf-8"))
-        nan = ctypes.c_int()
-        self.ids = []           # str, or None where pandas has NaN
-        for r in range(self.n):
-            L.rthio_profile_sample(handle, r, ctypes.byref(s), ctypes.byref(ln), ctypes.byref(nan))
-            self.ids.append(None if nan.value else ctypes.string_at(s.value, ln.value).decode("utf-8"))
+        hb, hl, ib, il, nf = ctypes.c_void_p(), ctypes.c_int64(), ctypes.c_void_p(), ctypes.c_int64(), ctypes.c_void_p()
+        if L.rthio_profile_names(handle, ctypes.byref(hb), ctypes.byref(hl), ctypes.byref(ib), ctypes.byref(il), ctypes.byref(nf)) != 0:
+            raise FastIOError(_err(L))
+        self.header = ctypes.string_at(hb.value, hl.value).decode("utf-8").split("\t")
+        self.ids = ctypes.string_at(ib.value, il.value).decode("utf-8").split("\n") if self.n else []   # str, or None where pandas has NaN
+        if len(self.header) != self.n_loci + 1 or len(self.ids) != self.n:
+            raise FastIOError("name tables do not match the profile shape")
+        if self.n:
+            flags = np.frombuffer(ctypes.string_at(nf.value, self.n), dtype=np.int8)
+            for r in np.flatnonzero(flags).tolist():
+                self.ids[r] = None
         addr = L.rthio_profile_codes(handle)
         if self.n and self.n_loci:
             buf = (ctypes.c_int32 * (self.n * self.n_loci)).from_address(addr)
@@ -117,6 +121,15 @@ class Profile:
         cols = np.ascontiguousarray(cols, dtype=np.int64)
         out = np.empty((rows.size, cols.size), dtype=np.int32)
         if self._L.rthio_profile_gather(self._h, _ptr(rows), rows.size, _ptr(cols), cols.size, _ptr(out)) != 0:
+            raise FastIOError(_err(self._L))
+        return out
+
+    def count_eq(self, rows, cols, value=0):
+        """out[r] = number of the selected loci whose code equals `value` in row rows[r]."""
+        rows = np.ascontiguousarray(rows, dtype=np.int64)
+        cols = np.ascontiguousarray(cols, dtype=np.int64)
+        out = np.empty(rows.size, dtype=np.int64)
+        if self._L.rthio_profile_count_eq(self._h, _ptr(rows), rows.size, _ptr(cols), cols.size, int(value), _ptr(out)) != 0:
             raise FastIOError(_err(self._L))
         return out
 

@@ -441,6 +441,13 @@ class _Columns:
         self.columns = header
 
 
+def _selected_codes(prof, rows, cols):
+    """int32 codes of the surviving samples x loci; the parsed matrix itself when nothing was dropped."""
+    if len(rows) == prof.n and len(cols) == prof.n_loci:       # both are ascending and distinct: the identity
+        return prof.codes
+    return prof.gather(rows, cols)
+
+
 def profile_to_distances_fast(args, say, log, ctx, prof):
     """`-a` branch on a profile parsed by librthc_hostio.so: same filters, messages and artefact
     files as profile_to_distances(), without a string DataFrame."""
@@ -479,9 +486,8 @@ def profile_to_distances_fast(args, say, log, ctx, prof):
     if thr >= 0.0:
         say("Cleaning the profile matrix using a threshold of >" + str(args.loci_called) + " alleles/positions called per sample...")
         len_schema = len(cols)
-        codes = prof.gather(rows, cols)
         id_is_zero = np.fromiter((prof.ids[i] == "0" for i in rows.tolist()), dtype=bool, count=len(rows))
-        missing = (codes == 0).sum(axis=1) + id_is_zero       # isin(["0"]) over every column incl. the id (:451)
+        missing = prof.count_eq(rows, cols, 0) + id_is_zero   # isin(["0"]) over every column incl. the id (:451)
         called = len_schema - missing
         ids = [prof.ids[i] if prof.ids[i] is not None else np.nan for i in rows.tolist()]
         report = pandas.DataFrame({"samples": pandas.Series(ids, dtype=object), "missing": missing, "called": called,
@@ -497,10 +503,11 @@ def profile_to_distances_fast(args, say, log, ctx, prof):
         # isin(passing): every row whose id equals the id of a passing row stays (duplicated ids)
         passing_ids = {prof.ids[i] for i, ok in zip(rows.tolist(), passed.tolist()) if ok}
         sel = np.fromiter((prof.ids[i] in passing_ids for i in rows.tolist()), dtype=bool, count=len(rows))
-        rows, codes = rows[sel], codes[sel]
+        rows = rows[sel]
+        codes = _selected_codes(prof, rows, cols)
         writers.append(Background(prof.write, out + "_flt_samples_matrix.tsv", rows, cols))   # overlaps the GPU stages
     else:
-        codes = prof.gather(rows, cols)
+        codes = _selected_codes(prof, rows, cols)
     PH.mark("row filter")
 
     say("Getting the pairwise distance matrix with cgmlst-dists (if your profile matrix is too big, this will be done in chunks of 2000 alleles/positions)...")
