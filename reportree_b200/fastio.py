@@ -175,12 +175,19 @@ def write_square_tsv(path, names, row_block_fn, n, block=1024, corner="dists", t
     h = ctypes.c_void_p()
     if L.rthio_square_open(os.fsencode(path), corner.encode("utf-8"), blob, _ptr(offs), n, int(threads), ctypes.byref(h)) != 0:
         raise FastIOError(_err(L))
+    # the next row block is fetched (device -> host) on a helper thread while this one is formatted and written
+    from concurrent.futures import ThreadPoolExecutor
+
+    def fetch(r0):
+        return np.ascontiguousarray(row_block_fn(r0, min(block, n - r0)), dtype=np.uint16)
     try:
-        for r0 in range(0, n, block):
-            nr = min(block, n - r0)
-            rows = np.ascontiguousarray(row_block_fn(r0, nr), dtype=np.uint16)
-            if L.rthio_square_append_u16(h, r0, nr, _ptr(rows)) != 0:
-                raise FastIOError(_err(L))
+        with ThreadPoolExecutor(max_workers=1) as pool:
+            nxt = pool.submit(fetch, 0) if n > 0 else None
+            for r0 in range(0, n, block):
+                rows = nxt.result()
+                nxt = pool.submit(fetch, r0 + block) if r0 + block < n else None
+                if L.rthio_square_append_u16(h, r0, rows.shape[0], _ptr(rows)) != 0:
+                    raise FastIOError(_err(L))
     finally:
         if L.rthio_square_close(h) != 0:
             raise FastIOError(_err(L))

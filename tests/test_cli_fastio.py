@@ -153,3 +153,28 @@ def test_cli_host_side_reproduces_reference_goldens(case, fast, tmp_path, monkey
             assert open(produced, "rb").read() == gzip.open(os.path.join(gdir, f), "rb").read(), f
     gold = open(os.path.join(gdir, case + "_stdout.txt")).read().split("\n")
     assert [l for l in out.split("\n") if str(tmp_path) not in l] == gold
+
+
+@pytest.mark.parametrize("use_map", ["1", "0"])
+def test_square_writer_blocks_and_modes(tmp_path, monkeypatch, use_map):
+    """Row blocks through the shared mapping (default) and through write(2) give the same bytes as a plain join."""
+    from reportree_b200 import fastio
+    monkeypatch.setenv("RTHIO_SQUARE_MMAP", use_map)
+    rng = np.random.default_rng(4)
+    n = 1231
+    D = rng.integers(0, 65536, (n, n)).astype(np.uint16)
+    D[rng.random((n, n)) < 0.5] = 0
+    names = ["sample_%d" % (k * 7) for k in range(n)]
+    calls = []
+
+    def rows(r0, nr):
+        calls.append((r0, nr))
+        return D[r0:r0 + nr]
+    path = tmp_path / "sq.tsv"
+    fastio.write_square_tsv(str(path), names, rows, n, block=100)
+    want = "dists\t" + "\t".join(names) + "\n" + "".join(
+        names[i] + "\t" + "\t".join(str(int(v)) for v in D[i]) + "\n" for i in range(n))
+    assert path.read_text() == want
+    assert calls == [(r0, min(100, n - r0)) for r0 in range(0, n, 100)]
+    fastio.write_square_tsv(str(path), names[:1], lambda r0, nr: D[:1, :1], 1)
+    assert path.read_text() == "dists\t" + names[0] + "\n" + names[0] + "\t" + str(int(D[0, 0])) + "\n"
