@@ -326,7 +326,7 @@ extern "C" int rthc_distance(rthc_ctx *ctx)
     int rc;
     if (!ctx->d_cond || ctx->cond_cap < ctx->owned_pairs) {
         ctx->cond_cap = 0;
-        if ((rc = rthc_dev_alloc(ctx, &ctx->d_cond, (size_t)std::max<int64_t>(ctx->owned_pairs, 1)))) return rc;
+        if ((rc = rthc_dev_alloc(ctx, &ctx->d_cond, (size_t)std::max<int64_t>(ctx->owned_pairs, 1) + RTHC_COND_PAD))) return rc;
         ctx->cond_cap = std::max<int64_t>(ctx->owned_pairs, 1);
     }
     if ((rc = rthc_run_distance(ctx))) return rc;
@@ -459,7 +459,7 @@ extern "C" int rthc_set_condensed_f64(rthc_ctx *ctx, const double *y, int64_t n)
     if ((rc = rthc_dev_alloc(ctx, &d_flags, 1))) return rc;
     if (!ctx->d_cond || ctx->cond_cap < P) {
         ctx->cond_cap = 0;
-        if ((rc = rthc_dev_alloc(ctx, &ctx->d_cond, (size_t)P))) return rc;
+        if ((rc = rthc_dev_alloc(ctx, &ctx->d_cond, (size_t)P + RTHC_COND_PAD))) return rc;
         ctx->cond_cap = P;
     }
     RTHC_CUDA(ctx, cudaMemsetAsync(d_flags, 0, sizeof(int), ctx->stream));

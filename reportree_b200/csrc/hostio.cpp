@@ -14,6 +14,7 @@
 
 #include <algorithm>
 #include <atomic>
+#include <chrono>
 #include <string>
 #include <thread>
 #include <unordered_set>
@@ -454,6 +455,7 @@ struct rthio_file {
     std::vector<std::string> names;
     std::string path;
     std::vector<std::vector<char>> bufs;        // per-thread text buffers, kept across calls
+    double t_format = 0, t_copy = 0;            // seconds per phase, printed at close when RTHIO_TIMING=1
 };
 
 static inline char *put_u32(char *o, uint32_t v)
@@ -500,6 +502,7 @@ extern "C" int rthio_square_append_u16(rthio_file *f, int64_t row0, int64_t nrow
     const int64_t n = f->n;
     const int T = f->n_threads;
     std::vector<size_t> used((size_t)T, 0);
+    const auto c0 = std::chrono::steady_clock::now();
     parallel_ranges(nrows, T, [&](int t, int64_t lo, int64_t hi) {
         size_t cap = 0;
         for (int64_t r = lo; r < hi; ++r) cap += f->names[(size_t)(row0 + r)].size() + (size_t)n * 6 + 2;
@@ -525,6 +528,12 @@ extern "C" int rthio_square_append_u16(rthio_file *f, int64_t row0, int64_t nrow
     for (int t = 0; t < T; ++t) start[(size_t)t + 1] = start[(size_t)t] + used[(size_t)t];
     const size_t total = start[(size_t)T];
     if (total == 0) return RTHIO_OK;
+    const auto c1 = std::chrono::steady_clock::now();
+    f->t_format += std::chrono::duration<double>(c1 - c0).count();
+    struct CopyTimer {
+        rthio_file *f; std::chrono::steady_clock::time_point t0;
+        ~CopyTimer() { f->t_copy += std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count(); }
+    } copy_timer{f, c1};
     // write(2) into the page cache is one memcpy under the inode lock (~2.5 GB/s); a shared mapping
     // lets every thread fault and fill its own pages of the file
     if (f->use_map) {
@@ -557,6 +566,9 @@ extern "C" int rthio_square_append_u16(rthio_file *f, int64_t row0, int64_t nrow
 extern "C" int rthio_square_close(rthio_file *f)
 {
     if (!f) return RTHIO_OK;
+    if (const char *e = getenv("RTHIO_TIMING"))
+        if (atoi(e)) fprintf(stderr, "[rthio] %s: format %.2f s, copy into the file %.2f s (%s), %.2f GB\n", f->path.c_str(), f->t_format,
+                             f->t_copy, f->use_map ? "shared mapping" : "write(2)", (double)f->pos / 1e9);
     int rc = close(f->fd);
     std::string path = f->path;
     delete f;

@@ -155,11 +155,18 @@ __device__ __forceinline__ void tile_push(bool has, int32_t c, uint64_t key, int
 {
     const unsigned act = __ballot_sync(0xffffffffu, has);
     if (!has) return;
+    // Only the component of the first active lane is merged inside the warp: that is the giant
+    // component of the late rounds (the same-address case), and every lane of that group passes the
+    // SAME mask, so the reductions are single instructions.  (Reducing every match_any group made the
+    // compiler loop over the distinct masks: 32 iterations per call in the first round.)
     const unsigned grp = __match_any_sync(act, c);
-    const uint32_t hi = (uint32_t)(key >> 32), lo = (uint32_t)key;
-    const uint32_t mh = __reduce_min_sync(grp, hi);
-    const uint32_t ml = __reduce_min_sync(grp, hi == mh ? lo : 0xFFFFFFFFu);
-    if (hi != mh || lo != ml) return;                      // keys are distinct: one lane per group survives
+    const unsigned lead = __shfl_sync(act, grp, __ffs(act) - 1);
+    if (grp == lead) {
+        const uint32_t hi = (uint32_t)(key >> 32), lo = (uint32_t)key;
+        const uint32_t mh = __reduce_min_sync(lead, hi);
+        const uint32_t ml = __reduce_min_sync(lead, hi == mh ? lo : 0xFFFFFFFFu);
+        if (hi != mh || lo != ml) return;                  // keys are distinct: one lane of the group survives
+    }
     const uint32_t slot = ((uint32_t)c * 2654435761u) >> 23;
     const int32_t old = atomicCAS(&tab_c[slot], -1, c);
     if (old == -1 || old == c) atomicMin(&tab_k[slot], (unsigned long long)key);
@@ -203,6 +210,72 @@ __device__ __forceinline__ void scan_tile_body(const uint16_t *__restrict__ cond
     }
 }
 
+// Interior tiles (no diagonal, no right edge): thread t owns the 8 CONTIGUOUS columns c0 + 8 t + e and
+// reads them with 16-byte loads.  Row i's segment starts at element off_i + c0 of the condensed vector,
+// which is 16-byte aligned only when s = (off_i + c0) mod 8 is 0; the thread therefore loads the two
+// aligned chunks that cover its columns and realigns by s (uniform per row) with funnel shifts.
+// Keys are built by PRMT straight from the packed words: (w << 16) | index in one instruction.
+struct TileRow {          // one row's two aligned 16-byte chunks in flight
+    uint4 lo, hi;
+    int s;                // misalignment of the row segment in elements (0..7), -1: row absent
+};
+__device__ __forceinline__ TileRow tile_row_load(const uint16_t *__restrict__ cond, const int64_t *s_off, int r, int64_t c0,
+                                                 int64_t n, int tid)
+{
+    TileRow R;
+    const int64_t off = s_off[r];
+    if (off < -n) { R.s = -1; R.lo = make_uint4(0, 0, 0, 0); R.hi = R.lo; return R; }     // uniform
+    const int64_t a = off + c0;
+    R.s = (int)(a & 7);
+    const uint4 *p = reinterpret_cast<const uint4 *>(cond + (a - R.s)) + tid;
+    R.lo = __ldg(p);
+    R.hi = __ldg(p + 1);
+    return R;
+}
+
+__device__ __forceinline__ void scan_tile_body_vec(const uint16_t *__restrict__ cond, const int64_t *s_off,
+                                                   const int32_t *s_ci, uint32_t *s_rowmin, int64_t c0, int64_t n,
+                                                   const int32_t (&cj)[8], uint32_t (&colmin)[8])
+{
+    const int tid = threadIdx.x;
+    const uint32_t jl0 = 8u * (uint32_t)tid;
+    TileRow nxt = tile_row_load(cond, s_off, 0, c0, n, tid);
+#pragma unroll 1
+    for (int r = 0; r < TS_ROWS; ++r) {
+        const TileRow cur = nxt;
+        if (r + 1 < TS_ROWS) nxt = tile_row_load(cond, s_off, r + 1, c0, n, tid);     // in flight while this row is scanned
+        if (cur.s < 0) continue;                    // uniform
+        const int32_t ci = s_ci[r];
+        const uint4 lo = cur.lo, hi = cur.hi;
+        uint32_t W[4];
+        switch (cur.s) {                            // uniform
+        case 0: W[0] = lo.x; W[1] = lo.y; W[2] = lo.z; W[3] = lo.w; break;
+        case 1: W[0] = __funnelshift_r(lo.x, lo.y, 16); W[1] = __funnelshift_r(lo.y, lo.z, 16);
+                W[2] = __funnelshift_r(lo.z, lo.w, 16); W[3] = __funnelshift_r(lo.w, hi.x, 16); break;
+        case 2: W[0] = lo.y; W[1] = lo.z; W[2] = lo.w; W[3] = hi.x; break;
+        case 3: W[0] = __funnelshift_r(lo.y, lo.z, 16); W[1] = __funnelshift_r(lo.z, lo.w, 16);
+                W[2] = __funnelshift_r(lo.w, hi.x, 16); W[3] = __funnelshift_r(hi.x, hi.y, 16); break;
+        case 4: W[0] = lo.z; W[1] = lo.w; W[2] = hi.x; W[3] = hi.y; break;
+        case 5: W[0] = __funnelshift_r(lo.z, lo.w, 16); W[1] = __funnelshift_r(lo.w, hi.x, 16);
+                W[2] = __funnelshift_r(hi.x, hi.y, 16); W[3] = __funnelshift_r(hi.y, hi.z, 16); break;
+        case 6: W[0] = lo.w; W[1] = hi.x; W[2] = hi.y; W[3] = hi.z; break;
+        default: W[0] = __funnelshift_r(lo.w, hi.x, 16); W[1] = __funnelshift_r(hi.x, hi.y, 16);
+                 W[2] = __funnelshift_r(hi.y, hi.z, 16); W[3] = __funnelshift_r(hi.z, hi.w, 16); break;
+        }
+        uint32_t rowmin = TS_KEY_INF;
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+            if (cj[e] != ci) {
+                const uint32_t sel = (e & 1) ? 0x3254u : 0x1054u;      // [index.b0, index.b1, w.b0, w.b1]
+                colmin[e] = min(colmin[e], __byte_perm(W[e >> 1], (uint32_t)r, sel));
+                rowmin = min(rowmin, __byte_perm(W[e >> 1], jl0 + (uint32_t)e, sel));
+            }
+        }
+        rowmin = __reduce_min_sync(0xffffffffu, rowmin);
+        if ((tid & 31) == 0 && rowmin != TS_KEY_INF) atomicMin(&s_rowmin[r], rowmin);
+    }
+}
+
 __global__ void __launch_bounds__(256)
 rthc_boruvka_scan_tile(const uint16_t *__restrict__ cond, const int64_t *__restrict__ row_base, int64_t n,
                        const int32_t *__restrict__ comp, uint64_t *best, const int32_t *__restrict__ bands)
@@ -227,18 +300,21 @@ rthc_boruvka_scan_tile(const uint16_t *__restrict__ cond, const int64_t *__restr
         }
         s_off[tid] = off; s_ci[tid] = ci; s_rowmin[tid] = TS_KEY_INF;
     }
+    // edge tiles (diagonal / right border): strided columns c0 + t + 256 k with bounds checks;
+    // interior tiles: contiguous columns c0 + 8 t + k, 16-byte loads
+    const bool edge = (c0 <= r0 + TS_ROWS - 1) || (c0 + TS_COLS > n);
+    const int cmul = edge ? 1 : 8, kmul = edge ? 256 : 1;
     int32_t cj[8];
     uint32_t colmin[8];
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
-        const int64_t j = c0 + tid + 256 * k;
+        const int64_t j = c0 + cmul * tid + kmul * k;
         cj[k] = j < n ? comp[j] : -2;
         colmin[k] = TS_KEY_INF;
     }
     __syncthreads();
-    const bool edge = (c0 <= r0 + TS_ROWS - 1) || (c0 + TS_COLS > n);
     if (edge) scan_tile_body<true>(cond, s_off, s_ci, s_rowmin, r0, c0, n, cj, colmin);
-    else scan_tile_body<false>(cond, s_off, s_ci, s_rowmin, r0, c0, n, cj, colmin);
+    else scan_tile_body_vec(cond, s_off, s_ci, s_rowmin, c0, n, cj, colmin);
     __syncthreads();
     // candidates of this tile -> at most one global operation per distinct component
     {
@@ -259,7 +335,7 @@ rthc_boruvka_scan_tile(const uint16_t *__restrict__ cond, const int64_t *__restr
     for (int k = 0; k < 8; ++k) {
         const uint32_t cm = colmin[k];
         const bool has = cm != TS_KEY_INF;
-        const uint64_t key = rthc_pack_key(cm >> 16, (uint32_t)(r0 + (cm & 0xFFFFu)), (uint32_t)(c0 + tid + 256 * k));
+        const uint64_t key = rthc_pack_key(cm >> 16, (uint32_t)(r0 + (cm & 0xFFFFu)), (uint32_t)(c0 + cmul * tid + kmul * k));
         tile_push(has, cj[k], key, tab_c, tab_k, best);
     }
     __syncthreads();

@@ -12,6 +12,7 @@
 #define RTHC_BLK 64              // samples per plane block in HBM / per bulk copy
 #define RTHC_MIN_BITS 3          // every locus group carries at least 3 bit planes (zero-padded)
 #define RTHC_KEY_INF 0xFFFFFFFFFFFFFFFFull
+#define RTHC_COND_PAD 64         // spare uint16 entries behind d_cond: 16-byte row loads may run 15 entries past a segment
 
 // (w, i, j) packed as w<<48 | i<<24 | j  (i < j < 2^24, w < 2^16): one total order
 __host__ __device__ inline uint64_t rthc_pack_key(uint32_t w, uint32_t i, uint32_t j)

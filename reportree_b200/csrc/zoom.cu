@@ -165,7 +165,7 @@ extern "C" int rthc_subset_from(rthc_ctx *child, rthc_ctx *parent, const int64_t
     const int64_t P = m * (m - 1) / 2;
     if (!child->d_cond || child->cond_cap < P) {
         child->cond_cap = 0;
-        if ((rc = rthc_dev_alloc(child, &child->d_cond, (size_t)P))) return rc;
+        if ((rc = rthc_dev_alloc(child, &child->d_cond, (size_t)P + RTHC_COND_PAD))) return rc;
         child->cond_cap = P;
     }
     int64_t *d_idx = nullptr;
