@@ -219,60 +219,79 @@ struct TileRow {          // one row's two aligned 16-byte chunks in flight
     uint4 lo, hi;
     int s;                // misalignment of the row segment in elements (0..7), -1: row absent
 };
-__device__ __forceinline__ TileRow tile_row_load(const uint16_t *__restrict__ cond, const int64_t *s_off, int r, int64_t c0,
-                                                 int64_t n, int tid)
+// s_seg[r] = element index of the aligned chunk that holds column c0 of row r, shifted left by 3, plus the
+// misalignment (0..7) in the low bits; -1: row absent.  One 64-bit shared load per row.
+__device__ __forceinline__ TileRow tile_row_load(const uint16_t *__restrict__ cond, const int64_t *s_seg, int r, int tid)
 {
     TileRow R;
-    const int64_t off = s_off[r];
-    if (off < -n) { R.s = -1; R.lo = make_uint4(0, 0, 0, 0); R.hi = R.lo; return R; }     // uniform
-    const int64_t a = off + c0;
-    R.s = (int)(a & 7);
-    const uint4 *p = reinterpret_cast<const uint4 *>(cond + (a - R.s)) + tid;
+    const int64_t seg = s_seg[r];
+    if (seg < 0) { R.s = -1; R.lo = make_uint4(0, 0, 0, 0); R.hi = R.lo; return R; }     // uniform
+    R.s = (int)(seg & 7);
+    const uint4 *p = reinterpret_cast<const uint4 *>(cond + (seg & ~(int64_t)7)) + tid;
     R.lo = __ldg(p);
     R.hi = __ldg(p + 1);
     return R;
 }
 
-__device__ __forceinline__ void scan_tile_body_vec(const uint16_t *__restrict__ cond, const int64_t *s_off,
-                                                   const int32_t *s_ci, uint32_t *s_rowmin, int64_t c0, int64_t n,
+__device__ __forceinline__ uint32_t prmt(uint32_t a, uint32_t b, uint32_t sel)
+{
+    uint32_t d;
+    asm("prmt.b32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(sel));
+    return d;
+}
+
+// one row of an interior tile: thread t holds columns c0 + 8 t + e
+__device__ __forceinline__ void tile_row_scan(const TileRow &R, int r, int32_t ci, const int32_t (&cj)[8], uint32_t (&colmin)[8],
+                                              uint32_t jl0, uint32_t *s_rowmin8)
+{
+    if (R.s < 0) return;                            // uniform
+    const uint4 lo = R.lo, hi = R.hi;
+    uint32_t W[4];
+    switch (R.s) {                                  // uniform
+    case 0: W[0] = lo.x; W[1] = lo.y; W[2] = lo.z; W[3] = lo.w; break;
+    case 1: W[0] = __funnelshift_r(lo.x, lo.y, 16); W[1] = __funnelshift_r(lo.y, lo.z, 16);
+            W[2] = __funnelshift_r(lo.z, lo.w, 16); W[3] = __funnelshift_r(lo.w, hi.x, 16); break;
+    case 2: W[0] = lo.y; W[1] = lo.z; W[2] = lo.w; W[3] = hi.x; break;
+    case 3: W[0] = __funnelshift_r(lo.y, lo.z, 16); W[1] = __funnelshift_r(lo.z, lo.w, 16);
+            W[2] = __funnelshift_r(lo.w, hi.x, 16); W[3] = __funnelshift_r(hi.x, hi.y, 16); break;
+    case 4: W[0] = lo.z; W[1] = lo.w; W[2] = hi.x; W[3] = hi.y; break;
+    case 5: W[0] = __funnelshift_r(lo.z, lo.w, 16); W[1] = __funnelshift_r(lo.w, hi.x, 16);
+            W[2] = __funnelshift_r(hi.x, hi.y, 16); W[3] = __funnelshift_r(hi.y, hi.z, 16); break;
+    case 6: W[0] = lo.w; W[1] = hi.x; W[2] = hi.y; W[3] = hi.z; break;
+    default: W[0] = __funnelshift_r(lo.w, hi.x, 16); W[1] = __funnelshift_r(hi.x, hi.y, 16);
+             W[2] = __funnelshift_r(hi.y, hi.z, 16); W[3] = __funnelshift_r(hi.z, hi.w, 16); break;
+    }
+    // keys by PRMT straight from the packed words: column key (w << 16) | r; row key (w << 16) | idx(e)
+    // with idx = e for e < 4 and 0x100 + (e - 4) above, both bytes taken from ONE constant register
+    // (0x03020100: byte k = k), so that no per-column index registers are needed
+    const uint32_t IDX = 0x03020100u;
+    uint32_t rk = TS_KEY_INF;
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+        if (cj[e] != ci) {
+            const uint32_t wsel = (e & 1) ? 0x3200u : 0x1000u;
+            colmin[e] = min(colmin[e], prmt(W[e >> 1], (uint32_t)r, wsel | 0x54u));
+            rk = min(rk, prmt(W[e >> 1], IDX, wsel | ((e < 4 ? 4u : 5u) << 4) | (4u + (e & 3))));
+        }
+    }
+    if (rk != TS_KEY_INF) rk = (rk & 0xFFFF0000u) | (jl0 + (rk & 3u) + ((rk >> 6) & 4u));
+    rk = __reduce_min_sync(0xffffffffu, rk);
+    if ((threadIdx.x & 31) == 0) s_rowmin8[r * 8 + (threadIdx.x >> 5)] = rk;      // plain store: one slot per (row, warp)
+}
+
+__device__ __forceinline__ void scan_tile_body_vec(const uint16_t *__restrict__ cond, const int64_t *s_seg,
+                                                   const int32_t *s_ci, uint32_t *s_rowmin8,
                                                    const int32_t (&cj)[8], uint32_t (&colmin)[8])
 {
     const int tid = threadIdx.x;
     const uint32_t jl0 = 8u * (uint32_t)tid;
-    TileRow nxt = tile_row_load(cond, s_off, 0, c0, n, tid);
+    TileRow A = tile_row_load(cond, s_seg, 0, tid);
 #pragma unroll 1
-    for (int r = 0; r < TS_ROWS; ++r) {
-        const TileRow cur = nxt;
-        if (r + 1 < TS_ROWS) nxt = tile_row_load(cond, s_off, r + 1, c0, n, tid);     // in flight while this row is scanned
-        if (cur.s < 0) continue;                    // uniform
-        const int32_t ci = s_ci[r];
-        const uint4 lo = cur.lo, hi = cur.hi;
-        uint32_t W[4];
-        switch (cur.s) {                            // uniform
-        case 0: W[0] = lo.x; W[1] = lo.y; W[2] = lo.z; W[3] = lo.w; break;
-        case 1: W[0] = __funnelshift_r(lo.x, lo.y, 16); W[1] = __funnelshift_r(lo.y, lo.z, 16);
-                W[2] = __funnelshift_r(lo.z, lo.w, 16); W[3] = __funnelshift_r(lo.w, hi.x, 16); break;
-        case 2: W[0] = lo.y; W[1] = lo.z; W[2] = lo.w; W[3] = hi.x; break;
-        case 3: W[0] = __funnelshift_r(lo.y, lo.z, 16); W[1] = __funnelshift_r(lo.z, lo.w, 16);
-                W[2] = __funnelshift_r(lo.w, hi.x, 16); W[3] = __funnelshift_r(hi.x, hi.y, 16); break;
-        case 4: W[0] = lo.z; W[1] = lo.w; W[2] = hi.x; W[3] = hi.y; break;
-        case 5: W[0] = __funnelshift_r(lo.z, lo.w, 16); W[1] = __funnelshift_r(lo.w, hi.x, 16);
-                W[2] = __funnelshift_r(hi.x, hi.y, 16); W[3] = __funnelshift_r(hi.y, hi.z, 16); break;
-        case 6: W[0] = lo.w; W[1] = hi.x; W[2] = hi.y; W[3] = hi.z; break;
-        default: W[0] = __funnelshift_r(lo.w, hi.x, 16); W[1] = __funnelshift_r(hi.x, hi.y, 16);
-                 W[2] = __funnelshift_r(hi.y, hi.z, 16); W[3] = __funnelshift_r(hi.z, hi.w, 16); break;
-        }
-        uint32_t rowmin = TS_KEY_INF;
-#pragma unroll
-        for (int e = 0; e < 8; ++e) {
-            if (cj[e] != ci) {
-                const uint32_t sel = (e & 1) ? 0x3254u : 0x1054u;      // [index.b0, index.b1, w.b0, w.b1]
-                colmin[e] = min(colmin[e], __byte_perm(W[e >> 1], (uint32_t)r, sel));
-                rowmin = min(rowmin, __byte_perm(W[e >> 1], jl0 + (uint32_t)e, sel));
-            }
-        }
-        rowmin = __reduce_min_sync(0xffffffffu, rowmin);
-        if ((tid & 31) == 0 && rowmin != TS_KEY_INF) atomicMin(&s_rowmin[r], rowmin);
+    for (int r = 0; r < TS_ROWS; r += 2) {          // two rows per trip: A / B swap roles without register copies
+        const TileRow B = tile_row_load(cond, s_seg, r + 1, tid);
+        tile_row_scan(A, r, s_ci[r], cj, colmin, jl0, s_rowmin8);
+        if (r + 2 < TS_ROWS) A = tile_row_load(cond, s_seg, r + 2, tid);
+        tile_row_scan(B, r + 1, s_ci[r + 1], cj, colmin, jl0, s_rowmin8);
     }
 }
 
@@ -286,6 +305,8 @@ rthc_boruvka_scan_tile(const uint16_t *__restrict__ cond, const int64_t *__restr
     __shared__ int64_t s_off[TS_ROWS];
     __shared__ int32_t s_ci[TS_ROWS];
     __shared__ uint32_t s_rowmin[TS_ROWS];
+    __shared__ int64_t s_seg[TS_ROWS];            // interior tiles: aligned segment start | misalignment
+    __shared__ uint32_t s_rowmin8[TS_ROWS * 8];   // interior tiles: row minimum of every warp
     __shared__ int32_t tab_c[TS_TAB];
     __shared__ unsigned long long tab_k[TS_TAB];
     const int tid = threadIdx.x;
@@ -299,6 +320,7 @@ rthc_boruvka_scan_tile(const uint16_t *__restrict__ cond, const int64_t *__restr
             if (base >= 0) { off = base - i - 1; ci = comp[i]; }
         }
         s_off[tid] = off; s_ci[tid] = ci; s_rowmin[tid] = TS_KEY_INF;
+        s_seg[tid] = off < -n ? (int64_t)-1 : off + c0;        // (off + c0): low 3 bits = misalignment of the segment
     }
     // edge tiles (diagonal / right border): strided columns c0 + t + 256 k with bounds checks;
     // interior tiles: contiguous columns c0 + 8 t + k, 16-byte loads
@@ -314,8 +336,14 @@ rthc_boruvka_scan_tile(const uint16_t *__restrict__ cond, const int64_t *__restr
     }
     __syncthreads();
     if (edge) scan_tile_body<true>(cond, s_off, s_ci, s_rowmin, r0, c0, n, cj, colmin);
-    else scan_tile_body_vec(cond, s_off, s_ci, s_rowmin, c0, n, cj, colmin);
+    else scan_tile_body_vec(cond, s_seg, s_ci, s_rowmin8, cj, colmin);
     __syncthreads();
+    if (!edge && tid < TS_ROWS) {
+        uint32_t m = TS_KEY_INF;
+#pragma unroll
+        for (int w = 0; w < 8; ++w) m = min(m, s_rowmin8[tid * 8 + w]);
+        s_rowmin[tid] = s_seg[tid] < 0 ? TS_KEY_INF : m;       // absent rows were never written
+    }
     // candidates of this tile -> at most one global operation per distinct component
     {
         bool has = false;
