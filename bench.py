@@ -194,6 +194,8 @@ def run_ours(args):
     labels_host = torch.empty((thr.size, n), dtype=torch.int32, pin_memory=True).numpy()   # result buffer, reused every step
     ctx = hc.HCContext(device=local, rank=rank, world=world)
     state = {"dist_ms": [], "link_ms": [], "cut_ms": [], "recode_ms": [], "h2d_ms": [], "d2h_bytes": 0}
+    exch = sharded.ForestExchange(n, dist) if world > 1 else None                 # device-resident forest gather
+    loader = sharded.ShardedProfileLoader(n, L, dist) if world > 1 else None      # 1/world of the rows per rank + all_gather
 
     seg = {}
 
@@ -206,6 +208,8 @@ def run_ours(args):
         t = time.perf_counter()
         if resident:
             ctx.set_profiles_device(dX.data_ptr(), n, L)
+        elif world > 1:
+            ctx.set_profiles_device(loader.load(host_codes), n, L)
         else:
             ctx.set_profiles(host_codes)
         t = lap("set_profiles", t)
@@ -219,18 +223,17 @@ def run_ours(args):
             t = lap("cut", t)
             d2h = Z.nbytes + labels.nbytes + (n - 1) * 8
         else:
-            keys = ctx.local_forest()
+            exch.local_forest(ctx)
             t = lap("local_forest", t)
-            allk = sharded.all_gather_forests(keys, n, dist, device="cuda")     # the one NCCL exchange
+            exch.gather()                                                        # the one NCCL exchange
             t = lap("all_gather", t)
-            d2h = keys.nbytes
             labels = None
             if rank == 0:
-                Z = ctx.linkage_from_forest(allk, n)
+                Z = exch.linkage(ctx)
                 t = lap("final_merge", t)
                 labels = ctx.fcluster(thr, out=labels_host)
                 t = lap("cut", t)
-                d2h += allk.nbytes + Z.nbytes + labels.nbytes
+                d2h = (n - 1) * 8 + Z.nbytes + labels.nbytes
         tm = ctx.timings()
         state["dist_ms"].append(tm["distance_ms"]); state["link_ms"].append(tm["linkage_ms"])
         state["cut_ms"].append(tm["cut_ms"]); state["recode_ms"].append(tm["recode_ms"])
@@ -276,6 +279,7 @@ def run_ours(args):
     if rank == 0:
         sampler.start()
     dt, launches, labels = timed(True, args.steps, args.warmup)
+    check = {"resident": result_check(labels)} if rank == 0 else {}
     kern = {k: float(np.mean(v)) for k, v in state.items() if isinstance(v, list) and v}
     kern_steps = {k: [round(float(x), 3) for x in v] for k, v in state.items() if isinstance(v, list) and v}
     host_seg = {k: round(float(np.mean(v)), 3) for k, v in seg.items()}
@@ -283,6 +287,8 @@ def run_ours(args):
     owned_pairs = ctx.owned_pairs()
     clocks = sampler.stop() if rank == 0 else None
     dt_e2e, _, labels_e2e = timed(False, args.steps, 1)
+    if rank == 0:
+        check["e2e"] = result_check(labels_e2e)
     d2h_bytes = state["d2h_bytes"]
 
     if rank == 0:
@@ -336,7 +342,10 @@ def run_ours(args):
             "e2e_stage_ms_per_step": {k: [round(float(x), 3) for x in v] for k, v in state.items() if isinstance(v, list) and v},
             "roofline": roofline,
             "e2e": {"value": e2e_value, "unit": "comparisons/s", "ms_per_step": 1e3 * dt_e2e / args.steps,
-                    "h2d_bytes_per_step": int(n) * int(L) * 4, "d2h_bytes_per_step": int(d2h_bytes)},
+                    "h2d_bytes_per_step": int(n) * int(L) * 4, "d2h_bytes_per_step": int(d2h_bytes),
+                    "h2d": "rank 0 copies the whole int32 matrix" if world == 1 else
+                           "summed over ranks: each copies n/%d rows from page-locked memory, one NCCL all_gather replicates" % world},
+            "result_check": check,
             "gpu_launches": int(launches),
             "timing": "CUDA events on the library stream around the K steps (max over ranks); wall/device = %.3f" % (
                 state.get("wall_over_device") or 0.0),
@@ -352,6 +361,15 @@ def run_ours(args):
     ctx.close()
     if world > 1:
         dist.destroy_process_group()
+
+
+def result_check(labels):
+    """Fingerprint of the T x n label matrix (taken outside the timed region): equal for every N and for the
+    resident / host-buffer runs, because the strict (w, i, j) order makes the MST -- hence Z and scipy's
+    numbering -- unique."""
+    import zlib
+    return {"labels_crc32": zlib.crc32(np.ascontiguousarray(labels).tobytes()),
+            "clusters_at_first_mid_last_threshold": [int(labels[k].max()) for k in (0, labels.shape[0] // 2, labels.shape[0] - 1)]}
 
 
 def ctx_npad(n):

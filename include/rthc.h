@@ -118,6 +118,15 @@ int rthc_local_forest(rthc_ctx *ctx, uint64_t *keys_out, int64_t *m_out);
 /* finish single linkage from the union of the ranks' forests (m keys, any order).  */
 int rthc_linkage_from_forest(rthc_ctx *ctx, const uint64_t *keys, int64_t m, int64_t n,
                              double *Z_out);
+/* Device-resident variants for the NCCL exchange ("one fixed-size all_gather of packed edges per
+ * rank"): d_keys_out is DEVICE memory of the caller (e.g. a torch tensor) with `capacity` >= n-1 slots; the
+ * forest is written unsorted and the remaining slots are set to +inf (0xFFFFFFFFFFFFFFFF), so the buffer can
+ * go straight into an all_gather.  Synchronous on return.                                              */
+int rthc_local_forest_device(rthc_ctx *ctx, uint64_t *d_keys_out, int64_t capacity, int64_t *m_out);
+/* d_keys: m slots of DEVICE memory (the gathered buffers, any order, +inf slots ignored); the caller
+ * must have synchronised whatever produced them.                                                       */
+int rthc_linkage_from_forest_device(rthc_ctx *ctx, const uint64_t *d_keys, int64_t m, int64_t n,
+                                    double *Z_out);
 /* labels_out: T x n int32, row k = fcluster(Z, t[k], "distance") of the last linkage. */
 int rthc_cut(rthc_ctx *ctx, const double *t, int T, int32_t *labels_out);
 

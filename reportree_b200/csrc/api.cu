@@ -125,12 +125,30 @@ extern "C" void rthc_destroy(rthc_ctx *ctx)
     rthc_free_linkage_state(ctx);
     if (ctx->ev0) cudaEventDestroy(ctx->ev0);
     if (ctx->ev1) cudaEventDestroy(ctx->ev1);
+    for (int k = 0; k < 3; ++k)
+        if (ctx->h_pin[k]) cudaFreeHost(ctx->h_pin[k]);
     for (int k = 0; k < 2; ++k)
         if (ctx->ev_mark[k]) cudaEventDestroy(ctx->ev_mark[k]);
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
     if (ctx->pool) cudaMemPoolDestroy(ctx->pool);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
+}
+
+// page-locked staging slot of at least `bytes` (grown geometrically, contents not preserved); nullptr on failure
+void *rthc_pinned(rthc_ctx *ctx, int slot, size_t bytes)
+{
+    if (bytes <= ctx->h_pin_cap[slot] && ctx->h_pin[slot]) return ctx->h_pin[slot];
+    if (ctx->h_pin[slot]) { cudaFreeHost(ctx->h_pin[slot]); ctx->h_pin[slot] = nullptr; ctx->h_pin_cap[slot] = 0; }
+    const size_t cap = std::max<size_t>(bytes + bytes / 2, 4096);
+    if (cudaMallocHost(&ctx->h_pin[slot], cap) != cudaSuccess) {
+        cudaGetLastError();
+        ctx->h_pin[slot] = nullptr;
+        rthc_fail(ctx, RTHC_E_NOMEM, "page-locked allocation of %zu bytes failed", cap);
+        return nullptr;
+    }
+    ctx->h_pin_cap[slot] = cap;
+    return ctx->h_pin[slot];
 }
 
 // tile-row r of B is owned by rank (min(r, B-1-r) mod world): rows pair up long + short

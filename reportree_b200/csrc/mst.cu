@@ -380,6 +380,7 @@ __global__ void rthc_boruvka_scan_edges(const uint64_t *__restrict__ keys, int64
     int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (e >= m) return;
     const uint64_t key = keys[e];
+    if (key == RTHC_KEY_INF) return;                // padding of a fixed-size gather
     const int32_t ci = comp[rthc_key_i(key)], cj = comp[rthc_key_j(key)];
     if (ci == cj) return;
     if (key < best[ci]) atomicMin((unsigned long long *)&best[ci], (unsigned long long)key);
@@ -440,35 +441,67 @@ __global__ void rthc_bitonic_step(uint64_t *a, uint32_t j, uint32_t k, uint32_t 
     }
 }
 
-static int sort_keys_device(rthc_ctx *ctx, uint64_t *d_keys, int64_t m, uint64_t **d_sorted_out)
+// every bitonic step whose partner distance j is below BS_CHUNK stays inside one aligned chunk of BS_CHUNK keys:
+// one CTA runs all of them for k = k_first .. k_last in shared memory (one pair per thread per step)
+#define BS_CHUNK 2048u
+__global__ void __launch_bounds__(BS_CHUNK / 2) rthc_bitonic_local(uint64_t *a, uint32_t N, uint32_t k_first, uint32_t k_last)
 {
-    // pad to a power of two with +inf keys
+    __shared__ uint64_t s[BS_CHUNK];
+    const uint32_t base = blockIdx.x * BS_CHUNK, tid = threadIdx.x;
+    for (uint32_t t = tid; t < BS_CHUNK; t += BS_CHUNK / 2) s[t] = base + t < N ? a[base + t] : RTHC_KEY_INF;
+    __syncthreads();
+    for (uint32_t k = k_first; k <= k_last; k <<= 1) {
+        for (uint32_t j = min(k >> 1, BS_CHUNK >> 1); j > 0; j >>= 1) {
+            const uint32_t lo = ((tid & ~(j - 1)) << 1) | (tid & (j - 1)), hi = lo | j;
+            const bool asc = ((base + lo) & k) == 0;
+            const uint64_t x = s[lo], y = s[hi];
+            if ((x > y) == asc) { s[lo] = y; s[hi] = x; }
+            __syncthreads();
+        }
+    }
+    for (uint32_t t = tid; t < BS_CHUNK; t += BS_CHUNK / 2)
+        if (base + t < N) a[base + t] = s[t];
+}
+
+// ascending sort of m packed keys: returns a new pool buffer padded to a power of two with +inf keys
+static int sort_keys_device(rthc_ctx *ctx, const uint64_t *d_keys, int64_t m, uint64_t **d_sorted_out)
+{
     uint32_t N = 1;
     while ((int64_t)N < m) N <<= 1;
     uint64_t *d_pad = nullptr;
     int rc = rthc_dev_alloc(ctx, &d_pad, (size_t)N);
     if (rc) return rc;
-    rthc_fill_u64<<<(N + 255) / 256, 256, 0, ctx->stream>>>(d_pad, N, RTHC_KEY_INF);
-    RTHC_LAUNCH_CHECK(ctx);
+    if ((int64_t)N > m) {
+        rthc_fill_u64<<<(unsigned)((N - m + 255) / 256), 256, 0, ctx->stream>>>(d_pad + m, (int64_t)N - m, RTHC_KEY_INF);
+        RTHC_LAUNCH_CHECK(ctx);
+    }
     RTHC_CUDA(ctx, cudaMemcpyAsync(d_pad, d_keys, sizeof(uint64_t) * (size_t)m, cudaMemcpyDeviceToDevice,
                                    ctx->stream));
-    for (uint32_t k = 2; k <= N; k <<= 1)
-        for (uint32_t j = k >> 1; j > 0; j >>= 1) {
+    const unsigned nchunks = (N + BS_CHUNK - 1) / BS_CHUNK;
+    rthc_bitonic_local<<<nchunks, BS_CHUNK / 2, 0, ctx->stream>>>(d_pad, N, 2, std::min(N, BS_CHUNK));
+    RTHC_LAUNCH_CHECK(ctx);
+    for (uint32_t k = 2 * BS_CHUNK; k <= N && k != 0; k <<= 1) {
+        for (uint32_t j = k >> 1; j >= BS_CHUNK; j >>= 1) {
             rthc_bitonic_step<<<(N + 255) / 256, 256, 0, ctx->stream>>>(d_pad, j, k, N);
             RTHC_LAUNCH_CHECK(ctx);
         }
+        rthc_bitonic_local<<<nchunks, BS_CHUNK / 2, 0, ctx->stream>>>(d_pad, N, k, k);
+        RTHC_LAUNCH_CHECK(ctx);
+    }
     *d_sorted_out = d_pad;
     return 0;
 }
 
-// shared round loop: `scan` launches the lightest-edge pass for the current components
+// shared round loop: `scan` launches the lightest-edge pass for the current components.  The forest stays on the
+// device: *d_out (caller frees) holds *m_out keys, ascending when `sorted`.
 template <typename ScanFn>
-static int boruvka_rounds(rthc_ctx *ctx, int64_t n, ScanFn scan, std::vector<uint64_t> &keys_out)
+static int boruvka_rounds(rthc_ctx *ctx, int64_t n, ScanFn scan, bool sorted, uint64_t **d_out, int64_t *m_out)
 {
     int32_t *d_comp = nullptr, *d_parent = nullptr;
-    uint64_t *d_best = nullptr, *d_keys = nullptr, *d_sorted = nullptr;
+    uint64_t *d_best = nullptr, *d_keys = nullptr;
     unsigned int *d_count = nullptr;
     int rc;
+    *d_out = nullptr; *m_out = 0;
     if ((rc = rthc_dev_alloc(ctx, &d_comp, (size_t)n))) return rc;
     if ((rc = rthc_dev_alloc(ctx, &d_parent, (size_t)n))) return rc;
     if ((rc = rthc_dev_alloc(ctx, &d_best, (size_t)n))) return rc;
@@ -492,6 +525,7 @@ static int boruvka_rounds(rthc_ctx *ctx, int64_t n, ScanFn scan, std::vector<uin
         ++rounds;
         if (now == total) break;   // forest of a disconnected (sharded) edge set is complete
         total = now;
+        if ((int64_t)total >= n - 1) break;   // spanning tree complete: the components are not needed again
         for (int it = 0; it < 4; ++it) {      // 16x path compression bounds the chase below on adversarial chains
             rthc_pointer_jump<<<nb, 256, 0, ctx->stream>>>(d_parent, n);
             RTHC_LAUNCH_CHECK(ctx);
@@ -500,20 +534,31 @@ static int boruvka_rounds(rthc_ctx *ctx, int64_t n, ScanFn scan, std::vector<uin
         RTHC_LAUNCH_CHECK(ctx);
     }
     ctx->boruvka_rounds = rounds;
-    keys_out.resize(total);
-    if (total > 0) {
-        if ((rc = sort_keys_device(ctx, d_keys, (int64_t)total, &d_sorted))) return rc;
-        RTHC_CUDA(ctx, cudaMemcpyAsync(keys_out.data(), d_sorted, sizeof(uint64_t) * total,
-                                       cudaMemcpyDeviceToHost, ctx->stream));
-    }
-    RTHC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-    rthc_dev_free(ctx, &d_sorted);
     rthc_dev_free(ctx, &d_comp); rthc_dev_free(ctx, &d_parent); rthc_dev_free(ctx, &d_best);
-    rthc_dev_free(ctx, &d_keys); rthc_dev_free(ctx, &d_count);
+    rthc_dev_free(ctx, &d_count);
+    if (sorted && total > 0) {
+        uint64_t *d_sorted = nullptr;
+        if ((rc = sort_keys_device(ctx, d_keys, (int64_t)total, &d_sorted))) return rc;
+        rthc_dev_free(ctx, &d_keys);
+        d_keys = d_sorted;
+    }
+    *d_out = d_keys;
+    *m_out = (int64_t)total;
     return 0;
 }
 
-int rthc_boruvka_owned(rthc_ctx *ctx, std::vector<uint64_t> &keys)
+int rthc_keys_to_host(rthc_ctx *ctx, const uint64_t *d_keys, int64_t m, const uint64_t **h_keys)
+{
+    uint64_t *h = (uint64_t *)rthc_pinned(ctx, 0, sizeof(uint64_t) * (size_t)std::max<int64_t>(m, 1));
+    if (!h) return RTHC_E_NOMEM;
+    if (m > 0)
+        RTHC_CUDA(ctx, cudaMemcpyAsync(h, d_keys, sizeof(uint64_t) * (size_t)m, cudaMemcpyDeviceToHost, ctx->stream));
+    RTHC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    *h_keys = h;
+    return 0;
+}
+
+int rthc_boruvka_owned(rthc_ctx *ctx, bool sorted, uint64_t **d_keys, int64_t *m)
 {
     const int64_t n = ctx->n;
     const int64_t n_owned = (int64_t)ctx->h_owned_rows.size();
@@ -541,27 +586,20 @@ int rthc_boruvka_owned(rthc_ctx *ctx, std::vector<uint64_t> &keys)
         }
         return 0;
     };
-    const int rc = boruvka_rounds(ctx, n, scan, keys);
+    const int rc = boruvka_rounds(ctx, n, scan, sorted, d_keys, m);
     rthc_dev_free(ctx, &d_bands);
     return rc;
 }
 
-int rthc_boruvka_edge_list(rthc_ctx *ctx, const uint64_t *h_keys, int64_t m, int64_t n,
-                           std::vector<uint64_t> &keys)
+// d_in: m_in packed edges on the device, any order; +inf entries (padding of a fixed-size gather) are skipped
+int rthc_boruvka_edge_list(rthc_ctx *ctx, const uint64_t *d_in, int64_t m_in, int64_t n, uint64_t **d_keys, int64_t *m)
 {
-    uint64_t *d_in = nullptr;
-    int rc = rthc_dev_alloc(ctx, &d_in, (size_t)m);
-    if (rc) return rc;
-    RTHC_CUDA(ctx, cudaMemcpyAsync(d_in, h_keys, sizeof(uint64_t) * (size_t)m, cudaMemcpyHostToDevice,
-                                   ctx->stream));
     auto scan = [&](int32_t *d_comp, uint64_t *d_best) -> int {
-        if (m > 0) {
-            rthc_boruvka_scan_edges<<<(unsigned)((m + 255) / 256), 256, 0, ctx->stream>>>(d_in, m, d_comp, d_best);
+        if (m_in > 0) {
+            rthc_boruvka_scan_edges<<<(unsigned)((m_in + 255) / 256), 256, 0, ctx->stream>>>(d_in, m_in, d_comp, d_best);
             RTHC_LAUNCH_CHECK(ctx);
         }
         return 0;
     };
-    rc = boruvka_rounds(ctx, n, scan, keys);
-    rthc_dev_free(ctx, &d_in);
-    return rc;
+    return boruvka_rounds(ctx, n, scan, true, d_keys, m);
 }

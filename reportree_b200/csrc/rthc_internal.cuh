@@ -72,6 +72,11 @@ struct rthc_ctx {
     int32_t *d_up = nullptr;       // [levels][2n-1] binary-lifting table over d_tpar (built by the first cut)
     int up_levels = 0;
     std::vector<double> h_heights;
+    std::vector<int32_t> h_uf, h_cid, h_nsize;     // dendrogram bookkeeping scratch (linkage.cu), kept across calls
+    std::vector<int32_t> h_ex, h_ey;               // merges unpacked from packed keys
+    std::vector<double> h_ew;
+    void *h_pin[3] = {nullptr, nullptr, nullptr};  // page-locked staging: 0 keys (D2H), 1 tpar, 2 event (H2D)
+    size_t h_pin_cap[3] = {0, 0, 0};
     bool have_linkage = false;
     int boruvka_rounds = 0;
     int64_t row_scans = 0;
@@ -140,9 +145,13 @@ int rthc_run_distance(rthc_ctx *ctx);                                 // distanc
 int rthc_launch_distance_ws(rthc_ctx *ctx, int max_np);                // distance_ws.cu
 int rthc_run_direct_pairs(rthc_ctx *ctx, const int32_t *d_pi, const int32_t *d_pj, int64_t np,
                           int32_t *d_out);                            // distance.cu
-int rthc_boruvka_owned(rthc_ctx *ctx, std::vector<uint64_t> &keys);   // mst.cu
-int rthc_boruvka_edge_list(rthc_ctx *ctx, const uint64_t *h_keys, int64_t m, int64_t n,
-                           std::vector<uint64_t> &keys);              // mst.cu
+// Boruvka results stay on the device: *d_keys (pool allocation, caller frees with rthc_dev_free) holds *m packed
+// edges, ascending when `sorted`; rthc_keys_to_host copies them into the page-locked slot 0 and synchronises
+int rthc_boruvka_owned(rthc_ctx *ctx, bool sorted, uint64_t **d_keys, int64_t *m);              // mst.cu
+int rthc_boruvka_edge_list(rthc_ctx *ctx, const uint64_t *d_in, int64_t m_in, int64_t n, uint64_t **d_keys,
+                           int64_t *m);                                                         // mst.cu
+int rthc_keys_to_host(rthc_ctx *ctx, const uint64_t *d_keys, int64_t m, const uint64_t **h_keys); // mst.cu
+void *rthc_pinned(rthc_ctx *ctx, int slot, size_t bytes);                                       // api.cu
 int rthc_prim_exact(rthc_ctx *ctx, std::vector<int32_t> &ex, std::vector<int32_t> &ey,
                     std::vector<double> &ew);                         // mst.cu
 int rthc_nn_chain(rthc_ctx *ctx, int method, std::vector<int32_t> &ex, std::vector<int32_t> &ey,

@@ -61,6 +61,8 @@ def load_library():
         "rthc_linkage": (ci, [vp, ci, vp]),
         "rthc_local_forest": (ci, [vp, vp, ctypes.POINTER(i64)]),
         "rthc_linkage_from_forest": (ci, [vp, vp, i64, i64, vp]),
+        "rthc_local_forest_device": (ci, [vp, vp, i64, ctypes.POINTER(i64)]),
+        "rthc_linkage_from_forest_device": (ci, [vp, vp, i64, i64, vp]),
         "rthc_cut": (ci, [vp, vp, ci, vp]),
         "rthc_info": (ci, [vp, vp, ci]),
         "rthc_timings": (ci, [vp, vp, ci]),
@@ -87,7 +89,7 @@ EXPORTED_SYMBOLS = [
     "rthc_set_profiles_i32", "rthc_set_profiles_i32_device", "rthc_distance", "rthc_owned_pairs",
     "rthc_get_condensed_u16", "rthc_get_owned_condensed_u16", "rthc_copy_rows_u16", "rthc_direct_pairs",
     "rthc_set_condensed_f64", "rthc_set_single_algo", "rthc_linkage", "rthc_local_forest",
-    "rthc_linkage_from_forest", "rthc_cut", "rthc_info", "rthc_timings", "rthc_mark", "rthc_mark_elapsed_ms", "rthc_alu_peak",
+    "rthc_linkage_from_forest", "rthc_local_forest_device", "rthc_linkage_from_forest_device", "rthc_cut", "rthc_info", "rthc_timings", "rthc_mark", "rthc_mark_elapsed_ms", "rthc_alu_peak",
     "rthc_alu_peak_block", "rthc_closest", "rthc_subset_from",
     "rthc_contingency_adjacent", "rthc_adjusted_wallace_sums",
 ]
@@ -217,6 +219,20 @@ class HCContext:
         self.n = int(n)
         Z = np.empty((self.n - 1, 4), dtype=np.float64)
         self._check(self._L.rthc_linkage_from_forest(self._h, _ptr(keys), keys.size, self.n, _ptr(Z)))
+        return Z
+
+    def local_forest_device(self, device_ptr, capacity):
+        """Forest of the owned edges written (unsorted, +inf padded to `capacity` slots) into caller-owned
+        device memory, e.g. `tensor.data_ptr()` of an int64 torch tensor; returns the edge count."""
+        m = ctypes.c_int64(0)
+        self._check(self._L.rthc_local_forest_device(self._h, ctypes.c_void_p(int(device_ptr)), int(capacity), ctypes.byref(m)))
+        return m.value
+
+    def linkage_from_forest_device(self, device_ptr, m, n):
+        """Z from `m` gathered key slots in device memory (+inf slots are ignored)."""
+        self.n = int(n)
+        Z = np.empty((self.n - 1, 4), dtype=np.float64)
+        self._check(self._L.rthc_linkage_from_forest_device(self._h, ctypes.c_void_p(int(device_ptr)), int(m), self.n, _ptr(Z)))
         return Z
 
     def fcluster(self, thresholds, out=None):

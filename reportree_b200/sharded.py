@@ -63,3 +63,68 @@ def all_gather_forests(local_keys, n, dist, device=None):
     dist.all_gather(out, t)
     allk = torch.cat(out).cpu().numpy().view(np.uint64)
     return allk[allk != KEY_INF]
+
+
+class ForestExchange:
+    """The same exchange without leaving the device (NCCL): every rank's forest is written by the library
+    straight into a torch buffer of n-1 slots (+inf padded, `rthc_local_forest_device`), ONE
+    `all_gather_into_tensor` concatenates them, and rank 0 hands the gathered buffer to
+    `rthc_linkage_from_forest_device`.  Buffers are allocated once and reused every step."""
+
+    def __init__(self, n, dist, device="cuda"):
+        import torch
+        self.n, self.dist, self.torch = int(n), dist, torch
+        self.cap = max(self.n - 1, 1)
+        self.world = dist.get_world_size()
+        self.local = torch.empty(self.cap, dtype=torch.int64, device=device)
+        self.gathered = torch.empty(self.cap * self.world, dtype=torch.int64, device=device)
+
+    def local_forest(self, ctx):
+        """Boruvka over the owned tile-rows; returns this rank's edge count (synchronous)."""
+        return ctx.local_forest_device(self.local.data_ptr(), self.cap)
+
+    def gather(self):
+        """The one collective of the path; returns when the gathered keys are visible to any stream."""
+        self.dist.all_gather_into_tensor(self.gathered, self.local)
+        if self.gathered.is_cuda:
+            self.torch.cuda.current_stream().synchronize()
+        return self.gathered
+
+    def linkage(self, ctx):
+        """rank 0: final MST over the <= world*(n-1) gathered edges -> Z."""
+        return ctx.linkage_from_forest_device(self.gathered.data_ptr(), self.gathered.numel(), self.n)
+
+    def gathered_keys(self):
+        """Real (non-padding) keys of the last gather as uint64 numpy (tests / debugging)."""
+        k = self.gathered.cpu().numpy().view(np.uint64)
+        return k[k != KEY_INF]
+
+
+class ShardedProfileLoader:
+    """Host -> device load of the n x L int32 code matrix for world > 1: every rank copies only its own
+    block of ceil(n / world) rows over PCIe and one all_gather over NVLink replicates the matrix, instead
+    of `world` full copies competing for the host's memory bandwidth."""
+
+    def __init__(self, n, L, dist, device="cuda"):
+        import torch
+        self.n, self.L, self.dist, self.torch = int(n), int(L), dist, torch
+        self.world, self.rank = dist.get_world_size(), dist.get_rank()
+        self.rows = (self.n + self.world - 1) // self.world
+        self.block = torch.zeros((self.rows, self.L), dtype=torch.int32, device=device)
+        self.full = torch.empty((self.rows * self.world, self.L), dtype=torch.int32, device=device)
+        self.r0 = min(self.n, self.rank * self.rows)
+        self.r1 = min(self.n, self.r0 + self.rows)
+
+    def own_bytes(self):
+        return (self.r1 - self.r0) * self.L * 4
+
+    def load(self, host_codes):
+        """host_codes: C-contiguous int32 [n, L] (page-locked for full PCIe speed).  Returns the device
+        pointer of the replicated matrix (first n rows are the data)."""
+        t = self.torch
+        if self.r1 > self.r0:
+            self.block[: self.r1 - self.r0].copy_(t.from_numpy(host_codes[self.r0:self.r1]), non_blocking=True)
+        self.dist.all_gather_into_tensor(self.full, self.block)
+        if self.full.is_cuda:
+            t.cuda.current_stream().synchronize()
+        return self.full.data_ptr()

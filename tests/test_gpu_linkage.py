@@ -77,6 +77,60 @@ def test_forest_union_equals_single_gpu(hc, oracle):
             assert np.array_equal(lab[k], fcluster(Zfull, t, criterion="distance"))
 
 
+def test_forest_exchange_on_device_equals_single_gpu(hc):
+    # the NCCL path of bench.py without NCCL: forests written into torch buffers (+inf padded, unsorted),
+    # concatenated on the device, final MST from the device pointer
+    import torch
+    rng = np.random.default_rng(6)
+    n = 1100
+    X = _rand_codes(rng, n, 30, 3, 0.05)
+    with hc.HCContext() as full:
+        full.set_profiles(X)
+        full.distance()
+        Zfull = full.linkage("single")
+    for world in (2, 3):
+        bufs, counts = [], []
+        for rank in range(world):
+            with hc.HCContext(rank=rank, world=world) as ctx:
+                ctx.set_profiles(X)
+                ctx.distance()
+                t = torch.zeros(n - 1, dtype=torch.int64, device="cuda")
+                counts.append(ctx.local_forest_device(t.data_ptr(), n - 1))
+                host = ctx.local_forest()
+                got = t.cpu().numpy().view(np.uint64)
+                assert np.all(got[counts[-1]:] == np.uint64(0xFFFFFFFFFFFFFFFF))
+                assert np.array_equal(np.sort(got[: counts[-1]]), host)          # same forest as the host entry point
+                assert np.all(host[1:] > host[:-1])                              # which returns it ascending
+                bufs.append(t)
+        allk = torch.cat(bufs)
+        torch.cuda.synchronize()
+        assert sum(counts) >= n - 1
+        with hc.HCContext() as ctx:
+            Z = ctx.linkage_from_forest_device(allk.data_ptr(), allk.numel(), n)
+            assert np.array_equal(Z, Zfull)
+            lab = ctx.fcluster([0.0, 2.0])
+        for k, t in enumerate([0.0, 2.0]):
+            assert np.array_equal(lab[k], fcluster(Zfull, t, criterion="distance"))
+
+
+def test_device_sort_of_forest_keys_all_sizes(hc):
+    # the key sort (shared-memory bitonic chunks + global steps) through linkage_from_forest at sizes around
+    # the chunk boundaries: a path graph with shuffled, duplicated and padded keys
+    from reportree_b200 import sharded
+    rng = np.random.default_rng(8)
+    for n in (2, 3, 1025, 2049, 2050, 4097, 9000):
+        i = np.arange(n - 1)
+        w = rng.integers(0, 50, n - 1)
+        keys = sharded.pack_keys(w, i, i + 1)
+        extra = sharded.pack_keys(rng.integers(50, 60, n // 2), np.zeros(n // 2, dtype=np.int64), 1 + rng.integers(0, n - 1, n // 2))
+        allk = np.concatenate([keys, extra, keys[: n // 3]])
+        rng.shuffle(allk)
+        with hc.HCContext() as ctx:
+            Z = ctx.linkage_from_forest(allk, n)
+        assert np.array_equal(Z[:, 2], np.sort(w).astype(np.float64))
+        assert Z[-1, 3] == n
+
+
 def test_event_marks_and_stage_timings(hc):
     """rthc_mark / rthc_mark_elapsed_ms (bench.py's device-side step clock) and rthc_timings."""
     from reportree_b200 import synth

@@ -127,3 +127,77 @@ def test_ownership_is_a_balanced_partition():
             if n >= 128 * 2 * world:
                 pairs = [int(np.sum(n - 1 - r)) for r in rows]
                 assert max(pairs) - min(pairs) <= 2 * 128 * n
+
+
+class _FakeForestCtx:
+    """Stands in for HCContext in the exchange helpers: 'device' memory is host memory here."""
+
+    def __init__(self, keys):
+        self.keys = np.ascontiguousarray(keys, dtype=np.uint64)
+        self.seen = None
+
+    def local_forest_device(self, ptr, capacity):
+        import ctypes
+        buf = np.full(capacity, np.uint64(0xFFFFFFFFFFFFFFFF), dtype=np.uint64)
+        buf[: self.keys.size] = self.keys[::-1]                     # unsorted on purpose
+        ctypes.memmove(ptr, buf.ctypes.data, buf.nbytes)
+        return int(self.keys.size)
+
+    def linkage_from_forest_device(self, ptr, m, n):
+        import ctypes
+        out = np.empty(m, dtype=np.uint64)
+        ctypes.memmove(out.ctypes.data, ptr, out.nbytes)
+        self.seen = out
+        return out
+
+
+def _exchange_worker(rank, world, port, n, L, q):
+    sys.path.insert(0, ROOT)
+    import torch.distributed as dist
+    from reportree_b200 import sharded
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    # forests of different lengths per rank (rank r holds r + 2 edges)
+    mine = sharded.pack_keys(np.arange(rank + 2) + 10 * rank, np.arange(rank + 2), np.arange(rank + 2) + 1)
+    ctx = _FakeForestCtx(mine)
+    ex = sharded.ForestExchange(n, dist, device="cpu")
+    m = ex.local_forest(ctx)
+    ex.gather()
+    slots = ex.linkage(ctx)
+    real = ex.gathered_keys()
+    # host matrix -> every rank copies its own row block, one all_gather replicates it
+    X = (np.arange(n * L, dtype=np.int32).reshape(n, L) * 7) % 1001
+    ld = sharded.ShardedProfileLoader(n, L, dist, device="cpu")
+    ptr = ld.load(X)
+    assert ptr == ld.full.data_ptr()
+    q.put((rank, m, slots.size, real, ld.full.numpy()[:n].copy(), ld.own_bytes()))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_device_resident_exchange_helpers_over_gloo(world):
+    """ForestExchange / ShardedProfileLoader (the NCCL path of bench.py) with CPU tensors: padding, one
+    all_gather_into_tensor each, ragged row blocks (n not divisible by world)."""
+    from reportree_b200 import sharded
+    n, L = 11, 5
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_exchange_worker, args=(r, world, port, n, L, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    got = [q.get(timeout=120) for _ in range(world)]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    X = (np.arange(n * L, dtype=np.int32).reshape(n, L) * 7) % 1001
+    expect = np.sort(np.concatenate([sharded.pack_keys(np.arange(r + 2) + 10 * r, np.arange(r + 2), np.arange(r + 2) + 1)
+                                     for r in range(world)]))
+    for rank, m, slots, real, full, own in got:
+        assert m == rank + 2
+        assert slots == world * (n - 1)                      # fixed-size gather
+        assert np.array_equal(np.sort(real), expect)         # every rank sees every forest, padding dropped
+        assert np.array_equal(full, X)
+    assert sum(g[5] for g in got) == n * L * 4               # the H2D bytes add up to one copy of the matrix
