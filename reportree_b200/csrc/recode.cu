@@ -62,21 +62,43 @@ rthc_rank_columns(const int32_t *__restrict__ colmajor, uint16_t *__restrict__ c
     uint16_t *dst = codes + (int64_t)col * n_pad;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 
+    __shared__ int32_t s_vmax;
     for (int w = tid; w < (int)BITMAP_WORDS; w += RANK_THREADS) bm[w] = 0;
+    if (tid == 0) s_vmax = 0;
     __syncthreads();
+    // mark: four independent loads in flight per thread; a bit that is already set (the common alleles, after
+    // the first few rows) is not set again, which takes the same-word atomics of a skewed locus off the path
     bool big = false;
-    for (int64_t r = tid; r < n; r += RANK_THREADS) {
-        int32_t v = src[r];
-        if (v > 0) {
-            if ((uint32_t)v >= BITMAP_BITS) big = true;
-            else atomicOr(&bm[v >> 5], 1u << (v & 31));
+    int32_t vmax = 0;
+    const volatile uint32_t *vbm = bm;
+    for (int64_t r0 = tid; r0 < n; r0 += 4 * RANK_THREADS) {
+        int32_t v[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int64_t r = r0 + (int64_t)u * RANK_THREADS;
+            v[u] = r < n ? __ldg(src + r) : 0;
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            if (v[u] > 0) {
+                if ((uint32_t)v[u] >= BITMAP_BITS) big = true;
+                else {
+                    vmax = max(vmax, v[u]);
+                    const uint32_t bit = 1u << (v[u] & 31);
+                    if (!(vbm[v[u] >> 5] & bit)) atomicOr(&bm[v[u] >> 5], bit);
+                }
+            }
         }
     }
     if (big) atomicOr(status, 1);
+    vmax = __reduce_max_sync(0xffffffffu, vmax);
+    if (lane == 0 && vmax > 0) atomicMax(&s_vmax, vmax);
     __syncthreads();
-    // warp w owns words [1024 w, 1024 (w+1)); conflict-free row-by-row scan
+    // warp w owns words [1024 w, 1024 (w+1)); conflict-free row-by-row scan, cut off behind the largest id seen
+    const int used_words = (s_vmax >> 5) + 1;
     uint32_t running = 0;
     for (int k = 0; k < 32; ++k) {
+        if (warp * 1024 + k * 32 >= used_words) break;             // uniform per warp
         int idx = warp * 1024 + k * 32 + lane;
         uint32_t c = __popc(bm[idx]);
         uint32_t inc = c;
@@ -106,17 +128,25 @@ rthc_rank_columns(const int32_t *__restrict__ colmajor, uint16_t *__restrict__ c
         n_alleles[col] = (int32_t)total;
         if (total > 65535u) atomicOr(status, 2);
     }
-    for (int64_t r = tid; r < n_pad; r += RANK_THREADS) {
-        uint16_t code = 0;
-        if (r < n) {
-            int32_t v = src[r];
-            if (v > 0 && (uint32_t)v < BITMAP_BITS) {
-                uint32_t w = (uint32_t)v >> 5;
-                uint32_t below = __popc(bm[w] & ((1u << (v & 31)) - 1u));
+    for (int64_t r0 = tid; r0 < n_pad; r0 += 4 * RANK_THREADS) {
+        int32_t v[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int64_t r = r0 + (int64_t)u * RANK_THREADS;
+            v[u] = r < n ? __ldg(src + r) : 0;
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int64_t r = r0 + (int64_t)u * RANK_THREADS;
+            if (r >= n_pad) break;
+            uint16_t code = 0;
+            if (v[u] > 0 && (uint32_t)v[u] < BITMAP_BITS) {
+                uint32_t w = (uint32_t)v[u] >> 5;
+                uint32_t below = __popc(bm[w] & ((1u << (v[u] & 31)) - 1u));
                 code = (uint16_t)(1u + warp_off[w >> 10] + pre[w] + below);
             }
+            dst[r] = code;
         }
-        dst[r] = code;
     }
 }
 
@@ -200,6 +230,31 @@ rthc_rank_column_wide(const int32_t *__restrict__ colmajor, uint16_t *__restrict
 }
 
 // ---- 3. bit-slice 32 loci into plane words --------------------------------------------
+// grid.y = group; the plane count of a group is uniform per CTA, so the bit loop is compiled per width
+template <int BITS>
+__device__ __forceinline__ void pack_group(const uint16_t *__restrict__ codes, const int32_t *__restrict__ perm, int g,
+                                           int64_t off, uint32_t *__restrict__ planes, int64_t n_pad, int plane_rows, int64_t s)
+{
+    uint32_t pl[BITS];
+#pragma unroll
+    for (int k = 0; k < BITS; ++k) pl[k] = 0;
+    uint32_t valid = 0;
+#pragma unroll 8
+    for (int l = 0; l < 32; ++l) {
+        int col = perm[g * 32 + l];
+        uint32_t c = col < 0 ? 0u : (uint32_t)codes[(int64_t)col * n_pad + s];
+        valid |= (c != 0u ? 1u : 0u) << l;
+#pragma unroll
+        for (int k = 0; k < BITS; ++k) pl[k] |= ((c >> k) & 1u) << l;
+    }
+    // tile-blocked layout: [s / 64][plane row][s % 64]
+    const int64_t blk = (s / RTHC_BLK) * (int64_t)plane_rows;
+    const int64_t lane_s = s % RTHC_BLK;
+#pragma unroll
+    for (int k = 0; k < BITS; ++k) planes[(blk + off + k) * RTHC_BLK + lane_s] = pl[k];
+    planes[(blk + off + BITS) * RTHC_BLK + lane_s] = valid;
+}
+
 __global__ void rthc_pack_planes(const uint16_t *__restrict__ codes, const int32_t *__restrict__ perm,
                                  const int32_t *__restrict__ grp_off, const int32_t *__restrict__ grp_np,
                                  uint32_t *__restrict__ planes, int64_t n_pad, int plane_rows)
@@ -208,26 +263,15 @@ __global__ void rthc_pack_planes(const uint16_t *__restrict__ codes, const int32
     const int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (s >= n_pad) return;
     const int bits = grp_np[g] - 1;
-    uint32_t pl[16];
-#pragma unroll
-    for (int k = 0; k < 16; ++k) pl[k] = 0;
-    uint32_t valid = 0;
-#pragma unroll 4
-    for (int l = 0; l < 32; ++l) {
-        int col = perm[g * 32 + l];
-        uint32_t c = col < 0 ? 0u : (uint32_t)codes[(int64_t)col * n_pad + s];
-        valid |= (c != 0u ? 1u : 0u) << l;
-#pragma unroll
-        for (int k = 0; k < 16; ++k) pl[k] |= ((c >> k) & 1u) << l;
-    }
-    // tile-blocked layout: [s / 64][plane row][s % 64]
     const int64_t off = grp_off[g];
-    const int64_t blk = (s / RTHC_BLK) * (int64_t)plane_rows;
-    const int64_t lane_s = s % RTHC_BLK;
-#pragma unroll
-    for (int k = 0; k < 16; ++k)
-        if (k < bits) planes[(blk + off + k) * RTHC_BLK + lane_s] = pl[k];
-    planes[(blk + off + bits) * RTHC_BLK + lane_s] = valid;
+#define RTHC_PACK_CASE(B) case B: pack_group<B>(codes, perm, g, off, planes, n_pad, plane_rows, s); break;
+    switch (bits) {
+        RTHC_PACK_CASE(3) RTHC_PACK_CASE(4) RTHC_PACK_CASE(5) RTHC_PACK_CASE(6) RTHC_PACK_CASE(7) RTHC_PACK_CASE(8)
+        RTHC_PACK_CASE(9) RTHC_PACK_CASE(10) RTHC_PACK_CASE(11) RTHC_PACK_CASE(12) RTHC_PACK_CASE(13)
+        RTHC_PACK_CASE(14) RTHC_PACK_CASE(15)
+    default: pack_group<16>(codes, perm, g, off, planes, n_pad, plane_rows, s); break;
+    }
+#undef RTHC_PACK_CASE
 }
 
 // ---- host driver -----------------------------------------------------------------------

@@ -76,6 +76,32 @@ def test_large_allele_ids_slow_path(hc, oracle):
     assert np.array_equal(got, ref)
 
 
+def test_sixteen_bit_loci_and_the_uint16_limit(hc, oracle):
+    # a locus with > 32,767 distinct called alleles needs all 16 bit planes (the widest plane packer);
+    # one more than 65,535 cannot be coded and must fail loudly, not wrap
+    rng = np.random.default_rng(19)
+    n = 33500
+    X = np.zeros((n, 3), dtype=np.int32)
+    X[:, 0] = rng.permutation(n) + 1                       # every sample its own allele: 16 bits
+    X[:, 1] = rng.integers(1, 40000, n)                    # ~ 22,000 distinct: 15 bits
+    X[:, 2] = rng.integers(0, 4, n)                        # 3 alleles + missing
+    X[rng.random(n) < 0.01, 0] = 0
+    with hc.HCContext() as ctx:
+        ctx.set_profiles(X)
+        info = ctx.info()
+        assert info["plane_rows"] == 17 and info["max_alleles"] >= 32768      # 16 bit planes + the valid plane
+        ctx.distance()
+        rows = ctx.square_rows(n - 700, 700)
+    ref = oracle.dist_square(np.ascontiguousarray(X[n - 2000:]))[-700:, :]
+    assert np.array_equal(rows[:, n - 2000:].astype(np.int32), ref)
+    head = (X[n - 700:, None, :] != X[None, :50, :]) & (X[n - 700:, None, :] != 0) & (X[None, :50, :] != 0)
+    assert np.array_equal(rows[:, :50].astype(np.int32), head.sum(axis=2))
+    Y = (np.arange(65537, dtype=np.int32) + 1).reshape(-1, 1).repeat(2, axis=1)
+    with hc.HCContext() as ctx:
+        with pytest.raises(hc.HCBackendError, match="65,535"):
+            ctx.set_profiles(np.ascontiguousarray(Y))
+
+
 def test_negative_codes_are_missing(hc, oracle):
     rng = np.random.default_rng(17)
     X = _rand_codes(rng, 64, 64, 5, 0.0)
