@@ -49,7 +49,7 @@ enum {
 };
 
 /* linkage methods (names follow scipy / --HC-threshold) */
-enum { RTHC_SINGLE = 0, RTHC_COMPLETE = 1, RTHC_AVERAGE = 2, RTHC_WEIGHTED = 3 };
+enum { RTHC_SINGLE = 0, RTHC_COMPLETE = 1, RTHC_AVERAGE = 2, RTHC_WEIGHTED = 3, RTHC_WARD = 4 };
 
 /* single-linkage algorithm selection for rthc_linkage(RTHC_SINGLE):
  *   RTHC_SL_BORUVKA : GPU Boruvka MST under the total order (w, i, j); membership at

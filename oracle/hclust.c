@@ -6,7 +6,7 @@
  *
  *   linkage(y, "single")                      scripts/partitioning_HC.py:197
  *       -> _hierarchy.mst_single_linkage + label   (scipy _hierarchy_impl.py:960-961)
- *   linkage(y, "complete"|"average"|"weighted")
+ *   linkage(y, "complete"|"average"|"weighted"|"ward")
  *       -> _hierarchy.nn_chain + label             (scipy _hierarchy_impl.py:962-963)
  *   maxdists(Z)[-1]                           scripts/partitioning_HC.py:198
  *   fcluster(Z, t, criterion="distance")      scripts/partitioning_HC.py:649,689,722,751
@@ -128,13 +128,21 @@ void oracle_prim_edges(const double *y, int64_t n, double *Z3)
     free(merged); free(D);
 }
 
-/* method: 1 complete, 2 average, 3 weighted (0 single is allowed too: min) */
-static inline double lance_williams(int method, double dxi, double dyi, double nx, double ny)
+/* method: 1 complete, 2 average, 3 weighted, 4 ward (0 single is allowed too: min).
+ * Ward: scipy's update takes t = 1/(nx+ny+ni) first and multiplies left to right; any other
+ * association rounds differently (pinned on the live scipy, tests/test_oracle_golden.py). */
+static inline double lance_williams(int method, double dxi, double dyi, double dxy, int64_t nx, int64_t ny,
+                                    int64_t ni)
 {
     switch (method) {
     case 0: return dxi < dyi ? dxi : dyi;
     case 1: return dxi > dyi ? dxi : dyi;
-    case 2: return (nx * dxi + ny * dyi) / (nx + ny);
+    case 2: return ((double)nx * dxi + (double)ny * dyi) / ((double)nx + (double)ny);
+    case 4: {
+        double t = 1.0 / (double)(nx + ny + ni);
+        return sqrt((double)(ni + nx) * t * dxi * dxi + (double)(ni + ny) * t * dyi * dyi
+                    - (double)ni * t * dxy * dxy);
+    }
     default: return 0.5 * (dxi + dyi);
     }
 }
@@ -177,8 +185,7 @@ void oracle_linkage_nn_chain(const double *y_in, int64_t n, int method, double *
         size[x] = 0; size[yv] = nx + ny;
         for (int64_t i = 0; i < n; ++i) {
             if (size[i] == 0 || i == yv) continue;
-            D[cidx(n, i, yv)] = lance_williams(method, D[cidx(n, i, x)], D[cidx(n, i, yv)],
-                                               (double)nx, (double)ny);
+            D[cidx(n, i, yv)] = lance_williams(method, D[cidx(n, i, x)], D[cidx(n, i, yv)], cur, nx, ny, size[i]);
         }
     }
     int64_t *order = (int64_t *)malloc(sizeof(int64_t) * (size_t)(m > 0 ? m : 1));

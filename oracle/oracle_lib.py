@@ -77,7 +77,7 @@ def dist_condensed(codes):
     return dist_condensed_rows(codes, 0, codes.shape[0])
 
 
-METHODS = {"single": 0, "complete": 1, "average": 2, "weighted": 3}
+METHODS = {"single": 0, "complete": 1, "average": 2, "weighted": 3, "ward": 4}
 
 
 def linkage(y, method):

@@ -135,7 +135,7 @@ extern "C" int rthc_linkage(rthc_ctx *ctx, int method, double *Z_out)
     } else if (method == RTHC_SINGLE) {
         if ((rc = rthc_prim_exact(ctx, ex, ey, ew))) return rc;
         stable_sort_merges(ex, ey, ew);
-    } else if (method == RTHC_COMPLETE || method == RTHC_AVERAGE || method == RTHC_WEIGHTED) {
+    } else if (method == RTHC_COMPLETE || method == RTHC_AVERAGE || method == RTHC_WEIGHTED || method == RTHC_WARD) {
         if ((rc = rthc_nn_chain(ctx, method, ex, ey, ew))) return rc;
         stable_sort_merges(ex, ey, ew);
     } else {

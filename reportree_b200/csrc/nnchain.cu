@@ -6,7 +6,7 @@
 //    keys (scipy's "first strictly smaller wins").  The edge list therefore equals scipy's,
 //    and Z is byte-identical after the stable sort + label pass (linkage.cu).
 //  * rthc_nn_chain   : scipy `_hierarchy.nn_chain` (scipy _hierarchy_impl.py:962-963) for
-//    complete / average / weighted: nearest-neighbour chain with scipy's tie rule (the previous
+//    complete / average / weighted / ward: nearest-neighbour chain with scipy's tie rule (the previous
 //    chain element wins ties, otherwise the lowest index of the minimum), Lance-Williams row
 //    update in HBM.  Works on a square working copy of the matrix so that every row scan and
 //    row update is contiguous; uint16 for complete linkage on integer distances, float64
@@ -180,15 +180,28 @@ int rthc_prim_exact(rthc_ctx *ctx, std::vector<int32_t> &ex, std::vector<int32_t
 // ---------------------------------------------------------------------------------------------
 // NN-chain merge loop on a square working matrix
 // ---------------------------------------------------------------------------------------------
-template <typename T> __device__ __forceinline__ T lance_williams(int method, T dx, T dy, double nx, double ny);
-template <> __device__ __forceinline__ uint16_t lance_williams<uint16_t>(int, uint16_t dx, uint16_t dy, double, double)
+template <typename T>
+__device__ __forceinline__ T lance_williams(int method, T dx, T dy, double dxy, int nx, int ny, int ni);
+template <>
+__device__ __forceinline__ uint16_t lance_williams<uint16_t>(int, uint16_t dx, uint16_t dy, double, int, int, int)
 {
     return dx > dy ? dx : dy;                                   // complete linkage on integer distances
 }
-template <> __device__ __forceinline__ double lance_williams<double>(int method, double dx, double dy, double nx, double ny)
+template <>
+__device__ __forceinline__ double lance_williams<double>(int method, double dx, double dy, double dxy, int nx, int ny,
+                                                         int ni)
 {
     if (method == RTHC_COMPLETE) return dx > dy ? dx : dy;
-    if (method == RTHC_AVERAGE) return __ddiv_rn(__dadd_rn(__dmul_rn(nx, dx), __dmul_rn(ny, dy)), __dadd_rn(nx, ny));
+    if (method == RTHC_AVERAGE)
+        return __ddiv_rn(__dadd_rn(__dmul_rn((double)nx, dx), __dmul_rn((double)ny, dy)), __dadd_rn((double)nx, (double)ny));
+    if (method == RTHC_WARD) {
+        // scipy's association: t = 1/(nx+ny+ni); ((ni+nx)*t*dx)*dx + ((ni+ny)*t*dy)*dy - ((ni*t)*dxy)*dxy
+        const double t = __ddiv_rn(1.0, (double)(nx + ny + ni));
+        const double a = __dmul_rn(__dmul_rn(__dmul_rn((double)(ni + nx), t), dx), dx);
+        const double b = __dmul_rn(__dmul_rn(__dmul_rn((double)(ni + ny), t), dy), dy);
+        const double c = __dmul_rn(__dmul_rn(__dmul_rn((double)ni, t), dxy), dxy);
+        return __dsqrt_rn(__dsub_rn(__dadd_rn(a, b), c));
+    }
     return __dmul_rn(0.5, __dadd_rn(dx, dy));                   // weighted
 }
 
@@ -271,9 +284,11 @@ rthc_nn_chain_kernel(T *W, int64_t n, int method, int32_t *size, int32_t *chain,
         if (leader) { ex[k] = a; ey[k] = b; ew[k] = from_bits(dmin, T()); }
         const T *ra = W + (int64_t)a * n;
         T *rb = W + (int64_t)b * n;
+        const double dab = from_bits(dmin, T());
         for (int64_t i = gtid; i < n; i += gthreads) {
-            if (i == a || i == b || __ldcg(&size[i]) == 0) continue;
-            const T v = lance_williams<T>(method, __ldcg(&ra[i]), __ldcg(&rb[i]), (double)na, (double)nb);
+            int32_t ni;
+            if (i == a || i == b || (ni = __ldcg(&size[i])) == 0) continue;
+            const T v = lance_williams<T>(method, __ldcg(&ra[i]), __ldcg(&rb[i]), dab, na, nb, ni);
             rb[i] = v;                       // row b (contiguous)
             W[i * n + b] = v;                // column b (symmetric copy)
         }

@@ -18,7 +18,7 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("RTHC_LIB_PATH") or os.path.join(_HERE, "libreportree_hc.so")   # override: kernel experiments only
 
-METHODS = {"single": 0, "complete": 1, "average": 2, "weighted": 3}
+METHODS = {"single": 0, "complete": 1, "average": 2, "weighted": 3, "ward": 4}
 SL_BORUVKA, SL_PRIM = 0, 1
 
 

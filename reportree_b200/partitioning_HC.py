@@ -32,7 +32,7 @@ from reportree_b200 import hostio
 version = "1.9.0"
 last_updated = "2025-10-21"
 
-GPU_METHODS = ("single", "complete", "average", "weighted")
+GPU_METHODS = ("single", "complete", "average", "weighted", "ward")
 
 
 class Phases:

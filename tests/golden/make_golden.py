@@ -8,6 +8,9 @@ C1: tests/allele_matrix.tsv, --HC-threshold single-1-10           (BASELINE.json
 C1b: same matrix, single,complete,average,weighted all thresholds + --loci-called 0.9
 C2: examples/Listeria/input/Listeria_alleles.tsv, single-1-50     (BASELINE.json configs[1])
 C2b: Listeria with --loci-called 0.95 --site-inclusion 0.99, complete-1-30,average-5
+C1c: tests/allele_matrix.tsv, ward at all thresholds + complete-3    (ward = scipy nn_chain, float heights)
+C2c: Listeria with --loci-called 0.95, ward-1-60 + --pct-HC-threshold ward-0.01
+Case names on the command line regenerate only those cases.
 Also stores the Listeria golden distance pair shipped with the reference
 (examples/Listeria/output/Lm_flt_samples_matrix.tsv -> Lm_dist_hamming.tsv) as compact arrays.
 """
@@ -33,6 +36,9 @@ CASES = {
     "C2b": (REF + "/examples/Listeria/input/Listeria_alleles.tsv",
             ["--HC-threshold", "complete-1-30,average-5", "--pct-HC-threshold", "single-0.004",
              "--loci-called", "0.95", "--site-inclusion", "0.99"]),
+    "C1c": (REF + "/tests/allele_matrix.tsv", ["--HC-threshold", "ward,complete-3"]),
+    "C2c": (REF + "/examples/Listeria/input/Listeria_alleles.tsv",
+            ["--HC-threshold", "ward-1-60", "--pct-HC-threshold", "ward-0.01", "--loci-called", "0.95"]),
 }
 KEEP = ["_partitions.tsv", "_clusterComposition.tsv", "_loci_report.tsv", "_loci_used.txt",
         "_parcentage2threshold.tsv"]
@@ -42,7 +48,10 @@ def main():
     from oracle import oracle_lib
     oracle_lib.build()
     env = dict(os.environ, PATH=os.path.dirname(oracle_lib.CGMLST_DISTS_BIN) + ":" + os.environ["PATH"])
+    only = sys.argv[1:]
     for name, (inp, extra) in CASES.items():
+        if only and name not in only:
+            continue
         tmp = tempfile.mkdtemp()
         tag = os.path.join(tmp, name)
         cmd = [sys.executable, REF + "/scripts/partitioning_HC.py", "-a", inp, "-o", tag] + extra
@@ -68,6 +77,8 @@ def main():
             fh.write("\n".join(lines))
         shutil.rmtree(tmp)
         print("golden", name, "ok")
+    if only:
+        return
     # the reference's own shipped distance golden
     mx = pd.read_table(REF + "/examples/Listeria/output/Lm_flt_samples_matrix.tsv", dtype=str)
     g = pd.read_table(REF + "/examples/Listeria/output/Lm_dist_hamming.tsv")

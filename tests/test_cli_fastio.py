@@ -133,6 +133,8 @@ GOLD = {
     "C1b": ("allele_matrix.tsv.gz", ["--HC-threshold", "single,complete,average,weighted", "--loci-called", "0.9"]),
     "C2b": ("Listeria_alleles.tsv.gz", ["--HC-threshold", "complete-1-30,average-5", "--pct-HC-threshold", "single-0.004",
                                          "--loci-called", "0.95", "--site-inclusion", "0.99"]),
+    "C1c": ("allele_matrix.tsv.gz", ["--HC-threshold", "ward,complete-3"]),
+    "C2c": ("Listeria_alleles.tsv.gz", ["--HC-threshold", "ward-1-60", "--pct-HC-threshold", "ward-0.01", "--loci-called", "0.95"]),
 }
 
 

@@ -45,7 +45,7 @@ def test_oracle_linkage_and_fcluster_equal_scipy_on_tie_heavy_matrices(oracle):
     for _ in range(150):
         n = int(rng.integers(2, 45))
         y = rng.integers(0, int(rng.integers(2, 9)), size=n * (n - 1) // 2).astype(np.float64)
-        for method in ("single", "complete", "average", "weighted"):
+        for method in ("single", "complete", "average", "weighted", "ward"):
             Zs = linkage(y, method)
             Zo = oracle.linkage(y, method)
             assert np.array_equal(Zs, Zo), (method, n)
