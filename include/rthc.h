@@ -110,7 +110,10 @@ int rthc_set_condensed_f64(rthc_ctx *ctx, const double *y, int64_t n);
 
 /* ---- clustering half --------------------------------------------------------- */
 int rthc_set_single_algo(rthc_ctx *ctx, int algo);
-/* Z_out: (n-1) x 4 float64, scipy linkage layout.  Full shard only.               */
+/* Z_out: (n-1) x 4 float64, scipy linkage layout.  Full shard only.
+ * method = RTHC_SINGLE .. RTHC_WARD: replaces scipy linkage(y, method) at
+ * scripts/partitioning_HC.py:197 (complete / average / weighted / ward = scipy nn_chain,
+ * same merge order, same floating-point operation order, so Z is byte-identical).   */
 int rthc_linkage(rthc_ctx *ctx, int method, double *Z_out);
 /* multi-GPU single linkage: minimum spanning forest of the owned edges.
  * keys_out holds up to n-1 packed edges (w<<48 | i<<24 | j); *m_out = count.       */

@@ -19,7 +19,9 @@ if "C3" in which:
         Za, t3 = t(lambda: ctx.linkage("average")); scans_a = ctx.info()["row_scans"]
         lab, t4 = t(lambda: ctx.fcluster(np.arange(0, 51.0)))
         Zc, t5 = t(lambda: ctx.linkage("complete")); scans_c = ctx.info()["row_scans"]
+        Zw, t6 = t(lambda: ctx.linkage("ward")); scans_w = ctx.info()["row_scans"]
         y = ctx.condensed()
+    print(f"C3 ward {t6:.3f}s ({scans_w} scans)")
     print(f"C3 20000x3002: set {ts:.3f}s dist {td:.3f}s boruvka {t1:.3f}s prim {t2:.3f}s average {t3:.3f}s ({scans_a} scans) "
           f"cut51(avg) {t4:.3f}s complete {t5:.3f}s ({scans_c} scans)")
     if "--verify" in sys.argv:
@@ -31,6 +33,7 @@ if "C3" in which:
         Z, ta = t(lambda: linkage(yf, "single")); print("  scipy single", round(ta, 2), "s  Z equal (prim):", np.array_equal(Z, Zp),
                                                         " heights equal (boruvka):", np.array_equal(Z[:, 2], Zs[:, 2]))
         Z, ta = t(lambda: linkage(yf, "complete")); print("  scipy complete", round(ta, 2), "s  Z equal:", np.array_equal(Z, Zc))
+        Z, ta = t(lambda: linkage(yf, "ward")); print("  scipy ward", round(ta, 2), "s  Z equal:", np.array_equal(Z, Zw))
 
 if "C5" in which:
     cfg = synth.config("C5")

@@ -31,7 +31,7 @@ def test_prim_exact_z_equals_scipy(hc, n, L, max_allele):
         assert np.array_equal(lab[k], fcluster(Zs, t, criterion="distance"))
 
 
-@pytest.mark.parametrize("method", ["complete", "average", "weighted"])
+@pytest.mark.parametrize("method", ["complete", "average", "weighted", "ward"])
 @pytest.mark.parametrize("n,L,max_allele", [(2, 3, 2), (3, 4, 2), (12, 6, 2), (150, 14, 3), (900, 40, 4)])
 def test_nn_chain_z_equals_scipy(hc, method, n, L, max_allele):
     rng = np.random.default_rng(11 * n + L)
@@ -50,7 +50,7 @@ def test_nn_chain_z_equals_scipy(hc, method, n, L, max_allele):
         assert np.array_equal(lab[k], fcluster(Zs, t, criterion="distance")), t
 
 
-@pytest.mark.parametrize("method", ["single", "complete", "average", "weighted"])
+@pytest.mark.parametrize("method", ["single", "complete", "average", "weighted", "ward"])
 def test_external_matrix_integer_and_float(hc, method):
     rng = np.random.default_rng(101)
     n = 300

@@ -74,7 +74,7 @@ def test_closest_on_computed_distances_with_heavy_ties():
             ctx.closest(3000, 1)
 
 
-@pytest.mark.parametrize("method", ["single", "complete", "average", "weighted"])
+@pytest.mark.parametrize("method", ["single", "complete", "average", "weighted", "ward"])
 def test_subset_clustering_equals_scipy_on_the_sub_matrix(method):
     rng = np.random.default_rng(5)
     codes = random_profiles(rng, 1500, 120)
