@@ -296,7 +296,9 @@ static int check_shape(rthc_ctx *ctx, int64_t n, int64_t L)
     if (n < 2) return rthc_fail(ctx, RTHC_E_ARG, "need at least 2 samples (n=%lld)", (long long)n);
     if (L < 1) return rthc_fail(ctx, RTHC_E_ARG, "need at least 1 locus (L=%lld)", (long long)L);
     if (n >= (1ll << 24)) return rthc_fail(ctx, RTHC_E_RANGE, "n=%lld exceeds 2^24-1 samples", (long long)n);
-    if (L > 65535) return rthc_fail(ctx, RTHC_E_RANGE, "L=%lld exceeds 65,535 loci (uint16 distances)", (long long)L);
+    // SNP matrices can be far wider than 65,535 columns; what bounds a uint16 distance is the number of
+    // loci that can mismatch at all (>= 2 called alleles), checked by the re-coder once it knows them
+    if (L >= (1ll << 24)) return rthc_fail(ctx, RTHC_E_RANGE, "L=%lld exceeds 2^24-1 loci", (long long)L);
     return 0;
 }
 

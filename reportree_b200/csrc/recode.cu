@@ -367,6 +367,12 @@ int rthc_recode_and_pack(rthc_ctx *ctx, const int32_t *d_rowmajor)
     std::stable_sort(kept.begin(), kept.end(), [&](int32_t a, int32_t b) {
         return bit_width(nall[(size_t)a]) > bit_width(nall[(size_t)b]);
     });
+    if (kept.size() > 65535) {
+        rthc_dev_free(ctx, &d_nall); rthc_dev_free(ctx, &d_status);
+        return rthc_fail(ctx, RTHC_E_RANGE, "%lld of the %lld loci have two or more called alleles; distances are "
+                         "stored as uint16, so at most 65,535 such loci are supported",
+                         (long long)kept.size(), (long long)L);
+    }
     ctx->max_alleles = max_all;
     ctx->L_kept = (int64_t)kept.size();
     const int G = (int)((kept.size() + 31) / 32);

@@ -102,6 +102,33 @@ def test_sixteen_bit_loci_and_the_uint16_limit(hc, oracle):
             ctx.set_profiles(np.ascontiguousarray(Y))
 
 
+def test_wide_snp_matrix_and_the_informative_loci_limit(hc, oracle):
+    # SNP matrices (conv_nucl, scripts/partitioning_HC.py:28-47) can have far more than 65,535 columns; only
+    # the columns with >= 2 called alleles can mismatch, and only their number is bounded by uint16 distances
+    rng = np.random.default_rng(23)
+    n, L = 150, 70001
+    X = np.full((n, L), 2, dtype=np.int32)                 # monomorphic background
+    info_cols = rng.choice(L, 4000, replace=False)
+    X[:, info_cols] = rng.integers(1, 5, (n, info_cols.size))
+    X[rng.random((n, L)) < 0.01] = 0
+    with hc.HCContext() as ctx:
+        ctx.set_profiles(X)
+        assert ctx.info()["loci_kept"] == info_cols.size
+        ctx.distance()
+        got = ctx.condensed()
+    assert np.array_equal(got, oracle.dist_condensed(X))
+    Y = rng.integers(1, 3, (40, 65600)).astype(np.int32)   # every column informative
+    Y[0], Y[1] = 1, 2                                      # one pair differs everywhere: d = 65,535 at the limit
+    with hc.HCContext() as ctx:
+        with pytest.raises(hc.HCBackendError, match="65,535"):
+            ctx.set_profiles(Y)
+        ctx.set_profiles(np.ascontiguousarray(Y[:, :65535]))    # exactly at the limit: distances up to 65,535 fit
+        ctx.distance()
+        got = ctx.condensed()
+    assert got[0] == 65535
+    assert np.array_equal(got, oracle.dist_condensed(np.ascontiguousarray(Y[:, :65535])))
+
+
 def test_negative_codes_are_missing(hc, oracle):
     rng = np.random.default_rng(17)
     X = _rand_codes(rng, 64, 64, 5, 0.0)
