@@ -11,6 +11,9 @@
 #include <sys/mman.h>
 #include <sys/stat.h>
 #include <unistd.h>
+#if defined(__x86_64__)
+#include <immintrin.h>
+#endif
 
 #include <algorithm>
 #include <atomic>
@@ -170,10 +173,95 @@ extern "C" void rthio_profile_close(rthio_profile *p)
     delete p;
 }
 
+// ---------------------------------------------------------------------------------------------
+// data cells of one row -> int32 codes
+// ---------------------------------------------------------------------------------------------
+struct RowSink {
+    const rthio_profile *p;
+    int32_t *dst;
+    int64_t L, c;
+    bool plain;
+    std::string *tmp;
+};
+
+// any token: the reference's cleaning + missing-code + conv_nucl + cell contract
+static inline void emit_general(RowSink &S, const char *a, size_t len)
+{
+    if (S.c >= S.L) { S.c = S.L + 1; return; }
+    bool nan;
+    Tok t = final_cell(S.p, a, len, *S.tmp, &nan);
+    if (nan || t.s != a || t.n != len) S.plain = false;
+    S.dst[S.c++] = cell_code(t, nan);
+}
+
+// 1..8 decimal digits ending at `end`, without a loop: the 8 bytes before `end` are loaded, the bytes in front of
+// the token are overwritten with '0', every byte is checked to be a digit and the value comes from three
+// multiplications (first character in the low byte).  Needs end - 8 inside the mapping.
+static inline bool digits8(const char *end, size_t len, uint32_t *out)
+{
+    uint64_t v;
+    memcpy(&v, end - 8, 8);
+    const unsigned sh = 8u * (unsigned)(8 - len);
+    const uint64_t low = sh ? (~0ull >> (64 - sh)) : 0ull;
+    v = (v & ~low) | (0x3030303030303030ull & low);
+    const bool ok = ((v & 0xF0F0F0F0F0F0F0F0ull) == 0x3030303030303030ull) &
+                    (((v + 0x0606060606060606ull) & 0xF0F0F0F0F0F0F0F0ull) == 0x3030303030303030ull);
+    v -= 0x3030303030303030ull;
+    v = v * 10 + (v >> 8);
+    v = (((v & 0x000000FF000000FFull) * 0x000F424000000064ull) + (((v >> 16) & 0x000000FF000000FFull) * 0x0000271000000001ull)) >> 32;
+    *out = (uint32_t)v;
+    return ok;
+}
+
+#if defined(__x86_64__)
+// The row's cells from `tok` (first data cell) to the line end `e`: tabs are found 32 bytes at a time, so the
+// only data-dependent branch per cell is "is it 1..8 digits" (nearly always yes) instead of one unpredictable
+// loop exit per token.  Caller guarantees tok - 8 and e + 32 lie inside the mapping.
+__attribute__((target("avx2,bmi"))) static void row_cells_avx2(RowSink &S, const char *tok, const char *e)
+{
+    const __m256i tabs = _mm256_set1_epi8('\t');
+    const char *pos = tok;
+    while (pos < e) {
+        const __m256i blk = _mm256_loadu_si256(reinterpret_cast<const __m256i *>(pos));
+        uint32_t m = (uint32_t)_mm256_movemask_epi8(_mm256_cmpeq_epi8(blk, tabs));
+        const size_t rem = (size_t)(e - pos);
+        if (rem < 32) m &= (1u << rem) - 1u;
+        while (m) {
+            const char *end = pos + _tzcnt_u32(m);
+            m &= m - 1;
+            const size_t len = (size_t)(end - tok);
+            uint32_t v;
+            if (len - 1 < 8 && S.c < S.L && digits8(end, len, &v)) S.dst[S.c++] = v ? (int32_t)v : (len == 1 ? 0 : -1);
+            else emit_general(S, tok, len);
+            tok = end + 1;
+        }
+        pos += 32;
+    }
+    const size_t len = (size_t)(e - tok);
+    uint32_t v;
+    if (len - 1 < 8 && S.c < S.L && digits8(e, len, &v)) S.dst[S.c++] = v ? (int32_t)v : (len == 1 ? 0 : -1);
+    else emit_general(S, tok, len);
+}
+#endif
+
+// RTHIO_TIMING=1: phase times of the ingest on stderr
+struct PhaseClock {
+    bool on = getenv("RTHIO_TIMING") != nullptr;
+    std::chrono::steady_clock::time_point t = std::chrono::steady_clock::now();
+    void mark(const char *what)
+    {
+        if (!on) return;
+        const auto now = std::chrono::steady_clock::now();
+        fprintf(stderr, "[rthio] %-24s %8.3f s\n", what, std::chrono::duration<double>(now - t).count());
+        t = now;
+    }
+};
+
 extern "C" int rthio_profile_open(const char *path, const char *missing_code, int n_threads, rthio_profile **out)
 {
     if (!path || !out) return fail(RTHIO_E_ARG, "rthio_profile_open: NULL argument");
     *out = nullptr;
+    PhaseClock clk;
     rthio_profile *p = new rthio_profile();
     p->n_threads = pick_threads(n_threads);
     const std::string mc = missing_code ? missing_code : "0";
@@ -204,18 +292,26 @@ extern "C" int rthio_profile_open(const char *path, const char *missing_code, in
         });
         if (odd.load()) { rthio_profile_close(p); return fail(RTHIO_IRREGULAR, "quote, CR or NUL in the file"); }
     }
+    clk.mark("map + irregular scan");
     // lines (blank lines are skipped like skip_blank_lines=True)
     std::vector<size_t> lb, le;
     {
+        std::vector<std::vector<size_t>> nls((size_t)p->n_threads);          // newline offsets, found in parallel
+        parallel_ranges((int64_t)size, p->n_threads, [&](int t, int64_t lo, int64_t hi) {
+            std::vector<size_t> &v = nls[(size_t)t];
+            const char *q = buf + lo, *end = buf + hi;
+            while (q < end && (q = (const char *)memchr(q, '\n', (size_t)(end - q)))) { v.push_back((size_t)(q - buf)); ++q; }
+        });
         size_t pos = 0;
-        while (pos < size) {
-            const char *nl = (const char *)memchr(buf + pos, '\n', size - pos);
-            const size_t end = nl ? (size_t)(nl - buf) : size;
-            if (end > pos) { lb.push_back(pos); le.push_back(end); }
-            pos = end + 1;
-        }
+        for (const std::vector<size_t> &v : nls)
+            for (const size_t end : v) {
+                if (end > pos) { lb.push_back(pos); le.push_back(end); }
+                pos = end + 1;
+            }
+        if (pos < size) { lb.push_back(pos); le.push_back(size); }            // last line without a newline
     }
     if (lb.size() < 1) { rthio_profile_close(p); return fail(RTHIO_IRREGULAR, "no header line"); }
+    clk.mark("line split");
     // header
     {
         std::unordered_set<std::string> seen;
@@ -250,8 +346,12 @@ extern "C" int rthio_profile_open(const char *path, const char *missing_code, in
         p->id_nan.assign((size_t)p->n, 0);
         p->row_plain.assign((size_t)p->n, 0);
     } catch (...) { rthio_profile_close(p); return fail(RTHIO_E_NOMEM, "out of host memory for %lld x %lld codes", (long long)p->n, (long long)p->L); }
+    clk.mark("header + allocations");
     std::atomic<int> ragged(0);
     const int64_t L = p->L;
+#if defined(__x86_64__)
+    const bool simd = __builtin_cpu_supports("avx2") && __builtin_cpu_supports("bmi") && !getenv("RTHIO_NO_SIMD");
+#endif
     parallel_ranges(p->n, p->n_threads, [&](int, int64_t lo, int64_t hi) {
         std::string tmp;
         for (int64_t r = lo; r < hi && !ragged.load(std::memory_order_relaxed); ++r) {
@@ -264,14 +364,21 @@ extern "C" int rthio_profile_open(const char *path, const char *missing_code, in
             if (is_na_token(a, (size_t)(b - a))) { p->id_nan[(size_t)r] = 1; plain = false; }
             else { Tok t = clean_token(a, (size_t)(b - a), tmp); p->ids[(size_t)r].assign(t.s, t.n); plain = t.s == a; }
             int64_t c = 0;
-            while (tab) {
+#if defined(__x86_64__)
+            if (simd && tab && p->miss_mode != MISS_STRING && a - buf >= 8 && e + 32 <= buf + size) {
+                RowSink S{p, dst, L, 0, plain, &tmp};
+                row_cells_avx2(S, tab + 1, e);
+                c = S.c; plain = S.plain;
+                tab = nullptr;
+            }
+#endif
+            while (tab) {                        // scalar path: no AVX2, --missing-code <string>, first / last bytes of the file
                 a = tab + 1;
+                if (c >= L) { c = L + 1; break; }
                 tab = (const char *)memchr(a, '\t', (size_t)(e - a));
                 b = tab ? tab : e;
-                if (c >= L) { c = L + 1; break; }
                 bool nan;
                 const size_t len = (size_t)(b - a);
-                // fast path: short all-digit token (the overwhelmingly common cell)
                 if (len >= 1 && len <= 9 && p->miss_mode != MISS_STRING) {
                     int32_t v = 0; bool digits = true;
                     for (size_t i = 0; i < len; ++i) { const unsigned d = (unsigned char)a[i] - '0'; if (d > 9) { digits = false; break; } v = v * 10 + (int32_t)d; }
@@ -286,6 +393,7 @@ extern "C" int rthio_profile_open(const char *path, const char *missing_code, in
         }
     });
     if (ragged.load()) { rthio_profile_close(p); return fail(RTHIO_IRREGULAR, "a row does not have %lld cells", (long long)(L + 1)); }
+    clk.mark("cells");
     for (int64_t r = 0; r < p->n; ++r) {
         if (r) p->ids_blob.push_back('\n');
         p->ids_blob += p->ids[(size_t)r];
@@ -294,6 +402,7 @@ extern "C" int rthio_profile_open(const char *path, const char *missing_code, in
         if (c) p->header_blob.push_back('\t');
         p->header_blob += p->header[c];
     }
+    clk.mark("name blobs");
     *out = p;
     return RTHIO_OK;
 }

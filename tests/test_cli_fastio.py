@@ -157,6 +157,37 @@ def test_cli_host_side_reproduces_reference_goldens(case, fast, tmp_path, monkey
     assert [l for l in out.split("\n") if str(tmp_path) not in l] == gold
 
 
+@pytest.mark.parametrize("trailing_newline", [True, False])
+def test_vector_cell_parser_equals_scalar_parser(tmp_path, monkeypatch, trailing_newline):
+    """The AVX2 tab scan + 8-digit SWAR parse gives the codes of the byte-by-byte loop, token by token."""
+    from reportree_b200 import fastio, hostio
+    import pandas as pd
+    rng = np.random.default_rng(12)
+    toks = ["0", "1", "9", "10", "437", "65535", "12345678", "99999999", "00000000", "123456789", "00", "01", "1:", ":1", "3;",
+            "<2", "/7", "1/", "12a", "a", "Z", "LNF", "", "NA", "*5", "INF-44", "4 ", " 4", "-1", "+1", "1.0", "1e3", "１"]
+    n, L = 300, 97                                   # 97 cells: rows end at every offset of the 32-byte blocks
+    cells = rng.choice(len(toks), size=(n, L), p=np.r_[[0.3, 0.2], np.full(len(toks) - 2, 0.5 / (len(toks) - 2))])
+    path = str(tmp_path / "m.tsv")
+    with open(path, "w", encoding="utf-8") as fh:
+        fh.write("F\t" + "\t".join("l%d" % k for k in range(L)) + "\n")
+        for i in range(n):
+            fh.write("s%d\t" % i + "\t".join(toks[c] for c in cells[i]) + ("\n" if trailing_newline or i < n - 1 else ""))
+    monkeypatch.delenv("RTHIO_NO_SIMD", raising=False)
+    a = fastio.open_profile(path, "0")
+    fast = np.array(a.codes, copy=True)
+    a.close()
+    monkeypatch.setenv("RTHIO_NO_SIMD", "1")
+    b = fastio.open_profile(path, "0")
+    slow = np.array(b.codes, copy=True)
+    b.close()
+    assert np.array_equal(fast, slow)
+    # and both follow the specification: pandas strings -> hostio.encode_cells, with -1 folded to 0 (missing)
+    mx = pd.read_table(path, dtype=str)
+    mx = mx.replace({"INF-": "", r"\*": ""}, regex=True)
+    spec = hostio.encode_cells(mx.iloc[:, 1:])
+    assert np.array_equal(np.maximum(fast, 0), spec)
+
+
 @pytest.mark.parametrize("use_map", ["1", "0"])
 def test_square_writer_blocks_and_modes(tmp_path, monkeypatch, use_map):
     """Row blocks through the shared mapping (default) and through write(2) give the same bytes as a plain join."""
