@@ -19,6 +19,7 @@
 
 #include <algorithm>
 #include <cmath>
+#include <type_traits>
 
 #include "rthc_internal.cuh"
 
@@ -138,6 +139,283 @@ rthc_prim_kernel(const T *__restrict__ cond, int64_t n, int per_thread, MinSlot 
     }
 }
 
+// ---------------------------------------------------------------------------------------------
+// Prim in scipy order inside ONE thread-block cluster (uint16 matrices)
+// ---------------------------------------------------------------------------------------------
+// The loop above is bound by the grid barrier (3.3 us per step whatever the CTA count).  A step only
+// needs one row of the matrix (<= 0.5 MB), which a 16-CTA cluster streams in well under a microsecond,
+// and the cluster has a hardware barrier and distributed shared memory: every CTA reduces its slice to one
+// (weight, index) word, stores it into the slot table of EVERY CTA of the cluster (st.shared::cluster),
+// one barrier.cluster later each warp reduces the <= 16 slots of its own CTA.  No global memory, no grid
+// barrier, no slot re-read through L2.  Keys live in registers (vertex v = rank*1024 + tid + q*C*1024).
+// SQUARE: rows come from a mirrored n x n copy (contiguous); otherwise from the condensed vector, where
+// the part v < x of a row is a strided column.
+// condensed upper triangle -> full n x n mirror, 64 x 64 tiles through shared memory so that both the
+// (i, j) and the (j, i) halves are written with coalesced rows (a direct gather of the lower half reads
+// one 32-byte sector per element)
+__global__ void __launch_bounds__(256) rthc_mirror_square_u16(const uint16_t *__restrict__ cond, int64_t n, int64_t pitch,
+                                                              uint16_t *__restrict__ W)
+{
+    const int ti = blockIdx.y, tj = blockIdx.x;
+    if (tj < ti) return;
+    __shared__ uint16_t tile[64][66];
+    const int64_t i0 = (int64_t)ti * 64, j0 = (int64_t)tj * 64;
+    const int c = threadIdx.x & 63, r4 = threadIdx.x >> 6;      // 4 rows per pass
+    for (int r = r4; r < 64; r += 4) {
+        const int64_t i = i0 + r, j = j0 + c;
+        uint16_t v = 0;
+        if (i < n && j < n && j > i) v = cond[n * i - (i * (i + 1)) / 2 + (j - i - 1)];
+        tile[r][c] = v;
+    }
+    __syncthreads();
+    for (int r = r4; r < 64; r += 4) {
+        const int64_t i = i0 + r, j = j0 + c;
+        if (i < n && j < n) {
+            if (ti != tj) W[i * pitch + j] = tile[r][c];
+            else W[i * pitch + j] = c > r ? tile[r][c] : (c < r ? tile[c][r] : (uint16_t)0);
+        }
+        if (ti != tj) {                                          // transposed block: row j0 + r, column i0 + c
+            const int64_t jj = j0 + r, ii = i0 + c;
+            if (jj < n && ii < n) W[jj * pitch + ii] = tile[c][r];
+        }
+    }
+}
+
+#define PC_THREADS 1024
+#define PC_MAX_CLUSTER 16
+
+template <int MAXQ, bool SQUARE>
+__global__ void __launch_bounds__(PC_THREADS, 1)
+rthc_prim_cluster_kernel(const uint16_t *__restrict__ mat, int64_t n, int32_t *ex, int32_t *ey, double *ew)
+{
+    cg::cluster_group cluster = cg::this_cluster();
+    const unsigned C = cluster.num_blocks(), rank = cluster.block_rank();
+    __shared__ unsigned long long slot[2][PC_MAX_CLUSTER];      // written by every CTA of the cluster
+    __shared__ unsigned int sw[PC_THREADS / 32], si[PC_THREADS / 32];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int64_t stride = (int64_t)C * PC_THREADS;
+    const int64_t v0 = (int64_t)rank * PC_THREADS + threadIdx.x;
+    uint32_t key[MAXQ];
+    uint32_t gone = 0;                                          // bit q: vertex q is in the tree (or beyond n)
+#pragma unroll
+    for (int q = 0; q < MAXQ; ++q) {
+        key[q] = 0xFFFFFFFFu;
+        if (v0 + q * stride >= n) gone |= 1u << q;
+    }
+    int64_t x = 0;
+    for (int64_t k = 0; k < n - 1; ++k) {
+        const int64_t xbase = SQUARE ? x * n : n * x - (x * (x + 1)) / 2;
+        uint32_t d[MAXQ];
+#pragma unroll
+        for (int q = 0; q < MAXQ; ++q) {                        // all loads of the step in flight together
+            const int64_t v = v0 + q * stride;
+            if (v == x) gone |= 1u << q;
+            d[q] = 0xFFFFFFFFu;
+            if (!((gone >> q) & 1u)) {
+                const int64_t idx = SQUARE ? xbase + v
+                                           : (v > x ? xbase + (v - x - 1) : n * v - (v * (v + 1)) / 2 + (x - v - 1));
+                d[q] = __ldg(mat + idx);
+            }
+        }
+        uint32_t bw = 0xFFFFFFFFu, bi = 0xFFFFFFFFu;
+#pragma unroll
+        for (int q = 0; q < MAXQ; ++q) {
+            if ((gone >> q) & 1u) continue;
+            key[q] = min(key[q], d[q]);
+            if (key[q] < bw) { bw = key[q]; bi = (uint32_t)(v0 + q * stride); }     // ascending v: lowest index of the minimum
+        }
+        // CTA minimum: two REDUX per warp (weight, then lowest index among the lanes that hold it)
+        uint32_t m = __reduce_min_sync(0xffffffffu, bw);
+        uint32_t i = __reduce_min_sync(0xffffffffu, bw == m ? bi : 0xFFFFFFFFu);
+        if (lane == 0) { sw[warp] = m; si[warp] = i; }
+        __syncthreads();
+        const int par = (int)(k & 1);
+        if (warp == 0) {
+            bw = sw[lane]; bi = si[lane];
+            m = __reduce_min_sync(0xffffffffu, bw);
+            i = __reduce_min_sync(0xffffffffu, bw == m ? bi : 0xFFFFFFFFu);
+            if ((unsigned)lane < C)                              // lane l publishes to CTA l
+                *cluster.map_shared_rank(&slot[par][rank], lane) = ((unsigned long long)m << 32) | i;
+        }
+        cluster.sync();
+        const unsigned long long sv = (unsigned)lane < C ? slot[par][lane] : ~0ull;
+        bw = (uint32_t)(sv >> 32); bi = (uint32_t)sv;
+        m = __reduce_min_sync(0xffffffffu, bw);
+        i = __reduce_min_sync(0xffffffffu, bw == m ? bi : 0xFFFFFFFFu);
+        if (rank == 0 && threadIdx.x == 0) { ex[k] = (int32_t)x; ey[k] = (int32_t)i; ew[k] = (double)m; }
+        x = i;
+    }
+}
+
+// Same step, rows from the mirrored copy with a pitch that is a multiple of 8: a thread owns 8 CONTIGUOUS
+// vertices per chunk (one 16-byte load), keys stay packed 2 x 16 bit (VIMNMX.U16x2), vertices already in the
+// tree are held at 0xFFFF by an OR mask and skipped when the index is resolved -- about 30 instructions per
+// thread and step instead of about 150, which matters because 32 warps share the four schedulers of an SM.
+template <int NCH>
+__global__ void __launch_bounds__(PC_THREADS, 1)
+rthc_prim_cluster_vec_kernel(const uint16_t *__restrict__ sq, int64_t n, int64_t pitch, int32_t *ex, int32_t *ey, double *ew,
+                             int prefetch)
+{
+    cg::cluster_group cluster = cg::this_cluster();
+    const unsigned C = cluster.num_blocks(), rank = cluster.block_rank();
+    __shared__ unsigned long long slot[2][PC_MAX_CLUSTER];
+    __shared__ unsigned int sw[PC_THREADS / 32], si[PC_THREADS / 32];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    uint32_t key[NCH][4], gm[NCH][4];
+    int64_t vbase[NCH];
+#pragma unroll
+    for (int c = 0; c < NCH; ++c) {
+        vbase[c] = (((int64_t)c * C + rank) * PC_THREADS + threadIdx.x) * 8;
+#pragma unroll
+        for (int w = 0; w < 4; ++w) {
+            key[c][w] = 0xFFFFFFFFu;
+            const int64_t v = vbase[c] + 2 * w;
+            gm[c][w] = (v >= n ? 0x0000FFFFu : 0u) | (v + 1 >= n ? 0xFFFF0000u : 0u);
+        }
+    }
+    int64_t x = 0;
+    for (int64_t k = 0; k < n - 1; ++k) {
+        const uint16_t *row = sq + x * pitch;
+        uint32_t bw = 0xFFFFFFFFu;
+        int bc = 0;
+#pragma unroll
+        for (int c = 0; c < NCH; ++c) {
+            const int64_t off = x - vbase[c];
+            if (off >= 0 && off < 8) {                          // x joins the tree; 64-bit shifts instead of a register
+                const unsigned long long bits = 0xFFFFull << (16 * (int)(off & 3));      // index (no local memory)
+                unsigned long long lo = ((unsigned long long)gm[c][1] << 32) | gm[c][0];
+                unsigned long long hi = ((unsigned long long)gm[c][3] << 32) | gm[c][2];
+                if (off < 4) lo |= bits; else hi |= bits;
+                gm[c][0] = (uint32_t)lo; gm[c][1] = (uint32_t)(lo >> 32);
+                gm[c][2] = (uint32_t)hi; gm[c][3] = (uint32_t)(hi >> 32);
+            }
+            if ((gm[c][0] & gm[c][1] & gm[c][2] & gm[c][3]) == 0xFFFFFFFFu) continue;      // nothing left here
+            const uint4 d = __ldg(reinterpret_cast<const uint4 *>(row + vbase[c]));
+            key[c][0] = __vminu2(key[c][0], d.x) | gm[c][0];
+            key[c][1] = __vminu2(key[c][1], d.y) | gm[c][1];
+            key[c][2] = __vminu2(key[c][2], d.z) | gm[c][2];
+            key[c][3] = __vminu2(key[c][3], d.w) | gm[c][3];
+            const uint32_t m2 = __vminu2(__vminu2(key[c][0], key[c][1]), __vminu2(key[c][2], key[c][3]));
+            const uint32_t m = min(m2 & 0xFFFFu, m2 >> 16);
+            if (m < bw) { bw = m; bc = c; }
+        }
+        uint32_t m = __reduce_min_sync(0xffffffffu, bw);
+        uint32_t bi = 0xFFFFFFFFu;
+        if (bw == m && m != 0xFFFFFFFFu) {                      // few lanes: resolve the lowest alive index that holds m
+#pragma unroll
+            for (int c = 0; c < NCH; ++c) {
+                if (c != bc) continue;
+#pragma unroll
+                for (int e = 7; e >= 0; --e) {
+                    const uint32_t kv = (key[c][e >> 1] >> (16 * (e & 1))) & 0xFFFFu;
+                    const bool alive = !((gm[c][e >> 1] >> (16 * (e & 1))) & 1u);
+                    if (alive && kv == m) bi = (uint32_t)(vbase[c] + e);
+                }
+            }
+        }
+        uint32_t i = __reduce_min_sync(0xffffffffu, bi);
+        if (lane == 0) { sw[warp] = m; si[warp] = i; }
+        __syncthreads();
+        const int par = (int)(k & 1);
+        if (warp == 0) {
+            bw = sw[lane]; bi = si[lane];
+            m = __reduce_min_sync(0xffffffffu, bw);
+            i = __reduce_min_sync(0xffffffffu, bw == m ? bi : 0xFFFFFFFFu);
+            if ((unsigned)lane < C)
+                *cluster.map_shared_rank(&slot[par][rank], lane) = ((unsigned long long)m << 32) | i;
+            // the next vertex is one of the <= 16 CTA winners: each CTA asks L2 for its own winner's row (one bulk
+            // prefetch) so that the DRAM access overlaps the cluster exchange instead of following it
+            if (prefetch && lane == 0 && i != 0xFFFFFFFFu)
+                asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(sq + (int64_t)i * pitch),
+                             "r"((uint32_t)(pitch * 2)) : "memory");
+        }
+        cluster.sync();
+        const unsigned long long sv = (unsigned)lane < C ? slot[par][lane] : ~0ull;
+        bw = (uint32_t)(sv >> 32); bi = (uint32_t)sv;
+        m = __reduce_min_sync(0xffffffffu, bw);
+        i = __reduce_min_sync(0xffffffffu, bw == m ? bi : 0xFFFFFFFFu);
+        if (rank == 0 && threadIdx.x == 0) { ex[k] = (int32_t)x; ey[k] = (int32_t)i; ew[k] = (double)m; }
+        x = i;
+    }
+}
+
+template <int NCH>
+static cudaError_t launch_prim_cluster_vec(int C, cudaStream_t stream, const uint16_t *sq, int64_t n, int64_t pitch,
+                                           int32_t *ex, int32_t *ey, double *ew)
+{
+    auto kern = rthc_prim_cluster_vec_kernel<NCH>;
+    cudaError_t e;
+    if (C > 8 && (e = cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1)) != cudaSuccess) return e;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)C);
+    cfg.blockDim = dim3(PC_THREADS);
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = (unsigned)C; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    int clusters = 0;
+    if ((e = cudaOccupancyMaxActiveClusters(&clusters, kern, &cfg)) != cudaSuccess) return e;
+    if (clusters < 1) return cudaErrorInvalidConfiguration;
+    static const int prefetch = getenv("RTHC_PRIM_PREFETCH") ? atoi(getenv("RTHC_PRIM_PREFETCH")) : 0;   // A/B: slower
+    return cudaLaunchKernelEx(&cfg, kern, sq, n, pitch, ex, ey, ew, prefetch);
+}
+
+template <int MAXQ, bool SQUARE>
+static cudaError_t launch_prim_cluster(int C, cudaStream_t stream, const uint16_t *mat, int64_t n, int32_t *ex, int32_t *ey,
+                                       double *ew)
+{
+    auto kern = rthc_prim_cluster_kernel<MAXQ, SQUARE>;
+    cudaError_t e;
+    if (C > 8 && (e = cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1)) != cudaSuccess) return e;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)C);
+    cfg.blockDim = dim3(PC_THREADS);
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = (unsigned)C; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    int clusters = 0;
+    if ((e = cudaOccupancyMaxActiveClusters(&clusters, kern, &cfg)) != cudaSuccess) return e;
+    if (clusters < 1) return cudaErrorInvalidConfiguration;
+    return cudaLaunchKernelEx(&cfg, kern, mat, n, ex, ey, ew);
+}
+
+// returns 1 when the cluster kernel is not applicable (size, RTHC_PRIM_CLUSTER=0, no cluster launch): caller falls
+// back to the cooperative kernel; 0 on success; < 0 on error
+static int run_prim_cluster(rthc_ctx *ctx, const uint16_t *d_cond, int32_t *d_ex, int32_t *d_ey, double *d_ew)
+{
+    static const int mode = getenv("RTHC_PRIM_CLUSTER") ? atoi(getenv("RTHC_PRIM_CLUSTER")) : 1;   // 0 off, 1 auto, 2 no square copy
+    if (mode == 0) return 1;
+    const int64_t n = ctx->n, pitch = (n + 7) / 8 * 8;
+    uint16_t *d_sq = nullptr;
+    if (mode == 1) {                                             // mirrored copy when 2 n^2 bytes are free (plus slack)
+        size_t free_b = 0, total_b = 0;
+        cudaMemGetInfo(&free_b, &total_b);
+        if ((double)free_b > 2.0 * (double)n * (double)pitch + 2e9 && rthc_dev_alloc(ctx, &d_sq, (size_t)(n * pitch)) == 0) {
+            const unsigned B = (unsigned)((n + 63) / 64);
+            rthc_mirror_square_u16<<<dim3(B, B), 256, 0, ctx->stream>>>(d_cond, n, pitch, d_sq);
+            ctx->launches++;
+        } else {
+            d_sq = nullptr;
+        }
+    }
+    cudaError_t e = cudaErrorInvalidConfiguration;
+    for (int C = PC_MAX_CLUSTER; C >= 8 && e != cudaSuccess; C >>= 1) {
+        const int64_t per = (n + (int64_t)C * PC_THREADS - 1) / ((int64_t)C * PC_THREADS);
+        if (per > 16) break;
+        if (d_sq) e = per <= 8 ? launch_prim_cluster_vec<1>(C, ctx->stream, d_sq, n, pitch, d_ex, d_ey, d_ew)
+                               : launch_prim_cluster_vec<2>(C, ctx->stream, d_sq, n, pitch, d_ex, d_ey, d_ew);
+        else e = per <= 8 ? launch_prim_cluster<8, false>(C, ctx->stream, d_cond, n, d_ex, d_ey, d_ew)
+                          : launch_prim_cluster<16, false>(C, ctx->stream, d_cond, n, d_ex, d_ey, d_ew);
+        if (e != cudaSuccess) cudaGetLastError();
+    }
+    if (e == cudaSuccess) ctx->launches++;
+    rthc_dev_free(ctx, &d_sq);                                   // stream-ordered: released after the kernel
+    return e == cudaSuccess ? 0 : 1;
+}
+
 template <typename T>
 static int run_prim(rthc_ctx *ctx, const T *d_cond, std::vector<int32_t> &ex, std::vector<int32_t> &ey,
                     std::vector<double> &ew)
@@ -145,8 +423,6 @@ static int run_prim(rthc_ctx *ctx, const T *d_cond, std::vector<int32_t> &ex, st
     const int64_t n = ctx->n, m = n - 1;
     int nblocks = ctx->sm_count;
     int per_thread = (int)((n + (int64_t)nblocks * SEQ_THREADS - 1) / ((int64_t)nblocks * SEQ_THREADS));
-    if (per_thread > 8)
-        return rthc_fail(ctx, RTHC_E_RANGE, "Prim-exact supports up to %lld samples", (long long)nblocks * SEQ_THREADS * 8);
     MinSlot *d_slots = nullptr;
     int32_t *d_ex = nullptr, *d_ey = nullptr;
     double *d_ew = nullptr;
@@ -156,11 +432,18 @@ static int run_prim(rthc_ctx *ctx, const T *d_cond, std::vector<int32_t> &ex, st
     if ((rc = rthc_dev_alloc(ctx, &d_ey, (size_t)m))) return rc;
     if ((rc = rthc_dev_alloc(ctx, &d_ew, (size_t)m))) return rc;
     int64_t nn = n;
-    void *args[] = {(void *)&d_cond, (void *)&nn, (void *)&per_thread, (void *)&d_slots, (void *)&d_ex, (void *)&d_ey,
-                    (void *)&d_ew};
-    RTHC_CUDA(ctx, cudaLaunchCooperativeKernel((void *)rthc_prim_kernel<T>, dim3(nblocks), dim3(SEQ_THREADS), args, 0,
-                                               ctx->stream));
-    ctx->launches++;
+    int clustered = 1;
+    if constexpr (std::is_same<T, uint16_t>::value) clustered = run_prim_cluster(ctx, d_cond, d_ex, d_ey, d_ew);
+    if (clustered < 0) return clustered;
+    if (clustered == 1) {
+        if (per_thread > 8)
+            return rthc_fail(ctx, RTHC_E_RANGE, "Prim-exact supports up to %lld samples", (long long)nblocks * SEQ_THREADS * 8);
+        void *args[] = {(void *)&d_cond, (void *)&nn, (void *)&per_thread, (void *)&d_slots, (void *)&d_ex, (void *)&d_ey,
+                        (void *)&d_ew};
+        RTHC_CUDA(ctx, cudaLaunchCooperativeKernel((void *)rthc_prim_kernel<T>, dim3(nblocks), dim3(SEQ_THREADS), args, 0,
+                                                   ctx->stream));
+        ctx->launches++;
+    }
     ex.resize((size_t)m); ey.resize((size_t)m); ew.resize((size_t)m);
     RTHC_CUDA(ctx, cudaMemcpyAsync(ex.data(), d_ex, sizeof(int32_t) * (size_t)m, cudaMemcpyDeviceToHost, ctx->stream));
     RTHC_CUDA(ctx, cudaMemcpyAsync(ey.data(), d_ey, sizeof(int32_t) * (size_t)m, cudaMemcpyDeviceToHost, ctx->stream));
@@ -208,8 +491,8 @@ __device__ __forceinline__ double lance_williams<double>(int method, double dx, 
 template <typename T, typename S>
 __global__ void rthc_expand_square(const S *__restrict__ cond, int64_t n, T *__restrict__ W)
 {
-    const int64_t i = blockIdx.y;
-    const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t i = blockIdx.x;                              // rows on grid.x: no 65,535 limit
+    const int64_t j = (int64_t)blockIdx.y * blockDim.x + threadIdx.x;
     if (j >= n) return;
     T v = 0;
     if (i != j) {
@@ -326,7 +609,7 @@ static int run_nn_chain(rthc_ctx *ctx, const S *d_cond, int method, std::vector<
     if ((rc = rthc_dev_alloc(ctx, &d_ew, (size_t)m))) return rc;
     if ((rc = rthc_dev_alloc(ctx, &d_ctl, 1))) return rc;
     {
-        dim3 grd((unsigned)((n + 255) / 256), (unsigned)n);
+        dim3 grd((unsigned)n, (unsigned)((n + 255) / 256));
         rthc_expand_square<T, S><<<grd, 256, 0, ctx->stream>>>(d_cond, n, d_W);
         RTHC_LAUNCH_CHECK(ctx);
         std::vector<int32_t> ones((size_t)n, 1);
