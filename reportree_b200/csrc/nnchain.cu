@@ -507,13 +507,36 @@ struct ChainCtl {
     int64_t scans;
 };
 
-template <typename T>
+// all-lanes lexicographic minimum of (w, i) over a warp
+__device__ __forceinline__ void warp_min_all(unsigned long long &w, unsigned int &i)
+{
+#pragma unroll
+    for (int s = 16; s > 0; s >>= 1) {
+        unsigned long long ow = __shfl_xor_sync(0xffffffffu, w, s);
+        unsigned int oi = __shfl_xor_sync(0xffffffffu, i, s);
+        if (slot_less(ow, oi, w, i)) { w = ow; i = oi; }
+    }
+}
+
+// step barrier + exchange of the per-CTA minima.  CL = false: cooperative grid, slots in global memory, grid.sync().
+// CL = true: the whole loop runs inside ONE thread-block cluster (<= 16 CTAs): every CTA stores its minimum into the
+// slot table of all CTAs through distributed shared memory and barrier.cluster replaces the grid barrier (the
+// step is latency-bound: 4.7 us with the grid barrier whatever the CTA count).
+template <bool CL> struct SeqSync {
+    __device__ static __forceinline__ void sync()
+    {
+        if constexpr (CL) cg::this_cluster().sync();
+        else cg::this_grid().sync();
+    }
+};
+
+template <typename T, bool CL>
 __global__ void __launch_bounds__(SEQ_THREADS, 1)
 rthc_nn_chain_kernel(T *W, int64_t n, int method, int32_t *size, int32_t *chain, MinSlot *slots, int32_t *ex,
                      int32_t *ey, double *ew, ChainCtl *ctl)
 {
-    cg::grid_group grid = cg::this_grid();
     __shared__ MinSlot sh[SEQ_THREADS / 32];
+    __shared__ MinSlot cslot[2][PC_MAX_CLUSTER];               // CL: written by every CTA of the cluster
     const int nblocks = gridDim.x;
     const int64_t gtid = (int64_t)blockIdx.x * SEQ_THREADS + threadIdx.x;
     const int64_t gthreads = (int64_t)nblocks * SEQ_THREADS;
@@ -544,14 +567,28 @@ rthc_nn_chain_kernel(T *W, int64_t n, int method, int32_t *size, int32_t *chain,
             const unsigned long long d = order_bits(__ldcg(&row[i]));
             if (slot_less(d, (unsigned int)i, bw, bi)) { bw = d; bi = (unsigned int)i; }
         }
-        block_min(bw, bi, sh);
+        block_min(bw, bi, sh);                                  // valid in warp 0
         MinSlot *cur = slots + (step & 1) * nblocks;
-        if (threadIdx.x == 0) { cur[blockIdx.x].w = bw; cur[blockIdx.x].i = bi; }
+        if constexpr (CL) {
+            if (threadIdx.x < (unsigned)nblocks) {
+                MinSlot *dst = cg::this_cluster().map_shared_rank(&cslot[step & 1][blockIdx.x], threadIdx.x);
+                dst->w = bw; dst->i = bi;
+            }
+        } else {
+            if (threadIdx.x == 0) { cur[blockIdx.x].w = bw; cur[blockIdx.x].i = bi; }
+        }
         if (leader && dead >= 0) { size[dead] = 0; size[grown] = grown_size; }   // publish last merge's sizes
-        grid.sync();
+        SeqSync<CL>::sync();
+        if constexpr (CL) {
+            const int l = threadIdx.x & 31;
+            bw = l < nblocks ? cslot[step & 1][l].w : ~0ull;
+            bi = l < nblocks ? cslot[step & 1][l].i : ~0u;
+            warp_min_all(bw, bi);
+        } else {
+            grid_min(cur, nblocks, bw, bi, sh);
+        }
         ++step; ++scans;
         dead = -1;
-        grid_min(cur, nblocks, bw, bi, sh);
         int32_t y = (int32_t)bi;
         unsigned long long dmin = bw;
         if (len > 1 && dprev <= dmin) { y = prev; dmin = dprev; }  // previous chain element wins ties
@@ -578,7 +615,7 @@ rthc_nn_chain_kernel(T *W, int64_t n, int method, int32_t *size, int32_t *chain,
         dead = a; grown = b; grown_size = na + nb;
         ++k;
         len -= 2;
-        grid.sync();                          // row/column b visible before the next scan
+        SeqSync<CL>::sync();                  // row/column b visible before the next scan
         ++step;
         if (len > 0) {
             x = __ldcg(&chain[len - 1]);
@@ -619,8 +656,35 @@ static int run_nn_chain(rthc_ctx *ctx, const S *d_cond, int method, std::vector<
     int64_t nn = n;
     void *args[] = {(void *)&d_W, (void *)&nn, (void *)&method, (void *)&d_size, (void *)&d_chain, (void *)&d_slots,
                     (void *)&d_ex, (void *)&d_ey, (void *)&d_ew, (void *)&d_ctl};
-    RTHC_CUDA(ctx, cudaLaunchCooperativeKernel((void *)rthc_nn_chain_kernel<T>, dim3(nblocks), dim3(SEQ_THREADS), args,
-                                               0, ctx->stream));
+    // A/B switch, off by default: unlike Prim the merge loop does not gain from the cluster (C3 average 0.29 vs 0.32 s,
+    // C5 complete 1.06 vs 0.89 s): its merges scatter a column over the matrix and want all 148 SMs
+    static const bool use_cluster = getenv("RTHC_NNCHAIN_CLUSTER") && atoi(getenv("RTHC_NNCHAIN_CLUSTER")) == 1;
+    cudaError_t ce = cudaErrorInvalidConfiguration;
+    if (use_cluster) {                                           // one cluster of 16 (or 8) CTAs
+        auto kern = rthc_nn_chain_kernel<T, true>;
+        for (int C = PC_MAX_CLUSTER; C >= 8 && ce != cudaSuccess; C >>= 1) {
+            if (C > 8 && cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) != cudaSuccess) {
+                cudaGetLastError();
+                continue;
+            }
+            cudaLaunchConfig_t cfg = {};
+            cfg.gridDim = dim3((unsigned)C);
+            cfg.blockDim = dim3(SEQ_THREADS);
+            cfg.stream = ctx->stream;
+            cudaLaunchAttribute attr[1];
+            attr[0].id = cudaLaunchAttributeClusterDimension;
+            attr[0].val.clusterDim.x = (unsigned)C; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+            cfg.attrs = attr; cfg.numAttrs = 1;
+            int clusters = 0;
+            ce = cudaOccupancyMaxActiveClusters(&clusters, kern, &cfg);
+            if (ce == cudaSuccess && clusters < 1) ce = cudaErrorInvalidConfiguration;
+            if (ce == cudaSuccess) ce = cudaLaunchKernelEx(&cfg, kern, d_W, nn, method, d_size, d_chain, d_slots, d_ex, d_ey, d_ew, d_ctl);
+            if (ce != cudaSuccess) cudaGetLastError();
+        }
+    }
+    if (ce != cudaSuccess)
+        RTHC_CUDA(ctx, cudaLaunchCooperativeKernel((void *)rthc_nn_chain_kernel<T, false>, dim3(nblocks), dim3(SEQ_THREADS), args,
+                                                   0, ctx->stream));
     ctx->launches++;
     ex.resize((size_t)m); ey.resize((size_t)m); ew.resize((size_t)m);
     ChainCtl ctl;
