@@ -60,6 +60,10 @@ enum { RTHC_SL_BORUVKA = 0, RTHC_SL_PRIM = 1 };
 
 /* ---- lifetime -------------------------------------------------------------- */
 int rthc_create(rthc_ctx **out, int device);
+/* Creates the CUDA primary context of `device` and nothing else (0.7 s of driver start-up on a B200 box),
+ * so that a host can pay it on a helper thread from its very first instruction -- before its own imports and
+ * argument parsing -- and find rthc_create() taking milliseconds later.  Needs no rthc_ctx; safe to skip. */
+int rthc_prewarm(int device);
 void rthc_destroy(rthc_ctx *ctx);
 const char *rthc_last_error(const rthc_ctx *ctx);   /* ctx may be NULL: last create error */
 int rthc_version(void);

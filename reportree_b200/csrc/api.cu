@@ -29,6 +29,15 @@ extern "C" const char *rthc_last_error(const rthc_ctx *ctx)
     return ctx ? ctx->err.c_str() : g_rthc_create_err.c_str();
 }
 
+extern "C" int rthc_prewarm(int device)
+{
+    if (cudaSetDevice(device) != cudaSuccess || cudaFree(nullptr) != cudaSuccess) {
+        cudaGetLastError();
+        return RTHC_E_CUDA;                      // not fatal here: rthc_create reports the reason
+    }
+    return RTHC_OK;
+}
+
 extern "C" int rthc_create(rthc_ctx **out, int device)
 {
     if (!out) return rthc_fail(nullptr, RTHC_E_ARG, "rthc_create: out is NULL");

@@ -393,7 +393,11 @@ static int run_prim_cluster(rthc_ctx *ctx, const uint16_t *d_cond, int32_t *d_ex
     if (mode == 1) {                                             // mirrored copy when 2 n^2 bytes are free (plus slack)
         size_t free_b = 0, total_b = 0;
         cudaMemGetInfo(&free_b, &total_b);
-        if ((double)free_b > 2.0 * (double)n * (double)pitch + 2e9 && rthc_dev_alloc(ctx, &d_sq, (size_t)(n * pitch)) == 0) {
+        // a cold pool allocation costs about 7 ms per GB, which at C4 (20 GB) eats what the contiguous rows save in a
+        // one-shot run (0.32-0.39 s cold vs 0.35 s from the condensed vector; 0.20 s once the pool is warm)
+        static const double mirror_gb = getenv("RTHC_PRIM_MIRROR_GB") ? atof(getenv("RTHC_PRIM_MIRROR_GB")) : 4.0;
+        const double need = 2.0 * (double)n * (double)pitch;
+        if (need <= mirror_gb * 1e9 && (double)free_b > need + 2e9 && rthc_dev_alloc(ctx, &d_sq, (size_t)(n * pitch)) == 0) {
             const unsigned B = (unsigned)((n + 63) / 64);
             rthc_mirror_square_u16<<<dim3(B, B), 256, 0, ctx->stream>>>(d_cond, n, pitch, d_sq);
             ctx->launches++;

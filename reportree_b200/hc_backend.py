@@ -84,7 +84,7 @@ def load_library():
 
 
 EXPORTED_SYMBOLS = [
-    "rthc_create", "rthc_destroy", "rthc_last_error", "rthc_version", "rthc_set_shard",
+    "rthc_create", "rthc_prewarm", "rthc_destroy", "rthc_last_error", "rthc_version", "rthc_set_shard",
     "rthc_set_shard_full_storage", "rthc_import_shard", "rthc_finish_import",
     "rthc_set_profiles_i32", "rthc_set_profiles_i32_device", "rthc_distance", "rthc_owned_pairs",
     "rthc_get_condensed_u16", "rthc_get_owned_condensed_u16", "rthc_copy_rows_u16", "rthc_direct_pairs",

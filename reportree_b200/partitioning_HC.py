@@ -18,9 +18,14 @@ Environment switches (argv stays frozen so reportree.py can call this unchanged)
                                      byte-identical to scipy; 0: Boruvka MST (same membership)
   REPORTREE_HC_SKIP_DIST_TSV=1       do not write <out>_dist_hamming.tsv (benchmark runs)
 """
-import argparse
 import os
 import sys
+
+if __name__ == "__main__":                 # CUDA start-up overlaps everything below, imports included
+    from reportree_b200 import early_cuda
+    early_cuda.start(int(os.environ.get("REPORTREE_HC_DEVICES", os.environ.get("REPORTREE_HC_DEVICE", "0")).split(",")[0] or 0))
+
+import argparse
 import textwrap
 
 import numpy as np
@@ -90,11 +95,13 @@ class LazyContext:
     """The GPU context is created on a helper thread while the profile is being read (CUDA
     start-up is ~1.3 s); the first use waits for it.  A failure surfaces at that first use."""
 
-    def __init__(self, device, devices=None):
-        if devices and len(devices) > 1:
-            self._bg = Background(lambda: hc_backend.MultiDeviceContext(devices))
-        else:
-            self._bg = Background(lambda: hc_backend.HCContext(device=device))
+    def __init__(self, device, devices=None, single_algo=None):
+        def create():
+            ctx = hc_backend.MultiDeviceContext(devices) if devices and len(devices) > 1 else hc_backend.HCContext(device=device)
+            if single_algo is not None:          # set here, not by the caller: touching the proxy would join the thread
+                ctx.set_single_algo(single_algo)
+            return ctx
+        self._bg = Background(create)
         self._ctx = None
 
     def __getattr__(self, name):
@@ -489,11 +496,14 @@ def profile_to_distances_fast(args, say, log, ctx, prof):
         id_is_zero = np.fromiter((prof.ids[i] == "0" for i in rows.tolist()), dtype=bool, count=len(rows))
         missing = prof.count_eq(rows, cols, 0) + id_is_zero   # isin(["0"]) over every column incl. the id (:451)
         called = len_schema - missing
-        ids = [prof.ids[i] if prof.ids[i] is not None else np.nan for i in rows.tolist()]
-        report = pandas.DataFrame({"samples": pandas.Series(ids, dtype=object), "missing": missing, "called": called,
-                                   "pct_called": called / len_schema})
-        passed = (report["pct_called"] >= thr).to_numpy()
-        report.to_csv(out + "_loci_report.tsv", index=False, header=True, sep="\t")
+        pct_called = called / len_schema                      # float64, as the reference's Series division (:453)
+        passed = pct_called >= thr
+        # DataFrame.to_csv without pandas (its import costs ~1 s, more than the whole parse): ints as str, float64 as
+        # the shortest round-trip repr, NaN ids as the empty field -- byte-identical on the goldens
+        with open(out + "_loci_report.tsv", "w") as fh:
+            fh.write("samples\tmissing\tcalled\tpct_called\n")
+            fh.write("".join("%s\t%d\t%d\t%r\n" % ("" if prof.ids[i] is None else prof.ids[i], m, c, p)
+                             for i, m, c, p in zip(rows.tolist(), missing.tolist(), called.tolist(), pct_called.tolist())))
         say("\tFrom the " + str(len(rows)) + " samples, " + str(int(passed.sum())) + " were kept in the profile matrix.")
         if int(passed.sum()) <= 1:
             say("\nCannot proceed because " + str(int(passed.sum())) + " samples were kept in the matrix!")
@@ -570,9 +580,10 @@ def matrix_to_distances(args, say, log, ctx):
 
 
 def main(argv=None):
-    from reportree_b200 import lazy_pandas
-    lazy_pandas.preload()                         # ~1 s of import, hidden behind the profile parse
     args = build_parser().parse_args(argv)
+    from reportree_b200 import fastio, lazy_pandas
+    if not (fastio.enabled() and args.allele_profile and args.metadata == ""):
+        lazy_pandas.preload()                     # ~1 s of import on a helper thread; the C++ text path never needs it
     log = Tee(args.out + ".log")
     say = log
     say("\n-------------------- partitioning_HC.py --------------------\n")
@@ -585,9 +596,9 @@ def main(argv=None):
 
     PH.__init__()
     devices = [int(d) for d in os.environ.get("REPORTREE_HC_DEVICES", "").split(",") if d.strip() != ""]
-    ctx = LazyContext(int(os.environ.get("REPORTREE_HC_DEVICE", "0")), devices)
     exact = os.environ.get("REPORTREE_HC_EXACT_NAMES", "1") != "0"
-    ctx.set_single_algo(hc_backend.SL_PRIM if exact else hc_backend.SL_BORUVKA)
+    ctx = LazyContext(int(os.environ.get("REPORTREE_HC_DEVICE", "0")), devices,
+                      single_algo=hc_backend.SL_PRIM if exact else hc_backend.SL_BORUVKA)
 
     if args.allele_profile:
         names, total_size = profile_to_distances(args, say, log, ctx)
@@ -665,10 +676,17 @@ def main(argv=None):
                 for pct in pcts:
                     print(str(pct) + "\t" + str(thr), file=fh)
     say("\npartitioning_HC.py is done!")
-    ctx.close()
     log.close()
+    ctx.close()               # explicit release: leaving tens of GB to the driver's process teardown measured slower
+    PH.mark("release device")
     PH.report()
 
 
 if __name__ == "__main__":
     main()
+    # every artefact is closed and every helper thread joined at this point: skip the interpreter's module
+    # teardown and the CUDA runtime's atexit handlers (0.1-0.2 s of a 2.5 s run at 100,000 samples)
+    sys.stdout.flush()
+    sys.stderr.flush()
+    if os.environ.get("REPORTREE_HC_FAST_EXIT", "1") != "0":
+        os._exit(0)
