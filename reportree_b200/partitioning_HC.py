@@ -21,7 +21,7 @@ Environment switches (argv stays frozen so reportree.py can call this unchanged)
 import os
 import sys
 
-if __name__ == "__main__":                 # CUDA start-up overlaps everything below, imports included
+if __name__ == "__main__" and os.environ.get("REPORTREE_HC_PREWARM", "1") != "0":   # CUDA start-up overlaps everything below, imports included
     from reportree_b200 import early_cuda
     early_cuda.start(int(os.environ.get("REPORTREE_HC_DEVICES", os.environ.get("REPORTREE_HC_DEVICE", "0")).split(",")[0] or 0))
 
