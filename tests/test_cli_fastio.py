@@ -209,5 +209,13 @@ def test_square_writer_blocks_and_modes(tmp_path, monkeypatch, use_map):
         names[i] + "\t" + "\t".join(str(int(v)) for v in D[i]) + "\n" for i in range(n))
     assert path.read_text() == want
     assert calls == [(r0, min(100, n - r0)) for r0 in range(0, n, 100)]
+    # short rows of one-digit cells, many threads: the 8-byte cell stores must never reach into a neighbour's row
+    for n2 in (2, 3, 5, 6, 40):
+        Z = (rng.integers(0, 12, (n2, n2)) * (rng.random((n2, n2)) < 0.3)).astype(np.uint16)
+        want2 = "dists\t" + "\t".join("x" for _ in range(n2)) + "\n" + "".join(
+            "x\t" + "\t".join(str(int(v)) for v in Z[i]) + "\n" for i in range(n2))
+        for _ in range(25):
+            fastio.write_square_tsv(str(path), ["x"] * n2, lambda r0, nr: Z[r0:r0 + nr], n2, threads=16)
+            assert path.read_text() == want2
     fastio.write_square_tsv(str(path), names[:1], lambda r0, nr: D[:1, :1], 1)
     assert path.read_text() == "dists\t" + names[0] + "\n" + names[0] + "\t" + str(int(D[0, 0])) + "\n"
