@@ -318,10 +318,11 @@ def run_ours(args):
             "lop3_per_32_loci": info["plane_rows"] / max(info["groups"], 1),
             "kernel_ms": kern["dist_ms"],
             # dram__bytes_read.sum + dram__bytes_write.sum of this kernel at C4 from the committed
-            # `ncu --set full` capture (profiles/r01_ncu_z_distance_C4.txt): 31.45 GB + 10.37 GB
-            # (the 378 MB plane matrix is re-read from HBM when tiles miss L2; 146 GB/s, 2 % of peak;
-            # earlier captures: r01_ncu_final 34.03 + 10.38 GB, r01_ncu_v5 40.78 + 10.40 GB)
-            "traffic": 41.83e9 if (n == 100000 and world == 1) else None,
+            # `ncu --set full` capture of the round's last build (profiles/r01_ncu_y_distance_C4.txt):
+            # 37.58 GB + 10.39 GB.  The write side is the condensed matrix; the read side is the 378 MB plane
+            # matrix re-read when tiles miss L2 and varies between captures (31.5 / 34.0 / 37.6 / 40.8 GB in
+            # r01_ncu_z / _final / _y / _v5) -- 110-140 GB/s, 2 % of the HBM peak either way
+            "traffic": 47.97e9 if (n == 100000 and world == 1) else None,
             "algorithmic_bytes": alg_bytes,
             "hbm": {"achieved": alg_bytes / t_k / 1e9, "peak": hbm_peak, "unit": "GB/s",
                     "frac": alg_bytes / t_k / 1e9 / hbm_peak,
