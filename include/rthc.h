@@ -99,6 +99,9 @@ int64_t rthc_owned_pairs(const rthc_ctx *ctx);
 int rthc_get_condensed_u16(rthc_ctx *ctx, uint16_t *out);
 /* owned part of the condensed matrix, rows in increasing order; out has rthc_owned_pairs() */
 int rthc_get_owned_condensed_u16(rthc_ctx *ctx, uint16_t *out);
+/* entries [first, first+count) of the owned condensed vector (block-wise checks of matrices
+ * that should not be copied to the host in one piece; same seam as rthc_get_condensed_u16) */
+int rthc_get_condensed_range_u16(rthc_ctx *ctx, int64_t first, int64_t count, uint16_t *out);
 /* rows [row0, row0+nrows) of the SQUARE matrix (nrows x n, uint16), full shard only:
  * the block the `_dist_hamming.tsv` writer streams.                                 */
 int rthc_copy_rows_u16(rthc_ctx *ctx, int64_t row0, int64_t nrows, uint16_t *out);
@@ -173,7 +176,9 @@ int rthc_adjusted_wallace_sums(const int32_t *cell_row, const int32_t *cell_coun
 /* ---- introspection ----------------------------------------------------------- */
 /* info[0]=n, [1]=L, [2]=loci kept, [3]=groups of 32 loci, [4]=plane rows,
  * [5]=tiles launched, [6]=Boruvka rounds of the last linkage, [7]=max alleles/locus,
- * [8]=row scans of the last merge loop                                             */
+ * [8]=row scans of the last merge loop (own barrier + fused with a merge),
+ * [9]=of those, scans that paid their own grid barrier, [10]=chain steps answered by the
+ * nearest-neighbour cache (no scan)                                                  */
 int rthc_info(const rthc_ctx *ctx, int64_t *info, int n_info);
 /* device-side durations (CUDA events, ms) of the last call of each stage:
  * [0]=h2d, [1]=recode+pack, [2]=distance kernel, [3]=mst/merge loop, [4]=cut,

@@ -15,7 +15,7 @@
  * scipy ships these only as a compiled extension (no .pyx in the wheel); the
  * algorithms are restated from scipy's published description (SURVEY.md section 8,
  * rows A7-A9) and PINNED against the live scipy 1.18.1 in this image on
- * tie-heavy integer matrices (tests/test_oracle_hclust.py): identical Z and
+ * tie-heavy integer matrices (tests/test_oracle_golden.py): identical Z and
  * identical fcluster labels.  scipy is importable on the GPU box too, so GPU
  * tests compare with scipy directly as well.
  */
@@ -231,4 +231,92 @@ void oracle_fcluster_distance(const double *Z, int64_t n, double cutoff, int32_t
         --k;
     }
     free(visited); free(stack); free(MD);
+}
+
+/* ---- uint16 condensed input (integer allelic distances as the distance kernel stores them) ----
+ * Same algorithms, same visiting order and tie rules as the float64 entry points above; only the
+ * storage type of the condensed matrix differs, so that configs[3] (100,000 samples: 10 GB instead of
+ * 40 GB) and configs[4] (2.3 GB instead of 9 GB) fit a workstation.  Every uint16 is exactly
+ * representable as a double, so Z is bit-identical to the float64 path (tests/test_oracle_golden.py
+ * checks that on the same tie-heavy matrices that pin the float64 path on scipy). */
+void oracle_linkage_single_u16(const uint16_t *y, int64_t n, double *Z)
+{
+    int64_t m = n - 1;
+    double *Z3 = (double *)malloc(sizeof(double) * 3 * (size_t)(m > 0 ? m : 1));
+    double *D = (double *)malloc(sizeof(double) * (size_t)n);
+    char *merged = (char *)calloc((size_t)n, 1);
+    for (int64_t i = 0; i < n; ++i) D[i] = INFINITY;
+    int64_t x = 0, yv = 0;
+    for (int64_t k = 0; k < m; ++k) {
+        double cur = INFINITY;
+        merged[x] = 1;
+        for (int64_t i = 0; i < n; ++i) {
+            if (merged[i]) continue;
+            double d = (double)y[cidx(n, x, i)];
+            if (D[i] > d) D[i] = d;
+            if (D[i] < cur) { yv = i; cur = D[i]; }
+        }
+        Z3[3 * k] = (double)x; Z3[3 * k + 1] = (double)yv; Z3[3 * k + 2] = cur;
+        x = yv;
+    }
+    int64_t *order = (int64_t *)malloc(sizeof(int64_t) * (size_t)(m > 0 ? m : 1));
+    stable_order_by_dist(Z3, m, order);
+    label_rows(Z3, order, n, Z);
+    free(order); free(merged); free(D); free(Z3);
+}
+
+/* complete (method 1) and single-by-chain (0) never leave the integers: the working copy stays uint16.
+ * average / weighted / ward need the float64 working copy and go through oracle_linkage_nn_chain. */
+void oracle_linkage_nn_chain_u16(const uint16_t *y_in, int64_t n, int method, double *Z)
+{
+    int64_t m = n - 1, P = n * (n - 1) / 2;
+    if (method != 0 && method != 1) {
+        double *yf = (double *)malloc(sizeof(double) * (size_t)(P > 0 ? P : 1));
+        for (int64_t p = 0; p < P; ++p) yf[p] = (double)y_in[p];
+        oracle_linkage_nn_chain(yf, n, method, Z);
+        free(yf);
+        return;
+    }
+    uint16_t *D = (uint16_t *)malloc(sizeof(uint16_t) * (size_t)(P > 0 ? P : 1));
+    memcpy(D, y_in, sizeof(uint16_t) * (size_t)P);
+    double *Z3 = (double *)malloc(sizeof(double) * 3 * (size_t)(m > 0 ? m : 1));
+    int64_t *size = (int64_t *)malloc(sizeof(int64_t) * (size_t)n);
+    int64_t *chain = (int64_t *)malloc(sizeof(int64_t) * (size_t)n);
+    for (int64_t i = 0; i < n; ++i) size[i] = 1;
+    int64_t len = 0;
+    for (int64_t k = 0; k < m; ++k) {
+        int64_t x = 0, yv = 0;
+        int32_t cur = 0;                       /* 0x10000 plays +inf: above every uint16 */
+        if (len == 0) {
+            len = 1;
+            for (int64_t i = 0; i < n; ++i)
+                if (size[i] > 0) { chain[0] = i; break; }
+        }
+        for (;;) {
+            x = chain[len - 1];
+            if (len > 1) { yv = chain[len - 2]; cur = D[cidx(n, x, yv)]; }
+            else cur = 0x10000;
+            for (int64_t i = 0; i < n; ++i) {
+                if (size[i] == 0 || x == i) continue;
+                int32_t d = D[cidx(n, x, i)];
+                if (d < cur) { cur = d; yv = i; }
+            }
+            if (len > 1 && yv == chain[len - 2]) break;
+            chain[len++] = yv;
+        }
+        len -= 2;
+        if (x > yv) { int64_t t = x; x = yv; yv = t; }
+        int64_t nx = size[x], ny = size[yv];
+        Z3[3 * k] = (double)x; Z3[3 * k + 1] = (double)yv; Z3[3 * k + 2] = (double)cur;
+        size[x] = 0; size[yv] = nx + ny;
+        for (int64_t i = 0; i < n; ++i) {
+            if (size[i] == 0 || i == yv) continue;
+            uint16_t dxi = D[cidx(n, i, x)], dyi = D[cidx(n, i, yv)];
+            D[cidx(n, i, yv)] = method == 1 ? (dxi > dyi ? dxi : dyi) : (dxi < dyi ? dxi : dyi);
+        }
+    }
+    int64_t *order = (int64_t *)malloc(sizeof(int64_t) * (size_t)(m > 0 ? m : 1));
+    stable_order_by_dist(Z3, m, order);
+    label_rows(Z3, order, n, Z);
+    free(order); free(chain); free(size); free(Z3); free(D);
 }

@@ -34,11 +34,14 @@ def lib():
         L.oracle_linkage_single.argtypes = [p, i64, p]
         L.oracle_prim_edges.argtypes = [p, i64, p]
         L.oracle_linkage_nn_chain.argtypes = [p, i64, ctypes.c_int, p]
+        L.oracle_linkage_single_u16.argtypes = [p, i64, p]
+        L.oracle_linkage_nn_chain_u16.argtypes = [p, i64, ctypes.c_int, p]
         L.oracle_maxdists.argtypes = [p, i64, p]
         L.oracle_fcluster_distance.argtypes = [p, i64, ctypes.c_double, p]
         for f in ("oracle_dist_square_i32", "oracle_dist_condensed_rows_u16",
                   "oracle_dist_square_chunked_i32", "oracle_linkage_single", "oracle_prim_edges",
-                  "oracle_linkage_nn_chain", "oracle_maxdists", "oracle_fcluster_distance"):
+                  "oracle_linkage_nn_chain", "oracle_linkage_single_u16", "oracle_linkage_nn_chain_u16",
+                  "oracle_maxdists", "oracle_fcluster_distance"):
             getattr(L, f).restype = None
         _lib = L
     return _lib
@@ -81,6 +84,19 @@ METHODS = {"single": 0, "complete": 1, "average": 2, "weighted": 3, "ward": 4}
 
 
 def linkage(y, method):
+    """scipy linkage(y, method).  A uint16 condensed vector (the distance kernel's storage type) is
+    consumed as it is -- no float64 copy for single / complete -- so configs[3] / [4] fit the host."""
+    y = np.asarray(y)
+    if y.dtype == np.uint16:
+        y = np.ascontiguousarray(y)
+        n = int(round((1 + (1 + 8 * y.size) ** 0.5) / 2))
+        assert n * (n - 1) // 2 == y.size
+        Z = np.empty((n - 1, 4), dtype=np.float64)
+        if method == "single":
+            lib().oracle_linkage_single_u16(_ptr(y), n, _ptr(Z))
+        else:
+            lib().oracle_linkage_nn_chain_u16(_ptr(y), n, METHODS[method], _ptr(Z))
+        return Z
     y = np.ascontiguousarray(y, dtype=np.float64)
     n = int(round((1 + (1 + 8 * y.size) ** 0.5) / 2))
     assert n * (n - 1) // 2 == y.size

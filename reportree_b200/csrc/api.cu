@@ -375,6 +375,17 @@ extern "C" int rthc_get_owned_condensed_u16(rthc_ctx *ctx, uint16_t *out)
     return 0;
 }
 
+extern "C" int rthc_get_condensed_range_u16(rthc_ctx *ctx, int64_t first, int64_t count, uint16_t *out)
+{
+    if (!ctx || !out) return rthc_fail(ctx, RTHC_E_ARG, "NULL argument");
+    if (!ctx->have_dist) return rthc_fail(ctx, RTHC_E_STATE, "no distance matrix yet");
+    if (first < 0 || count < 0 || first + count > ctx->owned_pairs) return rthc_fail(ctx, RTHC_E_ARG, "condensed range out of bounds");
+    if (count == 0) return 0;
+    RTHC_CUDA(ctx, cudaSetDevice(ctx->device));
+    RTHC_CUDA(ctx, cudaMemcpy(out, ctx->d_cond + first, sizeof(uint16_t) * (size_t)count, cudaMemcpyDeviceToHost));
+    return 0;
+}
+
 extern "C" int rthc_get_condensed_u16(rthc_ctx *ctx, uint16_t *out)
 {
     if (ctx && ctx->world != 1) return rthc_fail(ctx, RTHC_E_STATE, "full condensed copy needs a full shard");
@@ -441,9 +452,10 @@ extern "C" int rthc_direct_pairs(rthc_ctx *ctx, const int32_t *pi, const int32_t
 extern "C" int rthc_info(const rthc_ctx *ctx, int64_t *info, int n_info)
 {
     if (!ctx || !info) return RTHC_E_ARG;
-    const int64_t v[9] = {ctx->n, ctx->L, ctx->L_kept, ctx->G, ctx->plane_rows, ctx->n_tiles,
-                          ctx->boruvka_rounds, ctx->max_alleles, ctx->row_scans};
-    for (int k = 0; k < n_info && k < 9; ++k) info[k] = v[k];
+    const int64_t v[11] = {ctx->n, ctx->L, ctx->L_kept, ctx->G, ctx->plane_rows, ctx->n_tiles,
+                           ctx->boruvka_rounds, ctx->max_alleles, ctx->row_scans, ctx->chain_full_scans,
+                           ctx->chain_cache_hits};
+    for (int k = 0; k < n_info && k < 11; ++k) info[k] = v[k];
     return 0;
 }
 

@@ -175,7 +175,9 @@ int rthc_run_cut(rthc_ctx *ctx, const double *t, int T, int32_t *labels_out)
         limit[(size_t)q] = (int32_t)(n + K);
     }
     // thresholds are processed in chunks that bound device memory (labels + keys + flags)
-    const int64_t chunkT = std::max<int64_t>(1, std::min<int64_t>(T, (int64_t)(1ll << 27) / std::max<int64_t>(n, 1)));
+    // ... and the threshold index rides on gridDim.y (and gridDim.x of the aux scan), limit 65,535
+    const int64_t chunkT = std::max<int64_t>(1, std::min<int64_t>(std::min<int64_t>(T, 60000),
+                                                                  (int64_t)(1ll << 27) / std::max<int64_t>(n, 1)));
     const int64_t flag_stride = (nodes + 3) / 4 * 4;
     const int nbs = (int)((nodes + CUT_SCAN_ELEMS - 1) / CUT_SCAN_ELEMS);
     int32_t *d_limit = nullptr, *d_key = nullptr, *d_flags = nullptr, *d_labels = nullptr, *d_aux = nullptr;

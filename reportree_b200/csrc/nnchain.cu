@@ -508,125 +508,204 @@ __global__ void rthc_expand_square(const S *__restrict__ cond, int64_t n, T *__r
 
 // control block in global memory (written by block 0, thread 0 only)
 struct ChainCtl {
-    int64_t scans;
+    int64_t scans;      // full row scans (one grid barrier each)
+    int64_t fused;      // scans of the next chain tip that rode on a merge's barrier
+    int64_t hits;       // chain steps answered by the nearest-neighbour cache (no barrier)
 };
 
-// all-lanes lexicographic minimum of (w, i) over a warp
-__device__ __forceinline__ void warp_min_all(unsigned long long &w, unsigned int &i)
-{
-#pragma unroll
-    for (int s = 16; s > 0; s >>= 1) {
-        unsigned long long ow = __shfl_xor_sync(0xffffffffu, w, s);
-        unsigned int oi = __shfl_xor_sync(0xffffffffu, i, s);
-        if (slot_less(ow, oi, w, i)) { w = ow; i = oi; }
-    }
-}
-
-// step barrier + exchange of the per-CTA minima.  CL = false: cooperative grid, slots in global memory, grid.sync().
-// CL = true: the whole loop runs inside ONE thread-block cluster (<= 16 CTAs): every CTA stores its minimum into the
-// slot table of all CTAs through distributed shared memory and barrier.cluster replaces the grid barrier (the
-// step is latency-bound: 4.7 us with the grid barrier whatever the CTA count).
-template <bool CL> struct SeqSync {
-    __device__ static __forceinline__ void sync()
-    {
-        if constexpr (CL) cg::this_cluster().sync();
-        else cg::this_grid().sync();
-    }
-};
-
-template <typename T, bool CL>
-__global__ void __launch_bounds__(SEQ_THREADS, 1)
-rthc_nn_chain_kernel(T *W, int64_t n, int method, int32_t *size, int32_t *chain, MinSlot *slots, int32_t *ex,
-                     int32_t *ey, double *ew, ChainCtl *ctl)
+// nearest neighbour of every row: lexicographic minimum of (D[r, i], i) over i != r  (one CTA per row)
+template <typename T>
+__global__ void __launch_bounds__(SEQ_THREADS) rthc_nn_init(const T *__restrict__ W, int64_t n, MinSlot *__restrict__ nn)
 {
     __shared__ MinSlot sh[SEQ_THREADS / 32];
-    __shared__ MinSlot cslot[2][PC_MAX_CLUSTER];               // CL: written by every CTA of the cluster
+    const int64_t r = blockIdx.x;
+    const T *row = W + r * n;
+    unsigned long long bw = ~0ull;
+    unsigned int bi = ~0u;
+    for (int64_t i = threadIdx.x; i < n; i += SEQ_THREADS) {
+        if (i == r) continue;
+        const unsigned long long d = order_bits(row[i]);
+        if (slot_less(d, (unsigned int)i, bw, bi)) { bw = d; bi = (unsigned int)i; }
+    }
+    block_min(bw, bi, sh);
+    if (threadIdx.x == 0) { nn[r].w = bw; nn[r].i = bi; }
+}
+
+// The merge loop.  scipy's chain step asks for the nearest neighbour of the chain tip x: the previous chain
+// element if it ties the minimum, else the lowest index of the minimum of row x.  A grid-wide row scan costs one
+// grid barrier (about 2.4 us) however short the row is, so the kernel keeps, for every live row r, the exact
+// lexicographic minimum nn[r] = min over live i != r of (D[r, i], i) and only scans when that entry is unknown:
+//   * a merge (a dies, b = a u b) already visits every live row i to write D[i, b]; the same thread folds the new
+//     entry into the cache -- nn[i] = min(nn[i], (D[i, b], b)) is exact because every other entry of row i is
+//     unchanged -- and drops it (index = ~0) when the cached neighbour was a or b;
+//   * the candidates (D[b, i], i) of the new row b are reduced over the grid on the merge's own barrier;
+//   * so is a scan of the row of p, the chain element that becomes the tip after the merge (its neighbour was a
+//     or b by construction): row p only changes in column b, whose new value the thread that owns i == p has.
+// A chain step whose tip has a cached neighbour reads it (warp 0 of every CTA, broadcast through shared memory)
+// and costs no barrier.  The answer is the same (value, lowest index, previous-wins) triple as the scan, so Z
+// stays byte-identical to scipy.  nn[] is double-buffered by merge parity: a merge writes the other copy for every
+// live row, so a CTA still walking the chain never reads an entry that a faster CTA has already updated.
+// Every nn[r] is written by ONE thread (the owner of index r in the strided loops), reads of scalar state go
+// through warp 0 + shared memory (148 x 16 warps loading one address serialise in L2), size[] of the last merge
+// is patched from registers until the next barrier has published it.
+template <typename T>
+__global__ void __launch_bounds__(SEQ_THREADS, 1)
+rthc_nn_chain_kernel(T *W, int64_t n, int method, int32_t *size, int32_t *chains, MinSlot *slots, MinSlot *nn2,
+                     int32_t *ex, int32_t *ey, double *ew, ChainCtl *ctl)
+{
+    cg::grid_group grid = cg::this_grid();
+    __shared__ MinSlot sh[SEQ_THREADS / 32];
+    __shared__ MinSlot bcs[2];                                   // broadcast buffers, alternating
+    __shared__ unsigned long long bcd[2];
+    __shared__ int32_t bci[2][4];
     const int nblocks = gridDim.x;
     const int64_t gtid = (int64_t)blockIdx.x * SEQ_THREADS + threadIdx.x;
     const int64_t gthreads = (int64_t)nblocks * SEQ_THREADS;
     const bool leader = blockIdx.x == 0 && threadIdx.x == 0;
+    const int lane = threadIdx.x & 31;
+    const bool w0 = threadIdx.x < 32;
+    int32_t *chain = chains + (int64_t)blockIdx.x * n;          // this CTA's copy, touched by its thread 0 only
 
     // replicated scalar state (identical in every thread of the grid)
-    int64_t len = 0, first_live = 0, step = 0, scans = 0;
+    int64_t len = 0, first_live = 0, step = 0, scans = 0, fused = 0, hits = 0;
     int32_t x = -1, prev = -1;
-    int32_t dead = -1;                 // cluster retired by the previous merge: its size[] update may
-    int32_t grown = -1, grown_size = 0; // not be visible yet, so it is excluded / patched explicitly
+    int32_t dead = -1, grown = -1, grown_size = 0;              // last merge, until the next barrier publishes size[]
+    unsigned long long gw = ~0ull; unsigned int gi = ~0u;        // nn of `grown`
+    bool have_tip = false;                                       // nn of the tip is in (tw, ti, tdprev)
+    unsigned long long tw = ~0ull, tdprev = ~0ull; unsigned int ti = ~0u;
+    int q = 0, cur = 0;                                          // broadcast buffer, current nn copy
+
+#define SIZE_OF(i_) ((i_) == dead ? 0 : ((i_) == grown ? grown_size : __ldcg(&size[(i_)])))
 
     for (int64_t k = 0; k < n - 1;) {
+        MinSlot *nn = nn2 + (int64_t)cur * n;
         if (len == 0) {
-            while (first_live == dead || __ldcg(&size[first_live]) == 0) ++first_live;
-            x = (int32_t)first_live;
-            prev = -1;
-            len = 1;
-            if (leader) chain[0] = x;
-        }
-        // ---- scan row x: lowest index of the minimum over live i != x -------------------------
-        unsigned long long bw = ~0ull;
-        unsigned int bi = ~0u;
-        const T *row = W + (int64_t)x * n;
-        // D[x, prev] is needed right after the reduction: request it with the row, not after it
-        const unsigned long long dprev = len > 1 ? order_bits(__ldcg(&row[prev])) : ~0ull;
-        for (int64_t i = gtid; i < n; i += gthreads) {
-            if (i == x || i == dead || __ldcg(&size[i]) == 0) continue;
-            const unsigned long long d = order_bits(__ldcg(&row[i]));
-            if (slot_less(d, (unsigned int)i, bw, bi)) { bw = d; bi = (unsigned int)i; }
-        }
-        block_min(bw, bi, sh);                                  // valid in warp 0
-        MinSlot *cur = slots + (step & 1) * nblocks;
-        if constexpr (CL) {
-            if (threadIdx.x < (unsigned)nblocks) {
-                MinSlot *dst = cg::this_cluster().map_shared_rank(&cslot[step & 1][blockIdx.x], threadIdx.x);
-                dst->w = bw; dst->i = bi;
+            if (w0) {                                            // lowest live index, 32 candidates per trip
+                int64_t f = first_live;
+                for (;;) {
+                    const int64_t i = f + lane;
+                    const bool live = i < n && SIZE_OF(i) != 0;
+                    const unsigned m = __ballot_sync(0xffffffffu, live);
+                    if (m) { f += __ffs(m) - 1; break; }
+                    f += 32;
+                }
+                if (lane == 0) { bci[q][0] = (int32_t)f; chain[0] = (int32_t)f; }
             }
-        } else {
-            if (threadIdx.x == 0) { cur[blockIdx.x].w = bw; cur[blockIdx.x].i = bi; }
+            __syncthreads();
+            first_live = bci[q][0]; q ^= 1;
+            x = (int32_t)first_live; prev = -1; len = 1; have_tip = false;
         }
-        if (leader && dead >= 0) { size[dead] = 0; size[grown] = grown_size; }   // publish last merge's sizes
-        SeqSync<CL>::sync();
-        if constexpr (CL) {
-            const int l = threadIdx.x & 31;
-            bw = l < nblocks ? cslot[step & 1][l].w : ~0ull;
-            bi = l < nblocks ? cslot[step & 1][l].i : ~0u;
-            warp_min_all(bw, bi);
+        // ---- nearest neighbour of the tip x -----------------------------------------------------
+        unsigned long long cw, dprev;
+        unsigned int ci;
+        if (have_tip) {
+            cw = tw; ci = ti; dprev = tdprev;
+            have_tip = false;
         } else {
-            grid_min(cur, nblocks, bw, bi, sh);
+            if (threadIdx.x == 0) {
+                if (x == grown) { bcs[q].w = gw; bcs[q].i = gi; }
+                else { bcs[q].w = __ldcg(&nn[x].w); bcs[q].i = __ldcg(&nn[x].i); }
+                bcd[q] = len > 1 ? order_bits(__ldcg(&W[(int64_t)x * n + prev])) : ~0ull;
+            }
+            __syncthreads();
+            cw = bcs[q].w; ci = bcs[q].i; dprev = bcd[q]; q ^= 1;
+            if (ci != ~0u) ++hits;
         }
-        ++step; ++scans;
-        dead = -1;
-        int32_t y = (int32_t)bi;
-        unsigned long long dmin = bw;
+        if (ci == ~0u) {
+            // ---- unknown: scan row x over the grid (lowest index of the minimum over live i != x) --
+            unsigned long long bw = ~0ull;
+            unsigned int bi = ~0u;
+            const T *row = W + (int64_t)x * n;
+            for (int64_t i = gtid; i < n; i += gthreads) {
+                if (i == x || SIZE_OF(i) == 0) continue;
+                const unsigned long long d = order_bits(__ldcg(&row[i]));
+                if (slot_less(d, (unsigned int)i, bw, bi)) { bw = d; bi = (unsigned int)i; }
+            }
+            block_min(bw, bi, sh);
+            MinSlot *cs = slots + (step & 1) * nblocks;
+            if (threadIdx.x == 0) { cs[blockIdx.x].w = bw; cs[blockIdx.x].i = bi; }
+            grid.sync();
+            grid_min(cs, nblocks, cw, ci, sh);
+            ++step; ++scans;
+            dead = -1; grown = -1;
+            if (gtid == x % gthreads) { nn[x].w = cw; nn[x].i = ci; }
+        }
+        int32_t y = (int32_t)ci;
+        unsigned long long dmin = cw;
         if (len > 1 && dprev <= dmin) { y = prev; dmin = dprev; }  // previous chain element wins ties
         if (!(len > 1 && y == prev)) {
             // ---- extend the chain ---------------------------------------------------------------
-            if (leader) chain[len] = y;
+            if (threadIdx.x == 0) chain[len] = y;
             prev = x; x = y; ++len;
             continue;
         }
         // ---- merge x and y (reciprocal nearest neighbours) ---------------------------------------
-        int32_t a = x < y ? x : y, b = x < y ? y : x;             // a dies, b survives (scipy: x < y swap)
-        const int32_t na = __ldcg(&size[a]), nb = __ldcg(&size[b]);
+        const int32_t a = x < y ? x : y, b = x < y ? y : x;       // a dies, b survives (scipy: x < y swap)
+        if (threadIdx.x == 0) {
+            bci[q][0] = SIZE_OF(a); bci[q][1] = SIZE_OF(b);
+            const int32_t p0 = len >= 3 ? chain[len - 3] : -1, pp0 = len >= 4 ? chain[len - 4] : -1;
+            bci[q][2] = p0; bci[q][3] = pp0;
+            bcd[q] = pp0 >= 0 ? order_bits(__ldcg(&W[(int64_t)p0 * n + pp0])) : ~0ull;
+        }
+        __syncthreads();
+        const int32_t na = bci[q][0], nb = bci[q][1], p = bci[q][2], pp = bci[q][3];
+        const unsigned long long dpp = bcd[q];
+        q ^= 1;
         if (leader) { ex[k] = a; ey[k] = b; ew[k] = from_bits(dmin, T()); }
         const T *ra = W + (int64_t)a * n;
         T *rb = W + (int64_t)b * n;
+        const T *rp = W + (int64_t)(p >= 0 ? p : 0) * n;
+        MinSlot *nxt = nn2 + (int64_t)(cur ^ 1) * n;
         const double dab = from_bits(dmin, T());
+        unsigned long long bwb = ~0ull, bwp = ~0ull;
+        unsigned int bib = ~0u, bip = ~0u;
         for (int64_t i = gtid; i < n; i += gthreads) {
             int32_t ni;
-            if (i == a || i == b || (ni = __ldcg(&size[i])) == 0) continue;
+            if (i == a || i == b || (ni = SIZE_OF(i)) == 0) continue;
             const T v = lance_williams<T>(method, __ldcg(&ra[i]), __ldcg(&rb[i]), dab, na, nb, ni);
             rb[i] = v;                       // row b (contiguous)
             W[i * n + b] = v;                // column b (symmetric copy)
+            const unsigned long long ob = order_bits(v);
+            if (slot_less(ob, (unsigned int)i, bwb, bib)) { bwb = ob; bib = (unsigned int)i; }
+            if (i == p) {                    // row p: its only changed entry; the rest is scanned below
+                if (slot_less(ob, (unsigned int)b, bwp, bip)) { bwp = ob; bip = (unsigned int)b; }
+            } else {
+                unsigned long long ow = __ldcg(&nn[i].w);
+                unsigned int oi = __ldcg(&nn[i].i);
+                if (oi == (unsigned int)a || oi == (unsigned int)b) oi = ~0u;
+                else if (oi != ~0u && slot_less(ob, (unsigned int)b, ow, oi)) { ow = ob; oi = (unsigned int)b; }
+                __stcg(&nxt[i].w, ow); __stcg(&nxt[i].i, oi);
+                if (p >= 0) {
+                    const unsigned long long d = order_bits(__ldcg(&rp[i]));
+                    if (slot_less(d, (unsigned int)i, bwp, bip)) { bwp = d; bip = (unsigned int)i; }
+                }
+            }
         }
+        block_min(bwb, bib, sh);
+        MinSlot *sb = slots + (2 + (step & 1)) * nblocks, *sp = slots + (4 + (step & 1)) * nblocks;
+        if (threadIdx.x == 0) { sb[blockIdx.x].w = bwb; sb[blockIdx.x].i = bib; }
+        if (p >= 0) {
+            block_min(bwp, bip, sh);
+            if (threadIdx.x == 0) { sp[blockIdx.x].w = bwp; sp[blockIdx.x].i = bip; }
+        }
+        grid.sync();                          // row/column b and the other nn copy are visible
+        ++step;
+        cur ^= 1;
+        grid_min(sb, nblocks, gw, gi, sh);
+        if (gtid == b % gthreads) { __stcg(&nxt[b].w, gw); __stcg(&nxt[b].i, gi); }
+        if (p >= 0) {
+            grid_min(sp, nblocks, tw, ti, sh);
+            tdprev = dpp; have_tip = true; ++fused;
+            if (gtid == p % gthreads) { __stcg(&nxt[p].w, tw); __stcg(&nxt[p].i, ti); }
+        }
+        if (leader) { size[a] = 0; size[b] = na + nb; }
         dead = a; grown = b; grown_size = na + nb;
         ++k;
         len -= 2;
-        SeqSync<CL>::sync();                  // row/column b visible before the next scan
-        ++step;
-        if (len > 0) {
-            x = __ldcg(&chain[len - 1]);
-            prev = len > 1 ? __ldcg(&chain[len - 2]) : -1;
-        }
+        if (len > 0) { x = p; prev = pp; }
     }
-    if (leader) ctl->scans = scans;
+#undef SIZE_OF
+    if (leader) { ctl->scans = scans; ctl->fused = fused; ctl->hits = hits; }
 }
 
 template <typename T, typename S>
@@ -637,14 +716,15 @@ static int run_nn_chain(rthc_ctx *ctx, const S *d_cond, int method, std::vector<
     T *d_W = nullptr;
     int32_t *d_size = nullptr, *d_chain = nullptr, *d_ex = nullptr, *d_ey = nullptr;
     double *d_ew = nullptr;
-    MinSlot *d_slots = nullptr;
+    MinSlot *d_slots = nullptr, *d_nn = nullptr;
     ChainCtl *d_ctl = nullptr;
     int nblocks = ctx->sm_count;
     int rc;
     if ((rc = rthc_dev_alloc(ctx, &d_W, (size_t)(n * n)))) return rc;
     if ((rc = rthc_dev_alloc(ctx, &d_size, (size_t)n))) return rc;
-    if ((rc = rthc_dev_alloc(ctx, &d_chain, (size_t)n))) return rc;
-    if ((rc = rthc_dev_alloc(ctx, &d_slots, (size_t)2 * nblocks))) return rc;
+    if ((rc = rthc_dev_alloc(ctx, &d_chain, (size_t)n * (size_t)nblocks))) return rc;
+    if ((rc = rthc_dev_alloc(ctx, &d_slots, (size_t)6 * nblocks))) return rc;
+    if ((rc = rthc_dev_alloc(ctx, &d_nn, (size_t)2 * (size_t)n))) return rc;
     if ((rc = rthc_dev_alloc(ctx, &d_ex, (size_t)m))) return rc;
     if ((rc = rthc_dev_alloc(ctx, &d_ey, (size_t)m))) return rc;
     if ((rc = rthc_dev_alloc(ctx, &d_ew, (size_t)m))) return rc;
@@ -653,42 +733,17 @@ static int run_nn_chain(rthc_ctx *ctx, const S *d_cond, int method, std::vector<
         dim3 grd((unsigned)n, (unsigned)((n + 255) / 256));
         rthc_expand_square<T, S><<<grd, 256, 0, ctx->stream>>>(d_cond, n, d_W);
         RTHC_LAUNCH_CHECK(ctx);
+        rthc_nn_init<T><<<(unsigned)n, SEQ_THREADS, 0, ctx->stream>>>(d_W, n, d_nn);
+        RTHC_LAUNCH_CHECK(ctx);
         std::vector<int32_t> ones((size_t)n, 1);
         RTHC_CUDA(ctx, cudaMemcpyAsync(d_size, ones.data(), sizeof(int32_t) * (size_t)n, cudaMemcpyHostToDevice, ctx->stream));
         RTHC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     }
     int64_t nn = n;
     void *args[] = {(void *)&d_W, (void *)&nn, (void *)&method, (void *)&d_size, (void *)&d_chain, (void *)&d_slots,
-                    (void *)&d_ex, (void *)&d_ey, (void *)&d_ew, (void *)&d_ctl};
-    // A/B switch, off by default: unlike Prim the merge loop does not gain from the cluster (C3 average 0.29 vs 0.32 s,
-    // C5 complete 1.06 vs 0.89 s): its merges scatter a column over the matrix and want all 148 SMs
-    static const bool use_cluster = getenv("RTHC_NNCHAIN_CLUSTER") && atoi(getenv("RTHC_NNCHAIN_CLUSTER")) == 1;
-    cudaError_t ce = cudaErrorInvalidConfiguration;
-    if (use_cluster) {                                           // one cluster of 16 (or 8) CTAs
-        auto kern = rthc_nn_chain_kernel<T, true>;
-        for (int C = PC_MAX_CLUSTER; C >= 8 && ce != cudaSuccess; C >>= 1) {
-            if (C > 8 && cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) != cudaSuccess) {
-                cudaGetLastError();
-                continue;
-            }
-            cudaLaunchConfig_t cfg = {};
-            cfg.gridDim = dim3((unsigned)C);
-            cfg.blockDim = dim3(SEQ_THREADS);
-            cfg.stream = ctx->stream;
-            cudaLaunchAttribute attr[1];
-            attr[0].id = cudaLaunchAttributeClusterDimension;
-            attr[0].val.clusterDim.x = (unsigned)C; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
-            cfg.attrs = attr; cfg.numAttrs = 1;
-            int clusters = 0;
-            ce = cudaOccupancyMaxActiveClusters(&clusters, kern, &cfg);
-            if (ce == cudaSuccess && clusters < 1) ce = cudaErrorInvalidConfiguration;
-            if (ce == cudaSuccess) ce = cudaLaunchKernelEx(&cfg, kern, d_W, nn, method, d_size, d_chain, d_slots, d_ex, d_ey, d_ew, d_ctl);
-            if (ce != cudaSuccess) cudaGetLastError();
-        }
-    }
-    if (ce != cudaSuccess)
-        RTHC_CUDA(ctx, cudaLaunchCooperativeKernel((void *)rthc_nn_chain_kernel<T, false>, dim3(nblocks), dim3(SEQ_THREADS), args,
-                                                   0, ctx->stream));
+                    (void *)&d_nn, (void *)&d_ex, (void *)&d_ey, (void *)&d_ew, (void *)&d_ctl};
+    RTHC_CUDA(ctx, cudaLaunchCooperativeKernel((void *)rthc_nn_chain_kernel<T>, dim3(nblocks), dim3(SEQ_THREADS), args, 0,
+                                               ctx->stream));
     ctx->launches++;
     ex.resize((size_t)m); ey.resize((size_t)m); ew.resize((size_t)m);
     ChainCtl ctl;
@@ -697,9 +752,12 @@ static int run_nn_chain(rthc_ctx *ctx, const S *d_cond, int method, std::vector<
     RTHC_CUDA(ctx, cudaMemcpyAsync(ew.data(), d_ew, sizeof(double) * (size_t)m, cudaMemcpyDeviceToHost, ctx->stream));
     RTHC_CUDA(ctx, cudaMemcpyAsync(&ctl, d_ctl, sizeof(ChainCtl), cudaMemcpyDeviceToHost, ctx->stream));
     RTHC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-    ctx->row_scans = ctl.scans;
+    ctx->row_scans = ctl.scans + ctl.fused;
+    ctx->chain_full_scans = ctl.scans;
+    ctx->chain_cache_hits = ctl.hits;
     rthc_dev_free(ctx, &d_W); rthc_dev_free(ctx, &d_size); rthc_dev_free(ctx, &d_chain); rthc_dev_free(ctx, &d_slots);
-    rthc_dev_free(ctx, &d_ex); rthc_dev_free(ctx, &d_ey); rthc_dev_free(ctx, &d_ew); rthc_dev_free(ctx, &d_ctl);
+    rthc_dev_free(ctx, &d_nn); rthc_dev_free(ctx, &d_ex); rthc_dev_free(ctx, &d_ey); rthc_dev_free(ctx, &d_ew);
+    rthc_dev_free(ctx, &d_ctl);
     return 0;
 }
 

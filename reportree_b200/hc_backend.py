@@ -54,6 +54,7 @@ def load_library():
         "rthc_owned_pairs": (i64, [vp]),
         "rthc_get_condensed_u16": (ci, [vp, vp]),
         "rthc_get_owned_condensed_u16": (ci, [vp, vp]),
+        "rthc_get_condensed_range_u16": (ci, [vp, i64, i64, vp]),
         "rthc_copy_rows_u16": (ci, [vp, i64, i64, vp]),
         "rthc_direct_pairs": (ci, [vp, vp, vp, i64, vp]),
         "rthc_set_condensed_f64": (ci, [vp, vp, i64]),
@@ -87,7 +88,7 @@ EXPORTED_SYMBOLS = [
     "rthc_create", "rthc_prewarm", "rthc_destroy", "rthc_last_error", "rthc_version", "rthc_set_shard",
     "rthc_set_shard_full_storage", "rthc_import_shard", "rthc_finish_import",
     "rthc_set_profiles_i32", "rthc_set_profiles_i32_device", "rthc_distance", "rthc_owned_pairs",
-    "rthc_get_condensed_u16", "rthc_get_owned_condensed_u16", "rthc_copy_rows_u16", "rthc_direct_pairs",
+    "rthc_get_condensed_u16", "rthc_get_owned_condensed_u16", "rthc_get_condensed_range_u16", "rthc_copy_rows_u16", "rthc_direct_pairs",
     "rthc_set_condensed_f64", "rthc_set_single_algo", "rthc_linkage", "rthc_local_forest",
     "rthc_linkage_from_forest", "rthc_local_forest_device", "rthc_linkage_from_forest_device", "rthc_cut", "rthc_info", "rthc_timings", "rthc_mark", "rthc_mark_elapsed_ms", "rthc_alu_peak",
     "rthc_alu_peak_block", "rthc_closest", "rthc_subset_from",
@@ -170,6 +171,12 @@ class HCContext:
         """Full condensed uint16 distance vector in scipy pdist order (squareform-compatible)."""
         out = np.empty(self.n * (self.n - 1) // 2, dtype=np.uint16)
         self._check(self._L.rthc_get_condensed_u16(self._h, _ptr(out)))
+        return out
+
+    def condensed_range(self, first, count):
+        """Entries [first, first + count) of the (owned) condensed vector."""
+        out = np.empty(int(count), dtype=np.uint16)
+        self._check(self._L.rthc_get_condensed_range_u16(self._h, int(first), int(count), _ptr(out)))
         return out
 
     def owned_condensed(self):
@@ -299,9 +306,10 @@ class HCContext:
 
     # ---- introspection -----------------------------------------------------------------
     def info(self):
-        a = np.zeros(9, dtype=np.int64)
-        self._check(self._L.rthc_info(self._h, _ptr(a), 9))
-        keys = ["n", "L", "loci_kept", "groups", "plane_rows", "tiles", "boruvka_rounds", "max_alleles", "row_scans"]
+        a = np.zeros(11, dtype=np.int64)
+        self._check(self._L.rthc_info(self._h, _ptr(a), 11))
+        keys = ["n", "L", "loci_kept", "groups", "plane_rows", "tiles", "boruvka_rounds", "max_alleles", "row_scans",
+                "chain_full_scans", "chain_cache_hits"]
         return dict(zip(keys, (int(x) for x in a)))
 
     def timings(self):

@@ -71,9 +71,20 @@ def select_samples(meta, filters):
         elif op in ("==", "!="):
             mx = mx[_CMP[op](mx[col], cond)]
         else:
-            num = pandas.to_numeric(mx[col], errors="coerce")
-            # the reference maps "<=" to ">=" (scripts/partitioning_HC.py:152-153); kept for parity
-            keep = {">": num > float(cond), ">=": num >= float(cond), "<": num < float(cond),
-                    "<=": num >= float(cond)}[op]
-            mx = mx[keep.fillna(False)]
+            # scripts/partitioning_HC.py:144-155: the column becomes numeric, the comparison is applied ("<=" is
+            # mapped to ">=" there, :152-153; an operator outside the grammar filters nothing), and the column is
+            # then rewritten as int strings -- so a later '==' / '!=' / list filter on it sees "5", not "5.0", and a
+            # value that is still NaN at that point raises pandas' IntCastingNaNError exactly as in the reference
+            mx = mx.copy()
+            mx[col] = pandas.to_numeric(mx[col], errors="coerce")
+            if op == ">":
+                mx = mx[mx[col] > float(cond)]
+            elif op == ">=":
+                mx = mx[mx[col] >= float(cond)]
+            elif op == "<":
+                mx = mx[mx[col] < float(cond)]
+            elif op == "<=":
+                mx = mx[mx[col] >= float(cond)]
+            mx = mx.copy()
+            mx[col] = mx[col].astype(int).astype(str)
     return mx[sample_column].tolist()

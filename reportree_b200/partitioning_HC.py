@@ -332,7 +332,7 @@ def square_to_condensed(square):
     a = np.ascontiguousarray(square, dtype=np.float64)
     if a.ndim != 2 or a.shape[0] != a.shape[1]:
         raise ValueError("The matrix argument must be square.")
-    if not np.allclose(a, a.T):
+    if not (a == a.T).all():                     # is_valid_dm(tol=0): exact symmetry, as scipy checks it
         raise ValueError("Distance matrix 'X' must be symmetric.")
     if not (np.diag(a) == 0).all():
         raise ValueError("Distance matrix 'X' diagonal must be zero.")
@@ -405,7 +405,7 @@ def profile_to_distances(args, say, log, ctx):
     if os.environ.get("REPORTREE_HC_SKIP_DIST_TSV", "0") != "1":
         write_dist_tsv(args.out + "_dist_hamming.tsv", names, ctx)
         PH.mark("write dist_hamming.tsv")
-    return names, total_size
+    return names_as_read_back(names), total_size
 
 
 def _loci_selection_fast(prof, rows, args, say):
@@ -536,7 +536,19 @@ def profile_to_distances_fast(args, say, log, ctx, prof):
     if os.environ.get("REPORTREE_HC_SKIP_DIST_TSV", "0") != "1":
         write_dist_tsv(out + "_dist_hamming.tsv", names, ctx)
         PH.mark("write dist_hamming.tsv")
-    return names, total_size
+    return names_as_read_back(names), total_size
+
+
+def names_as_read_back(names):
+    """The reference names the samples from the HEADER of `<out>_dist_hamming.tsv` as pandas reads it back
+    (`dist.columns` after read_table, :518-520, :184), not from the profile's id column: duplicated ids
+    come back mangled ("A", "A.1", ...), an empty id as "Unnamed: k".  Plain distinct ids are unchanged, so
+    only those cases take the round trip through pandas' own writer and header parser."""
+    if len(set(names)) == len(names) and "" not in names and "dists" not in names:
+        return names
+    import io
+    text = pandas.DataFrame(columns=["dists"] + list(names)).to_csv(sep="\t", index=False)
+    return [str(c) for c in pandas.read_table(io.StringIO(text), nrows=0).columns[1:]]
 
 
 def write_dist_tsv(path, names, ctx):

@@ -67,3 +67,16 @@ def config(name):
     if name == "C5":
         return dict(n=50000, L=7600, seed=SEEDS["C5"], missing=0.03, bad_sample_frac=0.05, bad_missing=0.10)
     raise KeyError(name)
+
+
+def workload(name):
+    """The matrix that reaches the distance kernel for a BASELINE.json config: C3 / C4 as generated;
+    C5 = configs[4] after the reference's filters (scripts/partitioning_HC.py:400-477): a --loci subset
+    of 3,000 of the 7,600 columns, then --loci-called 0.95 on the rows (pct_called >= 0.95)."""
+    X = allele_matrix(**config(name))
+    if name != "C5":
+        return X
+    rng = np.random.default_rng(1)
+    cols = np.sort(rng.choice(X.shape[1], 3000, replace=False))
+    Xs = X[:, cols]
+    return np.ascontiguousarray(Xs[(Xs != 0).sum(1) / Xs.shape[1] >= 0.95])

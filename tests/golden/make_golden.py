@@ -10,6 +10,8 @@ C2: examples/Listeria/input/Listeria_alleles.tsv, single-1-50     (BASELINE.json
 C2b: Listeria with --loci-called 0.95 --site-inclusion 0.99, complete-1-30,average-5
 C1c: tests/allele_matrix.tsv, ward at all thresholds + complete-3    (ward = scipy nn_chain, float heights)
 C2c: Listeria with --loci-called 0.95, ward-1-60 + --pct-HC-threshold ward-0.01
+C1d: tests/allele_matrix.tsv with two sample ids duplicated (derived input, written by this script):
+     the reference names samples from the re-read TSV header, so duplicates come back as "id.1"
 Case names on the command line regenerate only those cases.
 Also stores the Listeria golden distance pair shipped with the reference
 (examples/Listeria/output/Lm_flt_samples_matrix.tsv -> Lm_dist_hamming.tsv) as compact arrays.
@@ -40,6 +42,8 @@ CASES = {
     "C2c": (REF + "/examples/Listeria/input/Listeria_alleles.tsv",
             ["--HC-threshold", "ward-1-60", "--pct-HC-threshold", "ward-0.01", "--loci-called", "0.95"]),
 }
+DERIVED = os.path.join(HERE, "inputs", "allele_matrix_dupids.tsv.gz")
+CASES["C1d"] = (DERIVED, ["--HC-threshold", "single-1-10,complete-4"])
 KEEP = ["_partitions.tsv", "_clusterComposition.tsv", "_loci_report.tsv", "_loci_used.txt",
         "_parcentage2threshold.tsv"]
 
@@ -54,6 +58,13 @@ def main():
             continue
         tmp = tempfile.mkdtemp()
         tag = os.path.join(tmp, name)
+        if inp == DERIVED:                      # duplicated sample ids: sample3_2 -> sample3, sample9_2 -> sample9
+            text = open(REF + "/tests/allele_matrix.tsv").read().replace("sample3_2\t", "sample3\t").replace("sample9_2\t", "sample9\t")
+            with gzip.GzipFile(DERIVED, "wb", mtime=0) as fo:
+                fo.write(text.encode())
+            inp = os.path.join(tmp, "allele_matrix_dupids.tsv")
+            with open(inp, "w") as fo:
+                fo.write(text)
         cmd = [sys.executable, REF + "/scripts/partitioning_HC.py", "-a", inp, "-o", tag] + extra
         out = subprocess.run(cmd, env=env, capture_output=True, text=True)
         if out.returncode != 0:

@@ -135,6 +135,7 @@ GOLD = {
                                          "--loci-called", "0.95", "--site-inclusion", "0.99"]),
     "C1c": ("allele_matrix.tsv.gz", ["--HC-threshold", "ward,complete-3"]),
     "C2c": ("Listeria_alleles.tsv.gz", ["--HC-threshold", "ward-1-60", "--pct-HC-threshold", "ward-0.01", "--loci-called", "0.95"]),
+    "C1d": ("allele_matrix_dupids.tsv.gz", ["--HC-threshold", "single-1-10,complete-4"]),     # duplicated sample ids
 }
 
 

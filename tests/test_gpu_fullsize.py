@@ -126,3 +126,70 @@ def test_c5_complete_linkage_properties(hc, oracle):
         D = oracle.dist_square(Xs[sub])
         got = np.stack([ctx.square_rows(int(r), 1)[0][sub] for r in sub[:32]])
         assert np.array_equal(got.astype(np.int32), D[:32])
+
+
+# ------------------------------------------------------------------------------------------------
+# BASELINE.json configs[2..4] against the CPU oracle's own answer (tests/golden/large/*.json, written
+# by tests/golden/make_golden_large.py: oracle/cgmlst_dists.c + oracle/hclust.c on this container's
+# host cores).  Distances: CRC32 of every 1,024-row block of the condensed matrix.  Z: byte-identical
+# (CRC32 of the float64 array) for the scipy-order paths.  Labels: at every threshold 0..50 the
+# fcluster ids (CRC32), the cluster count and the membership-only relabelling (CRC32).
+# ------------------------------------------------------------------------------------------------
+import json
+import os
+
+LARGE = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "large")
+
+
+def _golden(name):
+    with open(os.path.join(LARGE, name + ".json")) as f:
+        return json.load(f)
+
+
+def _check_distances(ctx, g):
+    from reportree_b200 import checksums as C
+    assert g["rows_per_block"] == C.ROWS_PER_BLOCK
+    bounds = C.block_bounds(ctx.n)
+    assert len(bounds) == len(g["condensed_block_crc32"])
+    bad = [b for b, (r0, r1, p0, p1) in enumerate(bounds)
+           if C.crc(ctx.condensed_range(p0, p1 - p0)) != g["condensed_block_crc32"][b]]
+    assert not bad, "distance blocks (1,024 rows each) that differ from the oracle: %s" % bad[:10]
+
+
+def _check_method(ctx, g, method, exact_z):
+    from reportree_b200 import checksums as C
+    gm = g["methods"][method]
+    Z = ctx.linkage(method)
+    zf = C.z_fingerprint(Z)
+    assert zf["heights_crc32"] == gm["heights_crc32"], method
+    if exact_z:
+        assert zf["z_crc32"] == gm["z_crc32"], method
+    lab = ctx.fcluster(np.asarray(g["thresholds"], dtype=np.float64))
+    for k, t in enumerate(g["thresholds"]):
+        f = C.labels_fingerprint(lab[k])
+        assert f["clusters"] == gm["labels"][k]["clusters"], (method, t)
+        assert f["membership_crc32"] == gm["labels"][k]["membership_crc32"], (method, t)
+        if exact_z:
+            assert f["ids_crc32"] == gm["labels"][k]["ids_crc32"], (method, t)
+
+
+@pytest.mark.parametrize("name", ["C3", "C5", "C4"])
+def test_full_configs_equal_the_cpu_oracle(hc, name):
+    """configs[2] (single / average / complete), configs[4] (complete, + average), configs[3] (single):
+    every distance block, Z and the partitions at all thresholds 0..50 equal the oracle's."""
+    from reportree_b200 import checksums as C, synth
+    g = _golden(name)
+    X = synth.workload(name)
+    assert X.shape == (g["n"], g["L"]) and C.crc(X) == g["input_crc32"]
+    with hc.HCContext() as ctx:
+        ctx.set_profiles(X)
+        ctx.distance()
+        _check_distances(ctx, g)
+        for method in g["methods"]:
+            if method == "single":
+                ctx.set_single_algo(hc.SL_PRIM)                 # scipy order: Z and ids byte-identical
+                _check_method(ctx, g, "single", exact_z=True)
+                ctx.set_single_algo(hc.SL_BORUVKA)              # the benchmarked path: same heights + membership
+                _check_method(ctx, g, "single", exact_z=False)
+            else:
+                _check_method(ctx, g, method, exact_z=True)

@@ -52,6 +52,22 @@ def test_cut_threshold_order_and_float_thresholds(hc, oracle):
         assert np.array_equal(labels[k], fcluster(Z, t, criterion="distance"))
 
 
+def test_cut_with_more_thresholds_than_a_grid_dimension(hc, oracle):
+    """70,000 thresholds on a small tree (`--HC-threshold ward` cuts at every integer up to the root
+    height, which grows like sqrt(n/2)*d; -d_mx matrices can exceed 65,535 too): the batched cut must
+    chunk below the gridDim.y limit instead of failing the launch."""
+    rng = np.random.default_rng(4)
+    X = _rand_codes(rng, 64, 50, 3, 0.02)
+    with hc.HCContext() as ctx:
+        ctx.set_profiles(X)
+        ctx.distance()
+        Z = ctx.linkage("complete")
+        thr = np.linspace(0.0, float(Z[-1, 2]) + 1.0, 70000)
+        labels = ctx.fcluster(thr)
+    for k in list(range(0, 70000, 997)) + [59999, 60000, 60001, 65535, 65536, 69999]:
+        assert np.array_equal(labels[k], fcluster(Z, thr[k], criterion="distance")), k
+
+
 def test_forest_union_equals_single_gpu(hc, oracle):
     # multi-GPU algebra on one GPU: per-shard forests, union, final MST == full MST
     rng = np.random.default_rng(5)

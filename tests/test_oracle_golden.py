@@ -54,6 +54,19 @@ def test_oracle_linkage_and_fcluster_equal_scipy_on_tie_heavy_matrices(oracle):
                 assert np.array_equal(fcluster(Zs, t, criterion="distance"), oracle.fcluster(Zo, t))
 
 
+def test_oracle_uint16_input_equals_scipy(oracle):
+    """The uint16-condensed entry points (what lets the oracle run configs[3] / [4] in host memory)
+    give the same Z as live scipy on the float64 copy of the same tie-heavy matrices."""
+    rng = np.random.default_rng(77)
+    for _ in range(120):
+        n = int(rng.integers(2, 60))
+        y16 = rng.integers(0, int(rng.integers(2, 12)), size=n * (n - 1) // 2).astype(np.uint16)
+        if rng.random() < 0.2:
+            y16[rng.integers(0, y16.size, size=max(1, y16.size // 7))] = 65535      # the storage maximum
+        for method in ("single", "complete", "average", "weighted", "ward"):
+            assert np.array_equal(linkage(y16.astype(np.float64), method), oracle.linkage(y16, method)), (method, n)
+
+
 def test_oracle_reproduces_reference_partitions_listeria(oracle):
     """Z from the oracle on the golden distances -> the partitions.tsv the reference wrote."""
     from reportree_b200 import hostio
