@@ -69,8 +69,10 @@ def build(force=False, verbose=False):
             sys.stderr.write(out)
         if p.returncode:
             raise RuntimeError("nvcc failed on " + src)
-    subprocess.check_call([NVCC, "-shared", "-o", OUT] + objs + ["-gencode", "arch=compute_100a,code=sm_100a",
-                                                                    "-cudart", "static"])
+    # link next to the target and rename: a snapshot (gpurun) or a concurrent dlopen never sees a partial library
+    subprocess.check_call([NVCC, "-shared", "-o", OUT + ".tmp"] + objs + ["-gencode", "arch=compute_100a,code=sm_100a",
+                                                                             "-cudart", "static"])
+    os.replace(OUT + ".tmp", OUT)
     build_cgmlst_dists(True)
     return OUT
 

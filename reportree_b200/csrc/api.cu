@@ -111,7 +111,7 @@ extern "C" int rthc_mark_elapsed_ms(rthc_ctx *ctx, double *ms)
 
 void rthc_free_distance_state(rthc_ctx *ctx)
 {
-    rthc_dev_free(ctx, &ctx->d_codes); rthc_dev_free(ctx, &ctx->d_planes);
+    rthc_dev_free(ctx, &ctx->d_codes); rthc_dev_free(ctx, &ctx->d_codes32); rthc_dev_free(ctx, &ctx->d_planes);
     rthc_dev_free(ctx, &ctx->d_grp_off); rthc_dev_free(ctx, &ctx->d_grp_np);
     rthc_dev_free(ctx, &ctx->d_tiles); rthc_dev_free(ctx, &ctx->d_row_base);
     rthc_dev_free(ctx, &ctx->d_owned_rows);
@@ -236,7 +236,6 @@ extern "C" int rthc_set_single_algo(rthc_ctx *ctx, int algo)
 int rthc_setup_geometry(rthc_ctx *ctx, int64_t n)
 {
     ctx->n = n;
-    if (const char *e = getenv("RTHC_DIST_NJ")) ctx->dist_nj = atoi(e) == 1 ? 1 : 2;
     ctx->n_pad = (n + RTHC_TILE - 1) / RTHC_TILE * RTHC_TILE;
     const int64_t B = ctx->n_pad / RTHC_TILE;
     ctx->n_tiles_edge = B;
@@ -258,7 +257,7 @@ int rthc_setup_geometry(rthc_ctx *ctx, int64_t n)
     // tiles are (128-sample row block I, first 64-sample column block J); supertiles of
     // 16 row blocks x 32 column blocks keep the blocks of concurrently running CTAs in L2
     std::vector<int2> tiles;
-    const int64_t S = 16, nj = ctx->dist_nj, B64 = 2 * B;
+    const int64_t S = 16, nj = 2, B64 = 2 * B;     // nj: 64-sample column blocks per tile (128 x 128)
     for (size_t rc0 = 0; rc0 < owned_tile_rows.size(); rc0 += (size_t)S)
         for (int64_t c0 = 0; c0 < B64; c0 += 2 * S)
             for (size_t q = rc0; q < std::min(owned_tile_rows.size(), rc0 + (size_t)S); ++q) {

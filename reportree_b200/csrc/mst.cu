@@ -15,8 +15,6 @@
 
 #include "rthc_internal.cuh"
 
-#define SCAN_THREADS 256
-
 __global__ void rthc_iota_i32(int32_t *a, int64_t n)
 {
     int64_t v = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -26,103 +24,6 @@ __global__ void rthc_fill_u64(uint64_t *a, int64_t n, uint64_t val)
 {
     int64_t v = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (v < n) a[v] = val;
-}
-
-__device__ __forceinline__ void consider(uint32_t w, uint32_t i, uint32_t j, int32_t ci,
-                                         const int32_t *__restrict__ comp, uint64_t &mine)
-{
-    if (comp[j] != ci) {
-        const uint64_t key = rthc_pack_key(w, i, j);
-        if (key < mine) mine = key;
-    }
-}
-
-// ROW PASS.  One CTA per owned row i: stream D[i, i+1..n-1] (16-byte loads), lightest edge
-// leaving comp[i] through a column j > i; block reduction, one atomic per row.
-__global__ void __launch_bounds__(SCAN_THREADS)
-rthc_boruvka_scan(const uint16_t *__restrict__ cond, const int64_t *__restrict__ row_base,
-                  const int32_t *__restrict__ owned_rows, int64_t n, const int32_t *__restrict__ comp,
-                  uint64_t *best)
-{
-    const uint32_t i = (uint32_t)owned_rows[blockIdx.x];
-    const int64_t len = n - 1 - (int64_t)i;
-    if (len <= 0) return;
-    const int64_t base = row_base[i];
-    const int32_t ci = comp[i];
-    const int tid = threadIdx.x;
-    uint64_t mine = RTHC_KEY_INF;
-
-    int64_t head = (8 - (base & 7)) & 7;
-    if (head > len) head = len;
-    if (tid < head) consider(cond[base + tid], i, i + 1 + (uint32_t)tid, ci, comp, mine);
-    const int64_t nvec = (len - head) >> 3;
-    const uint4 *vec = reinterpret_cast<const uint4 *>(cond + base + head);
-    for (int64_t v = tid; v < nvec; v += SCAN_THREADS) {
-        const uint4 q = vec[v];
-        const uint32_t j = i + 1 + (uint32_t)head + (uint32_t)(v << 3);
-        consider(q.x & 0xFFFFu, i, j + 0, ci, comp, mine);
-        consider(q.x >> 16, i, j + 1, ci, comp, mine);
-        consider(q.y & 0xFFFFu, i, j + 2, ci, comp, mine);
-        consider(q.y >> 16, i, j + 3, ci, comp, mine);
-        consider(q.z & 0xFFFFu, i, j + 4, ci, comp, mine);
-        consider(q.z >> 16, i, j + 5, ci, comp, mine);
-        consider(q.w & 0xFFFFu, i, j + 6, ci, comp, mine);
-        consider(q.w >> 16, i, j + 7, ci, comp, mine);
-    }
-    const int64_t done = head + (nvec << 3);
-    if (done + tid < len)
-        consider(cond[base + done + tid], i, i + 1 + (uint32_t)(done + tid), ci, comp, mine);
-
-    // block min
-#pragma unroll
-    for (int s = 16; s > 0; s >>= 1) {
-        uint64_t o = __shfl_xor_sync(0xffffffffu, mine, s);
-        if (o < mine) mine = o;
-    }
-    __shared__ uint64_t wmin[SCAN_THREADS / 32];
-    if ((tid & 31) == 0) wmin[tid >> 5] = mine;
-    __syncthreads();
-    if (tid == 0) {
-        for (int w = 1; w < SCAN_THREADS / 32; ++w)
-            if (wmin[w] < mine) mine = wmin[w];
-        if (mine != RTHC_KEY_INF && mine < best[ci])
-            atomicMin((unsigned long long *)&best[ci], (unsigned long long)mine);
-    }
-}
-
-// COLUMN PASS.  Edge (i, j), i < j, is also a candidate for comp[j].  A CTA owns 256
-// consecutive columns and a chunk of COL_ROWS rows; thread t walks down column j: for a fixed
-// row the 256 threads read 512 contiguous bytes of the condensed row, comp[i] and row_base[i]
-// are warp-uniform.  One filtered atomic per thread per chunk.
-#define COL_ROWS 512
-__global__ void __launch_bounds__(256)
-rthc_boruvka_scan_cols(const uint16_t *__restrict__ cond, const int64_t *__restrict__ row_base, int64_t n,
-                       const int32_t *__restrict__ comp, uint64_t *best)
-{
-    const int64_t j = (int64_t)blockIdx.x * 256 + threadIdx.x;
-    const int64_t r0 = (int64_t)blockIdx.y * COL_ROWS;
-    const int64_t jmax = (int64_t)blockIdx.x * 256 + 255;
-    if (r0 >= jmax || r0 >= n) return;
-    int64_t r1 = r0 + COL_ROWS;
-    if (r1 > jmax) r1 = jmax;            // rows i < j only
-    if (r1 > n) r1 = n;
-    const bool live = j < n;
-    const int32_t cj = live ? comp[j] : -1;
-    uint64_t mine = RTHC_KEY_INF;
-#pragma unroll 4
-    for (int64_t i = r0; i < r1; ++i) {
-        const int64_t base = row_base[i];
-        if (base < 0) continue;           // row not owned by this shard (uniform)
-        if (live && i < j) {
-            const uint32_t w = cond[base + (j - i - 1)];
-            if (comp[i] != cj) {
-                const uint64_t key = rthc_pack_key(w, (uint32_t)i, (uint32_t)j);
-                if (key < mine) mine = key;
-            }
-        }
-    }
-    if (mine != RTHC_KEY_INF && mine < best[cj])
-        atomicMin((unsigned long long *)&best[cj], (unsigned long long)mine);
 }
 
 // TILE PASS (row and column candidates in ONE sweep over the matrix).  A CTA owns TS_ROWS
@@ -562,7 +463,6 @@ int rthc_boruvka_owned(rthc_ctx *ctx, bool sorted, uint64_t **d_keys, int64_t *m
 {
     const int64_t n = ctx->n;
     const int64_t n_owned = (int64_t)ctx->h_owned_rows.size();
-    static const bool two_pass = getenv("RTHC_BORUVKA_TWO_PASS") != nullptr;     // A/B switch (older kernels)
     std::vector<int32_t> bands;
     for (int32_t i : ctx->h_owned_rows)
         if (bands.empty() || bands.back() != i / TS_ROWS) bands.push_back(i / TS_ROWS);      // rows are ascending
@@ -572,16 +472,9 @@ int rthc_boruvka_owned(rthc_ctx *ctx, bool sorted, uint64_t **d_keys, int64_t *m
     if (!bands.empty())
         RTHC_CUDA(ctx, cudaMemcpyAsync(d_bands, bands.data(), sizeof(int32_t) * bands.size(), cudaMemcpyHostToDevice, ctx->stream));
     auto scan = [&](int32_t *d_comp, uint64_t *d_best) -> int {
-        if (n_owned > 0 && !two_pass) {
+        if (n_owned > 0) {
             dim3 grd((unsigned)((n + TS_COLS - 1) / TS_COLS), (unsigned)bands.size());
             rthc_boruvka_scan_tile<<<grd, 256, 0, ctx->stream>>>(ctx->d_cond, ctx->d_row_base, n, d_comp, d_best, d_bands);
-            RTHC_LAUNCH_CHECK(ctx);
-        } else if (n_owned > 0) {
-            rthc_boruvka_scan<<<(unsigned)n_owned, SCAN_THREADS, 0, ctx->stream>>>(
-                ctx->d_cond, ctx->d_row_base, ctx->d_owned_rows, n, d_comp, d_best);
-            RTHC_LAUNCH_CHECK(ctx);
-            dim3 grd((unsigned)((n + 255) / 256), (unsigned)((n + COL_ROWS - 1) / COL_ROWS));
-            rthc_boruvka_scan_cols<<<grd, 256, 0, ctx->stream>>>(ctx->d_cond, ctx->d_row_base, n, d_comp, d_best);
             RTHC_LAUNCH_CHECK(ctx);
         }
         return 0;

@@ -253,8 +253,7 @@ rthc_prim_cluster_kernel(const uint16_t *__restrict__ mat, int64_t n, int32_t *e
 // thread and step instead of about 150, which matters because 32 warps share the four schedulers of an SM.
 template <int NCH>
 __global__ void __launch_bounds__(PC_THREADS, 1)
-rthc_prim_cluster_vec_kernel(const uint16_t *__restrict__ sq, int64_t n, int64_t pitch, int32_t *ex, int32_t *ey, double *ew,
-                             int prefetch)
+rthc_prim_cluster_vec_kernel(const uint16_t *__restrict__ sq, int64_t n, int64_t pitch, int32_t *ex, int32_t *ey, double *ew)
 {
     cg::cluster_group cluster = cg::this_cluster();
     const unsigned C = cluster.num_blocks(), rank = cluster.block_rank();
@@ -323,11 +322,6 @@ rthc_prim_cluster_vec_kernel(const uint16_t *__restrict__ sq, int64_t n, int64_t
             i = __reduce_min_sync(0xffffffffu, bw == m ? bi : 0xFFFFFFFFu);
             if ((unsigned)lane < C)
                 *cluster.map_shared_rank(&slot[par][rank], lane) = ((unsigned long long)m << 32) | i;
-            // the next vertex is one of the <= 16 CTA winners: each CTA asks L2 for its own winner's row (one bulk
-            // prefetch) so that the DRAM access overlaps the cluster exchange instead of following it
-            if (prefetch && lane == 0 && i != 0xFFFFFFFFu)
-                asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(sq + (int64_t)i * pitch),
-                             "r"((uint32_t)(pitch * 2)) : "memory");
         }
         cluster.sync();
         const unsigned long long sv = (unsigned)lane < C ? slot[par][lane] : ~0ull;
@@ -357,8 +351,7 @@ static cudaError_t launch_prim_cluster_vec(int C, cudaStream_t stream, const uin
     int clusters = 0;
     if ((e = cudaOccupancyMaxActiveClusters(&clusters, kern, &cfg)) != cudaSuccess) return e;
     if (clusters < 1) return cudaErrorInvalidConfiguration;
-    static const int prefetch = getenv("RTHC_PRIM_PREFETCH") ? atoi(getenv("RTHC_PRIM_PREFETCH")) : 0;   // A/B: slower
-    return cudaLaunchKernelEx(&cfg, kern, sq, n, pitch, ex, ey, ew, prefetch);
+    return cudaLaunchKernelEx(&cfg, kern, sq, n, pitch, ex, ey, ew);
 }
 
 template <int MAXQ, bool SQUARE>

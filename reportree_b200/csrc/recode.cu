@@ -43,13 +43,14 @@ __global__ void rthc_transpose_i32(const int32_t *__restrict__ in, int32_t *__re
 // ---- 2. per-locus dense rank through a shared-memory bitmap ---------------------------
 // One CTA per locus.  Allele ids < 2^20 are marked in a 128 KB bitmap; the rank of an id
 // is 1 + (number of set bits below it).  status[0] |= 1 if an id >= 2^20 was seen in the
-// fast path, |= 2 if a locus has more than 65,535 distinct called alleles.
-template <bool GLOBAL_BITMAP>
+// fast path, |= 2 if a locus has more than 65,535 distinct called alleles and the codes are
+// uint16 (CT): the driver then repeats the ranking with uint32 codes (the reference has no such
+// limit, scripts/partitioning_HC.py:293-298: any integer is an allele).
+template <typename CT>
 __global__ void __launch_bounds__(RANK_THREADS, 1)
-rthc_rank_columns(const int32_t *__restrict__ colmajor, uint16_t *__restrict__ codes,
+rthc_rank_columns(const int32_t *__restrict__ colmajor, CT *__restrict__ codes,
                   int32_t *__restrict__ n_alleles, int32_t *__restrict__ status, int64_t n,
-                  int64_t n_pad, const int32_t *__restrict__ col_list, uint32_t *g_bitmap,
-                  uint32_t g_words)
+                  int64_t n_pad)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     uint32_t *bm = reinterpret_cast<uint32_t *>(smem_raw);
@@ -57,9 +58,9 @@ rthc_rank_columns(const int32_t *__restrict__ colmajor, uint16_t *__restrict__ c
     __shared__ uint32_t warp_tot[32];
     __shared__ uint32_t warp_off[33];
 
-    const int col = col_list ? col_list[blockIdx.x] : (int)blockIdx.x;
+    const int col = (int)blockIdx.x;
     const int32_t *src = colmajor + (int64_t)col * n_pad;
-    uint16_t *dst = codes + (int64_t)col * n_pad;
+    CT *dst = codes + (int64_t)col * n_pad;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 
     __shared__ int32_t s_vmax;
@@ -126,7 +127,7 @@ rthc_rank_columns(const int32_t *__restrict__ colmajor, uint16_t *__restrict__ c
     const uint32_t total = warp_off[32];
     if (tid == 0) {
         n_alleles[col] = (int32_t)total;
-        if (total > 65535u) atomicOr(status, 2);
+        if (sizeof(CT) == 2 && total > 65535u) atomicOr(status, 2);
     }
     for (int64_t r0 = tid; r0 < n_pad; r0 += 4 * RANK_THREADS) {
         int32_t v[4];
@@ -139,11 +140,11 @@ rthc_rank_columns(const int32_t *__restrict__ colmajor, uint16_t *__restrict__ c
         for (int u = 0; u < 4; ++u) {
             const int64_t r = r0 + (int64_t)u * RANK_THREADS;
             if (r >= n_pad) break;
-            uint16_t code = 0;
+            CT code = 0;
             if (v[u] > 0 && (uint32_t)v[u] < BITMAP_BITS) {
                 uint32_t w = (uint32_t)v[u] >> 5;
                 uint32_t below = __popc(bm[w] & ((1u << (v[u] & 31)) - 1u));
-                code = (uint16_t)(1u + warp_off[w >> 10] + pre[w] + below);
+                code = (CT)(1u + warp_off[w >> 10] + pre[w] + below);
             }
             dst[r] = code;
         }
@@ -154,8 +155,9 @@ rthc_rank_columns(const int32_t *__restrict__ colmajor, uint16_t *__restrict__ c
 // One CTA per such locus, run one locus at a time against a 2^31-bit bitmap in HBM
 // (256 MB scratch).  Ranks are assigned by scanning only the 2,048-bit windows that a
 // level-1 shared bitmap marks as occupied.
+template <typename CT>
 __global__ void __launch_bounds__(RANK_THREADS, 1)
-rthc_rank_column_wide(const int32_t *__restrict__ colmajor, uint16_t *__restrict__ codes,
+rthc_rank_column_wide(const int32_t *__restrict__ colmajor, CT *__restrict__ codes,
                       int32_t *__restrict__ n_alleles, int32_t *__restrict__ status, int64_t n,
                       int64_t n_pad, int col, uint32_t *__restrict__ gbm,
                       uint32_t *__restrict__ win_prefix)
@@ -165,7 +167,7 @@ rthc_rank_column_wide(const int32_t *__restrict__ colmajor, uint16_t *__restrict
     uint32_t *l1 = reinterpret_cast<uint32_t *>(smem_raw);
     __shared__ uint32_t s_total;
     const int32_t *src = colmajor + (int64_t)col * n_pad;
-    uint16_t *dst = codes + (int64_t)col * n_pad;
+    CT *dst = codes + (int64_t)col * n_pad;
     const int tid = threadIdx.x;
 
     for (int w = tid; w < (int)BITMAP_WORDS; w += RANK_THREADS) l1[w] = 0;
@@ -205,10 +207,10 @@ rthc_rank_column_wide(const int32_t *__restrict__ colmajor, uint16_t *__restrict
     const uint32_t total = s_total;
     if (tid == 0) {
         n_alleles[col] = (int32_t)total;
-        if (total > 65535u) atomicOr(status, 2);
+        if (sizeof(CT) == 2 && total > 65535u) atomicOr(status, 2);
     }
     for (int64_t r = tid; r < n_pad; r += RANK_THREADS) {
-        uint16_t code = 0;
+        CT code = 0;
         if (r < n) {
             int32_t v = src[r];
             if (v > 0) {
@@ -216,7 +218,7 @@ rthc_rank_column_wide(const int32_t *__restrict__ colmajor, uint16_t *__restrict
                 uint32_t below = win_prefix[b];
                 for (uint32_t q = b * 64u; q < w; ++q) below += __popc(gbm[q]);
                 below += __popc(gbm[w] & ((1u << (v & 31)) - 1u));
-                code = (uint16_t)(1u + below);
+                code = (CT)(1u + below);
             }
         }
         dst[r] = code;
@@ -231,8 +233,8 @@ rthc_rank_column_wide(const int32_t *__restrict__ colmajor, uint16_t *__restrict
 
 // ---- 3. bit-slice 32 loci into plane words --------------------------------------------
 // grid.y = group; the plane count of a group is uniform per CTA, so the bit loop is compiled per width
-template <int BITS>
-__device__ __forceinline__ void pack_group(const uint16_t *__restrict__ codes, const int32_t *__restrict__ perm, int g,
+template <int BITS, typename CT>
+__device__ __forceinline__ void pack_group(const CT *__restrict__ codes, const int32_t *__restrict__ perm, int g,
                                            int64_t off, uint32_t *__restrict__ planes, int64_t n_pad, int plane_rows, int64_t s)
 {
     uint32_t pl[BITS];
@@ -255,7 +257,8 @@ __device__ __forceinline__ void pack_group(const uint16_t *__restrict__ codes, c
     planes[(blk + off + BITS) * RTHC_BLK + lane_s] = valid;
 }
 
-__global__ void rthc_pack_planes(const uint16_t *__restrict__ codes, const int32_t *__restrict__ perm,
+template <typename CT>
+__global__ void rthc_pack_planes(const CT *__restrict__ codes, const int32_t *__restrict__ perm,
                                  const int32_t *__restrict__ grp_off, const int32_t *__restrict__ grp_np,
                                  uint32_t *__restrict__ planes, int64_t n_pad, int plane_rows)
 {
@@ -264,17 +267,69 @@ __global__ void rthc_pack_planes(const uint16_t *__restrict__ codes, const int32
     if (s >= n_pad) return;
     const int bits = grp_np[g] - 1;
     const int64_t off = grp_off[g];
-#define RTHC_PACK_CASE(B) case B: pack_group<B>(codes, perm, g, off, planes, n_pad, plane_rows, s); break;
+#define RTHC_PACK_CASE(B) case B: pack_group<B, CT>(codes, perm, g, off, planes, n_pad, plane_rows, s); break;
     switch (bits) {
         RTHC_PACK_CASE(3) RTHC_PACK_CASE(4) RTHC_PACK_CASE(5) RTHC_PACK_CASE(6) RTHC_PACK_CASE(7) RTHC_PACK_CASE(8)
         RTHC_PACK_CASE(9) RTHC_PACK_CASE(10) RTHC_PACK_CASE(11) RTHC_PACK_CASE(12) RTHC_PACK_CASE(13)
-        RTHC_PACK_CASE(14) RTHC_PACK_CASE(15)
-    default: pack_group<16>(codes, perm, g, off, planes, n_pad, plane_rows, s); break;
+        RTHC_PACK_CASE(14) RTHC_PACK_CASE(15) RTHC_PACK_CASE(16)
+    default:
+        if constexpr (sizeof(CT) == 4) {             // 17..24 bits: n < 2^24 samples bounds the alleles of a locus
+            switch (bits) {
+                RTHC_PACK_CASE(17) RTHC_PACK_CASE(18) RTHC_PACK_CASE(19) RTHC_PACK_CASE(20) RTHC_PACK_CASE(21)
+                RTHC_PACK_CASE(22) RTHC_PACK_CASE(23)
+            default: pack_group<24, CT>(codes, perm, g, off, planes, n_pad, plane_rows, s); break;
+            }
+        }
+        break;
     }
 #undef RTHC_PACK_CASE
 }
 
 // ---- host driver -----------------------------------------------------------------------
+// dense-ranks every locus column into `codes` (uint16 or uint32); fills nall[] and status
+template <typename CT>
+static int rank_all(rthc_ctx *ctx, const int32_t *d_colmajor, CT *d_codes, int32_t *d_nall, int32_t *d_status,
+                    std::vector<int32_t> &nall, int32_t &status)
+{
+    const int64_t n = ctx->n, L = ctx->L, n_pad = ctx->n_pad;
+    int rc;
+    RTHC_CUDA(ctx, cudaMemsetAsync(d_status, 0, sizeof(int32_t), ctx->stream));
+    const size_t rank_smem = BITMAP_WORDS * 4 + BITMAP_WORDS * 2;
+    RTHC_CUDA(ctx, cudaFuncSetAttribute(rthc_rank_columns<CT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rank_smem));
+    rthc_rank_columns<CT><<<(unsigned)L, RANK_THREADS, rank_smem, ctx->stream>>>(d_colmajor, d_codes, d_nall, d_status, n, n_pad);
+    RTHC_LAUNCH_CHECK(ctx);
+    RTHC_CUDA(ctx, cudaMemcpyAsync(&status, d_status, sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->stream));
+    RTHC_CUDA(ctx, cudaMemcpyAsync(nall.data(), d_nall, sizeof(int32_t) * (size_t)L, cudaMemcpyDeviceToHost, ctx->stream));
+    RTHC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    if (!(status & 1)) return 0;
+    // some loci hold allele ids >= 2^20 (the rare path): find them and redo those through the HBM bitmap
+    std::vector<int32_t> colmax((size_t)L, 0), tmp((size_t)n_pad);
+    for (int64_t l = 0; l < L; ++l) {
+        RTHC_CUDA(ctx, cudaMemcpy(tmp.data(), d_colmajor + l * n_pad, sizeof(int32_t) * (size_t)n, cudaMemcpyDeviceToHost));
+        int32_t mx = 0;
+        for (int64_t r = 0; r < n; ++r) mx = std::max(mx, tmp[(size_t)r]);
+        colmax[(size_t)l] = mx;
+    }
+    uint32_t *d_gbm = nullptr, *d_winpre = nullptr;
+    if ((rc = rthc_dev_alloc(ctx, &d_gbm, (size_t)1 << 26))) return rc;
+    if ((rc = rthc_dev_alloc(ctx, &d_winpre, (size_t)1 << 20))) return rc;
+    RTHC_CUDA(ctx, cudaMemsetAsync(d_gbm, 0, sizeof(uint32_t) << 26, ctx->stream));
+    RTHC_CUDA(ctx, cudaFuncSetAttribute(rthc_rank_column_wide<CT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                        (int)(BITMAP_WORDS * 4)));
+    for (int64_t l = 0; l < L; ++l) {
+        if ((uint32_t)colmax[(size_t)l] < BITMAP_BITS) continue;
+        rthc_rank_column_wide<CT><<<1, RANK_THREADS, BITMAP_WORDS * 4, ctx->stream>>>(d_colmajor, d_codes, d_nall, d_status, n,
+                                                                                      n_pad, (int)l, d_gbm, d_winpre);
+        RTHC_LAUNCH_CHECK(ctx);
+    }
+    RTHC_CUDA(ctx, cudaMemcpyAsync(&status, d_status, sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->stream));
+    RTHC_CUDA(ctx, cudaMemcpyAsync(nall.data(), d_nall, sizeof(int32_t) * (size_t)L, cudaMemcpyDeviceToHost, ctx->stream));
+    RTHC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    rthc_dev_free(ctx, &d_gbm);
+    rthc_dev_free(ctx, &d_winpre);
+    return 0;
+}
+
 static inline int bit_width(int a)   // codes 1..a need this many bits
 {
     int b = 0;
@@ -291,71 +346,22 @@ int rthc_recode_and_pack(rthc_ctx *ctx, const int32_t *d_rowmajor)
     if ((rc = rthc_dev_alloc(ctx, &d_nall, (size_t)L))) return rc;
     if ((rc = rthc_dev_alloc(ctx, &d_status, 1))) return rc;
     if ((rc = rthc_dev_alloc(ctx, &ctx->d_codes, (size_t)(L * n_pad)))) return rc;
-    RTHC_CUDA(ctx, cudaMemsetAsync(d_status, 0, sizeof(int32_t), ctx->stream));
-
     {
         dim3 blk(32, 8), grd((unsigned)((L + 31) / 32), (unsigned)((n_pad + 31) / 32));
         rthc_transpose_i32<<<grd, blk, 0, ctx->stream>>>(d_rowmajor, d_colmajor, n, L, n_pad);
         RTHC_LAUNCH_CHECK(ctx);
     }
-    const size_t rank_smem = BITMAP_WORDS * 4 + BITMAP_WORDS * 2;
-    RTHC_CUDA(ctx, cudaFuncSetAttribute(rthc_rank_columns<false>,
-                                        cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rank_smem));
-    rthc_rank_columns<false><<<(unsigned)L, RANK_THREADS, rank_smem, ctx->stream>>>(
-        d_colmajor, ctx->d_codes, d_nall, d_status, n, n_pad, nullptr, nullptr, 0);
-    RTHC_LAUNCH_CHECK(ctx);
-
     std::vector<int32_t> nall((size_t)L);
     int32_t status = 0;
-    RTHC_CUDA(ctx, cudaMemcpyAsync(&status, d_status, sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->stream));
-    RTHC_CUDA(ctx, cudaMemcpyAsync(nall.data(), d_nall, sizeof(int32_t) * (size_t)L,
-                                   cudaMemcpyDeviceToHost, ctx->stream));
-    RTHC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-
-    if (status & 1) {
-        // some loci hold allele ids >= 2^20: find them and redo those through the HBM bitmap
-        std::vector<int32_t> colmax((size_t)L, 0);
-        {
-            // column maxima on the host side of a tiny reduction: reuse n_alleles buffer is not
-            // possible, so do a strided device reduction per column with thrust-free code
-            std::vector<int32_t> tmp((size_t)n_pad);
-            for (int64_t l = 0; l < L; ++l) {
-                // only columns whose fast-path count may be wrong need a check; checking all
-                // is L small D2H copies -- this whole branch is the rare path
-                RTHC_CUDA(ctx, cudaMemcpy(tmp.data(), d_colmajor + l * n_pad, sizeof(int32_t) * (size_t)n,
-                                          cudaMemcpyDeviceToHost));
-                int32_t mx = 0;
-                for (int64_t r = 0; r < n; ++r) mx = std::max(mx, tmp[(size_t)r]);
-                colmax[(size_t)l] = mx;
-            }
-        }
-        uint32_t *d_gbm = nullptr, *d_winpre = nullptr;
-        if ((rc = rthc_dev_alloc(ctx, &d_gbm, (size_t)1 << 26))) return rc;
-        if ((rc = rthc_dev_alloc(ctx, &d_winpre, (size_t)1 << 20))) return rc;
-        RTHC_CUDA(ctx, cudaMemsetAsync(d_gbm, 0, sizeof(uint32_t) << 26, ctx->stream));
-        RTHC_CUDA(ctx, cudaFuncSetAttribute(rthc_rank_column_wide,
-                                            cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                            (int)(BITMAP_WORDS * 4)));
-        for (int64_t l = 0; l < L; ++l) {
-            if ((uint32_t)colmax[(size_t)l] < BITMAP_BITS) continue;
-            rthc_rank_column_wide<<<1, RANK_THREADS, BITMAP_WORDS * 4, ctx->stream>>>(
-                d_colmajor, ctx->d_codes, d_nall, d_status, n, n_pad, (int)l, d_gbm, d_winpre);
-            RTHC_LAUNCH_CHECK(ctx);
-        }
-        RTHC_CUDA(ctx, cudaMemcpyAsync(&status, d_status, sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->stream));
-        RTHC_CUDA(ctx, cudaMemcpyAsync(nall.data(), d_nall, sizeof(int32_t) * (size_t)L,
-                                       cudaMemcpyDeviceToHost, ctx->stream));
-        RTHC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-        rthc_dev_free(ctx, &d_gbm);
-        rthc_dev_free(ctx, &d_winpre);
+    if ((rc = rank_all<uint16_t>(ctx, d_colmajor, ctx->d_codes, d_nall, d_status, nall, status))) return rc;
+    if (status & 2) {
+        // a locus with more than 65,535 distinct called alleles (needs n > 65,535): the codes of this matrix are
+        // kept as uint32 instead and the wide loci get 17..24 bit planes (generic group body of the distance kernel)
+        rthc_dev_free(ctx, &ctx->d_codes);
+        if ((rc = rthc_dev_alloc(ctx, &ctx->d_codes32, (size_t)(L * n_pad)))) return rc;
+        if ((rc = rank_all<uint32_t>(ctx, d_colmajor, ctx->d_codes32, d_nall, d_status, nall, status))) return rc;
     }
     rthc_dev_free(ctx, &d_colmajor);
-    if (status & 2) {
-        rthc_dev_free(ctx, &d_nall); rthc_dev_free(ctx, &d_status);
-        return rthc_fail(ctx, RTHC_E_RANGE,
-                         "a locus has more than 65,535 distinct called alleles; the uint16 re-coder "
-                         "cannot represent it");
-    }
 
     // order loci by bit width (widest first), drop loci that cannot mismatch
     std::vector<int32_t> kept;
@@ -408,8 +414,12 @@ int rthc_recode_and_pack(rthc_ctx *ctx, const int32_t *d_rowmajor)
         RTHC_CUDA(ctx, cudaMemcpyAsync(ctx->d_grp_np, gnp.data(), (size_t)G * sizeof(int32_t),
                                        cudaMemcpyHostToDevice, ctx->stream));
         dim3 grd((unsigned)((n_pad + 255) / 256), (unsigned)G);
-        rthc_pack_planes<<<grd, 256, 0, ctx->stream>>>(ctx->d_codes, d_perm, ctx->d_grp_off,
-                                                       ctx->d_grp_np, ctx->d_planes, n_pad, rows);
+        if (ctx->d_codes32)
+            rthc_pack_planes<uint32_t><<<grd, 256, 0, ctx->stream>>>(ctx->d_codes32, d_perm, ctx->d_grp_off, ctx->d_grp_np,
+                                                                     ctx->d_planes, n_pad, rows);
+        else
+            rthc_pack_planes<uint16_t><<<grd, 256, 0, ctx->stream>>>(ctx->d_codes, d_perm, ctx->d_grp_off, ctx->d_grp_np,
+                                                                     ctx->d_planes, n_pad, rows);
         RTHC_LAUNCH_CHECK(ctx);
     }
     RTHC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));

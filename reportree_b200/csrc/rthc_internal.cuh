@@ -33,7 +33,6 @@ struct rthc_ctx {
     // shard
     int rank = 0, world = 1;
     bool full_storage = false;     // sharded tiles, but d_cond is the FULL condensed vector (single-process multi-device)
-    int dist_nj = 2;               // 64-sample column blocks per distance tile (1: 128x64, 2: 128x128)
 
     // problem
     int64_t n = 0, L = 0, n_pad = 0;
@@ -46,6 +45,7 @@ struct rthc_ctx {
 
     // device buffers (distance half)
     uint16_t *d_codes = nullptr;   // [L][n_pad] dense-ranked codes, column-major per locus
+    uint32_t *d_codes32 = nullptr; // same, used INSTEAD of d_codes when a locus has more than 65,535 called alleles
     uint32_t *d_planes = nullptr;  // [plane_rows][n_pad]
     int32_t *d_grp_off = nullptr;  // [G]
     int32_t *d_grp_np = nullptr;   // [G]

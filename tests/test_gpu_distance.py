@@ -77,8 +77,7 @@ def test_large_allele_ids_slow_path(hc, oracle):
 
 
 def test_sixteen_bit_loci_and_the_uint16_limit(hc, oracle):
-    # a locus with > 32,767 distinct called alleles needs all 16 bit planes (the widest plane packer);
-    # one more than 65,535 cannot be coded and must fail loudly, not wrap
+    # a locus with > 32,767 distinct called alleles needs all 16 bit planes (the widest uint16 plane packer)
     rng = np.random.default_rng(19)
     n = 33500
     X = np.zeros((n, 3), dtype=np.int32)
@@ -96,10 +95,37 @@ def test_sixteen_bit_loci_and_the_uint16_limit(hc, oracle):
     assert np.array_equal(rows[:, n - 2000:].astype(np.int32), ref)
     head = (X[n - 700:, None, :] != X[None, :50, :]) & (X[n - 700:, None, :] != 0) & (X[None, :50, :] != 0)
     assert np.array_equal(rows[:, :50].astype(np.int32), head.sum(axis=2))
-    Y = (np.arange(65537, dtype=np.int32) + 1).reshape(-1, 1).repeat(2, axis=1)
+
+
+def test_more_than_65535_alleles_in_a_locus_take_the_uint32_codes(hc, oracle):
+    """The reference has no limit on the alleles of a locus (scripts/partitioning_HC.py:293-298: any integer
+    is an allele).  Past 65,535 distinct called alleles the re-coder switches the matrix to uint32 codes and
+    the locus gets 17+ bit planes (generic group body of the distance kernel): n = 70,000 with one locus where
+    every sample has its own allele, one with ~ 50,000 alleles incl. ids >= 2^20, and two ordinary loci."""
+    rng = np.random.default_rng(23)
+    n = 70000
+    X = np.zeros((n, 4), dtype=np.int32)
+    X[:, 0] = rng.permutation(n) + 1                                   # 70,000 alleles: 17 bits
+    X[:, 1] = rng.integers(1, 90000, n) * 37 + (1 << 20)               # ~ 48,000 alleles, all ids >= 2^20 (wide-id path)
+    X[:, 2] = rng.integers(0, 4, n)
+    X[:, 3] = rng.integers(0, 300, n)
+    X[rng.random(n) < 0.01, 0] = 0
     with hc.HCContext() as ctx:
-        with pytest.raises(hc.HCBackendError, match="65,535"):
-            ctx.set_profiles(np.ascontiguousarray(Y))
+        ctx.set_profiles(X)
+        info = ctx.info()
+        assert info["max_alleles"] > 65535 and info["plane_rows"] == 18           # one group: 17 bit planes + valid
+        ctx.distance()
+        rows = ctx.square_rows(n - 600, 600)
+        pi = np.repeat(np.arange(n - 40, n, dtype=np.int32), 500)
+        pj = np.tile(np.arange(0, 500, dtype=np.int32), 40)
+        direct = ctx.direct_pairs(pi, pj)                              # the scalar check kernel reads the uint32 codes too
+        Z = ctx.linkage("single")
+    ref = oracle.dist_square(np.ascontiguousarray(X[n - 1500:]))[-600:, :]
+    assert np.array_equal(rows[:, n - 1500:].astype(np.int32), ref)
+    head = (X[n - 600:, None, :] != X[None, :64, :]) & (X[n - 600:, None, :] != 0) & (X[None, :64, :] != 0)
+    assert np.array_equal(rows[:, :64].astype(np.int32), head.sum(axis=2))
+    assert np.array_equal(direct.reshape(40, 500), rows[-40:, :500].astype(np.int32))
+    assert Z.shape == (n - 1, 4) and Z[-1, 3] == n
 
 
 def test_wide_snp_matrix_and_the_informative_loci_limit(hc, oracle):
