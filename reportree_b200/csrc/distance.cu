@@ -20,7 +20,7 @@
 
 // Independent scalar kernel on the re-coded alleles (uint16, or uint32 when a locus has more than 65,535
 // alleles): one warp per requested pair.  Not on the product path -- the parity tests use it as a second
-// opinion on full-size matrices where the CPU oracle only covers a sample.
+// opinion on full-size matrices where the CPU reference only covers a sample.
 template <typename CT>
 __global__ void rthc_direct_pairs_kernel(const CT *__restrict__ codes, int64_t L, int64_t n_pad,
                                          const int32_t *__restrict__ pi, const int32_t *__restrict__ pj,
