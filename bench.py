@@ -193,7 +193,7 @@ def run_ours(args):
     thr = np.arange(WORKLOAD["thresholds"], dtype=np.float64)
     labels_host = torch.empty((thr.size, n), dtype=torch.int32, pin_memory=True).numpy()   # result buffer, reused every step
     ctx = hc.HCContext(device=local, rank=rank, world=world)
-    state = {"dist_ms": [], "link_ms": [], "cut_ms": [], "recode_ms": [], "h2d_ms": [], "d2h_bytes": 0}
+    state = {"dist_ms": [], "link_ms": [], "cut_ms": [], "recode_ms": [], "h2d_ms": [], "d2h_bytes": 0, "Z": None}
     exch = sharded.ForestExchange(n, dist) if world > 1 else None                 # device-resident forest gather
     loader = sharded.ShardedProfileLoader(n, L, dist) if world > 1 else None      # 1/world of the rows per rank + all_gather
 
@@ -221,6 +221,7 @@ def run_ours(args):
             t = lap("linkage", t)
             labels = ctx.fcluster(thr, out=labels_host)
             t = lap("cut", t)
+            state["Z"] = Z
             d2h = Z.nbytes + labels.nbytes + (n - 1) * 8
         else:
             exch.local_forest(ctx)
@@ -230,6 +231,7 @@ def run_ours(args):
             labels = None
             if rank == 0:
                 Z = exch.linkage(ctx)
+                state["Z"] = Z
                 t = lap("final_merge", t)
                 labels = ctx.fcluster(thr, out=labels_host)
                 t = lap("cut", t)
@@ -279,7 +281,7 @@ def run_ours(args):
     if rank == 0:
         sampler.start()
     dt, launches, labels = timed(True, args.steps, args.warmup)
-    check = {"resident": result_check(labels)} if rank == 0 else {}
+    check = {"resident": result_check(labels, state["Z"])} if rank == 0 else {}
     kern = {k: float(np.mean(v)) for k, v in state.items() if isinstance(v, list) and v}
     kern_steps = {k: [round(float(x), 3) for x in v] for k, v in state.items() if isinstance(v, list) and v}
     host_seg = {k: round(float(np.mean(v)), 3) for k, v in seg.items()}
@@ -288,8 +290,26 @@ def run_ours(args):
     clocks = sampler.stop() if rank == 0 else None
     dt_e2e, _, labels_e2e = timed(False, args.steps, 1)
     if rank == 0:
-        check["e2e"] = result_check(labels_e2e)
+        check["e2e"] = result_check(labels_e2e, state["Z"])
+        check["oracle_match"] = bool(check["resident"]["oracle_match"] and check["e2e"]["oracle_match"]) \
+            if check["resident"]["oracle_match"] is not None else None
     d2h_bytes = state["d2h_bytes"]
+    exact = None
+    if world == 1:
+        # the drop-in CLI's default (REPORTREE_HC_EXACT_NAMES=1) is the scipy-order Prim, whose Z and cluster ids are
+        # byte-identical to scipy's; the headline number above is Boruvka mode (same partitions, ids may differ on ties)
+        ctx.set_single_algo(hc.SL_PRIM)
+        ks = min(args.steps, 3)
+        dt_p, _, labels_p = timed(True, ks, 1)
+        ctx.set_single_algo(hc.SL_BORUVKA)
+        exact = {"ms_per_step": 1e3 * dt_p / ks, "value": float(P) * L * ks / dt_p, "unit": "comparisons/s", "steps": ks,
+                 "linkage_ms": float(np.mean(state["link_ms"])), "what": "same step with the scipy-order Prim linkage (CLI default)"}
+        gpath = os.path.join(ROOT, "tests", "golden", "large", WORKLOAD["cfg"] + ".json")
+        if os.path.exists(gpath) and n == synth_n():
+            from reportree_b200 import checksums as C
+            g = json.load(open(gpath))["methods"]["single"]
+            exact["oracle_ids_match"] = bool(C.crc(state["Z"]) == g["z_crc32"] and all(
+                C.crc(labels_p[k]) == g["labels"][k]["ids_crc32"] for k in range(labels_p.shape[0])))
 
     if rank == 0:
         work = float(P) * L
@@ -317,12 +337,10 @@ def run_ours(args):
             "alu_peak_lane_ops_per_s": alu_peak, "alu_peak_source": "measured live (rthc_alu_peak LOP3 stream)",
             "lop3_per_32_loci": info["plane_rows"] / max(info["groups"], 1),
             "kernel_ms": kern["dist_ms"],
-            # dram__bytes_read.sum + dram__bytes_write.sum of this kernel at C4 from the committed
-            # `ncu --set full` capture of the round's last build (profiles/r01_ncu_y_distance_C4.txt):
-            # 37.58 GB + 10.39 GB.  The write side is the condensed matrix; the read side is the 378 MB plane
-            # matrix re-read when tiles miss L2 and varies between captures (31.5 / 34.0 / 37.6 / 40.8 GB in
-            # r01_ncu_z / _final / _y / _v5) -- 110-140 GB/s, 2 % of the HBM peak either way
-            "traffic": 47.97e9 if (n == 100000 and world == 1) else None,
+            # dram__bytes_read.sum + dram__bytes_write.sum of this kernel: not measurable from inside the run (needs
+            # the profiler), so it is READ from the summary that scripts/gpu_round.sh extracts from this round's
+            # `ncu --set full` capture of the same command (profiles/<round>_ncu_distance_C4.json) and labelled
+            **ncu_traffic(n, world),
             "algorithmic_bytes": alg_bytes,
             "hbm": {"achieved": alg_bytes / t_k / 1e9, "peak": hbm_peak, "unit": "GB/s",
                     "frac": alg_bytes / t_k / 1e9 / hbm_peak,
@@ -336,7 +354,9 @@ def run_ours(args):
             "config": {"workload": WORKLOAD["name"], "n": n, "L": L, "pairs": P, "thresholds": WORKLOAD["thresholds"],
                        "l2": "inputs larger than L2 (bit planes %.0f MB + condensed output %.1f GB per step)" % (
                            info["plane_rows"] * ctx_npad(n) * 4 / 1e6, 2.0 * owned_pairs / 1e9),
-                       "sharding": "tile-rows of the upper triangle over %d rank(s)" % world},
+                       "sharding": "tile-rows of the upper triangle over %d rank(s)" % world,
+                       "single_linkage": "Boruvka MST (north_star; same partitions as scipy, cluster ids may differ on ties); "
+                                         "exact_names_mode times the CLI-default scipy-order Prim"},
             "stage_ms": kern,
             "stage_ms_per_step": kern_steps,
             "host_wall_ms_rank0": host_seg,
@@ -358,19 +378,71 @@ def run_ours(args):
             line["cpu_baseline"] = {"value": work_s / t_all, "unit": "comparisons/s", "cores": 1, "kind": "port",
                                     "sample": "first %d samples x %d loci, C port of the cgmlst-dists rule + scipy "
                                               "single linkage + %d cuts (%.1f s)" % (ns, L, WORKLOAD["thresholds"], t_all)}
+        if exact:
+            line["exact_names_mode"] = exact
+        ref_script = reference_script_timing()
+        if ref_script:
+            line["cpu_baseline_script"] = ref_script
         print(json.dumps(line))
     ctx.close()
     if world > 1:
         dist.destroy_process_group()
 
 
-def result_check(labels):
-    """Fingerprint of the T x n label matrix (taken outside the timed region): equal for every N and for the
-    resident / host-buffer runs, because the strict (w, i, j) order makes the MST -- hence Z and scipy's
-    numbering -- unique."""
+def result_check(labels, Z=None):
+    """Fingerprint of the T x n label matrix (taken outside the timed region) and its comparison with the CPU
+    oracle's answer for this workload, committed as tests/golden/large/C4.json (tests/golden/make_golden_large.py:
+    oracle distances + oracle single linkage + oracle fcluster at thresholds 0..50).  The benchmarked path is
+    Boruvka mode, whose cluster numbering may differ from scipy's on ties, so what is compared per threshold is
+    the cluster count and the CRC32 of the membership-only relabelling, plus the CRC32 of the merge heights."""
     import zlib
-    return {"labels_crc32": zlib.crc32(np.ascontiguousarray(labels).tobytes()),
-            "clusters_at_first_mid_last_threshold": [int(labels[k].max()) for k in (0, labels.shape[0] // 2, labels.shape[0] - 1)]}
+    from reportree_b200 import checksums as C
+    out = {"labels_crc32": zlib.crc32(np.ascontiguousarray(labels).tobytes()),
+           "clusters_at_first_mid_last_threshold": [int(labels[k].max()) for k in (0, labels.shape[0] // 2, labels.shape[0] - 1)],
+           "oracle_match": None}
+    gpath = os.path.join(ROOT, "tests", "golden", "large", WORKLOAD["cfg"] + ".json")
+    if os.path.exists(gpath) and labels.shape[1] == synth_n():
+        g = json.load(open(gpath))
+        gm = g["methods"]["single"]
+        ok = len(g["thresholds"]) == labels.shape[0]
+        bad = []
+        for k in range(labels.shape[0] if ok else 0):
+            f = C.labels_fingerprint(labels[k])
+            if f["clusters"] != gm["labels"][k]["clusters"] or f["membership_crc32"] != gm["labels"][k]["membership_crc32"]:
+                bad.append(k)
+        heights_ok = None
+        if Z is not None:
+            heights_ok = C.crc(np.ascontiguousarray(Z[:, 2])) == gm["heights_crc32"]
+        out["oracle_match"] = bool(ok and not bad and heights_ok is not False)
+        out["oracle"] = {"golden": "tests/golden/large/%s.json" % WORKLOAD["cfg"], "thresholds_compared": labels.shape[0],
+                         "thresholds_differing": bad[:5], "merge_heights_equal": heights_ok}
+    return out
+
+
+def synth_n():
+    from reportree_b200 import synth
+    return synth.config(WORKLOAD["cfg"])["n"]
+
+
+def ncu_traffic(n, world):
+    """{"traffic": bytes, "traffic_source": file} from the newest profiles/*_ncu_distance_C4.json, else nulls."""
+    import glob
+    if n != synth_n() or world != 1:
+        return {"traffic": None, "traffic_source": None}
+    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_ncu_distance_C4.json")))
+    if not files:
+        return {"traffic": None, "traffic_source": None}
+    rec = json.load(open(files[-1]))
+    return {"traffic": rec["dram_bytes_read"] + rec["dram_bytes_write"],
+            "traffic_source": "ncu --set full capture, " + os.path.relpath(files[-1], ROOT)}
+
+
+def reference_script_timing():
+    """Wall time of the UNMODIFIED reference script on a bounded TSV (scripts/time_reference_script.py, run in the
+    build container because /root/reference does not travel to the GPU box), newest profiles/*_reference_script.json."""
+    import glob
+    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_reference_script.json")))
+    return json.load(open(files[-1])) if files else None
 
 
 def ctx_npad(n):

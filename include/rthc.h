@@ -88,6 +88,11 @@ int rthc_finish_import(rthc_ctx *ctx);
 int rthc_set_profiles_i32(rthc_ctx *ctx, const int32_t *codes_rowmajor, int64_t n, int64_t L);
 /* same, but the matrix is already in device memory (n x L row-major int32) */
 int rthc_set_profiles_i32_device(rthc_ctx *ctx, const void *dev_codes_rowmajor, int64_t n, int64_t L);
+/* same two entry points for callers whose allele ids fit 16 bits (0 = missing): half the host-to-device
+ * bytes of the int32 form.  The tokenizer that feeds the seam (scripts/partitioning_HC.py:293-298 contract)
+ * knows the largest id of the matrix and picks the narrower form when it can.                            */
+int rthc_set_profiles_u16(rthc_ctx *ctx, const uint16_t *codes_rowmajor, int64_t n, int64_t L);
+int rthc_set_profiles_u16_device(rthc_ctx *ctx, const void *dev_codes_rowmajor, int64_t n, int64_t L);
 
 /* d(i,j) = #{l : a_il != a_jl, a_il != 0, a_jl != 0} for every owned pair, written to
  * the device-resident condensed uint16 matrix (scipy pdist order for a full shard). */

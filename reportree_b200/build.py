@@ -77,6 +77,32 @@ def build(force=False, verbose=False):
     return OUT
 
 
+def build_checked():
+    """build/lib_checked.so: the same sources with -DRTHC_CHECKED (device-side invariants, see rthc_internal.cuh);
+    load it with RTHC_LIB_PATH=reportree_b200/build/lib_checked.so."""
+    out = os.path.join(HERE, "build", "lib_checked.so")
+    odir = os.path.join(HERE, "build", "checked")
+    os.makedirs(odir, exist_ok=True)
+    procs, objs = [], []
+    for src in SOURCES:
+        obj = os.path.join(odir, src.replace(".cu", ".o"))
+        procs.append((src, subprocess.Popen([NVCC] + FLAGS + ["-DRTHC_CHECKED", "-c", os.path.join(CSRC, src), "-o", obj],
+                                            stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)))
+        objs.append(obj)
+    for src, p in procs:
+        text, _ = p.communicate()
+        if p.returncode:
+            sys.stderr.write(text)
+            raise RuntimeError("nvcc failed on " + src)
+    subprocess.check_call([NVCC, "-shared", "-o", out + ".tmp"] + objs + ["-gencode", "arch=compute_100a,code=sm_100a",
+                                                                             "-cudart", "static"])
+    os.replace(out + ".tmp", out)
+    return out
+
+
 if __name__ == "__main__":
-    build(force=True, verbose="-v" in sys.argv)
-    print(OUT)
+    if "--checked" in sys.argv:
+        print(build_checked())
+    else:
+        build(force=True, verbose="-v" in sys.argv)
+        print(OUT)

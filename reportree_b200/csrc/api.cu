@@ -283,13 +283,13 @@ int rthc_setup_geometry(rthc_ctx *ctx, int64_t n)
     return 0;
 }
 
-static int set_profiles_common(rthc_ctx *ctx, const int32_t *d_rowmajor, int64_t n, int64_t L)
+static int set_profiles_common(rthc_ctx *ctx, const void *d_rowmajor, int64_t n, int64_t L, bool in_u16)
 {
     int rc;
     ctx->L = L;
     if ((rc = rthc_setup_geometry(ctx, n))) return rc;
     RTHC_CUDA(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
-    if ((rc = rthc_recode_and_pack(ctx, d_rowmajor))) return rc;
+    if ((rc = rthc_recode_and_pack(ctx, d_rowmajor, in_u16))) return rc;
     RTHC_CUDA(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
     RTHC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     float ms = 0;
@@ -310,32 +310,32 @@ static int check_shape(rthc_ctx *ctx, int64_t n, int64_t L)
     return 0;
 }
 
-extern "C" int rthc_set_profiles_i32(rthc_ctx *ctx, const int32_t *codes, int64_t n, int64_t L)
+static int set_profiles_host(rthc_ctx *ctx, const void *codes, int64_t n, int64_t L, bool in_u16)
 {
-    if (!ctx || !codes) return rthc_fail(ctx, RTHC_E_ARG, "rthc_set_profiles_i32: NULL argument");
+    if (!ctx || !codes) return rthc_fail(ctx, RTHC_E_ARG, "rthc_set_profiles: NULL argument");
     int rc = check_shape(ctx, n, L);
     if (rc) return rc;
     RTHC_CUDA(ctx, cudaSetDevice(ctx->device));
     rthc_free_distance_state(ctx);
     rthc_free_linkage_state(ctx);
-    int32_t *d_in = nullptr;
-    if ((rc = rthc_dev_alloc(ctx, &d_in, (size_t)(n * L)))) return rc;
+    const size_t bytes = (size_t)(n * L) * (in_u16 ? sizeof(uint16_t) : sizeof(int32_t));
+    unsigned char *d_in = nullptr;
+    if ((rc = rthc_dev_alloc(ctx, &d_in, bytes))) return rc;
     RTHC_CUDA(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
-    RTHC_CUDA(ctx, cudaMemcpyAsync(d_in, codes, sizeof(int32_t) * (size_t)(n * L), cudaMemcpyHostToDevice,
-                                   ctx->stream));
+    RTHC_CUDA(ctx, cudaMemcpyAsync(d_in, codes, bytes, cudaMemcpyHostToDevice, ctx->stream));
     RTHC_CUDA(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
     RTHC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     float ms = 0;
     RTHC_CUDA(ctx, cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1));
     ctx->t_ms[0] = ms;
-    rc = set_profiles_common(ctx, d_in, n, L);
+    rc = set_profiles_common(ctx, d_in, n, L, in_u16);
     rthc_dev_free(ctx, &d_in);
     return rc;
 }
 
-extern "C" int rthc_set_profiles_i32_device(rthc_ctx *ctx, const void *dev_codes, int64_t n, int64_t L)
+static int set_profiles_device(rthc_ctx *ctx, const void *dev_codes, int64_t n, int64_t L, bool in_u16)
 {
-    if (!ctx || !dev_codes) return rthc_fail(ctx, RTHC_E_ARG, "rthc_set_profiles_i32_device: NULL argument");
+    if (!ctx || !dev_codes) return rthc_fail(ctx, RTHC_E_ARG, "rthc_set_profiles_*_device: NULL argument");
     int rc = check_shape(ctx, n, L);
     if (rc) return rc;
     RTHC_CUDA(ctx, cudaSetDevice(ctx->device));
@@ -343,7 +343,24 @@ extern "C" int rthc_set_profiles_i32_device(rthc_ctx *ctx, const void *dev_codes
     rthc_free_linkage_state(ctx);
     ctx->t_ms[0] = 0;
     RTHC_CUDA(ctx, cudaDeviceSynchronize());   // the caller's producer stream is unknown
-    return set_profiles_common(ctx, (const int32_t *)dev_codes, n, L);
+    return set_profiles_common(ctx, dev_codes, n, L, in_u16);
+}
+
+extern "C" int rthc_set_profiles_i32(rthc_ctx *ctx, const int32_t *codes, int64_t n, int64_t L)
+{
+    return set_profiles_host(ctx, codes, n, L, false);
+}
+extern "C" int rthc_set_profiles_i32_device(rthc_ctx *ctx, const void *dev_codes, int64_t n, int64_t L)
+{
+    return set_profiles_device(ctx, dev_codes, n, L, false);
+}
+extern "C" int rthc_set_profiles_u16(rthc_ctx *ctx, const uint16_t *codes, int64_t n, int64_t L)
+{
+    return set_profiles_host(ctx, codes, n, L, true);
+}
+extern "C" int rthc_set_profiles_u16_device(rthc_ctx *ctx, const void *dev_codes, int64_t n, int64_t L)
+{
+    return set_profiles_device(ctx, dev_codes, n, L, true);
 }
 
 extern "C" int rthc_distance(rthc_ctx *ctx)

@@ -44,6 +44,7 @@ __global__ void rthc_cut_leaders(const int32_t *__restrict__ up, int levels, int
         if (a < lim) x = a;
     }
     const int32_t e = event[x];
+    RTHC_DEV_ASSERT(x >= 0 && x < nodes && e >= 0 && e < nodes);
     key[(int64_t)t * n + v] = e;
     flags[(int64_t)t * flag_stride + e] = 1;
 }
@@ -140,6 +141,7 @@ __global__ void rthc_cut_labels(const int32_t *__restrict__ key, const int32_t *
     const int t = blockIdx.y;
     if (v >= n) return;
     const int32_t e = key[(int64_t)t * n + v];
+    RTHC_DEV_ASSERT(e >= 0 && e < 2 * n - 1);
     labels[(int64_t)t * n + v] = scanned[(int64_t)t * flag_stride + e] + aux[(int64_t)t * nb + e / CUT_SCAN_ELEMS];
 }
 

@@ -150,6 +150,7 @@ __device__ __forceinline__ void ws_group(WsRing &R, WsAcc &A, WsOps &cur, const 
     for (int b = 0; b < 8; ++b) ws_fold(A, 56 + b, p7[b]);
     ws_arrive(R.empty_bar + 8 * s);            // every consumer thread arrives (count = 256)
     R.it += 1;
+    RTHC_DEV_ASSERT(R.it <= R.total);
     cur = nxt;
 }
 
@@ -313,6 +314,7 @@ rthc_distance_ws(const uint32_t *__restrict__ planes, const int32_t *__restrict_
             for (int b = 0; b < 8; ++b) {
                 const int64_t j = j0 + (b < 4 ? 4 * tx + b : 64 + 4 * tx + (b - 4));
                 const uint32_t d = b < 4 ? (A.accp[a][b] & 0xFFFFu) : (A.accp[a][b & 3] >> 16);
+                RTHC_DEV_ASSERT(d <= 0xFFFFu && (int)d <= 32 * G);
                 if (j > i && j < n) cond[base + (j - i - 1)] = (uint16_t)d;
             }
         }

@@ -298,7 +298,9 @@ __global__ void rthc_boruvka_hook(const uint64_t *__restrict__ best, const int32
     if (comp[c] != (int32_t)c) { parent[c] = comp[c]; return; }
     const uint64_t key = best[c];
     if (key == RTHC_KEY_INF) { parent[c] = (int32_t)c; return; }
+    RTHC_DEV_ASSERT(rthc_key_i(key) < rthc_key_j(key) && (int64_t)rthc_key_j(key) < n);
     const int32_t ci = comp[rthc_key_i(key)], cj = comp[rthc_key_j(key)];
+    RTHC_DEV_ASSERT((ci == (int32_t)c) != (cj == (int32_t)c));       // the lightest edge LEAVES the component
     const int32_t other = (ci == (int32_t)c) ? cj : ci;
     const bool mutual = best[other] == key;
     if (mutual && (int32_t)c < other) { parent[c] = (int32_t)c; return; }

@@ -486,219 +486,290 @@ __device__ __forceinline__ double lance_williams<double>(int method, double dx, 
 }
 
 template <typename T, typename S>
-__global__ void rthc_expand_square(const S *__restrict__ cond, int64_t n, T *__restrict__ W)
+__global__ void rthc_expand_square(const S *__restrict__ cond, int64_t n, int64_t pitch, T *__restrict__ W)
 {
     const int64_t i = blockIdx.x;                              // rows on grid.x: no 65,535 limit
     const int64_t j = (int64_t)blockIdx.y * blockDim.x + threadIdx.x;
-    if (j >= n) return;
+    if (j >= pitch) return;
     T v = 0;
-    if (i != j) {
+    if (i != j && j < n) {
         const int64_t a = i < j ? i : j, b = i < j ? j : i;
         v = (T)cond[n * a - (a * (a + 1)) / 2 + (b - a - 1)];
     }
-    W[i * n + j] = v;
+    W[i * pitch + j] = v;
+}
+
+// all-lanes lexicographic minimum of (w, i) over a warp
+__device__ __forceinline__ void warp_min_all(unsigned long long &w, unsigned int &i)
+{
+#pragma unroll
+    for (int s = 16; s > 0; s >>= 1) {
+        unsigned long long ow = __shfl_xor_sync(0xffffffffu, w, s);
+        unsigned int oi = __shfl_xor_sync(0xffffffffu, i, s);
+        if (slot_less(ow, oi, w, i)) { w = ow; i = oi; }
+    }
 }
 
 // control block in global memory (written by block 0, thread 0 only)
 struct ChainCtl {
-    int64_t scans;      // full row scans (one grid barrier each)
-    int64_t fused;      // scans of the next chain tip that rode on a merge's barrier
-    int64_t hits;       // chain steps answered by the nearest-neighbour cache (no barrier)
+    int64_t repairs;    // row scans by a single CTA inside a merge phase (no barrier of their own)
+    int64_t hits;       // chain steps, all answered by the nearest-neighbour cache
+    int64_t barriers;   // grid barriers executed (one per merge + one after the initial scan)
 };
 
-// nearest neighbour of every row: lexicographic minimum of (D[r, i], i) over i != r  (one CTA per row)
-template <typename T>
-__global__ void __launch_bounds__(SEQ_THREADS) rthc_nn_init(const T *__restrict__ W, int64_t n, MinSlot *__restrict__ nn)
+// element e of a 16-byte chunk of a row, as order-preserving bits
+template <typename T> __device__ __forceinline__ unsigned long long chunk_bits(const uint4 &q, int e);
+template <> __device__ __forceinline__ unsigned long long chunk_bits<uint16_t>(const uint4 &q, int e)
 {
-    __shared__ MinSlot sh[SEQ_THREADS / 32];
-    const int64_t r = blockIdx.x;
-    const T *row = W + r * n;
-    unsigned long long bw = ~0ull;
-    unsigned int bi = ~0u;
-    for (int64_t i = threadIdx.x; i < n; i += SEQ_THREADS) {
-        if (i == r) continue;
-        const unsigned long long d = order_bits(row[i]);
-        if (slot_less(d, (unsigned int)i, bw, bi)) { bw = d; bi = (unsigned int)i; }
-    }
-    block_min(bw, bi, sh);
-    if (threadIdx.x == 0) { nn[r].w = bw; nn[r].i = bi; }
+    const uint32_t w = e < 2 ? q.x : (e < 4 ? q.y : (e < 6 ? q.z : q.w));
+    return (unsigned long long)((w >> (16 * (e & 1))) & 0xFFFFu);
+}
+template <> __device__ __forceinline__ unsigned long long chunk_bits<double>(const uint4 &q, int e)
+{
+    return e == 0 ? (((unsigned long long)q.y << 32) | q.x) : (((unsigned long long)q.w << 32) | q.z);
 }
 
+// One CTA: lexicographic minimum of (D[r, j], j) over the live columns j of row r, j not in {skip1, skip2}
+// (16-byte loads, liveness from the CTA's shared-memory bitmap; RS_U chunks in flight per thread).
+// Result valid in thread 0.  `row` is 16-byte aligned (rows are pitched).
+#define RS_U 8
+template <typename T>
+__device__ __forceinline__ void cta_row_min(const T *row, int64_t n, const uint32_t *s_live, int64_t skip1, int64_t skip2,
+                                            unsigned long long &bw, unsigned int &bi, MinSlot *sh)
+{
+    constexpr int E = 16 / (int)sizeof(T);
+    bw = ~0ull; bi = ~0u;
+    const int64_t stride = (int64_t)SEQ_THREADS * E;
+    for (int64_t g0 = (int64_t)threadIdx.x * E; g0 < n; g0 += stride * RS_U) {
+        uint4 q[RS_U];
+        uint32_t lb[RS_U];
+#pragma unroll
+        for (int u = 0; u < RS_U; ++u) {
+            const int64_t j0 = g0 + u * stride;
+            lb[u] = 0;
+            if (j0 < n) {
+                lb[u] = (s_live[j0 >> 5] >> (j0 & 31)) & ((1u << E) - 1u);
+                if ((unsigned long long)(skip1 - j0) < (unsigned long long)E) lb[u] &= ~(1u << (int)(skip1 - j0));
+                if ((unsigned long long)(skip2 - j0) < (unsigned long long)E) lb[u] &= ~(1u << (int)(skip2 - j0));
+            }
+            if (lb[u]) q[u] = __ldcg(reinterpret_cast<const uint4 *>(row + j0));
+        }
+#pragma unroll
+        for (int u = 0; u < RS_U; ++u) {
+            if (!lb[u]) continue;
+            const int64_t j0 = g0 + u * stride;
+#pragma unroll
+            for (int e = 0; e < E; ++e) {
+                if (!((lb[u] >> e) & 1u)) continue;
+                const unsigned long long d = chunk_bits<T>(q[u], e);
+                if (d < bw) { bw = d; bi = (unsigned int)(j0 + e); }      // ascending j: the lowest index of the minimum
+            }
+        }
+    }
+    block_min(bw, bi, sh);
+}
+
+struct ChainBc {                // scalar state read by thread 0 / warp 0 and broadcast through shared memory
+    unsigned long long cw, dprev, gw;
+    unsigned int ci, gi;
+    int32_t x, prev, sx, sprev;
+};
+
 // The merge loop.  scipy's chain step asks for the nearest neighbour of the chain tip x: the previous chain
-// element if it ties the minimum, else the lowest index of the minimum of row x.  A grid-wide row scan costs one
-// grid barrier (about 2.4 us) however short the row is, so the kernel keeps, for every live row r, the exact
-// lexicographic minimum nn[r] = min over live i != r of (D[r, i], i) and only scans when that entry is unknown:
-//   * a merge (a dies, b = a u b) already visits every live row i to write D[i, b]; the same thread folds the new
-//     entry into the cache -- nn[i] = min(nn[i], (D[i, b], b)) is exact because every other entry of row i is
-//     unchanged -- and drops it (index = ~0) when the cached neighbour was a or b;
-//   * the candidates (D[b, i], i) of the new row b are reduced over the grid on the merge's own barrier;
-//   * so is a scan of the row of p, the chain element that becomes the tip after the merge (its neighbour was a
-//     or b by construction): row p only changes in column b, whose new value the thread that owns i == p has.
-// A chain step whose tip has a cached neighbour reads it (warp 0 of every CTA, broadcast through shared memory)
-// and costs no barrier.  The answer is the same (value, lowest index, previous-wins) triple as the scan, so Z
-// stays byte-identical to scipy.  nn[] is double-buffered by merge parity: a merge writes the other copy for every
-// live row, so a CTA still walking the chain never reads an entry that a faster CTA has already updated.
-// Every nn[r] is written by ONE thread (the owner of index r in the strided loops), reads of scalar state go
-// through warp 0 + shared memory (148 x 16 warps loading one address serialise in L2), size[] of the last merge
-// is patched from registers until the next barrier has published it.
+// element if it ties the minimum, else the lowest index of the minimum of row x.  A grid-wide row scan costs a
+// grid barrier (2.4 us + the reductions around it) however short the row is, so the kernel keeps for EVERY live
+// row r the exact lexicographic minimum nn[r] = min over live i != r of (D[r, i], i), and a chain step is a
+// look-up (thread 0 of every CTA reads the same entry, broadcast through shared memory): no barrier.
+// Only a merge (a dies, b = a u b) has one, and the merge phase restores the invariant before it:
+//   * the thread that writes D[i, b] folds the new entry into the cache: nn[i] = min(nn[i], (D[i, b], b)) is exact
+//     because every other entry of row i is unchanged;
+//   * if the cached neighbour of row i was a or b, the CTA of that thread rescans row i by itself (a row is
+//     <= 0.2 MB: one SM streams it in about a microsecond; columns a and b are skipped -- a is dead, b's new value
+//     is the one just computed -- so the scan reads nothing that this phase writes);
+//   * the candidates (D[b, i], i) of the new row b are reduced per CTA and combined after the barrier.
+// The answer of a look-up is the same (value, lowest index, previous-wins) triple as scipy's scan, so Z stays
+// byte-identical.  nn[] is double-buffered by merge parity (a CTA still walking the chain must not see entries
+// that a faster CTA has already updated); every CTA keeps the liveness bitmap in shared memory and its own
+// copy of the chain (touched by its thread 0 only); size[] of the last merge is patched from registers until the
+// next barrier has published it; W is pitched so that every row starts on a 16-byte boundary.
 template <typename T>
 __global__ void __launch_bounds__(SEQ_THREADS, 1)
-rthc_nn_chain_kernel(T *W, int64_t n, int method, int32_t *size, int32_t *chains, MinSlot *slots, MinSlot *nn2,
-                     int32_t *ex, int32_t *ey, double *ew, ChainCtl *ctl)
+rthc_nn_chain_kernel(T *W, int64_t n, int64_t pitch, int method, int32_t *size, int32_t *chains, MinSlot *slots,
+                     MinSlot *nn2, int32_t *ex, int32_t *ey, double *ew, ChainCtl *ctl)
 {
     cg::grid_group grid = cg::this_grid();
+    extern __shared__ uint32_t s_live[];                         // bit j: cluster j is alive
     __shared__ MinSlot sh[SEQ_THREADS / 32];
-    __shared__ MinSlot bcs[2];                                   // broadcast buffers, alternating
-    __shared__ unsigned long long bcd[2];
-    __shared__ int32_t bci[2][4];
+    __shared__ ChainBc bc[2];                                    // alternating: one __syncthreads per round
+    __shared__ int32_t s_bad_i[SEQ_THREADS];                     // rows of this CTA whose cached neighbour was a or b
+    __shared__ unsigned long long s_bad_w[SEQ_THREADS];          // ... and their new D[i, b]
+    __shared__ int s_nbad;
     const int nblocks = gridDim.x;
-    const int64_t gtid = (int64_t)blockIdx.x * SEQ_THREADS + threadIdx.x;
+    const int tid = threadIdx.x, lane = tid & 31;
+    const int64_t gtid = (int64_t)blockIdx.x * SEQ_THREADS + tid;
     const int64_t gthreads = (int64_t)nblocks * SEQ_THREADS;
-    const bool leader = blockIdx.x == 0 && threadIdx.x == 0;
-    const int lane = threadIdx.x & 31;
-    const bool w0 = threadIdx.x < 32;
-    int32_t *chain = chains + (int64_t)blockIdx.x * n;          // this CTA's copy, touched by its thread 0 only
+    const bool leader = blockIdx.x == 0 && tid == 0;
+    int32_t *chain = chains + (int64_t)blockIdx.x * n;
+
+    // ---- initial state: everything alive, nn[] of every row by the CTA that owns it ----------------
+    const int64_t live_words = (pitch + 31) / 32;
+    for (int64_t w = tid; w < live_words; w += SEQ_THREADS) {
+        const int64_t j = w * 32;
+        s_live[w] = j + 32 <= n ? 0xFFFFFFFFu : (j >= n ? 0u : ((1u << (int)(n - j)) - 1u));
+    }
+    if (tid == 0) s_nbad = 0;
+    __syncthreads();
+    for (int64_t r = blockIdx.x; r < n; r += nblocks) {
+        unsigned long long w; unsigned int i;
+        cta_row_min<T>(W + r * pitch, n, s_live, r, -1, w, i, sh);
+        if (tid == 0) { __stcg(&nn2[r].w, w); __stcg(&nn2[r].i, i); }
+    }
+    grid.sync();
 
     // replicated scalar state (identical in every thread of the grid)
-    int64_t len = 0, first_live = 0, step = 0, scans = 0, fused = 0, hits = 0;
+    int64_t len = 0, first_live = 0, step = 0, hits = 0, repairs = 0;
     int32_t x = -1, prev = -1;
     int32_t dead = -1, grown = -1, grown_size = 0;              // last merge, until the next barrier publishes size[]
     unsigned long long gw = ~0ull; unsigned int gi = ~0u;        // nn of `grown`
-    bool have_tip = false;                                       // nn of the tip is in (tw, ti, tdprev)
-    unsigned long long tw = ~0ull, tdprev = ~0ull; unsigned int ti = ~0u;
     int q = 0, cur = 0;                                          // broadcast buffer, current nn copy
+    int32_t nxt_x = -1, nxt_prev = -1;                           // thread 0: chain tip after the pending pop
 
 #define SIZE_OF(i_) ((i_) == dead ? 0 : ((i_) == grown ? grown_size : __ldcg(&size[(i_)])))
 
     for (int64_t k = 0; k < n - 1;) {
-        MinSlot *nn = nn2 + (int64_t)cur * n;
+        const MinSlot *nn = nn2 + (int64_t)cur * n;
         if (len == 0) {
-            if (w0) {                                            // lowest live index, 32 candidates per trip
-                int64_t f = first_live;
+            if (tid < 32) {                                      // lowest live index from the bitmap
+                int64_t w = first_live >> 5;
                 for (;;) {
-                    const int64_t i = f + lane;
-                    const bool live = i < n && SIZE_OF(i) != 0;
-                    const unsigned m = __ballot_sync(0xffffffffu, live);
-                    if (m) { f += __ffs(m) - 1; break; }
-                    f += 32;
+                    const int64_t ww = w + lane;
+                    const uint32_t bits = ww < live_words ? s_live[ww] : 0u;
+                    const unsigned m = __ballot_sync(0xffffffffu, bits != 0u);
+                    if (m) {
+                        const int src = __ffs(m) - 1;
+                        const uint32_t b0 = __shfl_sync(0xffffffffu, bits, src);
+                        if (lane == 0) { bc[q].x = (int32_t)((w + src) * 32 + (__ffs(b0) - 1)); chain[0] = bc[q].x; }
+                        break;
+                    }
+                    w += 32;
                 }
-                if (lane == 0) { bci[q][0] = (int32_t)f; chain[0] = (int32_t)f; }
             }
             __syncthreads();
-            first_live = bci[q][0]; q ^= 1;
-            x = (int32_t)first_live; prev = -1; len = 1; have_tip = false;
+            first_live = bc[q].x; q ^= 1;
+            x = (int32_t)first_live; prev = -1; len = 1;
         }
-        // ---- nearest neighbour of the tip x -----------------------------------------------------
-        unsigned long long cw, dprev;
-        unsigned int ci;
-        if (have_tip) {
-            cw = tw; ci = ti; dprev = tdprev;
-            have_tip = false;
-        } else {
-            if (threadIdx.x == 0) {
-                if (x == grown) { bcs[q].w = gw; bcs[q].i = gi; }
-                else { bcs[q].w = __ldcg(&nn[x].w); bcs[q].i = __ldcg(&nn[x].i); }
-                bcd[q] = len > 1 ? order_bits(__ldcg(&W[(int64_t)x * n + prev])) : ~0ull;
-            }
-            __syncthreads();
-            cw = bcs[q].w; ci = bcs[q].i; dprev = bcd[q]; q ^= 1;
-            if (ci != ~0u) ++hits;
+        // ---- nearest neighbour of the tip x: a look-up ----------------------------------------------
+        if (tid == 0) {
+            ChainBc &o = bc[q];
+            if (x == grown) { o.cw = gw; o.ci = gi; }
+            else { o.cw = __ldcg(&nn[x].w); o.ci = __ldcg(&nn[x].i); }
+            o.dprev = len > 1 ? order_bits(__ldcg(&W[(int64_t)x * pitch + prev])) : ~0ull;
+            o.sx = SIZE_OF(x);
+            o.sprev = len > 1 ? SIZE_OF(prev) : 0;
         }
-        if (ci == ~0u) {
-            // ---- unknown: scan row x over the grid (lowest index of the minimum over live i != x) --
-            unsigned long long bw = ~0ull;
-            unsigned int bi = ~0u;
-            const T *row = W + (int64_t)x * n;
-            for (int64_t i = gtid; i < n; i += gthreads) {
-                if (i == x || SIZE_OF(i) == 0) continue;
-                const unsigned long long d = order_bits(__ldcg(&row[i]));
-                if (slot_less(d, (unsigned int)i, bw, bi)) { bw = d; bi = (unsigned int)i; }
-            }
-            block_min(bw, bi, sh);
-            MinSlot *cs = slots + (step & 1) * nblocks;
-            if (threadIdx.x == 0) { cs[blockIdx.x].w = bw; cs[blockIdx.x].i = bi; }
-            grid.sync();
-            grid_min(cs, nblocks, cw, ci, sh);
-            ++step; ++scans;
-            dead = -1; grown = -1;
-            if (gtid == x % gthreads) { nn[x].w = cw; nn[x].i = ci; }
-        }
+        __syncthreads();
+        const unsigned long long cw = bc[q].cw, dprev = bc[q].dprev;
+        const unsigned int ci = bc[q].ci;
+        const int32_t sx = bc[q].sx, sprev = bc[q].sprev;
+        q ^= 1;
+        ++hits;
+        RTHC_DEV_ASSERT(x >= 0 && x < n && ((s_live[x >> 5] >> (x & 31)) & 1u));
+        RTHC_DEV_ASSERT(ci < (unsigned int)n && ci != (unsigned int)x && ((s_live[ci >> 5] >> (ci & 31)) & 1u));
+        RTHC_DEV_ASSERT(sx > 0 && (len == 1 || sprev > 0));
         int32_t y = (int32_t)ci;
         unsigned long long dmin = cw;
         if (len > 1 && dprev <= dmin) { y = prev; dmin = dprev; }  // previous chain element wins ties
         if (!(len > 1 && y == prev)) {
             // ---- extend the chain ---------------------------------------------------------------
-            if (threadIdx.x == 0) chain[len] = y;
+            RTHC_DEV_ASSERT(len < n);
+            if (tid == 0) chain[len] = y;
             prev = x; x = y; ++len;
             continue;
         }
         // ---- merge x and y (reciprocal nearest neighbours) ---------------------------------------
         const int32_t a = x < y ? x : y, b = x < y ? y : x;       // a dies, b survives (scipy: x < y swap)
-        if (threadIdx.x == 0) {
-            bci[q][0] = SIZE_OF(a); bci[q][1] = SIZE_OF(b);
-            const int32_t p0 = len >= 3 ? chain[len - 3] : -1, pp0 = len >= 4 ? chain[len - 4] : -1;
-            bci[q][2] = p0; bci[q][3] = pp0;
-            bcd[q] = pp0 >= 0 ? order_bits(__ldcg(&W[(int64_t)p0 * n + pp0])) : ~0ull;
+        const int32_t na = x < y ? sx : sprev, nb = x < y ? sprev : sx;
+        if (tid == 0) {
+            s_live[a >> 5] &= ~(1u << (a & 31));
+            nxt_x = len >= 3 ? chain[len - 3] : -1;              // in flight while the pass runs
+            nxt_prev = len >= 4 ? chain[len - 4] : -1;
         }
-        __syncthreads();
-        const int32_t na = bci[q][0], nb = bci[q][1], p = bci[q][2], pp = bci[q][3];
-        const unsigned long long dpp = bcd[q];
-        q ^= 1;
         if (leader) { ex[k] = a; ey[k] = b; ew[k] = from_bits(dmin, T()); }
-        const T *ra = W + (int64_t)a * n;
-        T *rb = W + (int64_t)b * n;
-        const T *rp = W + (int64_t)(p >= 0 ? p : 0) * n;
+        __syncthreads();                                         // bitmap without a; s_nbad == 0 from the last phase
+        const T *ra = W + (int64_t)a * pitch;
+        T *rb = W + (int64_t)b * pitch;
         MinSlot *nxt = nn2 + (int64_t)(cur ^ 1) * n;
         const double dab = from_bits(dmin, T());
-        unsigned long long bwb = ~0ull, bwp = ~0ull;
-        unsigned int bib = ~0u, bip = ~0u;
-        for (int64_t i = gtid; i < n; i += gthreads) {
-            int32_t ni;
-            if (i == a || i == b || (ni = SIZE_OF(i)) == 0) continue;
-            const T v = lance_williams<T>(method, __ldcg(&ra[i]), __ldcg(&rb[i]), dab, na, nb, ni);
-            rb[i] = v;                       // row b (contiguous)
-            W[i * n + b] = v;                // column b (symmetric copy)
-            const unsigned long long ob = order_bits(v);
-            if (slot_less(ob, (unsigned int)i, bwb, bib)) { bwb = ob; bib = (unsigned int)i; }
-            if (i == p) {                    // row p: its only changed entry; the rest is scanned below
-                if (slot_less(ob, (unsigned int)b, bwp, bip)) { bwp = ob; bip = (unsigned int)b; }
-            } else {
+        unsigned long long bwb = ~0ull;
+        unsigned int bib = ~0u;
+        for (int64_t i0 = (int64_t)blockIdx.x * SEQ_THREADS; i0 < n; i0 += gthreads) {
+            const int64_t i = i0 + tid;
+            if (i < n && i != b && ((s_live[i >> 5] >> (i & 31)) & 1u)) {
+                const int32_t ni = SIZE_OF(i);
+                const T v = lance_williams<T>(method, __ldcg(&ra[i]), __ldcg(&rb[i]), dab, na, nb, ni);
+                rb[i] = v;                       // row b (contiguous)
+                W[i * pitch + b] = v;            // column b (symmetric copy)
+                const unsigned long long ob = order_bits(v);
+                if (slot_less(ob, (unsigned int)i, bwb, bib)) { bwb = ob; bib = (unsigned int)i; }
                 unsigned long long ow = __ldcg(&nn[i].w);
                 unsigned int oi = __ldcg(&nn[i].i);
-                if (oi == (unsigned int)a || oi == (unsigned int)b) oi = ~0u;
-                else if (oi != ~0u && slot_less(ob, (unsigned int)b, ow, oi)) { ow = ob; oi = (unsigned int)b; }
-                __stcg(&nxt[i].w, ow); __stcg(&nxt[i].i, oi);
-                if (p >= 0) {
-                    const unsigned long long d = order_bits(__ldcg(&rp[i]));
-                    if (slot_less(d, (unsigned int)i, bwp, bip)) { bwp = d; bip = (unsigned int)i; }
+                if (oi == (unsigned int)a || oi == (unsigned int)b) {
+                    const int slot = atomicAdd(&s_nbad, 1);
+                    RTHC_DEV_ASSERT(slot >= 0 && slot < SEQ_THREADS);
+                    s_bad_i[slot] = (int32_t)i; s_bad_w[slot] = ob;
+                } else {
+                    if (slot_less(ob, (unsigned int)b, ow, oi)) { ow = ob; oi = (unsigned int)b; }
+                    __stcg(&nxt[i].w, ow); __stcg(&nxt[i].i, oi);
                 }
             }
+            __syncthreads();
+            const int nbad = s_nbad;
+            for (int e = 0; e < nbad; ++e) {                     // this CTA rescans the rows it could not patch
+                const int32_t r = s_bad_i[e];
+                unsigned long long w; unsigned int j;
+                cta_row_min<T>(W + (int64_t)r * pitch, n, s_live, r, b, w, j, sh);
+                if (tid == 0) {
+                    const unsigned long long ob = s_bad_w[e];
+                    if (slot_less(ob, (unsigned int)b, w, j)) { w = ob; j = (unsigned int)b; }
+                    RTHC_DEV_ASSERT(j < (unsigned int)n && j != (unsigned int)r && j != (unsigned int)a);
+                    __stcg(&nxt[r].w, w); __stcg(&nxt[r].i, j);
+                }
+            }
+            repairs += nbad;
+            __syncthreads();
+            if (tid == 0) s_nbad = 0;
+            __syncthreads();
         }
         block_min(bwb, bib, sh);
-        MinSlot *sb = slots + (2 + (step & 1)) * nblocks, *sp = slots + (4 + (step & 1)) * nblocks;
-        if (threadIdx.x == 0) { sb[blockIdx.x].w = bwb; sb[blockIdx.x].i = bib; }
-        if (p >= 0) {
-            block_min(bwp, bip, sh);
-            if (threadIdx.x == 0) { sp[blockIdx.x].w = bwp; sp[blockIdx.x].i = bip; }
-        }
+        MinSlot *sb = slots + (step & 1) * nblocks;
+        if (tid == 0) { sb[blockIdx.x].w = bwb; sb[blockIdx.x].i = bib; }
         grid.sync();                          // row/column b and the other nn copy are visible
         ++step;
         cur ^= 1;
-        grid_min(sb, nblocks, gw, gi, sh);
-        if (gtid == b % gthreads) { __stcg(&nxt[b].w, gw); __stcg(&nxt[b].i, gi); }
-        if (p >= 0) {
-            grid_min(sp, nblocks, tw, ti, sh);
-            tdprev = dpp; have_tip = true; ++fused;
-            if (gtid == p % gthreads) { __stcg(&nxt[p].w, tw); __stcg(&nxt[p].i, ti); }
+        // nn of the new row b: warp 0 combines the CTA minima; thread 0 adds the chain tip after the pop
+        if (tid < 32) {
+            unsigned long long w = ~0ull; unsigned int i = ~0u;
+            for (int c = lane; c < nblocks; c += 32) {
+                const unsigned long long cw2 = __ldcg(&sb[c].w);
+                const unsigned int ci2 = __ldcg(&sb[c].i);
+                if (slot_less(cw2, ci2, w, i)) { w = cw2; i = ci2; }
+            }
+            warp_min_all(w, i);
+            if (lane == 0) { bc[q].gw = w; bc[q].gi = i; bc[q].x = nxt_x; bc[q].prev = nxt_prev; }
         }
+        __syncthreads();
+        gw = bc[q].gw; gi = bc[q].gi;
+        const int32_t px = bc[q].x, pprev = bc[q].prev;
+        q ^= 1;
+        if (gtid == b % gthreads) { __stcg(&nxt[b].w, gw); __stcg(&nxt[b].i, gi); }
         if (leader) { size[a] = 0; size[b] = na + nb; }
         dead = a; grown = b; grown_size = na + nb;
         ++k;
         len -= 2;
-        if (len > 0) { x = p; prev = pp; }
+        if (len > 0) { x = px; prev = pprev; }
     }
 #undef SIZE_OF
-    if (leader) { ctl->scans = scans; ctl->fused = fused; ctl->hits = hits; }
+    if (leader) { ctl->repairs = repairs; ctl->hits = hits; ctl->barriers = step + 1; }
 }
 
 template <typename T, typename S>
@@ -706,6 +777,7 @@ static int run_nn_chain(rthc_ctx *ctx, const S *d_cond, int method, std::vector<
                         std::vector<int32_t> &ey, std::vector<double> &ew)
 {
     const int64_t n = ctx->n, m = n - 1;
+    const int64_t per16 = 16 / (int64_t)sizeof(T), pitch = (n + per16 - 1) / per16 * per16;
     T *d_W = nullptr;
     int32_t *d_size = nullptr, *d_chain = nullptr, *d_ex = nullptr, *d_ey = nullptr;
     double *d_ew = nullptr;
@@ -713,29 +785,30 @@ static int run_nn_chain(rthc_ctx *ctx, const S *d_cond, int method, std::vector<
     ChainCtl *d_ctl = nullptr;
     int nblocks = ctx->sm_count;
     int rc;
-    if ((rc = rthc_dev_alloc(ctx, &d_W, (size_t)(n * n)))) return rc;
+    const size_t smem = sizeof(uint32_t) * (size_t)((pitch + 31) / 32 + 1);
+    if (smem > 160u * 1024u) return rthc_fail(ctx, RTHC_E_RANGE, "merge loop: %lld samples exceed the liveness bitmap", (long long)n);
+    if ((rc = rthc_dev_alloc(ctx, &d_W, (size_t)(n * pitch)))) return rc;
     if ((rc = rthc_dev_alloc(ctx, &d_size, (size_t)n))) return rc;
     if ((rc = rthc_dev_alloc(ctx, &d_chain, (size_t)n * (size_t)nblocks))) return rc;
-    if ((rc = rthc_dev_alloc(ctx, &d_slots, (size_t)6 * nblocks))) return rc;
+    if ((rc = rthc_dev_alloc(ctx, &d_slots, (size_t)2 * nblocks))) return rc;
     if ((rc = rthc_dev_alloc(ctx, &d_nn, (size_t)2 * (size_t)n))) return rc;
     if ((rc = rthc_dev_alloc(ctx, &d_ex, (size_t)m))) return rc;
     if ((rc = rthc_dev_alloc(ctx, &d_ey, (size_t)m))) return rc;
     if ((rc = rthc_dev_alloc(ctx, &d_ew, (size_t)m))) return rc;
     if ((rc = rthc_dev_alloc(ctx, &d_ctl, 1))) return rc;
     {
-        dim3 grd((unsigned)n, (unsigned)((n + 255) / 256));
-        rthc_expand_square<T, S><<<grd, 256, 0, ctx->stream>>>(d_cond, n, d_W);
-        RTHC_LAUNCH_CHECK(ctx);
-        rthc_nn_init<T><<<(unsigned)n, SEQ_THREADS, 0, ctx->stream>>>(d_W, n, d_nn);
+        dim3 grd((unsigned)n, (unsigned)((pitch + 255) / 256));
+        rthc_expand_square<T, S><<<grd, 256, 0, ctx->stream>>>(d_cond, n, pitch, d_W);
         RTHC_LAUNCH_CHECK(ctx);
         std::vector<int32_t> ones((size_t)n, 1);
         RTHC_CUDA(ctx, cudaMemcpyAsync(d_size, ones.data(), sizeof(int32_t) * (size_t)n, cudaMemcpyHostToDevice, ctx->stream));
         RTHC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     }
-    int64_t nn = n;
-    void *args[] = {(void *)&d_W, (void *)&nn, (void *)&method, (void *)&d_size, (void *)&d_chain, (void *)&d_slots,
+    int64_t nn = n, pp = pitch;
+    void *args[] = {(void *)&d_W, (void *)&nn, (void *)&pp, (void *)&method, (void *)&d_size, (void *)&d_chain, (void *)&d_slots,
                     (void *)&d_nn, (void *)&d_ex, (void *)&d_ey, (void *)&d_ew, (void *)&d_ctl};
-    RTHC_CUDA(ctx, cudaLaunchCooperativeKernel((void *)rthc_nn_chain_kernel<T>, dim3(nblocks), dim3(SEQ_THREADS), args, 0,
+    RTHC_CUDA(ctx, cudaFuncSetAttribute(rthc_nn_chain_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    RTHC_CUDA(ctx, cudaLaunchCooperativeKernel((void *)rthc_nn_chain_kernel<T>, dim3(nblocks), dim3(SEQ_THREADS), args, smem,
                                                ctx->stream));
     ctx->launches++;
     ex.resize((size_t)m); ey.resize((size_t)m); ew.resize((size_t)m);
@@ -745,8 +818,8 @@ static int run_nn_chain(rthc_ctx *ctx, const S *d_cond, int method, std::vector<
     RTHC_CUDA(ctx, cudaMemcpyAsync(ew.data(), d_ew, sizeof(double) * (size_t)m, cudaMemcpyDeviceToHost, ctx->stream));
     RTHC_CUDA(ctx, cudaMemcpyAsync(&ctl, d_ctl, sizeof(ChainCtl), cudaMemcpyDeviceToHost, ctx->stream));
     RTHC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-    ctx->row_scans = ctl.scans + ctl.fused;
-    ctx->chain_full_scans = ctl.scans;
+    ctx->row_scans = ctl.repairs + n;               // CTA-local rescans + the initial scan of every row
+    ctx->chain_full_scans = ctl.barriers;           // grid barriers (info[9])
     ctx->chain_cache_hits = ctl.hits;
     rthc_dev_free(ctx, &d_W); rthc_dev_free(ctx, &d_size); rthc_dev_free(ctx, &d_chain); rthc_dev_free(ctx, &d_slots);
     rthc_dev_free(ctx, &d_nn); rthc_dev_free(ctx, &d_ex); rthc_dev_free(ctx, &d_ey); rthc_dev_free(ctx, &d_ew);

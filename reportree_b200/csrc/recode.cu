@@ -23,20 +23,132 @@
 #define BITMAP_BITS (1u << 20)
 #define BITMAP_WORDS (BITMAP_BITS / 32)
 
-// ---- 1. transpose n x L (row-major int32) -> L x n_pad ------------------------------
-__global__ void rthc_transpose_i32(const int32_t *__restrict__ in, int32_t *__restrict__ out,
+// ---- 1. transpose n x L (row-major int32 / uint16) -> L x n_pad int32 (general path only) ----
+template <typename IT>
+__global__ void rthc_transpose_i32(const IT *__restrict__ in, int32_t *__restrict__ out,
                                    int64_t n, int64_t L, int64_t n_pad)
 {
     __shared__ int32_t tile[32][33];
     int64_t l0 = (int64_t)blockIdx.x * 32, s0 = (int64_t)blockIdx.y * 32;
     for (int r = threadIdx.y; r < 32; r += blockDim.y) {
         int64_t s = s0 + r, l = l0 + threadIdx.x;
-        tile[r][threadIdx.x] = (s < n && l < L) ? in[s * L + l] : 0;
+        tile[r][threadIdx.x] = (s < n && l < L) ? (int32_t)in[s * L + l] : 0;
     }
     __syncthreads();
     for (int r = threadIdx.y; r < 32; r += blockDim.y) {
         int64_t l = l0 + r, s = s0 + threadIdx.x;
         if (l < L && s < n_pad) out[l * n_pad + s] = tile[threadIdx.x][r];
+    }
+}
+
+// ---- 1'. fast path: 32 consecutive loci per CTA, straight from the row-major input ------------------
+// Real cg/wgMLST allele ids are small integers, so the common case needs neither the transposed int32 copy nor
+// the 2^20-bit bitmap: a CTA owns 32 neighbouring loci, a warp reads one 128-byte (int32) or 64-byte (uint16)
+// row segment per load (lane = locus), marks the ids in 32 shared-memory bitmaps of 2^14 bits, ranks them by
+// popcount prefix, re-reads its columns and writes the uint16 codes transposed ([locus][sample], 128-byte runs)
+// through a shared tile.  2 reads of the input + 1 write of the codes instead of transpose (read + write) +
+// 2 reads.  Any id >= 2^14 in the matrix sets status bit 1 and the driver repeats with the general path below.
+#define R32_BITS 16384
+#define R32_WORDS (R32_BITS / 32)
+#define R32_STRIDE (R32_WORDS + 1)       // lane * stride + word: lanes marking the same id hit 32 different banks
+#define R32_CHUNK 512                    // samples per transposed tile
+#define R32_TSTRIDE (R32_CHUNK + 2)      // uint16 row stride of the tile: 257 words, conflict-free both ways
+#define R32_SMEM (32 * R32_STRIDE * 4 + 32 * R32_STRIDE * 2 + 32 * R32_TSTRIDE * 2)
+template <typename IT>
+__global__ void __launch_bounds__(RANK_THREADS, 1)
+rthc_rank32(const IT *__restrict__ in, int64_t n, int64_t L, int64_t n_pad, uint16_t *__restrict__ codes,
+            int32_t *__restrict__ n_alleles, int32_t *__restrict__ status)
+{
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    uint32_t *bm = reinterpret_cast<uint32_t *>(smem_raw);
+    uint16_t *pre = reinterpret_cast<uint16_t *>(bm + 32 * R32_STRIDE);
+    uint16_t *tile = pre + 32 * R32_STRIDE;
+    __shared__ uint32_t s_tot[32];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int64_t l0 = (int64_t)blockIdx.x * 32, l = l0 + lane;
+    const bool lv = l < L;
+    for (int w = tid; w < 32 * R32_STRIDE; w += RANK_THREADS) bm[w] = 0;
+    __syncthreads();
+    // ---- mark: 16 row segments in flight per warp; a bit that is already set is not set again --------
+    bool big = false;
+    const volatile uint32_t *vbm = bm;
+    uint32_t *mybm = bm + lane * R32_STRIDE;
+    for (int64_t s0 = warp; s0 < n; s0 += 32 * 16) {
+        int32_t v[16];
+#pragma unroll
+        for (int u = 0; u < 16; ++u) {
+            const int64_t r = s0 + 32 * u;
+            v[u] = (lv && r < n) ? (int32_t)__ldg(in + r * L + l) : 0;
+        }
+#pragma unroll
+        for (int u = 0; u < 16; ++u) {
+            if (v[u] > 0) {
+                if (v[u] >= R32_BITS) big = true;
+                else {
+                    const uint32_t bit = 1u << (v[u] & 31);
+                    if (!(vbm[lane * R32_STRIDE + (v[u] >> 5)] & bit)) atomicOr(&mybm[v[u] >> 5], bit);
+                }
+            }
+        }
+    }
+    if (__syncthreads_or(big)) {                   // the whole matrix goes through the general path
+        if (tid == 0) atomicOr(status, 1);
+        return;
+    }
+    // ---- rank tables: warp w scans the bitmap of locus l0 + w (conflict-free rows of 32 words) ---------
+    {
+        uint32_t running = 0;
+        const uint32_t *b = bm + warp * R32_STRIDE;
+        uint16_t *p = pre + warp * R32_STRIDE;
+        for (int k = 0; k < R32_WORDS / 32; ++k) {
+            const int idx = k * 32 + lane;
+            const uint32_t c = __popc(b[idx]);
+            uint32_t inc = c;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const uint32_t t = __shfl_up_sync(0xffffffffu, inc, d);
+                if (lane >= d) inc += t;
+            }
+            p[idx] = (uint16_t)(running + inc - c);
+            running += __shfl_sync(0xffffffffu, inc, 31);
+        }
+        if (lane == 0) {
+            s_tot[warp] = running;
+            if (l0 + warp < L) n_alleles[l0 + warp] = (int32_t)running;
+        }
+    }
+    __syncthreads();
+    // ---- code + transposed write, 512 samples per tile (16 row segments in flight per warp) ------------
+    const uint16_t *mypre = pre + lane * R32_STRIDE;
+    for (int64_t c0 = 0; c0 < n_pad; c0 += R32_CHUNK) {
+        int32_t v[16];
+#pragma unroll
+        for (int u = 0; u < 16; ++u) {
+            const int64_t r = c0 + warp + 32 * u;
+            v[u] = (lv && r < n) ? (int32_t)__ldg(in + r * L + l) : 0;
+        }
+#pragma unroll
+        for (int u = 0; u < 16; ++u) {
+            uint16_t code = 0;
+            if (v[u] > 0) {
+                const uint32_t w = (uint32_t)v[u] >> 5;
+                code = (uint16_t)(1u + mypre[w] + __popc(mybm[w] & ((1u << (v[u] & 31)) - 1u)));
+                RTHC_DEV_ASSERT((mybm[w] >> (v[u] & 31)) & 1u);              // the id was marked in pass 1
+                RTHC_DEV_ASSERT(code >= 1 && code <= s_tot[lane]);
+            }
+            tile[lane * R32_TSTRIDE + warp + 32 * u] = code;
+        }
+        __syncthreads();
+        if (l0 + warp < L) {                       // warp w writes locus row l0 + w: 2 samples per lane and store
+            const uint32_t *trow = reinterpret_cast<const uint32_t *>(tile + warp * R32_TSTRIDE);
+            uint32_t *dst = reinterpret_cast<uint32_t *>(codes + (l0 + warp) * n_pad + c0);
+#pragma unroll
+            for (int k = 0; k < R32_CHUNK / 64; ++k) {
+                const int64_t sidx = c0 + 64 * k + 2 * lane;
+                if (sidx < n_pad) dst[32 * k + lane] = trow[32 * k + lane];
+            }
+        }
+        __syncthreads();
     }
 }
 
@@ -337,22 +449,37 @@ static inline int bit_width(int a)   // codes 1..a need this many bits
     return b;
 }
 
-int rthc_recode_and_pack(rthc_ctx *ctx, const int32_t *d_rowmajor)
+template <typename IT>
+static int rank_fast(rthc_ctx *ctx, const IT *d_rowmajor, int32_t *d_nall, int32_t *d_status, std::vector<int32_t> &nall,
+                     int32_t &status)
 {
     const int64_t n = ctx->n, L = ctx->L, n_pad = ctx->n_pad;
-    int32_t *d_colmajor = nullptr, *d_nall = nullptr, *d_status = nullptr, *d_perm = nullptr;
+    RTHC_CUDA(ctx, cudaMemsetAsync(d_status, 0, sizeof(int32_t), ctx->stream));
+    RTHC_CUDA(ctx, cudaFuncSetAttribute(rthc_rank32<IT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)R32_SMEM));
+    rthc_rank32<IT><<<(unsigned)((L + 31) / 32), RANK_THREADS, R32_SMEM, ctx->stream>>>(d_rowmajor, n, L, n_pad, ctx->d_codes,
+                                                                                     d_nall, d_status);
+    RTHC_LAUNCH_CHECK(ctx);
+    RTHC_CUDA(ctx, cudaMemcpyAsync(&status, d_status, sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->stream));
+    RTHC_CUDA(ctx, cudaMemcpyAsync(nall.data(), d_nall, sizeof(int32_t) * (size_t)L, cudaMemcpyDeviceToHost, ctx->stream));
+    RTHC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+
+// general path: transposed int32 copy, 2^20-bit bitmap per locus, HBM bitmap for ids >= 2^20, uint32 codes when a
+// locus has more than 65,535 alleles
+template <typename IT>
+static int rank_general(rthc_ctx *ctx, const IT *d_rowmajor, int32_t *d_nall, int32_t *d_status, std::vector<int32_t> &nall,
+                        int32_t &status)
+{
+    const int64_t n = ctx->n, L = ctx->L, n_pad = ctx->n_pad;
+    int32_t *d_colmajor = nullptr;
     int rc;
     if ((rc = rthc_dev_alloc(ctx, &d_colmajor, (size_t)(L * n_pad)))) return rc;
-    if ((rc = rthc_dev_alloc(ctx, &d_nall, (size_t)L))) return rc;
-    if ((rc = rthc_dev_alloc(ctx, &d_status, 1))) return rc;
-    if ((rc = rthc_dev_alloc(ctx, &ctx->d_codes, (size_t)(L * n_pad)))) return rc;
     {
         dim3 blk(32, 8), grd((unsigned)((L + 31) / 32), (unsigned)((n_pad + 31) / 32));
-        rthc_transpose_i32<<<grd, blk, 0, ctx->stream>>>(d_rowmajor, d_colmajor, n, L, n_pad);
+        rthc_transpose_i32<IT><<<grd, blk, 0, ctx->stream>>>(d_rowmajor, d_colmajor, n, L, n_pad);
         RTHC_LAUNCH_CHECK(ctx);
     }
-    std::vector<int32_t> nall((size_t)L);
-    int32_t status = 0;
     if ((rc = rank_all<uint16_t>(ctx, d_colmajor, ctx->d_codes, d_nall, d_status, nall, status))) return rc;
     if (status & 2) {
         // a locus with more than 65,535 distinct called alleles (needs n > 65,535): the codes of this matrix are
@@ -362,6 +489,29 @@ int rthc_recode_and_pack(rthc_ctx *ctx, const int32_t *d_rowmajor)
         if ((rc = rank_all<uint32_t>(ctx, d_colmajor, ctx->d_codes32, d_nall, d_status, nall, status))) return rc;
     }
     rthc_dev_free(ctx, &d_colmajor);
+    return 0;
+}
+
+// in_u16: the caller's matrix is uint16 (0 = missing) instead of int32 (<= 0 = missing)
+int rthc_recode_and_pack(rthc_ctx *ctx, const void *d_rowmajor, bool in_u16)
+{
+    const int64_t L = ctx->L, n_pad = ctx->n_pad;
+    int32_t *d_nall = nullptr, *d_status = nullptr, *d_perm = nullptr;
+    int rc;
+    if ((rc = rthc_dev_alloc(ctx, &d_nall, (size_t)L))) return rc;
+    if ((rc = rthc_dev_alloc(ctx, &d_status, 1))) return rc;
+    if ((rc = rthc_dev_alloc(ctx, &ctx->d_codes, (size_t)(L * n_pad)))) return rc;
+    std::vector<int32_t> nall((size_t)L);
+    int32_t status = 0;
+    rc = in_u16 ? rank_fast<uint16_t>(ctx, (const uint16_t *)d_rowmajor, d_nall, d_status, nall, status)
+                : rank_fast<int32_t>(ctx, (const int32_t *)d_rowmajor, d_nall, d_status, nall, status);
+    if (rc) return rc;
+    ctx->recode_general = (status & 1) != 0;
+    if (status & 1) {
+        rc = in_u16 ? rank_general<uint16_t>(ctx, (const uint16_t *)d_rowmajor, d_nall, d_status, nall, status)
+                    : rank_general<int32_t>(ctx, (const int32_t *)d_rowmajor, d_nall, d_status, nall, status);
+        if (rc) return rc;
+    }
 
     // order loci by bit width (widest first), drop loci that cannot mismatch
     std::vector<int32_t> kept;

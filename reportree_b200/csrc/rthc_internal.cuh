@@ -45,6 +45,7 @@ struct rthc_ctx {
 
     // device buffers (distance half)
     uint16_t *d_codes = nullptr;   // [L][n_pad] dense-ranked codes, column-major per locus
+    bool recode_general = false;   // last re-code left the fast path (an allele id >= 2^14 somewhere)
     uint32_t *d_codes32 = nullptr; // same, used INSTEAD of d_codes when a locus has more than 65,535 called alleles
     uint32_t *d_planes = nullptr;  // [plane_rows][n_pad]
     int32_t *d_grp_off = nullptr;  // [G]
@@ -89,6 +90,24 @@ struct rthc_ctx {
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     cudaEvent_t ev_mark[2] = {nullptr, nullptr};   // rthc_mark(): caller-placed events on the library stream
 };
+
+// Checked build (python -m reportree_b200.build --checked -> build/lib_checked.so, used by scripts/gpu_checked.sh):
+// device-side invariants compiled in; a violation prints its location and traps, which the host sees as a CUDA
+// error.  compute-sanitizer is not available on the GPU pool, so these asserts + parity against scipy on small and
+// ragged shapes are the memory / ordering evidence.
+#ifdef RTHC_CHECKED
+#include <cstdio>
+#define RTHC_DEV_ASSERT(cond)                                                                              \
+    do {                                                                                                   \
+        if (!(cond)) {                                                                                     \
+            printf("RTHC_DEV_ASSERT failed %s:%d: %s (block %d, thread %d)\n", __FILE__, __LINE__, #cond,   \
+                   (int)blockIdx.x, (int)threadIdx.x);                                                     \
+            __trap();                                                                                      \
+        }                                                                                                  \
+    } while (0)
+#else
+#define RTHC_DEV_ASSERT(cond) ((void)0)
+#endif
 
 extern std::string g_rthc_create_err;
 
@@ -142,7 +161,7 @@ void rthc_free_linkage_state(rthc_ctx *ctx);
 int rthc_setup_geometry(rthc_ctx *ctx, int64_t n);
 
 // stage entry points implemented in the other translation units
-int rthc_recode_and_pack(rthc_ctx *ctx, const int32_t *d_rowmajor);   // recode.cu
+int rthc_recode_and_pack(rthc_ctx *ctx, const void *d_rowmajor, bool in_u16);   // recode.cu
 int rthc_run_distance(rthc_ctx *ctx);                                 // distance.cu
 int rthc_launch_distance_ws(rthc_ctx *ctx, int max_np);                // distance_ws.cu
 int rthc_run_direct_pairs(rthc_ctx *ctx, const int32_t *d_pi, const int32_t *d_pj, int64_t np,

@@ -50,6 +50,8 @@ def load_library():
         "rthc_finish_import": (ci, [vp]),
         "rthc_set_profiles_i32": (ci, [vp, vp, i64, i64]),
         "rthc_set_profiles_i32_device": (ci, [vp, vp, i64, i64]),
+        "rthc_set_profiles_u16": (ci, [vp, vp, i64, i64]),
+        "rthc_set_profiles_u16_device": (ci, [vp, vp, i64, i64]),
         "rthc_distance": (ci, [vp]),
         "rthc_owned_pairs": (i64, [vp]),
         "rthc_get_condensed_u16": (ci, [vp, vp]),
@@ -87,7 +89,8 @@ def load_library():
 EXPORTED_SYMBOLS = [
     "rthc_create", "rthc_prewarm", "rthc_destroy", "rthc_last_error", "rthc_version", "rthc_set_shard",
     "rthc_set_shard_full_storage", "rthc_import_shard", "rthc_finish_import",
-    "rthc_set_profiles_i32", "rthc_set_profiles_i32_device", "rthc_distance", "rthc_owned_pairs",
+    "rthc_set_profiles_i32", "rthc_set_profiles_i32_device", "rthc_set_profiles_u16", "rthc_set_profiles_u16_device",
+    "rthc_distance", "rthc_owned_pairs",
     "rthc_get_condensed_u16", "rthc_get_owned_condensed_u16", "rthc_get_condensed_range_u16", "rthc_copy_rows_u16", "rthc_direct_pairs",
     "rthc_set_condensed_f64", "rthc_set_single_algo", "rthc_linkage", "rthc_local_forest",
     "rthc_linkage_from_forest", "rthc_local_forest_device", "rthc_linkage_from_forest_device", "rthc_cut", "rthc_info", "rthc_timings", "rthc_mark", "rthc_mark_elapsed_ms", "rthc_alu_peak",
@@ -142,16 +145,24 @@ class HCContext:
 
     # ---- distance half ---------------------------------------------------------------
     def set_profiles(self, codes):
-        """codes: n x L integer allele codes (0 = missing), host numpy array."""
-        codes = np.ascontiguousarray(codes, dtype=np.int32)
+        """codes: n x L integer allele codes (0 = missing), host numpy array.  A uint16 array is sent as it
+        is (half the host-to-device bytes); every other dtype goes through int32."""
+        codes = np.asarray(codes)
         if codes.ndim != 2:
             raise HCBackendError("allele code matrix must be 2-D")
         self.n, self.L = codes.shape
-        self._check(self._L.rthc_set_profiles_i32(self._h, _ptr(codes), self.n, self.L))
+        if codes.dtype == np.uint16:
+            codes = np.ascontiguousarray(codes)
+            self._check(self._L.rthc_set_profiles_u16(self._h, _ptr(codes), self.n, self.L))
+        else:
+            codes = np.ascontiguousarray(codes, dtype=np.int32)
+            self._check(self._L.rthc_set_profiles_i32(self._h, _ptr(codes), self.n, self.L))
 
-    def set_profiles_device(self, dev_ptr, n, L):
+    def set_profiles_device(self, dev_ptr, n, L, dtype=np.int32):
+        """The matrix is already in device memory (row-major int32, or uint16 with dtype=np.uint16)."""
         self.n, self.L = int(n), int(L)
-        self._check(self._L.rthc_set_profiles_i32_device(self._h, ctypes.c_void_p(int(dev_ptr)), self.n, self.L))
+        fn = self._L.rthc_set_profiles_u16_device if np.dtype(dtype) == np.uint16 else self._L.rthc_set_profiles_i32_device
+        self._check(fn(self._h, ctypes.c_void_p(int(dev_ptr)), self.n, self.L))
 
     def distance(self):
         self._check(self._L.rthc_distance(self._h))

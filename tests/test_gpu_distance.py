@@ -128,6 +128,32 @@ def test_more_than_65535_alleles_in_a_locus_take_the_uint32_codes(hc, oracle):
     assert Z.shape == (n - 1, 4) and Z[-1, 3] == n
 
 
+@pytest.mark.parametrize("n,L", [(5, 1), (130, 33), (700, 95), (1500, 260)])
+def test_uint16_input_and_both_recoder_paths_agree(hc, oracle, n, L):
+    """The re-coder has a fast path (ids < 2^14: 32 loci per CTA straight from the row-major input) and a general
+    one (transposed copy, 2^20-bit bitmaps); the input may be int32 or uint16.  Dense ranking is equality-preserving,
+    so the four combinations must give the oracle's distances on the same matrix (ids scaled by 40 leave the
+    fast path but still fit uint16)."""
+    rng = np.random.default_rng(n * 31 + L)
+    X = rng.integers(0, 1500, size=(n, L)).astype(np.int32)
+    X[rng.random((n, L)) < 0.05] = 0
+    X[:, 0] = rng.integers(1, 3, n)
+    ref = oracle.dist_condensed(X)
+    for scale in (1, 40):
+        for dtype in (np.int32, np.uint16):
+            with hc.HCContext() as ctx:
+                ctx.set_profiles((X * scale).astype(dtype))
+                ctx.distance()
+                assert np.array_equal(ctx.condensed(), ref), (scale, dtype)
+    # negative int32 ids are missing on both paths
+    Y = X.copy()
+    Y[X == 0] = -7
+    with hc.HCContext() as ctx:
+        ctx.set_profiles(Y)
+        ctx.distance()
+        assert np.array_equal(ctx.condensed(), ref)
+
+
 def test_wide_snp_matrix_and_the_informative_loci_limit(hc, oracle):
     # SNP matrices (conv_nucl, scripts/partitioning_HC.py:28-47) can have far more than 65,535 columns; only
     # the columns with >= 2 called alleles can mismatch, and only their number is bounded by uint16 distances
