@@ -139,6 +139,9 @@ extern "C" void rthc_destroy(rthc_ctx *ctx)
     for (int k = 0; k < 2; ++k)
         if (ctx->ev_mark[k]) cudaEventDestroy(ctx->ev_mark[k]);
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+    if (ctx->copy_stream) { cudaStreamSynchronize(ctx->copy_stream); cudaStreamDestroy(ctx->copy_stream); }
+    for (int k = 0; k < 4; ++k)
+        if (ctx->ev_piece[k]) cudaEventDestroy(ctx->ev_piece[k]);
     if (ctx->pool) cudaMemPoolDestroy(ctx->pool);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;

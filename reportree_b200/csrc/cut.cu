@@ -190,21 +190,36 @@ int rthc_run_cut(rthc_ctx *ctx, const double *t, int T, int32_t *labels_out)
     if ((rc = rthc_dev_alloc(ctx, &d_aux, (size_t)(chunkT * nbs)))) return rc;
     RTHC_CUDA(ctx, cudaMemcpyAsync(d_limit, limit.data(), sizeof(int32_t) * (size_t)T, cudaMemcpyHostToDevice, ctx->stream));
     const unsigned nb = (unsigned)((n + 255) / 256);
+    if (!ctx->copy_stream) {
+        RTHC_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
+        for (int k = 0; k < 4; ++k) RTHC_CUDA(ctx, cudaEventCreateWithFlags(&ctx->ev_piece[k], cudaEventDisableTiming));
+    }
     for (int64_t q0 = 0; q0 < T; q0 += chunkT) {
         const int64_t tc = std::min<int64_t>(chunkT, T - q0);
+        // a chunk is cut in up to 4 pieces of thresholds: the labels of piece p travel to the host (copy stream) while
+        // the kernels of piece p + 1 run; small results stay in one piece (a launch set costs more than it hides)
+        const int np = (tc * n * 4 >= (4ll << 20)) ? (int)std::min<int64_t>(4, tc) : 1;
         RTHC_CUDA(ctx, cudaMemsetAsync(d_flags, 0, sizeof(int32_t) * (size_t)(tc * flag_stride), ctx->stream));
-        rthc_cut_leaders<<<dim3(nb, (unsigned)tc), 256, 0, ctx->stream>>>(ctx->d_up, ctx->up_levels, nodes, n, d_limit + q0,
-                                                                          ctx->d_event, d_key, d_flags, flag_stride);
-        RTHC_LAUNCH_CHECK(ctx);
-        rthc_cut_scan_blocks<<<dim3((unsigned)nbs, (unsigned)tc), 1024, 0, ctx->stream>>>(d_flags, nodes, flag_stride, d_aux, nbs);
-        RTHC_LAUNCH_CHECK(ctx);
-        rthc_cut_scan_aux<<<(unsigned)tc, 1024, 0, ctx->stream>>>(d_aux, nbs);
-        RTHC_LAUNCH_CHECK(ctx);
-        rthc_cut_labels<<<dim3(nb, (unsigned)tc), 256, 0, ctx->stream>>>(d_key, d_flags, flag_stride, d_aux, nbs, d_labels, n);
-        RTHC_LAUNCH_CHECK(ctx);
-        if (q0 + tc >= T) RTHC_CUDA(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
-        RTHC_CUDA(ctx, cudaMemcpyAsync(labels_out + q0 * n, d_labels, sizeof(int32_t) * (size_t)(tc * n), cudaMemcpyDeviceToHost,
-                                       ctx->stream));
+        for (int p = 0; p < np; ++p) {
+            const int64_t p0 = tc * p / np, p1 = tc * (p + 1) / np, pc = p1 - p0;
+            if (pc == 0) continue;
+            int32_t *key = d_key + p0 * n, *flags = d_flags + p0 * flag_stride, *aux = d_aux + p0 * nbs, *lab = d_labels + p0 * n;
+            rthc_cut_leaders<<<dim3(nb, (unsigned)pc), 256, 0, ctx->stream>>>(ctx->d_up, ctx->up_levels, nodes, n, d_limit + q0 + p0,
+                                                                              ctx->d_event, key, flags, flag_stride);
+            RTHC_LAUNCH_CHECK(ctx);
+            rthc_cut_scan_blocks<<<dim3((unsigned)nbs, (unsigned)pc), 1024, 0, ctx->stream>>>(flags, nodes, flag_stride, aux, nbs);
+            RTHC_LAUNCH_CHECK(ctx);
+            rthc_cut_scan_aux<<<(unsigned)pc, 1024, 0, ctx->stream>>>(aux, nbs);
+            RTHC_LAUNCH_CHECK(ctx);
+            rthc_cut_labels<<<dim3(nb, (unsigned)pc), 256, 0, ctx->stream>>>(key, flags, flag_stride, aux, nbs, lab, n);
+            RTHC_LAUNCH_CHECK(ctx);
+            if (q0 + tc >= T && p == np - 1) RTHC_CUDA(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
+            RTHC_CUDA(ctx, cudaEventRecord(ctx->ev_piece[p], ctx->stream));
+            RTHC_CUDA(ctx, cudaStreamWaitEvent(ctx->copy_stream, ctx->ev_piece[p], 0));
+            RTHC_CUDA(ctx, cudaMemcpyAsync(labels_out + (q0 + p0) * n, lab, sizeof(int32_t) * (size_t)(pc * n), cudaMemcpyDeviceToHost,
+                                           ctx->copy_stream));
+        }
+        RTHC_CUDA(ctx, cudaStreamSynchronize(ctx->copy_stream));      // the device buffers are reused by the next chunk
         RTHC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     }
     float ms = 0;

@@ -26,6 +26,8 @@ __host__ __device__ inline uint32_t rthc_key_j(uint64_t k) { return (uint32_t)(k
 struct rthc_ctx {
     int device = 0;
     cudaStream_t stream = nullptr;
+    cudaStream_t copy_stream = nullptr;            // label download of one threshold piece under the kernels of the next (cut.cu)
+    cudaEvent_t ev_piece[4] = {nullptr, nullptr, nullptr, nullptr};
     cudaMemPool_t pool = nullptr;   // stream-ordered allocation pool of this context
     std::string err;
     int sm_count = 148;

@@ -3,6 +3,7 @@ usage: python scripts/ncu_summary.py gpurun_out/prof.ncu-rep > profiles/rNN_name
 import csv, subprocess, sys, io
 
 rep = sys.argv[1]
+json_out = sys.argv[sys.argv.index("--json") + 1] if "--json" in sys.argv else None      # {kernel, ms, dram bytes} of the first kernel
 raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
 rows = list(csv.reader(io.StringIO(raw)))
 hdr, units = rows[0], rows[1]
@@ -17,6 +18,17 @@ KEYS = ["gpu__time_duration.sum", "launch__registers_per_thread", "launch__grid_
 for r in rows[2:]:
     d = dict(zip(hdr, r))
     print("== kernel:", d.get("Kernel Name", "?")[:100])
+    if json_out:
+        import json
+
+        def num(key, scale):
+            unit = units[hdr.index(key)]
+            mult = {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "ns": 1e-6, "us": 1e-3, "ms": 1.0, "s": 1e3}.get(unit, scale)
+            return float(d[key].replace(",", "")) * mult
+        json.dump({"kernel": d.get("Kernel Name", "?")[:60], "capture": rep.split("/")[-1], "kernel_ms": num("gpu__time_duration.sum", 1e-6),
+                   "dram_bytes_read": num("dram__bytes_read.sum", 1), "dram_bytes_write": num("dram__bytes_write.sum", 1),
+                   "how": "ncu --set full --clock-control none, one launch; read with ncu -i --page raw --csv"}, open(json_out, "w"), indent=1)
+        json_out = None
     for k in KEYS:
         if k in d:
             print("  %-72s %s %s" % (k, d[k], units[hdr.index(k)]))
