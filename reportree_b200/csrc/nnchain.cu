@@ -659,13 +659,16 @@ rthc_nn_chain_kernel(T *W, int64_t n, int64_t pitch, int method, int32_t *size, 
             x = (int32_t)first_live; prev = -1; len = 1;
         }
         // ---- nearest neighbour of the tip x: a look-up ----------------------------------------------
-        if (tid == 0) {
+        // five scalars, five lanes: the loads are in flight together (one thread would issue them in order,
+        // each waiting for the shared-memory store of the one before: five L2 / DRAM latencies per chain step)
+        if (tid < 5) {
             ChainBc &o = bc[q];
-            if (x == grown) { o.cw = gw; o.ci = gi; }
-            else { o.cw = __ldcg(&nn[x].w); o.ci = __ldcg(&nn[x].i); }
-            o.dprev = len > 1 ? order_bits(__ldcg(&W[(int64_t)x * pitch + prev])) : ~0ull;
-            o.sx = SIZE_OF(x);
-            o.sprev = len > 1 ? SIZE_OF(prev) : 0;
+            const int32_t pv = len > 1 ? prev : x;
+            if (tid == 0) o.cw = x == grown ? gw : __ldcg(&nn[x].w);
+            else if (tid == 1) o.ci = x == grown ? gi : __ldcg(&nn[x].i);
+            else if (tid == 2) o.dprev = len > 1 ? order_bits(__ldcg(&W[(int64_t)x * pitch + pv])) : ~0ull;
+            else if (tid == 3) o.sx = SIZE_OF(x);
+            else o.sprev = len > 1 ? SIZE_OF(pv) : 0;
         }
         __syncthreads();
         const unsigned long long cw = bc[q].cw, dprev = bc[q].dprev;
@@ -705,14 +708,17 @@ rthc_nn_chain_kernel(T *W, int64_t n, int64_t pitch, int method, int32_t *size, 
         for (int64_t i0 = (int64_t)blockIdx.x * SEQ_THREADS; i0 < n; i0 += gthreads) {
             const int64_t i = i0 + tid;
             if (i < n && i != b && ((s_live[i >> 5] >> (i & 31)) & 1u)) {
-                const int32_t ni = SIZE_OF(i);
-                const T v = lance_williams<T>(method, __ldcg(&ra[i]), __ldcg(&rb[i]), dab, na, nb, ni);
+                // every load of the element first (the stores below may alias them as far as the compiler knows)
+                const T da = __ldcg(&ra[i]), db = __ldcg(&rb[i]);
+                unsigned long long ow = __ldcg(&nn[i].w);
+                unsigned int oi = __ldcg(&nn[i].i);
+                const int32_t szi = __ldcg(&size[i]);
+                const int32_t ni = i == grown ? grown_size : szi;
+                const T v = lance_williams<T>(method, da, db, dab, na, nb, ni);
                 rb[i] = v;                       // row b (contiguous)
                 W[i * pitch + b] = v;            // column b (symmetric copy)
                 const unsigned long long ob = order_bits(v);
                 if (slot_less(ob, (unsigned int)i, bwb, bib)) { bwb = ob; bib = (unsigned int)i; }
-                unsigned long long ow = __ldcg(&nn[i].w);
-                unsigned int oi = __ldcg(&nn[i].i);
                 if (oi == (unsigned int)a || oi == (unsigned int)b) {
                     const int slot = atomicAdd(&s_nbad, 1);
                     RTHC_DEV_ASSERT(slot >= 0 && slot < SEQ_THREADS);
@@ -749,10 +755,17 @@ rthc_nn_chain_kernel(T *W, int64_t n, int64_t pitch, int method, int32_t *size, 
         // nn of the new row b: warp 0 combines the CTA minima; thread 0 adds the chain tip after the pop
         if (tid < 32) {
             unsigned long long w = ~0ull; unsigned int i = ~0u;
-            for (int c = lane; c < nblocks; c += 32) {
-                const unsigned long long cw2 = __ldcg(&sb[c].w);
-                const unsigned int ci2 = __ldcg(&sb[c].i);
-                if (slot_less(cw2, ci2, w, i)) { w = cw2; i = ci2; }
+            for (int c0 = 0; c0 < nblocks; c0 += 32 * 8) {       // <= 256 CTAs per trip, the loads of a trip in flight together
+                unsigned long long cw2[8]; unsigned int ci2[8];
+#pragma unroll
+                for (int u = 0; u < 8; ++u) {
+                    const int c = c0 + 32 * u + lane;
+                    cw2[u] = c < nblocks ? __ldcg(&sb[c].w) : ~0ull;
+                    ci2[u] = c < nblocks ? __ldcg(&sb[c].i) : ~0u;
+                }
+#pragma unroll
+                for (int u = 0; u < 8; ++u)
+                    if (slot_less(cw2[u], ci2[u], w, i)) { w = cw2[u]; i = ci2[u]; }
             }
             warp_min_all(w, i);
             if (lane == 0) { bc[q].gw = w; bc[q].gi = i; bc[q].x = nxt_x; bc[q].prev = nxt_prev; }
