@@ -569,18 +569,20 @@ __device__ __forceinline__ void cta_row_min(const T *row, int64_t n, const uint3
     block_min(bw, bi, sh);
 }
 
-struct ChainBc {                // scalar state read by thread 0 / warp 0 and broadcast through shared memory
-    unsigned long long cw, dprev, gw;
-    unsigned int ci, gi;
-    int32_t x, prev, sx, sprev;
+struct ChainBc {                // the merge decision of warp 0, broadcast through shared memory
+    unsigned long long dmin, gw;
+    unsigned int gi;
+    int32_t a, b, na, nb, grown, grown_size;
 };
 
 // The merge loop.  scipy's chain step asks for the nearest neighbour of the chain tip x: the previous chain
 // element if it ties the minimum, else the lowest index of the minimum of row x.  A grid-wide row scan costs a
 // grid barrier (2.4 us + the reductions around it) however short the row is, so the kernel keeps for EVERY live
 // row r the exact lexicographic minimum nn[r] = min over live i != r of (D[r, i], i), and a chain step is a
-// look-up (thread 0 of every CTA reads the same entry, broadcast through shared memory): no barrier.
-// Only a merge (a dies, b = a u b) has one, and the merge phase restores the invariant before it:
+// look-up: warp 0 of every CTA walks the chain by itself (three L2 loads in three lanes, no block barrier; the
+// distance to the previous element and the sizes of the chain elements ride along in the CTA's private chain
+// arrays) while the other warps wait for its merge decision.  Only a merge (a dies, b = a u b) has a grid barrier,
+// and the merge phase restores the invariant before it:
 //   * the thread that writes D[i, b] folds the new entry into the cache: nn[i] = min(nn[i], (D[i, b], b)) is exact
 //     because every other entry of row i is unchanged;
 //   * if the cached neighbour of row i was a or b, the CTA of that thread rescans row i by itself (a row is
@@ -589,27 +591,30 @@ struct ChainBc {                // scalar state read by thread 0 / warp 0 and br
 //   * the candidates (D[b, i], i) of the new row b are reduced per CTA and combined after the barrier.
 // The answer of a look-up is the same (value, lowest index, previous-wins) triple as scipy's scan, so Z stays
 // byte-identical.  nn[] is double-buffered by merge parity (a CTA still walking the chain must not see entries
-// that a faster CTA has already updated); every CTA keeps the liveness bitmap in shared memory and its own
-// copy of the chain (touched by its thread 0 only); size[] of the last merge is patched from registers until the
-// next barrier has published it; W is pitched so that every row starts on a 16-byte boundary.
+// that a faster CTA has already updated); every CTA keeps the liveness bitmap in shared memory; size[] and nn[]
+// of the cluster created by the last merge are carried in registers until the next barrier has published them;
+// W is pitched so that every row starts on a 16-byte boundary.
 template <typename T>
 __global__ void __launch_bounds__(SEQ_THREADS, 1)
-rthc_nn_chain_kernel(T *W, int64_t n, int64_t pitch, int method, int32_t *size, int32_t *chains, MinSlot *slots,
-                     MinSlot *nn2, int32_t *ex, int32_t *ey, double *ew, ChainCtl *ctl)
+rthc_nn_chain_kernel(T *W, int64_t n, int64_t pitch, int method, int32_t *size, int32_t *chains, unsigned long long *chains_d,
+                     int32_t *chains_s, MinSlot *slots, MinSlot *nn2, int32_t *ex, int32_t *ey, double *ew, ChainCtl *ctl)
 {
     cg::grid_group grid = cg::this_grid();
     extern __shared__ uint32_t s_live[];                         // bit j: cluster j is alive
     __shared__ MinSlot sh[SEQ_THREADS / 32];
-    __shared__ ChainBc bc[2];                                    // alternating: one __syncthreads per round
+    __shared__ ChainBc bc[2];                                    // alternating: one __syncthreads per merge
     __shared__ int32_t s_bad_i[SEQ_THREADS];                     // rows of this CTA whose cached neighbour was a or b
     __shared__ unsigned long long s_bad_w[SEQ_THREADS];          // ... and their new D[i, b]
     __shared__ int s_nbad;
     const int nblocks = gridDim.x;
     const int tid = threadIdx.x, lane = tid & 31;
-    const int64_t gtid = (int64_t)blockIdx.x * SEQ_THREADS + tid;
+    const bool w0 = tid < 32;
     const int64_t gthreads = (int64_t)nblocks * SEQ_THREADS;
     const bool leader = blockIdx.x == 0 && tid == 0;
+    // this CTA's copy of the chain, touched by its thread 0 only: element, D[element, previous element], size
     int32_t *chain = chains + (int64_t)blockIdx.x * n;
+    unsigned long long *chain_d = chains_d + (int64_t)blockIdx.x * n;
+    int32_t *chain_s = chains_s + (int64_t)blockIdx.x * n;
 
     // ---- initial state: everything alive, nn[] of every row by the CTA that owns it ----------------
     const int64_t live_words = (pitch + 31) / 32;
@@ -626,83 +631,93 @@ rthc_nn_chain_kernel(T *W, int64_t n, int64_t pitch, int method, int32_t *size, 
     }
     grid.sync();
 
-    // replicated scalar state (identical in every thread of the grid)
-    int64_t len = 0, first_live = 0, step = 0, hits = 0, repairs = 0;
-    int32_t x = -1, prev = -1;
+    // walk state: warp 0 only (uniform over its lanes)
+    int64_t len = 0, first_live = 0, hits = 0;
+    int32_t x = -1, prev = -1, sx = 0, sprev = 0;
+    unsigned long long dprev = ~0ull;                            // D[x, prev]
+    bool need_sx = false;
     int32_t dead = -1, grown = -1, grown_size = 0;              // last merge, until the next barrier publishes size[]
     unsigned long long gw = ~0ull; unsigned int gi = ~0u;        // nn of `grown`
-    int q = 0, cur = 0;                                          // broadcast buffer, current nn copy
-    int32_t nxt_x = -1, nxt_prev = -1;                           // thread 0: chain tip after the pending pop
+    // all threads
+    int64_t step = 0, repairs = 0;
+    int q = 0, cur = 0;
 
-#define SIZE_OF(i_) ((i_) == dead ? 0 : ((i_) == grown ? grown_size : __ldcg(&size[(i_)])))
-
-    for (int64_t k = 0; k < n - 1;) {
+    for (int64_t k = 0; k < n - 1; ++k) {
         const MinSlot *nn = nn2 + (int64_t)cur * n;
-        if (len == 0) {
-            if (tid < 32) {                                      // lowest live index from the bitmap
-                int64_t w = first_live >> 5;
-                for (;;) {
-                    const int64_t ww = w + lane;
-                    const uint32_t bits = ww < live_words ? s_live[ww] : 0u;
-                    const unsigned m = __ballot_sync(0xffffffffu, bits != 0u);
-                    if (m) {
-                        const int src = __ffs(m) - 1;
-                        const uint32_t b0 = __shfl_sync(0xffffffffu, bits, src);
-                        if (lane == 0) { bc[q].x = (int32_t)((w + src) * 32 + (__ffs(b0) - 1)); chain[0] = bc[q].x; }
-                        break;
+        if (w0) {
+            for (;;) {
+                if (len == 0) {                                  // lowest live index from the bitmap
+                    int64_t w = first_live >> 5;
+                    for (;;) {
+                        const int64_t ww = w + lane;
+                        const uint32_t bits = ww < live_words ? s_live[ww] : 0u;
+                        const unsigned m = __ballot_sync(0xffffffffu, bits != 0u);
+                        if (m) {
+                            const int src = __ffs(m) - 1;
+                            const uint32_t b0 = __shfl_sync(0xffffffffu, bits, src);
+                            first_live = (w + src) * 32 + (__ffs(b0) - 1);
+                            break;
+                        }
+                        w += 32;
                     }
-                    w += 32;
+                    x = (int32_t)first_live; prev = -1; len = 1; dprev = ~0ull; need_sx = true;
+                    if (lane == 0) chain[0] = x;
                 }
+                // look-up: three lanes, three independent L2 loads
+                unsigned long long v = 0;
+                if (lane == 0) v = x == grown ? gw : __ldcg(&nn[x].w);
+                else if (lane == 1) v = x == grown ? (unsigned long long)gi : (unsigned long long)__ldcg(&nn[x].i);
+                else if (lane == 2 && need_sx) v = (unsigned long long)(x == dead ? 0 : (x == grown ? grown_size : __ldcg(&size[x])));
+                const unsigned long long cw = __shfl_sync(0xffffffffu, v, 0);
+                const unsigned int ci = (unsigned int)__shfl_sync(0xffffffffu, v, 1);
+                if (need_sx) {
+                    sx = (int32_t)__shfl_sync(0xffffffffu, v, 2);
+                    if (lane == 0) chain_s[len - 1] = sx;
+                    need_sx = false;
+                }
+                ++hits;
+                RTHC_DEV_ASSERT(x >= 0 && x < n && ((s_live[x >> 5] >> (x & 31)) & 1u));
+                RTHC_DEV_ASSERT(ci < (unsigned int)n && ci != (unsigned int)x && ((s_live[ci >> 5] >> (ci & 31)) & 1u));
+                RTHC_DEV_ASSERT(sx > 0 && (len == 1 || sprev > 0));
+                int32_t y = (int32_t)ci;
+                unsigned long long dmin = cw;
+                if (len > 1 && dprev <= dmin) { y = prev; dmin = dprev; }      // previous chain element wins ties
+                if (len > 1 && y == prev) {
+                    // ---- reciprocal nearest neighbours: the merge decision -------------------------------
+                    if (lane == 0) {
+                        ChainBc &o = bc[q];
+                        const bool xs = x < y;                   // a dies, b survives (scipy: x < y swap)
+                        o.a = xs ? x : y; o.b = xs ? y : x; o.na = xs ? sx : sprev; o.nb = xs ? sprev : sx;
+                        o.dmin = dmin; o.gw = gw; o.gi = gi; o.grown = grown; o.grown_size = grown_size;
+                    }
+                    break;
+                }
+                // ---- extend the chain -----------------------------------------------------------------
+                RTHC_DEV_ASSERT(len < n);
+                if (lane == 0) { chain[len] = y; chain_d[len] = dmin; }
+                prev = x; sprev = sx; x = y; dprev = dmin; ++len; need_sx = true;
             }
-            __syncthreads();
-            first_live = bc[q].x; q ^= 1;
-            x = (int32_t)first_live; prev = -1; len = 1;
-        }
-        // ---- nearest neighbour of the tip x: a look-up ----------------------------------------------
-        // five scalars, five lanes: the loads are in flight together (one thread would issue them in order,
-        // each waiting for the shared-memory store of the one before: five L2 / DRAM latencies per chain step)
-        if (tid < 5) {
-            ChainBc &o = bc[q];
-            const int32_t pv = len > 1 ? prev : x;
-            if (tid == 0) o.cw = x == grown ? gw : __ldcg(&nn[x].w);
-            else if (tid == 1) o.ci = x == grown ? gi : __ldcg(&nn[x].i);
-            else if (tid == 2) o.dprev = len > 1 ? order_bits(__ldcg(&W[(int64_t)x * pitch + pv])) : ~0ull;
-            else if (tid == 3) o.sx = SIZE_OF(x);
-            else o.sprev = len > 1 ? SIZE_OF(pv) : 0;
         }
         __syncthreads();
-        const unsigned long long cw = bc[q].cw, dprev = bc[q].dprev;
-        const unsigned int ci = bc[q].ci;
-        const int32_t sx = bc[q].sx, sprev = bc[q].sprev;
+        const int32_t a = bc[q].a, b = bc[q].b, na = bc[q].na, nb = bc[q].nb;
+        const int32_t pgrown = bc[q].grown, pgrown_size = bc[q].grown_size;
+        const unsigned long long dminb = bc[q].dmin, pgw = bc[q].gw;
+        const unsigned int pgi = bc[q].gi;
         q ^= 1;
-        ++hits;
-        RTHC_DEV_ASSERT(x >= 0 && x < n && ((s_live[x >> 5] >> (x & 31)) & 1u));
-        RTHC_DEV_ASSERT(ci < (unsigned int)n && ci != (unsigned int)x && ((s_live[ci >> 5] >> (ci & 31)) & 1u));
-        RTHC_DEV_ASSERT(sx > 0 && (len == 1 || sprev > 0));
-        int32_t y = (int32_t)ci;
-        unsigned long long dmin = cw;
-        if (len > 1 && dprev <= dmin) { y = prev; dmin = dprev; }  // previous chain element wins ties
-        if (!(len > 1 && y == prev)) {
-            // ---- extend the chain ---------------------------------------------------------------
-            RTHC_DEV_ASSERT(len < n);
-            if (tid == 0) chain[len] = y;
-            prev = x; x = y; ++len;
-            continue;
-        }
-        // ---- merge x and y (reciprocal nearest neighbours) ---------------------------------------
-        const int32_t a = x < y ? x : y, b = x < y ? y : x;       // a dies, b survives (scipy: x < y swap)
-        const int32_t na = x < y ? sx : sprev, nb = x < y ? sprev : sx;
+        // thread 0: the chain tip after the pop, in flight while the pass runs
+        int32_t nx = -1, nprev = -1, nsx = 0, nsprev = 0;
+        unsigned long long ndprev = ~0ull;
         if (tid == 0) {
             s_live[a >> 5] &= ~(1u << (a & 31));
-            nxt_x = len >= 3 ? chain[len - 3] : -1;              // in flight while the pass runs
-            nxt_prev = len >= 4 ? chain[len - 4] : -1;
+            if (len >= 3) { nx = chain[len - 3]; nsx = chain_s[len - 3]; }
+            if (len >= 4) { nprev = chain[len - 4]; nsprev = chain_s[len - 4]; ndprev = chain_d[len - 3]; }
         }
-        if (leader) { ex[k] = a; ey[k] = b; ew[k] = from_bits(dmin, T()); }
+        if (leader) { ex[k] = a; ey[k] = b; ew[k] = from_bits(dminb, T()); }
         __syncthreads();                                         // bitmap without a; s_nbad == 0 from the last phase
         const T *ra = W + (int64_t)a * pitch;
         T *rb = W + (int64_t)b * pitch;
         MinSlot *nxt = nn2 + (int64_t)(cur ^ 1) * n;
-        const double dab = from_bits(dmin, T());
+        const double dab = from_bits(dminb, T());
         unsigned long long bwb = ~0ull;
         unsigned int bib = ~0u;
         for (int64_t i0 = (int64_t)blockIdx.x * SEQ_THREADS; i0 < n; i0 += gthreads) {
@@ -713,7 +728,9 @@ rthc_nn_chain_kernel(T *W, int64_t n, int64_t pitch, int method, int32_t *size, 
                 unsigned long long ow = __ldcg(&nn[i].w);
                 unsigned int oi = __ldcg(&nn[i].i);
                 const int32_t szi = __ldcg(&size[i]);
-                const int32_t ni = i == grown ? grown_size : szi;
+                const bool ig = i == pgrown;                     // the previous merge's cluster: not published yet
+                const int32_t ni = ig ? pgrown_size : szi;
+                if (ig) { ow = pgw; oi = pgi; }
                 const T v = lance_williams<T>(method, da, db, dab, na, nb, ni);
                 rb[i] = v;                       // row b (contiguous)
                 W[i * pitch + b] = v;            // column b (symmetric copy)
@@ -752,10 +769,10 @@ rthc_nn_chain_kernel(T *W, int64_t n, int64_t pitch, int method, int32_t *size, 
         grid.sync();                          // row/column b and the other nn copy are visible
         ++step;
         cur ^= 1;
-        // nn of the new row b: warp 0 combines the CTA minima; thread 0 adds the chain tip after the pop
-        if (tid < 32) {
+        if (w0) {
+            // nn of the new row b: warp 0 combines the CTA minima (all loads of a trip in flight together)
             unsigned long long w = ~0ull; unsigned int i = ~0u;
-            for (int c0 = 0; c0 < nblocks; c0 += 32 * 8) {       // <= 256 CTAs per trip, the loads of a trip in flight together
+            for (int c0 = 0; c0 < nblocks; c0 += 32 * 8) {
                 unsigned long long cw2[8]; unsigned int ci2[8];
 #pragma unroll
                 for (int u = 0; u < 8; ++u) {
@@ -768,21 +785,20 @@ rthc_nn_chain_kernel(T *W, int64_t n, int64_t pitch, int method, int32_t *size, 
                     if (slot_less(cw2[u], ci2[u], w, i)) { w = cw2[u]; i = ci2[u]; }
             }
             warp_min_all(w, i);
-            if (lane == 0) { bc[q].gw = w; bc[q].gi = i; bc[q].x = nxt_x; bc[q].prev = nxt_prev; }
+            gw = w; gi = i;
+            if (leader) { __stcg(&nxt[b].w, gw); __stcg(&nxt[b].i, gi); size[a] = 0; size[b] = na + nb; }
+            dead = a; grown = b; grown_size = na + nb;
+            len -= 2;
+            if (len > 0) {                                       // the tip after the pop, from thread 0's registers
+                x = __shfl_sync(0xffffffffu, nx, 0); prev = __shfl_sync(0xffffffffu, nprev, 0);
+                sx = __shfl_sync(0xffffffffu, nsx, 0); sprev = __shfl_sync(0xffffffffu, nsprev, 0);
+                dprev = __shfl_sync(0xffffffffu, ndprev, 0);
+                need_sx = false;
+            }
         }
-        __syncthreads();
-        gw = bc[q].gw; gi = bc[q].gi;
-        const int32_t px = bc[q].x, pprev = bc[q].prev;
-        q ^= 1;
-        if (gtid == b % gthreads) { __stcg(&nxt[b].w, gw); __stcg(&nxt[b].i, gi); }
-        if (leader) { size[a] = 0; size[b] = na + nb; }
-        dead = a; grown = b; grown_size = na + nb;
-        ++k;
-        len -= 2;
-        if (len > 0) { x = px; prev = pprev; }
     }
-#undef SIZE_OF
-    if (leader) { ctl->repairs = repairs; ctl->hits = hits; ctl->barriers = step + 1; }
+    if (tid == 0) atomicAdd((unsigned long long *)&ctl->repairs, (unsigned long long)repairs);      // per-CTA counts
+    if (leader) { ctl->hits = hits; ctl->barriers = step + 1; }
 }
 
 template <typename T, typename S>
@@ -792,7 +808,8 @@ static int run_nn_chain(rthc_ctx *ctx, const S *d_cond, int method, std::vector<
     const int64_t n = ctx->n, m = n - 1;
     const int64_t per16 = 16 / (int64_t)sizeof(T), pitch = (n + per16 - 1) / per16 * per16;
     T *d_W = nullptr;
-    int32_t *d_size = nullptr, *d_chain = nullptr, *d_ex = nullptr, *d_ey = nullptr;
+    int32_t *d_size = nullptr, *d_chain = nullptr, *d_chain_s = nullptr, *d_ex = nullptr, *d_ey = nullptr;
+    unsigned long long *d_chain_d = nullptr;
     double *d_ew = nullptr;
     MinSlot *d_slots = nullptr, *d_nn = nullptr;
     ChainCtl *d_ctl = nullptr;
@@ -803,6 +820,8 @@ static int run_nn_chain(rthc_ctx *ctx, const S *d_cond, int method, std::vector<
     if ((rc = rthc_dev_alloc(ctx, &d_W, (size_t)(n * pitch)))) return rc;
     if ((rc = rthc_dev_alloc(ctx, &d_size, (size_t)n))) return rc;
     if ((rc = rthc_dev_alloc(ctx, &d_chain, (size_t)n * (size_t)nblocks))) return rc;
+    if ((rc = rthc_dev_alloc(ctx, &d_chain_s, (size_t)n * (size_t)nblocks))) return rc;
+    if ((rc = rthc_dev_alloc(ctx, &d_chain_d, (size_t)n * (size_t)nblocks))) return rc;
     if ((rc = rthc_dev_alloc(ctx, &d_slots, (size_t)2 * nblocks))) return rc;
     if ((rc = rthc_dev_alloc(ctx, &d_nn, (size_t)2 * (size_t)n))) return rc;
     if ((rc = rthc_dev_alloc(ctx, &d_ex, (size_t)m))) return rc;
@@ -815,11 +834,12 @@ static int run_nn_chain(rthc_ctx *ctx, const S *d_cond, int method, std::vector<
         RTHC_LAUNCH_CHECK(ctx);
         std::vector<int32_t> ones((size_t)n, 1);
         RTHC_CUDA(ctx, cudaMemcpyAsync(d_size, ones.data(), sizeof(int32_t) * (size_t)n, cudaMemcpyHostToDevice, ctx->stream));
+        RTHC_CUDA(ctx, cudaMemsetAsync(d_ctl, 0, sizeof(ChainCtl), ctx->stream));
         RTHC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     }
     int64_t nn = n, pp = pitch;
-    void *args[] = {(void *)&d_W, (void *)&nn, (void *)&pp, (void *)&method, (void *)&d_size, (void *)&d_chain, (void *)&d_slots,
-                    (void *)&d_nn, (void *)&d_ex, (void *)&d_ey, (void *)&d_ew, (void *)&d_ctl};
+    void *args[] = {(void *)&d_W, (void *)&nn, (void *)&pp, (void *)&method, (void *)&d_size, (void *)&d_chain, (void *)&d_chain_d,
+                    (void *)&d_chain_s, (void *)&d_slots, (void *)&d_nn, (void *)&d_ex, (void *)&d_ey, (void *)&d_ew, (void *)&d_ctl};
     RTHC_CUDA(ctx, cudaFuncSetAttribute(rthc_nn_chain_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     RTHC_CUDA(ctx, cudaLaunchCooperativeKernel((void *)rthc_nn_chain_kernel<T>, dim3(nblocks), dim3(SEQ_THREADS), args, smem,
                                                ctx->stream));
@@ -835,7 +855,7 @@ static int run_nn_chain(rthc_ctx *ctx, const S *d_cond, int method, std::vector<
     ctx->chain_full_scans = ctl.barriers;           // grid barriers (info[9])
     ctx->chain_cache_hits = ctl.hits;
     rthc_dev_free(ctx, &d_W); rthc_dev_free(ctx, &d_size); rthc_dev_free(ctx, &d_chain); rthc_dev_free(ctx, &d_slots);
-    rthc_dev_free(ctx, &d_nn); rthc_dev_free(ctx, &d_ex); rthc_dev_free(ctx, &d_ey); rthc_dev_free(ctx, &d_ew);
+    rthc_dev_free(ctx, &d_chain_s); rthc_dev_free(ctx, &d_chain_d); rthc_dev_free(ctx, &d_nn); rthc_dev_free(ctx, &d_ex); rthc_dev_free(ctx, &d_ey); rthc_dev_free(ctx, &d_ew);
     rthc_dev_free(ctx, &d_ctl);
     return 0;
 }
