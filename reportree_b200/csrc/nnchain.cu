@@ -529,16 +529,51 @@ template <> __device__ __forceinline__ unsigned long long chunk_bits<double>(con
     return e == 0 ? (((unsigned long long)q.y << 32) | q.x) : (((unsigned long long)q.w << 32) | q.z);
 }
 
-// One CTA: lexicographic minimum of (D[r, j], j) over the live columns j of row r, j not in {skip1, skip2}
+// The two lexicographically smallest (value bits, index) entries of a row.  (~0, ~0) = none.
+struct __align__(16) Top2 {
+    unsigned long long w1, w2;
+    unsigned int i1, i2, pad0, pad1;
+    __device__ __forceinline__ void clear() { w1 = w2 = ~0ull; i1 = i2 = ~0u; }
+    __device__ __forceinline__ void insert(unsigned long long w, unsigned int i)
+    {
+        if (slot_less(w, i, w1, i1)) { w2 = w1; i2 = i1; w1 = w; i1 = i; }
+        else if (slot_less(w, i, w2, i2)) { w2 = w; i2 = i; }
+    }
+};
+__device__ __forceinline__ void warp_top2(Top2 &t)                // all lanes end with the warp's top-2
+{
+#pragma unroll
+    for (int s = 16; s > 0; s >>= 1) {
+        const unsigned long long ow1 = __shfl_xor_sync(0xffffffffu, t.w1, s), ow2 = __shfl_xor_sync(0xffffffffu, t.w2, s);
+        const unsigned int oi1 = __shfl_xor_sync(0xffffffffu, t.i1, s), oi2 = __shfl_xor_sync(0xffffffffu, t.i2, s);
+        t.insert(ow1, oi1);
+        t.insert(ow2, oi2);
+    }
+}
+// block-wide top-2; result valid in warp 0 (all its lanes)
+__device__ __forceinline__ void block_top2(Top2 &t, Top2 *sh)
+{
+    warp_top2(t);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (lane == 0) sh[warp] = t;
+    __syncthreads();
+    if (warp == 0) {
+        if (lane < SEQ_THREADS / 32) t = sh[lane]; else t.clear();
+        warp_top2(t);
+    }
+    __syncthreads();
+}
+
+// One CTA: the two smallest (D[r, j], j) over the live columns j of row r, j not in {skip1, skip2}
 // (16-byte loads, liveness from the CTA's shared-memory bitmap; RS_U chunks in flight per thread).
-// Result valid in thread 0.  `row` is 16-byte aligned (rows are pitched).
-#define RS_U 8
+// Result valid in warp 0.  `row` is 16-byte aligned (rows are pitched).
+#define RS_U 4
 template <typename T>
-__device__ __forceinline__ void cta_row_min(const T *row, int64_t n, const uint32_t *s_live, int64_t skip1, int64_t skip2,
-                                            unsigned long long &bw, unsigned int &bi, MinSlot *sh)
+__device__ __forceinline__ void cta_row_top2(const T *row, int64_t n, const uint32_t *s_live, int64_t skip1, int64_t skip2,
+                                             Top2 &t, Top2 *sh)
 {
     constexpr int E = 16 / (int)sizeof(T);
-    bw = ~0ull; bi = ~0u;
+    t.clear();
     const int64_t stride = (int64_t)SEQ_THREADS * E;
     for (int64_t g0 = (int64_t)threadIdx.x * E; g0 < n; g0 += stride * RS_U) {
         uint4 q[RS_U];
@@ -559,51 +594,71 @@ __device__ __forceinline__ void cta_row_min(const T *row, int64_t n, const uint3
             if (!lb[u]) continue;
             const int64_t j0 = g0 + u * stride;
 #pragma unroll
-            for (int e = 0; e < E; ++e) {
-                if (!((lb[u] >> e) & 1u)) continue;
-                const unsigned long long d = chunk_bits<T>(q[u], e);
-                if (d < bw) { bw = d; bi = (unsigned int)(j0 + e); }      // ascending j: the lowest index of the minimum
-            }
+            for (int e = 0; e < E; ++e)
+                if ((lb[u] >> e) & 1u) t.insert(chunk_bits<T>(q[u], e), (unsigned int)(j0 + e));
         }
     }
-    block_min(bw, bi, sh);
+    block_top2(t, sh);
+}
+
+// cache entry of a row: E1 = its nearest neighbour (exact, always); E2 = the runner-up when `act`, otherwise only a
+// bound: every entry of the row other than E1 (and E2 when act) is lexicographically greater than (w2, i2)
+struct __align__(16) NNEntry {
+    unsigned long long w1, w2;
+    unsigned int i1, i2, act, pad;
+};
+__device__ __forceinline__ NNEntry nn_load(const NNEntry *p)
+{
+    const uint4 lo = __ldcg(reinterpret_cast<const uint4 *>(p)), hi = __ldcg(reinterpret_cast<const uint4 *>(p) + 1);
+    NNEntry e;
+    e.w1 = ((unsigned long long)lo.y << 32) | lo.x; e.w2 = ((unsigned long long)lo.w << 32) | lo.z;
+    e.i1 = hi.x; e.i2 = hi.y; e.act = hi.z; e.pad = 0;
+    return e;
+}
+__device__ __forceinline__ void nn_store(NNEntry *p, unsigned long long w1, unsigned int i1, unsigned long long w2, unsigned int i2,
+                                         unsigned int act)
+{
+    __stcg(reinterpret_cast<uint4 *>(p), make_uint4((uint32_t)w1, (uint32_t)(w1 >> 32), (uint32_t)w2, (uint32_t)(w2 >> 32)));
+    __stcg(reinterpret_cast<uint4 *>(p) + 1, make_uint4(i1, i2, act, 0u));
 }
 
 struct ChainBc {                // the merge decision of warp 0, broadcast through shared memory
-    unsigned long long dmin, gw;
-    unsigned int gi;
+    unsigned long long dmin, gw1, gw2;      // g*: cache entry of `grown` (registers of warp 0: not published yet)
+    unsigned int gi1, gi2, gact;
     int32_t a, b, na, nb, grown, grown_size;
 };
 
 // The merge loop.  scipy's chain step asks for the nearest neighbour of the chain tip x: the previous chain
 // element if it ties the minimum, else the lowest index of the minimum of row x.  A grid-wide row scan costs a
 // grid barrier (2.4 us + the reductions around it) however short the row is, so the kernel keeps for EVERY live
-// row r the exact lexicographic minimum nn[r] = min over live i != r of (D[r, i], i), and a chain step is a
-// look-up: warp 0 of every CTA walks the chain by itself (three L2 loads in three lanes, no block barrier; the
-// distance to the previous element and the sizes of the chain elements ride along in the CTA's private chain
-// arrays) while the other warps wait for its merge decision.  Only a merge (a dies, b = a u b) has a grid barrier,
-// and the merge phase restores the invariant before it:
-//   * the thread that writes D[i, b] folds the new entry into the cache: nn[i] = min(nn[i], (D[i, b], b)) is exact
-//     because every other entry of row i is unchanged;
-//   * if the cached neighbour of row i was a or b, the CTA of that thread rescans row i by itself (a row is
-//     <= 0.2 MB: one SM streams it in about a microsecond; columns a and b are skipped -- a is dead, b's new value
-//     is the one just computed -- so the scan reads nothing that this phase writes);
-//   * the candidates (D[b, i], i) of the new row b are reduced per CTA and combined after the barrier.
-// The answer of a look-up is the same (value, lowest index, previous-wins) triple as scipy's scan, so Z stays
-// byte-identical.  nn[] is double-buffered by merge parity (a CTA still walking the chain must not see entries
-// that a faster CTA has already updated); every CTA keeps the liveness bitmap in shared memory; size[] and nn[]
-// of the cluster created by the last merge are carried in registers until the next barrier has published them;
-// W is pitched so that every row starts on a 16-byte boundary.
+// row r its exact nearest neighbour E1 = min over live i != r of (D[r, i], i), and a chain step is a look-up:
+// warp 0 of every CTA walks the chain by itself (three L2 loads in three lanes, no block barrier; the distance to
+// the previous element and the sizes of the chain elements ride along in the CTA's private chain arrays) while the
+// other warps wait for its merge decision.  Only a merge (a dies, b = a u b) has a grid barrier, and the merge
+// phase restores the invariant before it.  The thread that writes the new D[i, b] updates the entry of row i from
+// what it knows: E1, the runner-up E2 (or, when E2 is not known, a bound below every other entry) and the new entry
+// N = (D[i, b], b).  Entries of a and b leave the candidate set, N joins it; the smallest candidate is the new E1
+// if it does not exceed the bound (everything unknown lies above the bound), the next one the new E2 under the same
+// condition.  Only when E1 was a or b, no runner-up is left and N exceeds the bound does the row need a scan, and
+// then the CTA of that thread rescans it by itself (a row is <= 0.2 MB: one SM streams it in two or three
+// microseconds; columns a and b are skipped -- a is dead, b's new value is N -- so the scan reads nothing that this
+// phase writes).  With the runner-up about one row per merge needs that (C5: measured in `row_scans`), with E1 alone
+// 14 (complete, C5) to 75 (average, C3) did.  The top-2 of the new row b is reduced per CTA and combined after the
+// barrier.  A look-up returns the same (value, lowest index, previous-wins) triple as scipy's scan, so Z stays
+// byte-identical.  nn[] is double-buffered by merge parity (a CTA still walking the chain must not see entries that a
+// faster CTA has already updated); every CTA keeps the liveness bitmap in shared memory; size[] and nn[] of the
+// cluster created by the last merge are carried in registers until the next barrier has published them; W is
+// pitched so that every row starts on a 16-byte boundary.
 template <typename T>
 __global__ void __launch_bounds__(SEQ_THREADS, 1)
 rthc_nn_chain_kernel(T *W, int64_t n, int64_t pitch, int method, int32_t *size, int32_t *chains, unsigned long long *chains_d,
-                     int32_t *chains_s, MinSlot *slots, MinSlot *nn2, int32_t *ex, int32_t *ey, double *ew, ChainCtl *ctl)
+                     int32_t *chains_s, Top2 *slots, NNEntry *nn2, int32_t *ex, int32_t *ey, double *ew, ChainCtl *ctl)
 {
     cg::grid_group grid = cg::this_grid();
     extern __shared__ uint32_t s_live[];                         // bit j: cluster j is alive
-    __shared__ MinSlot sh[SEQ_THREADS / 32];
+    __shared__ Top2 sh[SEQ_THREADS / 32];
     __shared__ ChainBc bc[2];                                    // alternating: one __syncthreads per merge
-    __shared__ int32_t s_bad_i[SEQ_THREADS];                     // rows of this CTA whose cached neighbour was a or b
+    __shared__ int32_t s_bad_i[SEQ_THREADS];                     // rows of this CTA that need a scan
     __shared__ unsigned long long s_bad_w[SEQ_THREADS];          // ... and their new D[i, b]
     __shared__ int s_nbad;
     const int nblocks = gridDim.x;
@@ -616,7 +671,7 @@ rthc_nn_chain_kernel(T *W, int64_t n, int64_t pitch, int method, int32_t *size, 
     unsigned long long *chain_d = chains_d + (int64_t)blockIdx.x * n;
     int32_t *chain_s = chains_s + (int64_t)blockIdx.x * n;
 
-    // ---- initial state: everything alive, nn[] of every row by the CTA that owns it ----------------
+    // ---- initial state: everything alive, the entry of every row by the CTA that owns it -----------
     const int64_t live_words = (pitch + 31) / 32;
     for (int64_t w = tid; w < live_words; w += SEQ_THREADS) {
         const int64_t j = w * 32;
@@ -625,9 +680,9 @@ rthc_nn_chain_kernel(T *W, int64_t n, int64_t pitch, int method, int32_t *size, 
     if (tid == 0) s_nbad = 0;
     __syncthreads();
     for (int64_t r = blockIdx.x; r < n; r += nblocks) {
-        unsigned long long w; unsigned int i;
-        cta_row_min<T>(W + r * pitch, n, s_live, r, -1, w, i, sh);
-        if (tid == 0) { __stcg(&nn2[r].w, w); __stcg(&nn2[r].i, i); }
+        Top2 t;
+        cta_row_top2<T>(W + r * pitch, n, s_live, r, -1, t, sh);
+        if (tid == 0) nn_store(&nn2[r], t.w1, t.i1, t.w2, t.i2, t.i2 != ~0u);
     }
     grid.sync();
 
@@ -637,13 +692,14 @@ rthc_nn_chain_kernel(T *W, int64_t n, int64_t pitch, int method, int32_t *size, 
     unsigned long long dprev = ~0ull;                            // D[x, prev]
     bool need_sx = false;
     int32_t dead = -1, grown = -1, grown_size = 0;              // last merge, until the next barrier publishes size[]
-    unsigned long long gw = ~0ull; unsigned int gi = ~0u;        // nn of `grown`
+    unsigned long long gw1 = ~0ull, gw2 = ~0ull;                 // entry of `grown`
+    unsigned int gi1 = ~0u, gi2 = ~0u, gact = 0;
     // all threads
     int64_t step = 0, repairs = 0;
     int q = 0, cur = 0;
 
     for (int64_t k = 0; k < n - 1; ++k) {
-        const MinSlot *nn = nn2 + (int64_t)cur * n;
+        const NNEntry *nn = nn2 + (int64_t)cur * n;
         if (w0) {
             for (;;) {
                 if (len == 0) {                                  // lowest live index from the bitmap
@@ -665,8 +721,8 @@ rthc_nn_chain_kernel(T *W, int64_t n, int64_t pitch, int method, int32_t *size, 
                 }
                 // look-up: three lanes, three independent L2 loads
                 unsigned long long v = 0;
-                if (lane == 0) v = x == grown ? gw : __ldcg(&nn[x].w);
-                else if (lane == 1) v = x == grown ? (unsigned long long)gi : (unsigned long long)__ldcg(&nn[x].i);
+                if (lane == 0) v = x == grown ? gw1 : __ldcg(&nn[x].w1);
+                else if (lane == 1) v = x == grown ? (unsigned long long)gi1 : (unsigned long long)__ldcg(&nn[x].i1);
                 else if (lane == 2 && need_sx) v = (unsigned long long)(x == dead ? 0 : (x == grown ? grown_size : __ldcg(&size[x])));
                 const unsigned long long cw = __shfl_sync(0xffffffffu, v, 0);
                 const unsigned int ci = (unsigned int)__shfl_sync(0xffffffffu, v, 1);
@@ -688,7 +744,8 @@ rthc_nn_chain_kernel(T *W, int64_t n, int64_t pitch, int method, int32_t *size, 
                         ChainBc &o = bc[q];
                         const bool xs = x < y;                   // a dies, b survives (scipy: x < y swap)
                         o.a = xs ? x : y; o.b = xs ? y : x; o.na = xs ? sx : sprev; o.nb = xs ? sprev : sx;
-                        o.dmin = dmin; o.gw = gw; o.gi = gi; o.grown = grown; o.grown_size = grown_size;
+                        o.dmin = dmin; o.gw1 = gw1; o.gw2 = gw2; o.gi1 = gi1; o.gi2 = gi2; o.gact = gact;
+                        o.grown = grown; o.grown_size = grown_size;
                     }
                     break;
                 }
@@ -701,8 +758,8 @@ rthc_nn_chain_kernel(T *W, int64_t n, int64_t pitch, int method, int32_t *size, 
         __syncthreads();
         const int32_t a = bc[q].a, b = bc[q].b, na = bc[q].na, nb = bc[q].nb;
         const int32_t pgrown = bc[q].grown, pgrown_size = bc[q].grown_size;
-        const unsigned long long dminb = bc[q].dmin, pgw = bc[q].gw;
-        const unsigned int pgi = bc[q].gi;
+        const unsigned long long dminb = bc[q].dmin, pgw1 = bc[q].gw1, pgw2 = bc[q].gw2;
+        const unsigned int pgi1 = bc[q].gi1, pgi2 = bc[q].gi2, pgact = bc[q].gact;
         q ^= 1;
         // thread 0: the chain tip after the pop, in flight while the pass runs
         int32_t nx = -1, nprev = -1, nsx = 0, nsprev = 0;
@@ -716,46 +773,55 @@ rthc_nn_chain_kernel(T *W, int64_t n, int64_t pitch, int method, int32_t *size, 
         __syncthreads();                                         // bitmap without a; s_nbad == 0 from the last phase
         const T *ra = W + (int64_t)a * pitch;
         T *rb = W + (int64_t)b * pitch;
-        MinSlot *nxt = nn2 + (int64_t)(cur ^ 1) * n;
+        NNEntry *nxt = nn2 + (int64_t)(cur ^ 1) * n;
         const double dab = from_bits(dminb, T());
-        unsigned long long bwb = ~0ull;
-        unsigned int bib = ~0u;
+        Top2 tb;
+        tb.clear();
         for (int64_t i0 = (int64_t)blockIdx.x * SEQ_THREADS; i0 < n; i0 += gthreads) {
             const int64_t i = i0 + tid;
             if (i < n && i != b && ((s_live[i >> 5] >> (i & 31)) & 1u)) {
                 // every load of the element first (the stores below may alias them as far as the compiler knows)
                 const T da = __ldcg(&ra[i]), db = __ldcg(&rb[i]);
-                unsigned long long ow = __ldcg(&nn[i].w);
-                unsigned int oi = __ldcg(&nn[i].i);
+                const uint4 elo = __ldcg(reinterpret_cast<const uint4 *>(&nn[i])), ehi = __ldcg(reinterpret_cast<const uint4 *>(&nn[i]) + 1);
                 const int32_t szi = __ldcg(&size[i]);
                 const bool ig = i == pgrown;                     // the previous merge's cluster: not published yet
                 const int32_t ni = ig ? pgrown_size : szi;
-                if (ig) { ow = pgw; oi = pgi; }
+                struct { unsigned long long w1, w2; unsigned int i1, i2, act; } e;
+                e.w1 = ig ? pgw1 : (((unsigned long long)elo.y << 32) | elo.x);
+                e.w2 = ig ? pgw2 : (((unsigned long long)elo.w << 32) | elo.z);
+                e.i1 = ig ? pgi1 : ehi.x; e.i2 = ig ? pgi2 : ehi.y; e.act = ig ? pgact : ehi.z;
                 const T v = lance_williams<T>(method, da, db, dab, na, nb, ni);
                 rb[i] = v;                       // row b (contiguous)
                 W[i * pitch + b] = v;            // column b (symmetric copy)
                 const unsigned long long ob = order_bits(v);
-                if (slot_less(ob, (unsigned int)i, bwb, bib)) { bwb = ob; bib = (unsigned int)i; }
-                if (oi == (unsigned int)a || oi == (unsigned int)b) {
+                tb.insert(ob, (unsigned int)i);
+                // candidates: N = (ob, b), E1 unless it was a or b, E2 if known and not a or b; bound = (w2, i2)
+                const bool h1 = e.i1 == (unsigned int)a || e.i1 == (unsigned int)b;
+                const bool k2 = e.act && !(e.i2 == (unsigned int)a || e.i2 == (unsigned int)b);
+                Top2 c;
+                c.clear();
+                c.insert(ob, (unsigned int)b);
+                if (!h1) c.insert(e.w1, e.i1);
+                if (k2) c.insert(e.w2, e.i2);                                    // only the two smallest matter
+                if (!slot_less(e.w2, e.i2, c.w1, c.i1)) {                        // c1 <= bound: exact
+                    const bool second = c.i2 != ~0u && !slot_less(e.w2, e.i2, c.w2, c.i2);
+                    nn_store(&nxt[i], c.w1, c.i1, second ? c.w2 : e.w2, second ? c.i2 : e.i2, second ? 1u : 0u);
+                } else {
                     const int slot = atomicAdd(&s_nbad, 1);
                     RTHC_DEV_ASSERT(slot >= 0 && slot < SEQ_THREADS);
                     s_bad_i[slot] = (int32_t)i; s_bad_w[slot] = ob;
-                } else {
-                    if (slot_less(ob, (unsigned int)b, ow, oi)) { ow = ob; oi = (unsigned int)b; }
-                    __stcg(&nxt[i].w, ow); __stcg(&nxt[i].i, oi);
                 }
             }
             __syncthreads();
             const int nbad = s_nbad;
             for (int e = 0; e < nbad; ++e) {                     // this CTA rescans the rows it could not patch
                 const int32_t r = s_bad_i[e];
-                unsigned long long w; unsigned int j;
-                cta_row_min<T>(W + (int64_t)r * pitch, n, s_live, r, b, w, j, sh);
+                Top2 t;
+                cta_row_top2<T>(W + (int64_t)r * pitch, n, s_live, r, b, t, sh);
                 if (tid == 0) {
-                    const unsigned long long ob = s_bad_w[e];
-                    if (slot_less(ob, (unsigned int)b, w, j)) { w = ob; j = (unsigned int)b; }
-                    RTHC_DEV_ASSERT(j < (unsigned int)n && j != (unsigned int)r && j != (unsigned int)a);
-                    __stcg(&nxt[r].w, w); __stcg(&nxt[r].i, j);
+                    t.insert(s_bad_w[e], (unsigned int)b);
+                    RTHC_DEV_ASSERT(t.i1 < (unsigned int)n && t.i1 != (unsigned int)r && t.i1 != (unsigned int)a);
+                    nn_store(&nxt[r], t.w1, t.i1, t.w2, t.i2, t.i2 != ~0u);
                 }
             }
             repairs += nbad;
@@ -763,30 +829,38 @@ rthc_nn_chain_kernel(T *W, int64_t n, int64_t pitch, int method, int32_t *size, 
             if (tid == 0) s_nbad = 0;
             __syncthreads();
         }
-        block_min(bwb, bib, sh);
-        MinSlot *sb = slots + (step & 1) * nblocks;
-        if (tid == 0) { sb[blockIdx.x].w = bwb; sb[blockIdx.x].i = bib; }
+        block_top2(tb, sh);
+        Top2 *sb = slots + (step & 1) * nblocks;
+        if (tid == 0) sb[blockIdx.x] = tb;
         grid.sync();                          // row/column b and the other nn copy are visible
         ++step;
         cur ^= 1;
         if (w0) {
-            // nn of the new row b: warp 0 combines the CTA minima (all loads of a trip in flight together)
-            unsigned long long w = ~0ull; unsigned int i = ~0u;
-            for (int c0 = 0; c0 < nblocks; c0 += 32 * 8) {
-                unsigned long long cw2[8]; unsigned int ci2[8];
+            // entry of the new row b: warp 0 combines the CTA top-2s (all loads of a trip in flight together)
+            Top2 t;
+            t.clear();
+            for (int c0 = 0; c0 < nblocks; c0 += 32 * 5) {       // 148 CTAs: one trip, five entries per lane in flight
+                uint4 lo[5], hi[5];
 #pragma unroll
-                for (int u = 0; u < 8; ++u) {
+                for (int u = 0; u < 5; ++u) {
                     const int c = c0 + 32 * u + lane;
-                    cw2[u] = c < nblocks ? __ldcg(&sb[c].w) : ~0ull;
-                    ci2[u] = c < nblocks ? __ldcg(&sb[c].i) : ~0u;
+                    if (c < nblocks) {
+                        lo[u] = __ldcg(reinterpret_cast<const uint4 *>(&sb[c]));
+                        hi[u] = __ldcg(reinterpret_cast<const uint4 *>(&sb[c]) + 1);
+                    }
                 }
 #pragma unroll
-                for (int u = 0; u < 8; ++u)
-                    if (slot_less(cw2[u], ci2[u], w, i)) { w = cw2[u]; i = ci2[u]; }
+                for (int u = 0; u < 5; ++u) {
+                    const int c = c0 + 32 * u + lane;
+                    if (c < nblocks) {
+                        t.insert(((unsigned long long)lo[u].y << 32) | lo[u].x, hi[u].x);
+                        t.insert(((unsigned long long)lo[u].w << 32) | lo[u].z, hi[u].y);
+                    }
+                }
             }
-            warp_min_all(w, i);
-            gw = w; gi = i;
-            if (leader) { __stcg(&nxt[b].w, gw); __stcg(&nxt[b].i, gi); size[a] = 0; size[b] = na + nb; }
+            warp_top2(t);
+            gw1 = t.w1; gi1 = t.i1; gw2 = t.w2; gi2 = t.i2; gact = t.i2 != ~0u;
+            if (leader) { nn_store(&nxt[b], gw1, gi1, gw2, gi2, gact); size[a] = 0; size[b] = na + nb; }
             dead = a; grown = b; grown_size = na + nb;
             len -= 2;
             if (len > 0) {                                       // the tip after the pop, from thread 0's registers
@@ -811,7 +885,8 @@ static int run_nn_chain(rthc_ctx *ctx, const S *d_cond, int method, std::vector<
     int32_t *d_size = nullptr, *d_chain = nullptr, *d_chain_s = nullptr, *d_ex = nullptr, *d_ey = nullptr;
     unsigned long long *d_chain_d = nullptr;
     double *d_ew = nullptr;
-    MinSlot *d_slots = nullptr, *d_nn = nullptr;
+    Top2 *d_slots = nullptr;
+    NNEntry *d_nn = nullptr;
     ChainCtl *d_ctl = nullptr;
     int nblocks = ctx->sm_count;
     int rc;

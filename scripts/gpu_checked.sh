@@ -13,4 +13,4 @@ echo "checked rc=$?" | tee -a $out/driver_checked.log
 RTHC_LIB_PATH=$PWD/reportree_b200/build/lib_checked.so timeout 900 python -m pytest tests/test_gpu_distance.py tests/test_gpu_linkage.py tests/test_gpu_exact_linkage.py -m gpu -x -q > $out/pytest_checked.log 2>&1
 echo "pytest checked rc=$?" | tee -a $out/pytest_checked.log
 timeout 120 /usr/local/cuda/bin/compute-sanitizer --tool memcheck python -c "print(1)" > $out/compute_sanitizer_probe.log 2>&1; echo "compute-sanitizer rc=$?" | tee -a $out/compute_sanitizer_probe.log
-tail -2 $out/driver_plain.log $out/driver_checked.log $out/pytest_checked.log
+for f in driver_plain driver_checked pytest_checked; do tail -n 2 $out/$f.log; done
