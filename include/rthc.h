@@ -182,8 +182,9 @@ int rthc_adjusted_wallace_sums(const int32_t *cell_row, const int32_t *cell_coun
 /* info[0]=n, [1]=L, [2]=loci kept, [3]=groups of 32 loci, [4]=plane rows,
  * [5]=tiles launched, [6]=Boruvka rounds of the last linkage, [7]=max alleles/locus,
  * [8]=row scans of the last merge loop (own barrier + fused with a merge),
- * [9]=of those, scans that paid their own grid barrier, [10]=chain steps answered by the
- * nearest-neighbour cache (no scan)                                                  */
+ * [9]=grid barriers of the last merge loop, [10]=chain steps answered by the nearest-neighbour
+ * cache (no scan), [11]=loci re-coded with an escape code for their singleton alleles,
+ * [12]=cells holding it, [13]=pairs fixed up after the plane kernel (rthc_escape_correct)   */
 int rthc_info(const rthc_ctx *ctx, int64_t *info, int n_info);
 /* device-side durations (CUDA events, ms) of the last call of each stage:
  * [0]=h2d, [1]=recode+pack, [2]=distance kernel, [3]=mst/merge loop, [4]=cut,

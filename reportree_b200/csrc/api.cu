@@ -52,7 +52,8 @@ extern "C" int rthc_create(rthc_ctx **out, int device)
     rthc_ctx *ctx = new rthc_ctx();
     ctx->device = device;
     if ((e = cudaSetDevice(device)) != cudaSuccess || (e = cudaStreamCreate(&ctx->stream)) != cudaSuccess ||
-        (e = cudaEventCreate(&ctx->ev0)) != cudaSuccess || (e = cudaEventCreate(&ctx->ev1)) != cudaSuccess) {
+        (e = cudaEventCreate(&ctx->ev0)) != cudaSuccess || (e = cudaEventCreate(&ctx->ev1)) != cudaSuccess ||
+        (e = cudaEventCreate(&ctx->ev_aux)) != cudaSuccess) {
         rthc_fail(nullptr, RTHC_E_CUDA, "context setup failed: %s", cudaGetErrorString(e));
         delete ctx;
         return RTHC_E_CUDA;
@@ -112,6 +113,7 @@ extern "C" int rthc_mark_elapsed_ms(rthc_ctx *ctx, double *ms)
 void rthc_free_distance_state(rthc_ctx *ctx)
 {
     rthc_dev_free(ctx, &ctx->d_codes); rthc_dev_free(ctx, &ctx->d_codes32); rthc_dev_free(ctx, &ctx->d_planes);
+    rthc_dev_free(ctx, &ctx->d_esc_code); rthc_dev_free(ctx, &ctx->d_esc_cnt); rthc_dev_free(ctx, &ctx->d_esc_list);
     rthc_dev_free(ctx, &ctx->d_grp_off); rthc_dev_free(ctx, &ctx->d_grp_np);
     rthc_dev_free(ctx, &ctx->d_tiles); rthc_dev_free(ctx, &ctx->d_row_base);
     rthc_dev_free(ctx, &ctx->d_owned_rows);
@@ -134,6 +136,7 @@ extern "C" void rthc_destroy(rthc_ctx *ctx)
     rthc_free_linkage_state(ctx);
     if (ctx->ev0) cudaEventDestroy(ctx->ev0);
     if (ctx->ev1) cudaEventDestroy(ctx->ev1);
+    if (ctx->ev_aux) cudaEventDestroy(ctx->ev_aux);
     for (int k = 0; k < 3; ++k)
         if (ctx->h_pin[k]) cudaFreeHost(ctx->h_pin[k]);
     for (int k = 0; k < 2; ++k)
@@ -471,17 +474,17 @@ extern "C" int rthc_direct_pairs(rthc_ctx *ctx, const int32_t *pi, const int32_t
 extern "C" int rthc_info(const rthc_ctx *ctx, int64_t *info, int n_info)
 {
     if (!ctx || !info) return RTHC_E_ARG;
-    const int64_t v[11] = {ctx->n, ctx->L, ctx->L_kept, ctx->G, ctx->plane_rows, ctx->n_tiles,
+    const int64_t v[14] = {ctx->n, ctx->L, ctx->L_kept, ctx->G, ctx->plane_rows, ctx->n_tiles,
                            ctx->boruvka_rounds, ctx->max_alleles, ctx->row_scans, ctx->chain_full_scans,
-                           ctx->chain_cache_hits};
-    for (int k = 0; k < n_info && k < 11; ++k) info[k] = v[k];
+                           ctx->chain_cache_hits, ctx->escape_loci, ctx->escape_cells, ctx->escape_pairs};
+    for (int k = 0; k < n_info && k < 14; ++k) info[k] = v[k];
     return 0;
 }
 
 extern "C" int rthc_timings(const rthc_ctx *ctx, double *ms, int n_ms)
 {
     if (!ctx || !ms) return RTHC_E_ARG;
-    for (int k = 0; k < n_ms && k < 7; ++k) ms[k] = k == 5 ? (double)ctx->launches : ctx->t_ms[k];
+    for (int k = 0; k < n_ms && k < 8; ++k) ms[k] = k == 5 ? (double)ctx->launches : ctx->t_ms[k];
     return 0;
 }
 

@@ -317,16 +317,16 @@ class HCContext:
 
     # ---- introspection -----------------------------------------------------------------
     def info(self):
-        a = np.zeros(11, dtype=np.int64)
-        self._check(self._L.rthc_info(self._h, _ptr(a), 11))
+        a = np.zeros(14, dtype=np.int64)
+        self._check(self._L.rthc_info(self._h, _ptr(a), 14))
         keys = ["n", "L", "loci_kept", "groups", "plane_rows", "tiles", "boruvka_rounds", "max_alleles", "row_scans",
-                "chain_full_scans", "chain_cache_hits"]
+                "chain_barriers", "chain_cache_hits", "escape_loci", "escape_cells", "escape_pairs"]
         return dict(zip(keys, (int(x) for x in a)))
 
     def timings(self):
-        a = np.zeros(7, dtype=np.float64)
-        self._check(self._L.rthc_timings(self._h, _ptr(a), 7))
-        keys = ["h2d_ms", "recode_ms", "distance_ms", "linkage_ms", "cut_ms", "launches", "stability_ms"]
+        a = np.zeros(8, dtype=np.float64)
+        self._check(self._L.rthc_timings(self._h, _ptr(a), 8))
+        keys = ["h2d_ms", "recode_ms", "distance_ms", "linkage_ms", "cut_ms", "launches", "stability_ms", "escape_fixup_ms"]
         return dict(zip(keys, (float(x) for x in a)))
 
     def mark(self, slot):

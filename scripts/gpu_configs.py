@@ -17,7 +17,7 @@ if "C3" in which:
         Zs, t1 = t(lambda: ctx.linkage("single"))
         ctx.set_single_algo(hc.SL_PRIM); Zp, t2 = t(lambda: ctx.linkage("single"))
         Za, t3 = t(lambda: ctx.linkage("average")); scans_a = ctx.info()["row_scans"]
-        print("C3 average: grid barriers %d, look-ups %d" % (ctx.info()["chain_full_scans"], ctx.info()["chain_cache_hits"]))
+        print("C3 average: grid barriers %d, look-ups %d" % (ctx.info()["chain_barriers"], ctx.info()["chain_cache_hits"]))
         lab, t4 = t(lambda: ctx.fcluster(np.arange(0, 51.0)))
         Zc, t5 = t(lambda: ctx.linkage("complete")); scans_c = ctx.info()["row_scans"]
         Zw, t6 = t(lambda: ctx.linkage("ward")); scans_w = ctx.info()["row_scans"]
@@ -48,7 +48,7 @@ if "C5" in which:
         _, ts = t(lambda: ctx.set_profiles(Xs)); _, td = t(ctx.distance)
         Zc, t5 = t(lambda: ctx.linkage("complete")); scans = ctx.info()["row_scans"]; inf = ctx.info()
         Zc2, t5b = t(lambda: ctx.linkage("complete"))
-        print("C5 complete again (warm pool) %.3fs; grid barriers %d, look-ups %d" % (t5b, inf["chain_full_scans"], inf["chain_cache_hits"]))
+        print("C5 complete again (warm pool) %.3fs; grid barriers %d, look-ups %d" % (t5b, inf["chain_barriers"], inf["chain_cache_hits"]))
         lab, t4 = t(lambda: ctx.fcluster(np.arange(0, 51.0)))
     print(f"C5 {Xs.shape[0]}x{Xs.shape[1]} (of 50000x7600): set {ts:.3f}s dist {td:.3f}s complete {t5:.3f}s ({scans} scans) cut51 {t4:.3f}s"
           f"  clusters@t=20: {lab[20].max()}")

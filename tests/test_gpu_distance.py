@@ -154,6 +154,55 @@ def test_uint16_input_and_both_recoder_paths_agree(hc, oracle, n, L):
         assert np.array_equal(ctx.condensed(), ref)
 
 
+@pytest.mark.parametrize("world", [1, 3])
+def test_escape_coded_singletons_are_fixed_up_exactly(hc, oracle, world):
+    """Loci whose allele count is dominated by singletons are re-coded with one shared escape code (fewer bit
+    planes) and the pairs of escaped cells get their mismatch back from rthc_escape_correct.  n = 3,000 so that the
+    device's cost rule accepts the escape; mixtures: no singletons, a few, hundreds, only singletons + one shared
+    allele, singletons next to missing cells, and a locus the rule must refuse (more singletons than the cap)."""
+    rng = np.random.default_rng(77)
+    n, L = 3000, 40
+    X = rng.integers(1, 6, size=(n, L)).astype(np.int32)
+    for l in range(L):
+        k = [0, 2, 3, 17, 60, 250, 700, 1500][l % 8]                    # singletons of this locus
+        rows = rng.choice(n, k, replace=False)
+        X[rows, l] = 1000 + np.arange(k)
+        if l % 5 == 0:
+            X[rng.choice(n, 40, replace=False), l] = 0
+    X[:, 7] = 1
+    X[rng.choice(n, 300, replace=False), 7] = 2000 + np.arange(300)      # one shared allele + 300 singletons
+    ref = oracle.dist_condensed(X)
+    ctxs = [hc.HCContext(rank=r, world=world) for r in range(world)]
+    try:
+        got = np.zeros_like(ref)
+        seen = np.zeros(ref.size, dtype=bool)
+        from reportree_b200 import sharded
+        for r, ctx in enumerate(ctxs):
+            ctx.set_profiles(X)
+            info = ctx.info()
+            assert info["escape_loci"] >= 10 and info["escape_pairs"] > 0, info
+            assert info["max_alleles"] >= 1500                            # distinct alleles, not codes
+            ctx.distance()
+            rows = sharded.owned_rows(n, r, world)
+            own = ctx.owned_condensed()
+            p = 0
+            for i in rows:
+                base = n * i - i * (i + 1) // 2
+                cnt = n - 1 - i
+                got[base:base + cnt] = own[p:p + cnt]
+                seen[base:base + cnt] = True
+                p += cnt
+            if world == 1:                                                # the scalar check kernel knows the escape codes
+                pi = rng.integers(0, n, 4000).astype(np.int32)
+                pj = rng.integers(0, n, 4000).astype(np.int32)
+                sq = (X[pi] != X[pj]) & (X[pi] != 0) & (X[pj] != 0)
+                assert np.array_equal(ctx.direct_pairs(pi, pj), sq.sum(1))
+        assert seen.all() and np.array_equal(got, ref)
+    finally:
+        for c in ctxs:
+            c.close()
+
+
 def test_wide_snp_matrix_and_the_informative_loci_limit(hc, oracle):
     # SNP matrices (conv_nucl, scripts/partitioning_HC.py:28-47) can have far more than 65,535 columns; only
     # the columns with >= 2 called alleles can mismatch, and only their number is bounded by uint16 distances
