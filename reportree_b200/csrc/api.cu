@@ -115,10 +115,16 @@ void rthc_free_distance_state(rthc_ctx *ctx)
     rthc_dev_free(ctx, &ctx->d_codes); rthc_dev_free(ctx, &ctx->d_codes32); rthc_dev_free(ctx, &ctx->d_planes);
     rthc_dev_free(ctx, &ctx->d_esc_code); rthc_dev_free(ctx, &ctx->d_esc_cnt); rthc_dev_free(ctx, &ctx->d_esc_list);
     rthc_dev_free(ctx, &ctx->d_grp_off); rthc_dev_free(ctx, &ctx->d_grp_np);
-    rthc_dev_free(ctx, &ctx->d_tiles); rthc_dev_free(ctx, &ctx->d_row_base);
-    rthc_dev_free(ctx, &ctx->d_owned_rows);
     rthc_dev_free(ctx, &ctx->d_cond_f64);
     ctx->have_profiles = ctx->have_dist = false;
+}
+// tile list, row offsets and owned rows depend on (n, rank, world, storage mode) only: they survive a new matrix of
+// the same shape (the tile list of C4 has 306,153 entries: 1.2 ms of host work + copies per call otherwise)
+void rthc_free_geometry(rthc_ctx *ctx)
+{
+    rthc_dev_free(ctx, &ctx->d_tiles); rthc_dev_free(ctx, &ctx->d_row_base);
+    rthc_dev_free(ctx, &ctx->d_owned_rows);
+    ctx->geom_n = -1;
 }
 void rthc_free_linkage_state(rthc_ctx *ctx)
 {
@@ -132,6 +138,7 @@ extern "C" void rthc_destroy(rthc_ctx *ctx)
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     rthc_free_distance_state(ctx);
+    rthc_free_geometry(ctx);
     rthc_dev_free(ctx, &ctx->d_cond);
     rthc_free_linkage_state(ctx);
     if (ctx->ev0) cudaEventDestroy(ctx->ev0);
@@ -219,6 +226,7 @@ extern "C" int rthc_finish_import(rthc_ctx *ctx)
     if (!ctx || !ctx->full_storage || !ctx->have_dist) return rthc_fail(ctx, RTHC_E_STATE, "rthc_finish_import: nothing to finish");
     RTHC_CUDA(ctx, cudaSetDevice(ctx->device));
     ctx->rank = 0; ctx->world = 1; ctx->full_storage = false;      // from here on: an ordinary full shard
+    ctx->geom_n = -1;                                              // the owned-row list below is not the sharded one
     ctx->h_owned_rows.resize((size_t)ctx->n);
     for (int64_t i = 0; i < ctx->n; ++i) ctx->h_owned_rows[(size_t)i] = (int32_t)i;
     int rc = rthc_dev_alloc(ctx, &ctx->d_owned_rows, (size_t)ctx->n);
@@ -241,6 +249,12 @@ extern "C" int rthc_set_single_algo(rthc_ctx *ctx, int algo)
 // geometry of the owned part of the condensed matrix + the tile list
 int rthc_setup_geometry(rthc_ctx *ctx, int64_t n)
 {
+    if (ctx->geom_n == n && ctx->geom_rank == ctx->rank && ctx->geom_world == ctx->world && ctx->geom_full == ctx->full_storage &&
+        ctx->d_tiles && ctx->d_row_base) {
+        ctx->n = n;
+        return 0;
+    }
+    rthc_free_geometry(ctx);
     ctx->n = n;
     ctx->n_pad = (n + RTHC_TILE - 1) / RTHC_TILE * RTHC_TILE;
     const int64_t B = ctx->n_pad / RTHC_TILE;
@@ -286,6 +300,7 @@ int rthc_setup_geometry(rthc_ctx *ctx, int64_t n)
         RTHC_CUDA(ctx, cudaMemcpyAsync(ctx->d_tiles, tiles.data(), sizeof(int2) * tiles.size(),
                                        cudaMemcpyHostToDevice, ctx->stream));
     RTHC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    ctx->geom_n = n; ctx->geom_rank = ctx->rank; ctx->geom_world = ctx->world; ctx->geom_full = ctx->full_storage;
     return 0;
 }
 

@@ -512,22 +512,10 @@ __device__ __forceinline__ void warp_min_all(unsigned long long &w, unsigned int
 
 // control block in global memory (written by block 0, thread 0 only)
 struct ChainCtl {
-    int64_t repairs;    // row scans by a single CTA inside a merge phase (no barrier of their own)
-    int64_t hits;       // chain steps, all answered by the nearest-neighbour cache
-    int64_t barriers;   // grid barriers executed (one per merge + one after the initial scan)
+    int64_t scans;      // row scans that had a barrier of their own (cache entry unknown when the chain needed it)
+    int64_t fused;      // scans of the next chain tip that rode on a merge's barrier
+    int64_t hits;       // chain steps answered by the cache
 };
-
-// element e of a 16-byte chunk of a row, as order-preserving bits
-template <typename T> __device__ __forceinline__ unsigned long long chunk_bits(const uint4 &q, int e);
-template <> __device__ __forceinline__ unsigned long long chunk_bits<uint16_t>(const uint4 &q, int e)
-{
-    const uint32_t w = e < 2 ? q.x : (e < 4 ? q.y : (e < 6 ? q.z : q.w));
-    return (unsigned long long)((w >> (16 * (e & 1))) & 0xFFFFu);
-}
-template <> __device__ __forceinline__ unsigned long long chunk_bits<double>(const uint4 &q, int e)
-{
-    return e == 0 ? (((unsigned long long)q.y << 32) | q.x) : (((unsigned long long)q.w << 32) | q.z);
-}
 
 // The two lexicographically smallest (value bits, index) entries of a row.  (~0, ~0) = none.
 struct __align__(16) Top2 {
@@ -564,57 +552,13 @@ __device__ __forceinline__ void block_top2(Top2 &t, Top2 *sh)
     __syncthreads();
 }
 
-// One CTA: the two smallest (D[r, j], j) over the live columns j of row r, j not in {skip1, skip2}
-// (16-byte loads, liveness from the CTA's shared-memory bitmap; RS_U chunks in flight per thread).
-// Result valid in warp 0.  `row` is 16-byte aligned (rows are pitched).
-#define RS_U 4
-template <typename T>
-__device__ __forceinline__ void cta_row_top2(const T *row, int64_t n, const uint32_t *s_live, int64_t skip1, int64_t skip2,
-                                             Top2 &t, Top2 *sh)
-{
-    constexpr int E = 16 / (int)sizeof(T);
-    t.clear();
-    const int64_t stride = (int64_t)SEQ_THREADS * E;
-    for (int64_t g0 = (int64_t)threadIdx.x * E; g0 < n; g0 += stride * RS_U) {
-        uint4 q[RS_U];
-        uint32_t lb[RS_U];
-#pragma unroll
-        for (int u = 0; u < RS_U; ++u) {
-            const int64_t j0 = g0 + u * stride;
-            lb[u] = 0;
-            if (j0 < n) {
-                lb[u] = (s_live[j0 >> 5] >> (j0 & 31)) & ((1u << E) - 1u);
-                if ((unsigned long long)(skip1 - j0) < (unsigned long long)E) lb[u] &= ~(1u << (int)(skip1 - j0));
-                if ((unsigned long long)(skip2 - j0) < (unsigned long long)E) lb[u] &= ~(1u << (int)(skip2 - j0));
-            }
-            if (lb[u]) q[u] = __ldcg(reinterpret_cast<const uint4 *>(row + j0));
-        }
-#pragma unroll
-        for (int u = 0; u < RS_U; ++u) {
-            if (!lb[u]) continue;
-            const int64_t j0 = g0 + u * stride;
-#pragma unroll
-            for (int e = 0; e < E; ++e)
-                if ((lb[u] >> e) & 1u) t.insert(chunk_bits<T>(q[u], e), (unsigned int)(j0 + e));
-        }
-    }
-    block_top2(t, sh);
-}
-
-// cache entry of a row: E1 = its nearest neighbour (exact, always); E2 = the runner-up when `act`, otherwise only a
-// bound: every entry of the row other than E1 (and E2 when act) is lexicographically greater than (w2, i2)
+// cache entry of a row: E1 = its nearest neighbour (exact) or i1 == ~0: unknown; E2 = the runner-up when `act`,
+// otherwise only a bound: every entry of the row other than E1 (and E2 when act) is lexicographically greater
+// than (w2, i2)
 struct __align__(16) NNEntry {
     unsigned long long w1, w2;
     unsigned int i1, i2, act, pad;
 };
-__device__ __forceinline__ NNEntry nn_load(const NNEntry *p)
-{
-    const uint4 lo = __ldcg(reinterpret_cast<const uint4 *>(p)), hi = __ldcg(reinterpret_cast<const uint4 *>(p) + 1);
-    NNEntry e;
-    e.w1 = ((unsigned long long)lo.y << 32) | lo.x; e.w2 = ((unsigned long long)lo.w << 32) | lo.z;
-    e.i1 = hi.x; e.i2 = hi.y; e.act = hi.z; e.pad = 0;
-    return e;
-}
 __device__ __forceinline__ void nn_store(NNEntry *p, unsigned long long w1, unsigned int i1, unsigned long long w2, unsigned int i2,
                                          unsigned int act)
 {
@@ -622,84 +566,84 @@ __device__ __forceinline__ void nn_store(NNEntry *p, unsigned long long w1, unsi
     __stcg(reinterpret_cast<uint4 *>(p) + 1, make_uint4(i1, i2, act, 0u));
 }
 
-struct ChainBc {                // the merge decision of warp 0, broadcast through shared memory
-    unsigned long long dmin, gw1, gw2;      // g*: cache entry of `grown` (registers of warp 0: not published yet)
-    unsigned int gi1, gi2, gact;
-    int32_t a, b, na, nb, grown, grown_size;
+#define NNC_MAX_CLUSTER 16
+#define NNC_SCAN 1
+#define NNC_MERGE 2
+struct ChainBc {                // the decision of warp 0, broadcast through shared memory
+    unsigned long long dmin;
+    int32_t what, x, a, b, na, nb, p;
 };
 
-// The merge loop.  scipy's chain step asks for the nearest neighbour of the chain tip x: the previous chain
-// element if it ties the minimum, else the lowest index of the minimum of row x.  A grid-wide row scan costs a
-// grid barrier (2.4 us + the reductions around it) however short the row is, so the kernel keeps for EVERY live
-// row r its exact nearest neighbour E1 = min over live i != r of (D[r, i], i), and a chain step is a look-up:
-// warp 0 of every CTA walks the chain by itself (three L2 loads in three lanes, no block barrier; the distance to
-// the previous element and the sizes of the chain elements ride along in the CTA's private chain arrays) while the
-// other warps wait for its merge decision.  Only a merge (a dies, b = a u b) has a grid barrier, and the merge
-// phase restores the invariant before it.  The thread that writes the new D[i, b] updates the entry of row i from
-// what it knows: E1, the runner-up E2 (or, when E2 is not known, a bound below every other entry) and the new entry
-// N = (D[i, b], b).  Entries of a and b leave the candidate set, N joins it; the smallest candidate is the new E1
-// if it does not exceed the bound (everything unknown lies above the bound), the next one the new E2 under the same
-// condition.  Only when E1 was a or b, no runner-up is left and N exceeds the bound does the row need a scan, and
-// then the CTA of that thread rescans it by itself (a row is <= 0.2 MB: one SM streams it in two or three
-// microseconds; columns a and b are skipped -- a is dead, b's new value is N -- so the scan reads nothing that this
-// phase writes).  With the runner-up about one row per merge needs that (C5: measured in `row_scans`), with E1 alone
-// 14 (complete, C5) to 75 (average, C3) did.  The top-2 of the new row b is reduced per CTA and combined after the
-// barrier.  A look-up returns the same (value, lowest index, previous-wins) triple as scipy's scan, so Z stays
-// byte-identical.  nn[] is double-buffered by merge parity (a CTA still walking the chain must not see entries that a
-// faster CTA has already updated); every CTA keeps the liveness bitmap in shared memory; size[] and nn[] of the
-// cluster created by the last merge are carried in registers until the next barrier has published them; W is
-// pitched so that every row starts on a 16-byte boundary.
+// The merge loop: scipy's nn_chain inside ONE thread-block cluster.
+//
+// A chain step asks for the nearest neighbour of the chain tip x: the previous chain element if it ties the minimum,
+// else the lowest index of the minimum of row x.  The loop is a chain of dependent steps, so what it costs is
+// latency, and the grid-wide version paid 5.5 us per step for a cooperative grid barrier and the L2 round trips
+// around it (round 1: 0.3 % of the HBM roofline).  Here
+//   * the loop runs in one cluster of 16 CTAs (8 where 16 cannot be scheduled): barrier.cluster instead of a grid
+//     barrier, and the per-CTA results of a reduction are written straight into the shared memory of every CTA of
+//     the cluster (st.shared::cluster), so nothing is re-read through L2 after a barrier.  A row is <= 0.2 MB:
+//     16 SMs stream it in about a microsecond, more SMs would only wait longer at the barrier;
+//   * every row keeps a cache entry: its exact nearest neighbour E1 and the runner-up E2 (or a bound below every
+//     other entry).  A chain step whose tip has a known E1 is a look-up by warp 0 of every CTA (no barrier; the
+//     distance to the previous element and the sizes of the chain elements ride along in the CTA's private chain
+//     arrays, so no matrix element is read).  A merge (a dies, b = a u b) visits every live row i to write D[i, b];
+//     the same thread updates the entry of row i from E1, E2 / the bound and the new entry N = (D[i, b], b): entries
+//     of a and b leave the candidate set, N joins it, the smallest candidate is the new E1 if it does not exceed the
+//     bound (everything unknown lies above the bound), the next one the new E2 under the same condition; otherwise
+//     E1 becomes unknown and the row is scanned over the cluster when (if) the chain reaches it;
+//   * the merge's barrier also carries the top-2 of the new row b and the scan of p, the chain element that becomes
+//     the tip after the merge (its neighbour was a or b by construction): row p only changes in column b, whose new
+//     value the thread that owns i == p has, so the scan reads nothing that the phase writes.
+// A look-up returns the same (value, lowest index, previous-wins) triple as scipy's scan, so Z stays byte-identical
+// (tests/test_gpu_exact_linkage.py, the C3 / C5 goldens).  Cache entries and size[] of rows touched after the last
+// barrier are carried in the registers of warp 0 (`grown`, `known`); a barrier before every merge pass makes the
+// leader's earlier stores visible to the pass.  W is pitched so that every row starts on a 16-byte boundary.
 template <typename T>
 __global__ void __launch_bounds__(SEQ_THREADS, 1)
 rthc_nn_chain_kernel(T *W, int64_t n, int64_t pitch, int method, int32_t *size, int32_t *chains, unsigned long long *chains_d,
-                     int32_t *chains_s, Top2 *slots, NNEntry *nn2, int32_t *ex, int32_t *ey, double *ew, ChainCtl *ctl)
+                     int32_t *chains_s, NNEntry *nn, int32_t *ex, int32_t *ey, double *ew, ChainCtl *ctl)
 {
-    cg::grid_group grid = cg::this_grid();
+    cg::cluster_group cluster = cg::this_cluster();
+    const int C = (int)cluster.num_blocks(), rank = (int)cluster.block_rank();
     extern __shared__ uint32_t s_live[];                         // bit j: cluster j is alive
     __shared__ Top2 sh[SEQ_THREADS / 32];
-    __shared__ ChainBc bc[2];                                    // alternating: one __syncthreads per merge
-    __shared__ int32_t s_bad_i[SEQ_THREADS];                     // rows of this CTA that need a scan
-    __shared__ unsigned long long s_bad_w[SEQ_THREADS];          // ... and their new D[i, b]
-    __shared__ int s_nbad;
-    const int nblocks = gridDim.x;
+    __shared__ Top2 slotA[2][NNC_MAX_CLUSTER], slotB[2][NNC_MAX_CLUSTER];      // written by every CTA of the cluster
+    __shared__ ChainBc bc[2];                                    // alternating: one __syncthreads per decision
     const int tid = threadIdx.x, lane = tid & 31;
     const bool w0 = tid < 32;
-    const int64_t gthreads = (int64_t)nblocks * SEQ_THREADS;
-    const bool leader = blockIdx.x == 0 && tid == 0;
+    const int64_t TT = (int64_t)C * SEQ_THREADS, gt = (int64_t)rank * SEQ_THREADS + tid;
+    const bool leader = rank == 0 && tid == 0;
     // this CTA's copy of the chain, touched by its thread 0 only: element, D[element, previous element], size
-    int32_t *chain = chains + (int64_t)blockIdx.x * n;
-    unsigned long long *chain_d = chains_d + (int64_t)blockIdx.x * n;
-    int32_t *chain_s = chains_s + (int64_t)blockIdx.x * n;
+    int32_t *chain = chains + (int64_t)rank * n;
+    unsigned long long *chain_d = chains_d + (int64_t)rank * n;
+    int32_t *chain_s = chains_s + (int64_t)rank * n;
 
-    // ---- initial state: everything alive, the entry of every row by the CTA that owns it -----------
     const int64_t live_words = (pitch + 31) / 32;
     for (int64_t w = tid; w < live_words; w += SEQ_THREADS) {
         const int64_t j = w * 32;
         s_live[w] = j + 32 <= n ? 0xFFFFFFFFu : (j >= n ? 0u : ((1u << (int)(n - j)) - 1u));
     }
-    if (tid == 0) s_nbad = 0;
+    for (int64_t i = gt; i < n; i += TT) nn_store(&nn[i], ~0ull, ~0u, ~0ull, ~0u, 0u);      // nothing known yet
     __syncthreads();
-    for (int64_t r = blockIdx.x; r < n; r += nblocks) {
-        Top2 t;
-        cta_row_top2<T>(W + r * pitch, n, s_live, r, -1, t, sh);
-        if (tid == 0) nn_store(&nn2[r], t.w1, t.i1, t.w2, t.i2, t.i2 != ~0u);
-    }
-    grid.sync();
+    cluster.sync();
 
     // walk state: warp 0 only (uniform over its lanes)
-    int64_t len = 0, first_live = 0, hits = 0;
+    int64_t len = 0, first_live = 0, hits = 0, scans = 0, fused = 0;
     int32_t x = -1, prev = -1, sx = 0, sprev = 0;
     unsigned long long dprev = ~0ull;                            // D[x, prev]
     bool need_sx = false;
-    int32_t dead = -1, grown = -1, grown_size = 0;              // last merge, until the next barrier publishes size[]
-    unsigned long long gw1 = ~0ull, gw2 = ~0ull;                 // entry of `grown`
-    unsigned int gi1 = ~0u, gi2 = ~0u, gact = 0;
+    // rows whose entry / size was produced after the last barrier (not yet visible in global memory)
+    int32_t dead = -1, grown = -1, grown_size = 0, known = -1;
+    unsigned long long gw1 = ~0ull, kw1 = ~0ull;
+    unsigned int gi1 = ~0u, ki1 = ~0u;
+    int32_t nx = -1, nprev = -1, nsx = 0, nsprev = 0;            // the chain below the tip, prefetched
+    unsigned long long ndprev = ~0ull;
     // all threads
-    int64_t step = 0, repairs = 0;
-    int q = 0, cur = 0;
+    int64_t step = 0;
+    int q = 0;
 
-    for (int64_t k = 0; k < n - 1; ++k) {
-        const NNEntry *nn = nn2 + (int64_t)cur * n;
+    for (int64_t k = 0; k < n - 1;) {
         if (w0) {
             for (;;) {
                 if (len == 0) {                                  // lowest live index from the bitmap
@@ -719,11 +663,20 @@ rthc_nn_chain_kernel(T *W, int64_t n, int64_t pitch, int method, int32_t *size, 
                     x = (int32_t)first_live; prev = -1; len = 1; dprev = ~0ull; need_sx = true;
                     if (lane == 0) chain[0] = x;
                 }
-                // look-up: three lanes, three independent L2 loads
-                unsigned long long v = 0;
-                if (lane == 0) v = x == grown ? gw1 : __ldcg(&nn[x].w1);
-                else if (lane == 1) v = x == grown ? (unsigned long long)gi1 : (unsigned long long)__ldcg(&nn[x].i1);
-                else if (lane == 2 && need_sx) v = (unsigned long long)(x == dead ? 0 : (x == grown ? grown_size : __ldcg(&size[x])));
+                // look-up: independent loads in separate lanes (entry, size, and the chain below the tip in case
+                // this step ends in a merge)
+                // (the chain arrays are private to lane 0, which wrote them: program order keeps them coherent)
+                unsigned long long v = 0, c3d = ~0ull;
+                int32_t c3 = -1, c3s = 0, c4 = -1, c4s = 0;
+                if (lane == 0) {
+                    v = x == grown ? gw1 : (x == known ? kw1 : __ldcg(&nn[x].w1));
+                    if (len >= 3) { c3 = chain[len - 3]; c3s = chain_s[len - 3]; }
+                    if (len >= 4) { c4 = chain[len - 4]; c4s = chain_s[len - 4]; c3d = chain_d[len - 3]; }
+                } else if (lane == 1) {
+                    v = x == grown ? (unsigned long long)gi1 : (x == known ? (unsigned long long)ki1 : (unsigned long long)__ldcg(&nn[x].i1));
+                } else if (lane == 2 && need_sx) {
+                    v = (unsigned long long)(x == dead ? 0 : (x == grown ? grown_size : __ldcg(&size[x])));
+                }
                 const unsigned long long cw = __shfl_sync(0xffffffffu, v, 0);
                 const unsigned int ci = (unsigned int)__shfl_sync(0xffffffffu, v, 1);
                 if (need_sx) {
@@ -731,8 +684,15 @@ rthc_nn_chain_kernel(T *W, int64_t n, int64_t pitch, int method, int32_t *size, 
                     if (lane == 0) chain_s[len - 1] = sx;
                     need_sx = false;
                 }
-                ++hits;
+                nx = __shfl_sync(0xffffffffu, c3, 0); nsx = __shfl_sync(0xffffffffu, c3s, 0);
+                nprev = __shfl_sync(0xffffffffu, c4, 0); nsprev = __shfl_sync(0xffffffffu, c4s, 0);
+                ndprev = __shfl_sync(0xffffffffu, c3d, 0);
                 RTHC_DEV_ASSERT(x >= 0 && x < n && ((s_live[x >> 5] >> (x & 31)) & 1u));
+                if (ci == ~0u) {                                 // unknown: scan row x over the cluster
+                    if (lane == 0) { bc[q].what = NNC_SCAN; bc[q].x = x; }
+                    break;
+                }
+                ++hits;
                 RTHC_DEV_ASSERT(ci < (unsigned int)n && ci != (unsigned int)x && ((s_live[ci >> 5] >> (ci & 31)) & 1u));
                 RTHC_DEV_ASSERT(sx > 0 && (len == 1 || sprev > 0));
                 int32_t y = (int32_t)ci;
@@ -743,9 +703,9 @@ rthc_nn_chain_kernel(T *W, int64_t n, int64_t pitch, int method, int32_t *size, 
                     if (lane == 0) {
                         ChainBc &o = bc[q];
                         const bool xs = x < y;                   // a dies, b survives (scipy: x < y swap)
+                        o.what = NNC_MERGE;
                         o.a = xs ? x : y; o.b = xs ? y : x; o.na = xs ? sx : sprev; o.nb = xs ? sprev : sx;
-                        o.dmin = dmin; o.gw1 = gw1; o.gw2 = gw2; o.gi1 = gi1; o.gi2 = gi2; o.gact = gact;
-                        o.grown = grown; o.grown_size = grown_size;
+                        o.dmin = dmin; o.p = nx;
                     }
                     break;
                 }
@@ -756,123 +716,132 @@ rthc_nn_chain_kernel(T *W, int64_t n, int64_t pitch, int method, int32_t *size, 
             }
         }
         __syncthreads();
-        const int32_t a = bc[q].a, b = bc[q].b, na = bc[q].na, nb = bc[q].nb;
-        const int32_t pgrown = bc[q].grown, pgrown_size = bc[q].grown_size;
-        const unsigned long long dminb = bc[q].dmin, pgw1 = bc[q].gw1, pgw2 = bc[q].gw2;
-        const unsigned int pgi1 = bc[q].gi1, pgi2 = bc[q].gi2, pgact = bc[q].gact;
-        q ^= 1;
-        // thread 0: the chain tip after the pop, in flight while the pass runs
-        int32_t nx = -1, nprev = -1, nsx = 0, nsprev = 0;
-        unsigned long long ndprev = ~0ull;
-        if (tid == 0) {
-            s_live[a >> 5] &= ~(1u << (a & 31));
-            if (len >= 3) { nx = chain[len - 3]; nsx = chain_s[len - 3]; }
-            if (len >= 4) { nprev = chain[len - 4]; nsprev = chain_s[len - 4]; ndprev = chain_d[len - 3]; }
+        const int what = bc[q].what;
+        const int par = (int)(step & 1);
+        if (what == NNC_SCAN) {
+            // ---- scan row x: the two smallest (D[x, i], i) over live i != x ---------------------------
+            const int32_t xr = bc[q].x;
+            q ^= 1;
+            const T *row = W + (int64_t)xr * pitch;
+            Top2 t;
+            t.clear();
+            for (int64_t i0 = gt; i0 < n; i0 += TT * 8) {        // up to 8 elements of this thread in flight
+                T d[8];
+                bool ok[8];
+#pragma unroll
+                for (int u = 0; u < 8; ++u) {
+                    const int64_t i = i0 + u * TT;
+                    ok[u] = i < n && i != xr && ((s_live[i >> 5] >> (i & 31)) & 1u);
+                    if (ok[u]) d[u] = __ldcg(&row[i]);
+                }
+#pragma unroll
+                for (int u = 0; u < 8; ++u)
+                    if (ok[u]) t.insert(order_bits(d[u]), (unsigned int)(i0 + u * TT));
+            }
+            block_top2(t, sh);
+            if (w0 && lane < C) *cluster.map_shared_rank(&slotA[par][rank], lane) = t;      // lane l publishes to CTA l
+            cluster.sync();
+            ++step;
+            if (w0) {
+                if (lane < C) t = slotA[par][lane]; else t.clear();
+                warp_top2(t);
+                known = xr; kw1 = t.w1; ki1 = t.i1;
+                if (leader) nn_store(&nn[xr], t.w1, t.i1, t.w2, t.i2, t.i2 != ~0u);
+                dead = -1;                                       // the barrier published the last merge's sizes
+                ++scans;
+            }
+            continue;
         }
+        // ---- merge a and b ----------------------------------------------------------------------------
+        const int32_t a = bc[q].a, b = bc[q].b, na = bc[q].na, nb = bc[q].nb, p = bc[q].p;
+        const unsigned long long dminb = bc[q].dmin;
+        q ^= 1;
+        if (tid == 0) s_live[a >> 5] &= ~(1u << (a & 31));
         if (leader) { ex[k] = a; ey[k] = b; ew[k] = from_bits(dminb, T()); }
-        __syncthreads();                                         // bitmap without a; s_nbad == 0 from the last phase
+        cluster.sync();                       // every CTA has left the walk; the leader's earlier stores are visible
         const T *ra = W + (int64_t)a * pitch;
         T *rb = W + (int64_t)b * pitch;
-        NNEntry *nxt = nn2 + (int64_t)(cur ^ 1) * n;
+        const T *rp = W + (int64_t)(p >= 0 ? p : 0) * pitch;
         const double dab = from_bits(dminb, T());
-        Top2 tb;
-        tb.clear();
-        for (int64_t i0 = (int64_t)blockIdx.x * SEQ_THREADS; i0 < n; i0 += gthreads) {
-            const int64_t i = i0 + tid;
-            if (i < n && i != b && ((s_live[i >> 5] >> (i & 31)) & 1u)) {
-                // every load of the element first (the stores below may alias them as far as the compiler knows)
-                const T da = __ldcg(&ra[i]), db = __ldcg(&rb[i]);
-                const uint4 elo = __ldcg(reinterpret_cast<const uint4 *>(&nn[i])), ehi = __ldcg(reinterpret_cast<const uint4 *>(&nn[i]) + 1);
-                const int32_t szi = __ldcg(&size[i]);
-                const bool ig = i == pgrown;                     // the previous merge's cluster: not published yet
-                const int32_t ni = ig ? pgrown_size : szi;
-                struct { unsigned long long w1, w2; unsigned int i1, i2, act; } e;
-                e.w1 = ig ? pgw1 : (((unsigned long long)elo.y << 32) | elo.x);
-                e.w2 = ig ? pgw2 : (((unsigned long long)elo.w << 32) | elo.z);
-                e.i1 = ig ? pgi1 : ehi.x; e.i2 = ig ? pgi2 : ehi.y; e.act = ig ? pgact : ehi.z;
-                const T v = lance_williams<T>(method, da, db, dab, na, nb, ni);
+        Top2 tb, tp;
+        tb.clear(); tp.clear();
+        constexpr int PB = sizeof(T) == 8 ? 2 : 3;               // elements of this thread in flight (register budget)
+        for (int64_t i0 = gt; i0 < n; i0 += TT * PB) {
+            T da[PB], db[PB], dp[PB];
+            uint4 elo[PB], ehi[PB];
+            int32_t szi[PB];
+            bool ok[PB];
+#pragma unroll
+            for (int u = 0; u < PB; ++u) {
+                const int64_t i = i0 + u * TT;
+                ok[u] = i < n && i != b && ((s_live[i >> 5] >> (i & 31)) & 1u);
+                if (ok[u]) {
+                    da[u] = __ldcg(&ra[i]); db[u] = __ldcg(&rb[i]);
+                    elo[u] = __ldcg(reinterpret_cast<const uint4 *>(&nn[i])); ehi[u] = __ldcg(reinterpret_cast<const uint4 *>(&nn[i]) + 1);
+                    szi[u] = __ldcg(&size[i]);
+                    if (p >= 0) dp[u] = __ldcg(&rp[i]);
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < PB; ++u) {
+                if (!ok[u]) continue;
+                const int64_t i = i0 + u * TT;
+                const T v = lance_williams<T>(method, da[u], db[u], dab, na, nb, szi[u]);
                 rb[i] = v;                       // row b (contiguous)
                 W[i * pitch + b] = v;            // column b (symmetric copy)
                 const unsigned long long ob = order_bits(v);
                 tb.insert(ob, (unsigned int)i);
+                if (i == p) { tp.insert(ob, (unsigned int)b); continue; }       // row p is rescanned as a whole
+                if (p >= 0) tp.insert(order_bits(dp[u]), (unsigned int)i);
+                const unsigned long long w1 = ((unsigned long long)elo[u].y << 32) | elo[u].x;
+                const unsigned long long w2 = ((unsigned long long)elo[u].w << 32) | elo[u].z;
+                const unsigned int i1 = ehi[u].x, i2 = ehi[u].y, act = ehi[u].z;
+                if (i1 == ~0u) continue;                                         // unknown stays unknown
                 // candidates: N = (ob, b), E1 unless it was a or b, E2 if known and not a or b; bound = (w2, i2)
-                const bool h1 = e.i1 == (unsigned int)a || e.i1 == (unsigned int)b;
-                const bool k2 = e.act && !(e.i2 == (unsigned int)a || e.i2 == (unsigned int)b);
+                const bool h1 = i1 == (unsigned int)a || i1 == (unsigned int)b;
+                const bool k2 = act && !(i2 == (unsigned int)a || i2 == (unsigned int)b);
                 Top2 c;
                 c.clear();
                 c.insert(ob, (unsigned int)b);
-                if (!h1) c.insert(e.w1, e.i1);
-                if (k2) c.insert(e.w2, e.i2);                                    // only the two smallest matter
-                if (!slot_less(e.w2, e.i2, c.w1, c.i1)) {                        // c1 <= bound: exact
-                    const bool second = c.i2 != ~0u && !slot_less(e.w2, e.i2, c.w2, c.i2);
-                    nn_store(&nxt[i], c.w1, c.i1, second ? c.w2 : e.w2, second ? c.i2 : e.i2, second ? 1u : 0u);
+                if (!h1) c.insert(w1, i1);
+                if (k2) c.insert(w2, i2);                                        // only the two smallest matter
+                if (!slot_less(w2, i2, c.w1, c.i1)) {                            // c1 <= bound: exact
+                    const bool second = c.i2 != ~0u && !slot_less(w2, i2, c.w2, c.i2);
+                    nn_store(&nn[i], c.w1, c.i1, second ? c.w2 : w2, second ? c.i2 : i2, second ? 1u : 0u);
                 } else {
-                    const int slot = atomicAdd(&s_nbad, 1);
-                    RTHC_DEV_ASSERT(slot >= 0 && slot < SEQ_THREADS);
-                    s_bad_i[slot] = (int32_t)i; s_bad_w[slot] = ob;
+                    nn_store(&nn[i], ~0ull, ~0u, ~0ull, ~0u, 0u);
                 }
             }
-            __syncthreads();
-            const int nbad = s_nbad;
-            for (int e = 0; e < nbad; ++e) {                     // this CTA rescans the rows it could not patch
-                const int32_t r = s_bad_i[e];
-                Top2 t;
-                cta_row_top2<T>(W + (int64_t)r * pitch, n, s_live, r, b, t, sh);
-                if (tid == 0) {
-                    t.insert(s_bad_w[e], (unsigned int)b);
-                    RTHC_DEV_ASSERT(t.i1 < (unsigned int)n && t.i1 != (unsigned int)r && t.i1 != (unsigned int)a);
-                    nn_store(&nxt[r], t.w1, t.i1, t.w2, t.i2, t.i2 != ~0u);
-                }
-            }
-            repairs += nbad;
-            __syncthreads();
-            if (tid == 0) s_nbad = 0;
-            __syncthreads();
         }
         block_top2(tb, sh);
-        Top2 *sb = slots + (step & 1) * nblocks;
-        if (tid == 0) sb[blockIdx.x] = tb;
-        grid.sync();                          // row/column b and the other nn copy are visible
-        ++step;
-        cur ^= 1;
-        if (w0) {
-            // entry of the new row b: warp 0 combines the CTA top-2s (all loads of a trip in flight together)
-            Top2 t;
-            t.clear();
-            for (int c0 = 0; c0 < nblocks; c0 += 32 * 5) {       // 148 CTAs: one trip, five entries per lane in flight
-                uint4 lo[5], hi[5];
-#pragma unroll
-                for (int u = 0; u < 5; ++u) {
-                    const int c = c0 + 32 * u + lane;
-                    if (c < nblocks) {
-                        lo[u] = __ldcg(reinterpret_cast<const uint4 *>(&sb[c]));
-                        hi[u] = __ldcg(reinterpret_cast<const uint4 *>(&sb[c]) + 1);
-                    }
-                }
-#pragma unroll
-                for (int u = 0; u < 5; ++u) {
-                    const int c = c0 + 32 * u + lane;
-                    if (c < nblocks) {
-                        t.insert(((unsigned long long)lo[u].y << 32) | lo[u].x, hi[u].x);
-                        t.insert(((unsigned long long)lo[u].w << 32) | lo[u].z, hi[u].y);
-                    }
-                }
-            }
-            warp_top2(t);
-            gw1 = t.w1; gi1 = t.i1; gw2 = t.w2; gi2 = t.i2; gact = t.i2 != ~0u;
-            if (leader) { nn_store(&nxt[b], gw1, gi1, gw2, gi2, gact); size[a] = 0; size[b] = na + nb; }
-            dead = a; grown = b; grown_size = na + nb;
-            len -= 2;
-            if (len > 0) {                                       // the tip after the pop, from thread 0's registers
-                x = __shfl_sync(0xffffffffu, nx, 0); prev = __shfl_sync(0xffffffffu, nprev, 0);
-                sx = __shfl_sync(0xffffffffu, nsx, 0); sprev = __shfl_sync(0xffffffffu, nsprev, 0);
-                dprev = __shfl_sync(0xffffffffu, ndprev, 0);
-                need_sx = false;
-            }
+        if (w0 && lane < C) *cluster.map_shared_rank(&slotA[par][rank], lane) = tb;
+        if (p >= 0) {
+            block_top2(tp, sh);
+            if (w0 && lane < C) *cluster.map_shared_rank(&slotB[par][rank], lane) = tp;
         }
+        cluster.sync();                       // row / column b, the cache entries and the slots are visible
+        ++step;
+        if (w0) {
+            Top2 t;
+            if (lane < C) t = slotA[par][lane]; else t.clear();
+            warp_top2(t);
+            gw1 = t.w1; gi1 = t.i1;
+            if (leader) { nn_store(&nn[b], t.w1, t.i1, t.w2, t.i2, t.i2 != ~0u); size[a] = 0; size[b] = na + nb; }
+            dead = a; grown = b; grown_size = na + nb;
+            known = -1;
+            if (p >= 0) {
+                if (lane < C) t = slotB[par][lane]; else t.clear();
+                warp_top2(t);
+                known = p; kw1 = t.w1; ki1 = t.i1;
+                if (leader) nn_store(&nn[p], t.w1, t.i1, t.w2, t.i2, t.i2 != ~0u);
+                ++fused;
+            }
+            len -= 2;
+            if (len > 0) { x = nx; prev = nprev; sx = nsx; sprev = nsprev; dprev = ndprev; need_sx = false; }
+        }
+        ++k;
     }
-    if (tid == 0) atomicAdd((unsigned long long *)&ctl->repairs, (unsigned long long)repairs);      // per-CTA counts
-    if (leader) { ctl->hits = hits; ctl->barriers = step + 1; }
+    if (leader) { ctl->scans = scans; ctl->fused = fused; ctl->hits = hits; }
 }
 
 template <typename T, typename S>
@@ -885,20 +854,17 @@ static int run_nn_chain(rthc_ctx *ctx, const S *d_cond, int method, std::vector<
     int32_t *d_size = nullptr, *d_chain = nullptr, *d_chain_s = nullptr, *d_ex = nullptr, *d_ey = nullptr;
     unsigned long long *d_chain_d = nullptr;
     double *d_ew = nullptr;
-    Top2 *d_slots = nullptr;
     NNEntry *d_nn = nullptr;
     ChainCtl *d_ctl = nullptr;
-    int nblocks = ctx->sm_count;
     int rc;
     const size_t smem = sizeof(uint32_t) * (size_t)((pitch + 31) / 32 + 1);
     if (smem > 160u * 1024u) return rthc_fail(ctx, RTHC_E_RANGE, "merge loop: %lld samples exceed the liveness bitmap", (long long)n);
     if ((rc = rthc_dev_alloc(ctx, &d_W, (size_t)(n * pitch)))) return rc;
     if ((rc = rthc_dev_alloc(ctx, &d_size, (size_t)n))) return rc;
-    if ((rc = rthc_dev_alloc(ctx, &d_chain, (size_t)n * (size_t)nblocks))) return rc;
-    if ((rc = rthc_dev_alloc(ctx, &d_chain_s, (size_t)n * (size_t)nblocks))) return rc;
-    if ((rc = rthc_dev_alloc(ctx, &d_chain_d, (size_t)n * (size_t)nblocks))) return rc;
-    if ((rc = rthc_dev_alloc(ctx, &d_slots, (size_t)2 * nblocks))) return rc;
-    if ((rc = rthc_dev_alloc(ctx, &d_nn, (size_t)2 * (size_t)n))) return rc;
+    if ((rc = rthc_dev_alloc(ctx, &d_chain, (size_t)n * NNC_MAX_CLUSTER))) return rc;
+    if ((rc = rthc_dev_alloc(ctx, &d_chain_s, (size_t)n * NNC_MAX_CLUSTER))) return rc;
+    if ((rc = rthc_dev_alloc(ctx, &d_chain_d, (size_t)n * NNC_MAX_CLUSTER))) return rc;
+    if ((rc = rthc_dev_alloc(ctx, &d_nn, (size_t)n))) return rc;
     if ((rc = rthc_dev_alloc(ctx, &d_ex, (size_t)m))) return rc;
     if ((rc = rthc_dev_alloc(ctx, &d_ey, (size_t)m))) return rc;
     if ((rc = rthc_dev_alloc(ctx, &d_ew, (size_t)m))) return rc;
@@ -912,12 +878,31 @@ static int run_nn_chain(rthc_ctx *ctx, const S *d_cond, int method, std::vector<
         RTHC_CUDA(ctx, cudaMemsetAsync(d_ctl, 0, sizeof(ChainCtl), ctx->stream));
         RTHC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     }
-    int64_t nn = n, pp = pitch;
-    void *args[] = {(void *)&d_W, (void *)&nn, (void *)&pp, (void *)&method, (void *)&d_size, (void *)&d_chain, (void *)&d_chain_d,
-                    (void *)&d_chain_s, (void *)&d_slots, (void *)&d_nn, (void *)&d_ex, (void *)&d_ey, (void *)&d_ew, (void *)&d_ctl};
-    RTHC_CUDA(ctx, cudaFuncSetAttribute(rthc_nn_chain_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    RTHC_CUDA(ctx, cudaLaunchCooperativeKernel((void *)rthc_nn_chain_kernel<T>, dim3(nblocks), dim3(SEQ_THREADS), args, smem,
-                                               ctx->stream));
+    auto kern = rthc_nn_chain_kernel<T>;
+    RTHC_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    cudaError_t ce = cudaErrorInvalidConfiguration;
+    for (int C = NNC_MAX_CLUSTER; C >= 1 && ce != cudaSuccess; C >>= 1) {       // one cluster of 16, 8, ... CTAs
+        if (C > 8 && cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) != cudaSuccess) {
+            cudaGetLastError();
+            continue;
+        }
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3((unsigned)C);
+        cfg.blockDim = dim3(SEQ_THREADS);
+        cfg.dynamicSmemBytes = smem;
+        cfg.stream = ctx->stream;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeClusterDimension;
+        attr[0].val.clusterDim.x = (unsigned)C; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+        cfg.attrs = attr; cfg.numAttrs = 1;
+        int clusters = 0;
+        ce = cudaOccupancyMaxActiveClusters(&clusters, kern, &cfg);
+        if (ce == cudaSuccess && clusters < 1) ce = cudaErrorInvalidConfiguration;
+        if (ce == cudaSuccess)
+            ce = cudaLaunchKernelEx(&cfg, kern, d_W, n, pitch, method, d_size, d_chain, d_chain_d, d_chain_s, d_nn, d_ex, d_ey, d_ew, d_ctl);
+        if (ce != cudaSuccess) cudaGetLastError();
+    }
+    if (ce != cudaSuccess) return rthc_fail(ctx, RTHC_E_CUDA, "merge loop: no thread-block cluster could be launched (%s)", cudaGetErrorString(ce));
     ctx->launches++;
     ex.resize((size_t)m); ey.resize((size_t)m); ew.resize((size_t)m);
     ChainCtl ctl;
@@ -926,12 +911,12 @@ static int run_nn_chain(rthc_ctx *ctx, const S *d_cond, int method, std::vector<
     RTHC_CUDA(ctx, cudaMemcpyAsync(ew.data(), d_ew, sizeof(double) * (size_t)m, cudaMemcpyDeviceToHost, ctx->stream));
     RTHC_CUDA(ctx, cudaMemcpyAsync(&ctl, d_ctl, sizeof(ChainCtl), cudaMemcpyDeviceToHost, ctx->stream));
     RTHC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-    ctx->row_scans = ctl.repairs + n;               // CTA-local rescans + the initial scan of every row
-    ctx->chain_full_scans = ctl.barriers;           // grid barriers (info[9])
+    ctx->row_scans = ctl.scans + ctl.fused;         // row scans: own barrier + fused with a merge
+    ctx->chain_full_scans = ctl.scans + 2 * m;      // cluster barriers (info[9]): one per scan, two per merge
     ctx->chain_cache_hits = ctl.hits;
-    rthc_dev_free(ctx, &d_W); rthc_dev_free(ctx, &d_size); rthc_dev_free(ctx, &d_chain); rthc_dev_free(ctx, &d_slots);
-    rthc_dev_free(ctx, &d_chain_s); rthc_dev_free(ctx, &d_chain_d); rthc_dev_free(ctx, &d_nn); rthc_dev_free(ctx, &d_ex); rthc_dev_free(ctx, &d_ey); rthc_dev_free(ctx, &d_ew);
-    rthc_dev_free(ctx, &d_ctl);
+    rthc_dev_free(ctx, &d_W); rthc_dev_free(ctx, &d_size); rthc_dev_free(ctx, &d_chain);
+    rthc_dev_free(ctx, &d_chain_s); rthc_dev_free(ctx, &d_chain_d); rthc_dev_free(ctx, &d_nn);
+    rthc_dev_free(ctx, &d_ex); rthc_dev_free(ctx, &d_ey); rthc_dev_free(ctx, &d_ew); rthc_dev_free(ctx, &d_ctl);
     return 0;
 }
 

@@ -51,6 +51,7 @@ struct rthc_ctx {
     // escape coding (recode.cu): per locus the escape code (0: none), the number of escaped cells and their samples
     int32_t *d_esc_code = nullptr, *d_esc_cnt = nullptr, *d_esc_list = nullptr;
     int64_t escape_loci = 0, escape_cells = 0, escape_pairs = 0, max_alleles_raw = -1;
+    int64_t geom_n = -1; int geom_rank = -1, geom_world = -1; bool geom_full = false;      // what d_tiles / d_row_base were built for
     bool recode_general = false;   // last re-code left the fast path (an allele id >= 2^14 somewhere)
     uint32_t *d_codes32 = nullptr; // same, used INSTEAD of d_codes when a locus has more than 65,535 called alleles
     uint32_t *d_planes = nullptr;  // [plane_rows][n_pad]
@@ -163,6 +164,7 @@ template <typename T> inline int rthc_dev_alloc(rthc_ctx *ctx, T **p, size_t cou
 
 // context state helpers (api.cu)
 void rthc_free_distance_state(rthc_ctx *ctx);
+void rthc_free_geometry(rthc_ctx *ctx);
 void rthc_free_linkage_state(rthc_ctx *ctx);
 int rthc_setup_geometry(rthc_ctx *ctx, int64_t n);
 
