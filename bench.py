@@ -209,7 +209,8 @@ def run_ours(args):
         if resident:
             ctx.set_profiles_device(dX.data_ptr(), n, L)
         elif world > 1:
-            ctx.set_profiles_device(loader.load(host_codes), n, L)
+            ptr = loader.load(host_codes)
+            ctx.set_profiles_device(ptr, n, L, loader.dtype)
         else:
             ctx.set_profiles(host_codes)
         t = lap("set_profiles", t)
@@ -365,7 +366,8 @@ def run_ours(args):
             "e2e": {"value": e2e_value, "unit": "comparisons/s", "ms_per_step": 1e3 * dt_e2e / args.steps,
                     "h2d_bytes_per_step": int(n) * int(L) * 4, "d2h_bytes_per_step": int(d2h_bytes),
                     "h2d": "rank 0 copies the whole int32 matrix" if world == 1 else
-                           "summed over ranks: each copies n/%d rows from page-locked memory, one NCCL all_gather replicates" % world},
+                           "summed over ranks: each copies n/%d rows (int32) from page-locked memory, narrows them to uint16 on the device when "
+                           "every id fits, one NCCL all_gather replicates" % world},
             "result_check": check,
             "gpu_launches": int(launches),
             "timing": "CUDA events on the library stream around the K steps (max over ranks); wall/device = %.3f" % (

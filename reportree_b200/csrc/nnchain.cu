@@ -17,6 +17,9 @@
 // Mutable data is read with ld.global.cg (L1 is not coherent across SMs).
 #include <cooperative_groups.h>
 
+#include <cstdio>
+#include <cstdlib>
+
 #include <algorithm>
 #include <cmath>
 #include <type_traits>
@@ -515,6 +518,8 @@ struct ChainCtl {
     int64_t scans;      // row scans that had a barrier of their own (cache entry unknown when the chain needed it)
     int64_t fused;      // scans of the next chain tip that rode on a merge's barrier
     int64_t hits;       // chain steps answered by the cache
+    int64_t clk[8];     // SM cycles of CTA 0, thread 0 per section: walk, scan loads + reduce, scan barrier + combine,
+                        // merge pre-barrier, merge pass, merge reductions, merge barrier, merge combine
 };
 
 // The two lexicographically smallest (value bits, index) entries of a row.  (~0, ~0) = none.
@@ -642,6 +647,8 @@ rthc_nn_chain_kernel(T *W, int64_t n, int64_t pitch, int method, int32_t *size, 
     // all threads
     int64_t step = 0;
     int q = 0;
+    long long clk[8] = {0, 0, 0, 0, 0, 0, 0, 0}, t0 = clock64();
+#define NNC_LAP(slot_) do { const long long t1_ = clock64(); clk[slot_] += t1_ - t0; t0 = t1_; } while (0)
 
     for (int64_t k = 0; k < n - 1;) {
         if (w0) {
@@ -716,6 +723,7 @@ rthc_nn_chain_kernel(T *W, int64_t n, int64_t pitch, int method, int32_t *size, 
             }
         }
         __syncthreads();
+        NNC_LAP(0);
         const int what = bc[q].what;
         const int par = (int)(step & 1);
         if (what == NNC_SCAN) {
@@ -740,6 +748,7 @@ rthc_nn_chain_kernel(T *W, int64_t n, int64_t pitch, int method, int32_t *size, 
             }
             block_top2(t, sh);
             if (w0 && lane < C) *cluster.map_shared_rank(&slotA[par][rank], lane) = t;      // lane l publishes to CTA l
+            NNC_LAP(1);
             cluster.sync();
             ++step;
             if (w0) {
@@ -750,6 +759,7 @@ rthc_nn_chain_kernel(T *W, int64_t n, int64_t pitch, int method, int32_t *size, 
                 dead = -1;                                       // the barrier published the last merge's sizes
                 ++scans;
             }
+            NNC_LAP(2);
             continue;
         }
         // ---- merge a and b ----------------------------------------------------------------------------
@@ -759,6 +769,7 @@ rthc_nn_chain_kernel(T *W, int64_t n, int64_t pitch, int method, int32_t *size, 
         if (tid == 0) s_live[a >> 5] &= ~(1u << (a & 31));
         if (leader) { ex[k] = a; ey[k] = b; ew[k] = from_bits(dminb, T()); }
         cluster.sync();                       // every CTA has left the walk; the leader's earlier stores are visible
+        NNC_LAP(3);
         const T *ra = W + (int64_t)a * pitch;
         T *rb = W + (int64_t)b * pitch;
         const T *rp = W + (int64_t)(p >= 0 ? p : 0) * pitch;
@@ -813,13 +824,16 @@ rthc_nn_chain_kernel(T *W, int64_t n, int64_t pitch, int method, int32_t *size, 
                 }
             }
         }
+        NNC_LAP(4);
         block_top2(tb, sh);
         if (w0 && lane < C) *cluster.map_shared_rank(&slotA[par][rank], lane) = tb;
         if (p >= 0) {
             block_top2(tp, sh);
             if (w0 && lane < C) *cluster.map_shared_rank(&slotB[par][rank], lane) = tp;
         }
+        NNC_LAP(5);
         cluster.sync();                       // row / column b, the cache entries and the slots are visible
+        NNC_LAP(6);
         ++step;
         if (w0) {
             Top2 t;
@@ -839,9 +853,14 @@ rthc_nn_chain_kernel(T *W, int64_t n, int64_t pitch, int method, int32_t *size, 
             len -= 2;
             if (len > 0) { x = nx; prev = nprev; sx = nsx; sprev = nsprev; dprev = ndprev; need_sx = false; }
         }
+        NNC_LAP(7);
         ++k;
     }
-    if (leader) { ctl->scans = scans; ctl->fused = fused; ctl->hits = hits; }
+#undef NNC_LAP
+    if (leader) {
+        ctl->scans = scans; ctl->fused = fused; ctl->hits = hits;
+        for (int c = 0; c < 8; ++c) ctl->clk[c] = clk[c];
+    }
 }
 
 template <typename T, typename S>
@@ -911,6 +930,16 @@ static int run_nn_chain(rthc_ctx *ctx, const S *d_cond, int method, std::vector<
     RTHC_CUDA(ctx, cudaMemcpyAsync(ew.data(), d_ew, sizeof(double) * (size_t)m, cudaMemcpyDeviceToHost, ctx->stream));
     RTHC_CUDA(ctx, cudaMemcpyAsync(&ctl, d_ctl, sizeof(ChainCtl), cudaMemcpyDeviceToHost, ctx->stream));
     RTHC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    if (getenv("RTHC_NNC_TIMING")) {                 // section cycles of CTA 0 / thread 0
+        static const char *name[8] = {"walk", "scan: loads + CTA top-2", "scan: barrier + combine", "merge: pre-barrier",
+                                      "merge: pass", "merge: CTA top-2 x2", "merge: barrier", "merge: combine"};
+        long long tot = 0;
+        for (int c = 0; c < 8; ++c) tot += ctl.clk[c];
+        for (int c = 0; c < 8; ++c)
+            fprintf(stderr, "nn_chain %-26s %8.1f Mcycles %5.1f %%\n", name[c], ctl.clk[c] * 1e-6, 100.0 * ctl.clk[c] / (double)(tot ? tot : 1));
+        fprintf(stderr, "nn_chain scans %lld fused %lld merges %lld look-ups %lld\n", (long long)ctl.scans, (long long)ctl.fused,
+                (long long)m, (long long)ctl.hits);
+    }
     ctx->row_scans = ctl.scans + ctl.fused;         // row scans: own barrier + fused with a merge
     ctx->chain_full_scans = ctl.scans + 2 * m;      // cluster barriers (info[9]): one per scan, two per merge
     ctx->chain_cache_hits = ctl.hits;

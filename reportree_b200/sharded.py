@@ -103,28 +103,53 @@ class ForestExchange:
 class ShardedProfileLoader:
     """Host -> device load of the n x L int32 code matrix for world > 1: every rank copies only its own
     block of ceil(n / world) rows over PCIe and one all_gather over NVLink replicates the matrix, instead
-    of `world` full copies competing for the host's memory bandwidth."""
+    of `world` full copies competing for the host's memory bandwidth.  When every allele id of the matrix
+    fits 16 bits (one tiny all_reduce(max) decides, so that all ranks take the same branch) the blocks are
+    narrowed on the device first and the all_gather moves half the bytes; `load` then returns the uint16
+    replica, which `rthc_set_profiles_u16_device` takes as it is."""
 
-    def __init__(self, n, L, dist, device="cuda"):
+    def __init__(self, n, L, dist, device="cuda", narrow=True):
         import torch
         self.n, self.L, self.dist, self.torch = int(n), int(L), dist, torch
         self.world, self.rank = dist.get_world_size(), dist.get_rank()
         self.rows = (self.n + self.world - 1) // self.world
         self.block = torch.zeros((self.rows, self.L), dtype=torch.int32, device=device)
         self.full = torch.empty((self.rows * self.world, self.L), dtype=torch.int32, device=device)
+        self.narrow = bool(narrow) and hasattr(torch, "uint16")
+        if self.narrow:
+            self.block16 = torch.zeros((self.rows, self.L), dtype=torch.uint16, device=device)
+            self.full16 = torch.empty((self.rows * self.world, self.L), dtype=torch.uint16, device=device)
+            self.vmax = torch.zeros(1, dtype=torch.int32, device=device)
         self.r0 = min(self.n, self.rank * self.rows)
         self.r1 = min(self.n, self.r0 + self.rows)
+        self.dtype = np.int32                     # of the replica returned by the last load()
 
     def own_bytes(self):
         return (self.r1 - self.r0) * self.L * 4
 
     def load(self, host_codes):
         """host_codes: C-contiguous int32 [n, L] (page-locked for full PCIe speed).  Returns the device
-        pointer of the replicated matrix (first n rows are the data)."""
+        pointer of the replicated matrix (first n rows are the data); `self.dtype` says int32 or uint16."""
         t = self.torch
         if self.r1 > self.r0:
             self.block[: self.r1 - self.r0].copy_(t.from_numpy(host_codes[self.r0:self.r1]), non_blocking=True)
+        if self.narrow:
+            self.vmax[0] = self.block.max()
+            self.dist.all_reduce(self.vmax, op=self.dist.ReduceOp.MAX)
+            if int(self.vmax[0]) < 65536:                              # ids <= 0 are missing either way
+                t.clamp(self.block, min=0, out=self.block)
+                self.block16.copy_(self.block)
+                self.dist.all_gather_into_tensor(self.full16.view(t.uint8), self.block16.view(t.uint8))
+                if self.full16.is_cuda:
+                    t.cuda.current_stream().synchronize()
+                self.dtype = np.uint16
+                return self.full16.data_ptr()
         self.dist.all_gather_into_tensor(self.full, self.block)
         if self.full.is_cuda:
             t.cuda.current_stream().synchronize()
+        self.dtype = np.int32
         return self.full.data_ptr()
+
+    def replica(self):
+        """The replicated matrix of the last load() as a tensor (tests)."""
+        return self.full16 if self.dtype == np.uint16 else self.full

@@ -169,9 +169,16 @@ def _exchange_worker(rank, world, port, n, L, q):
     # host matrix -> every rank copies its own row block, one all_gather replicates it
     X = (np.arange(n * L, dtype=np.int32).reshape(n, L) * 7) % 1001
     ld = sharded.ShardedProfileLoader(n, L, dist, device="cpu")
-    ptr = ld.load(X)
-    assert ptr == ld.full.data_ptr()
-    q.put((rank, m, slots.size, real, ld.full.numpy()[:n].copy(), ld.own_bytes()))
+    ptr = ld.load(X)                                   # ids < 65,536: narrowed to uint16 before the gather
+    assert ld.dtype == np.uint16 and ptr == ld.full16.data_ptr()
+    narrow = ld.replica().numpy()[:n].astype(np.int32)
+    Y = X.copy()
+    Y[0, 0] = 70000                                    # one wide id: every rank must fall back to int32
+    Y[n - 1, 1] = -3                                   # negative = missing, kept as it is on the int32 path
+    ptr = ld.load(Y)
+    assert ld.dtype == np.int32 and ptr == ld.full.data_ptr()
+    assert np.array_equal(ld.replica().numpy()[:n], Y)
+    q.put((rank, m, slots.size, real, narrow, ld.own_bytes()))
     dist.barrier()
     dist.destroy_process_group()
 
