@@ -489,378 +489,228 @@ __device__ __forceinline__ double lance_williams<double>(int method, double dx, 
 }
 
 template <typename T, typename S>
-__global__ void rthc_expand_square(const S *__restrict__ cond, int64_t n, int64_t pitch, T *__restrict__ W)
+__global__ void rthc_expand_square(const S *__restrict__ cond, int64_t n, T *__restrict__ W)
 {
     const int64_t i = blockIdx.x;                              // rows on grid.x: no 65,535 limit
     const int64_t j = (int64_t)blockIdx.y * blockDim.x + threadIdx.x;
-    if (j >= pitch) return;
+    if (j >= n) return;
     T v = 0;
-    if (i != j && j < n) {
+    if (i != j) {
         const int64_t a = i < j ? i : j, b = i < j ? j : i;
         v = (T)cond[n * a - (a * (a + 1)) / 2 + (b - a - 1)];
     }
-    W[i * pitch + j] = v;
-}
-
-// all-lanes lexicographic minimum of (w, i) over a warp
-__device__ __forceinline__ void warp_min_all(unsigned long long &w, unsigned int &i)
-{
-#pragma unroll
-    for (int s = 16; s > 0; s >>= 1) {
-        unsigned long long ow = __shfl_xor_sync(0xffffffffu, w, s);
-        unsigned int oi = __shfl_xor_sync(0xffffffffu, i, s);
-        if (slot_less(ow, oi, w, i)) { w = ow; i = oi; }
-    }
+    W[i * n + j] = v;
 }
 
 // control block in global memory (written by block 0, thread 0 only)
 struct ChainCtl {
-    int64_t scans;      // row scans that had a barrier of their own (cache entry unknown when the chain needed it)
+    int64_t scans;      // full row scans (one grid barrier each)
     int64_t fused;      // scans of the next chain tip that rode on a merge's barrier
-    int64_t hits;       // chain steps answered by the cache
-    int64_t clk[8];     // SM cycles of CTA 0, thread 0 per section: walk, scan loads + reduce, scan barrier + combine,
-                        // merge pre-barrier, merge pass, merge reductions, merge barrier, merge combine
+    int64_t hits;       // chain steps answered by the nearest-neighbour cache (no barrier)
 };
 
-// The two lexicographically smallest (value bits, index) entries of a row.  (~0, ~0) = none.
-struct __align__(16) Top2 {
-    unsigned long long w1, w2;
-    unsigned int i1, i2, pad0, pad1;
-    __device__ __forceinline__ void clear() { w1 = w2 = ~0ull; i1 = i2 = ~0u; }
-    __device__ __forceinline__ void insert(unsigned long long w, unsigned int i)
-    {
-        if (slot_less(w, i, w1, i1)) { w2 = w1; i2 = i1; w1 = w; i1 = i; }
-        else if (slot_less(w, i, w2, i2)) { w2 = w; i2 = i; }
-    }
-};
-__device__ __forceinline__ void warp_top2(Top2 &t)                // all lanes end with the warp's top-2
+// nearest neighbour of every row: lexicographic minimum of (D[r, i], i) over i != r  (one CTA per row)
+template <typename T>
+__global__ void __launch_bounds__(SEQ_THREADS) rthc_nn_init(const T *__restrict__ W, int64_t n, MinSlot *__restrict__ nn)
 {
-#pragma unroll
-    for (int s = 16; s > 0; s >>= 1) {
-        const unsigned long long ow1 = __shfl_xor_sync(0xffffffffu, t.w1, s), ow2 = __shfl_xor_sync(0xffffffffu, t.w2, s);
-        const unsigned int oi1 = __shfl_xor_sync(0xffffffffu, t.i1, s), oi2 = __shfl_xor_sync(0xffffffffu, t.i2, s);
-        t.insert(ow1, oi1);
-        t.insert(ow2, oi2);
+    __shared__ MinSlot sh[SEQ_THREADS / 32];
+    const int64_t r = blockIdx.x;
+    const T *row = W + r * n;
+    unsigned long long bw = ~0ull;
+    unsigned int bi = ~0u;
+    for (int64_t i = threadIdx.x; i < n; i += SEQ_THREADS) {
+        if (i == r) continue;
+        const unsigned long long d = order_bits(row[i]);
+        if (slot_less(d, (unsigned int)i, bw, bi)) { bw = d; bi = (unsigned int)i; }
     }
-}
-// block-wide top-2; result valid in warp 0 (all its lanes)
-__device__ __forceinline__ void block_top2(Top2 &t, Top2 *sh)
-{
-    warp_top2(t);
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    if (lane == 0) sh[warp] = t;
-    __syncthreads();
-    if (warp == 0) {
-        if (lane < SEQ_THREADS / 32) t = sh[lane]; else t.clear();
-        warp_top2(t);
-    }
-    __syncthreads();
+    block_min(bw, bi, sh);
+    if (threadIdx.x == 0) { nn[r].w = bw; nn[r].i = bi; }
 }
 
-// cache entry of a row: E1 = its nearest neighbour (exact) or i1 == ~0: unknown; E2 = the runner-up when `act`,
-// otherwise only a bound: every entry of the row other than E1 (and E2 when act) is lexicographically greater
-// than (w2, i2)
-struct __align__(16) NNEntry {
-    unsigned long long w1, w2;
-    unsigned int i1, i2, act, pad;
-};
-__device__ __forceinline__ void nn_store(NNEntry *p, unsigned long long w1, unsigned int i1, unsigned long long w2, unsigned int i2,
-                                         unsigned int act)
-{
-    __stcg(reinterpret_cast<uint4 *>(p), make_uint4((uint32_t)w1, (uint32_t)(w1 >> 32), (uint32_t)w2, (uint32_t)(w2 >> 32)));
-    __stcg(reinterpret_cast<uint4 *>(p) + 1, make_uint4(i1, i2, act, 0u));
-}
-
-#define NNC_MAX_CLUSTER 16
-#define NNC_SCAN 1
-#define NNC_MERGE 2
-struct ChainBc {                // the decision of warp 0, broadcast through shared memory
-    unsigned long long dmin;
-    int32_t what, x, a, b, na, nb, p;
-};
-
-// The merge loop: scipy's nn_chain inside ONE thread-block cluster.
-//
-// A chain step asks for the nearest neighbour of the chain tip x: the previous chain element if it ties the minimum,
-// else the lowest index of the minimum of row x.  The loop is a chain of dependent steps, so what it costs is
-// latency, and the grid-wide version paid 5.5 us per step for a cooperative grid barrier and the L2 round trips
-// around it (round 1: 0.3 % of the HBM roofline).  Here
-//   * the loop runs in one cluster of 16 CTAs (8 where 16 cannot be scheduled): barrier.cluster instead of a grid
-//     barrier, and the per-CTA results of a reduction are written straight into the shared memory of every CTA of
-//     the cluster (st.shared::cluster), so nothing is re-read through L2 after a barrier.  A row is <= 0.2 MB:
-//     16 SMs stream it in about a microsecond, more SMs would only wait longer at the barrier;
-//   * every row keeps a cache entry: its exact nearest neighbour E1 and the runner-up E2 (or a bound below every
-//     other entry).  A chain step whose tip has a known E1 is a look-up by warp 0 of every CTA (no barrier; the
-//     distance to the previous element and the sizes of the chain elements ride along in the CTA's private chain
-//     arrays, so no matrix element is read).  A merge (a dies, b = a u b) visits every live row i to write D[i, b];
-//     the same thread updates the entry of row i from E1, E2 / the bound and the new entry N = (D[i, b], b): entries
-//     of a and b leave the candidate set, N joins it, the smallest candidate is the new E1 if it does not exceed the
-//     bound (everything unknown lies above the bound), the next one the new E2 under the same condition; otherwise
-//     E1 becomes unknown and the row is scanned over the cluster when (if) the chain reaches it;
-//   * the merge's barrier also carries the top-2 of the new row b and the scan of p, the chain element that becomes
-//     the tip after the merge (its neighbour was a or b by construction): row p only changes in column b, whose new
-//     value the thread that owns i == p has, so the scan reads nothing that the phase writes.
-// A look-up returns the same (value, lowest index, previous-wins) triple as scipy's scan, so Z stays byte-identical
-// (tests/test_gpu_exact_linkage.py, the C3 / C5 goldens).  Cache entries and size[] of rows touched after the last
-// barrier are carried in the registers of warp 0 (`grown`, `known`); a barrier before every merge pass makes the
-// leader's earlier stores visible to the pass.  W is pitched so that every row starts on a 16-byte boundary.
+// The merge loop.  scipy's chain step asks for the nearest neighbour of the chain tip x: the previous chain
+// element if it ties the minimum, else the lowest index of the minimum of row x.  A grid-wide row scan costs one
+// grid barrier (about 2.4 us) however short the row is, so the kernel keeps, for every live row r, the exact
+// lexicographic minimum nn[r] = min over live i != r of (D[r, i], i) and only scans when that entry is unknown:
+//   * a merge (a dies, b = a u b) already visits every live row i to write D[i, b]; the same thread folds the new
+//     entry into the cache -- nn[i] = min(nn[i], (D[i, b], b)) is exact because every other entry of row i is
+//     unchanged -- and drops it (index = ~0) when the cached neighbour was a or b;
+//   * the candidates (D[b, i], i) of the new row b are reduced over the grid on the merge's own barrier;
+//   * so is a scan of the row of p, the chain element that becomes the tip after the merge (its neighbour was a
+//     or b by construction): row p only changes in column b, whose new value the thread that owns i == p has.
+// A chain step whose tip has a cached neighbour reads it (warp 0 of every CTA, broadcast through shared memory)
+// and costs no barrier.  The answer is the same (value, lowest index, previous-wins) triple as the scan, so Z
+// stays byte-identical to scipy.  nn[] is double-buffered by merge parity: a merge writes the other copy for every
+// live row, so a CTA still walking the chain never reads an entry that a faster CTA has already updated.
+// Every nn[r] is written by ONE thread (the owner of index r in the strided loops), reads of scalar state go
+// through warp 0 + shared memory (148 x 16 warps loading one address serialise in L2), size[] of the last merge
+// is patched from registers until the next barrier has published it.
 template <typename T>
 __global__ void __launch_bounds__(SEQ_THREADS, 1)
-rthc_nn_chain_kernel(T *W, int64_t n, int64_t pitch, int method, int32_t *size, int32_t *chains, unsigned long long *chains_d,
-                     int32_t *chains_s, NNEntry *nn, int32_t *ex, int32_t *ey, double *ew, ChainCtl *ctl)
+rthc_nn_chain_kernel(T *W, int64_t n, int method, int32_t *size, int32_t *chains, MinSlot *slots, MinSlot *nn2,
+                     int32_t *ex, int32_t *ey, double *ew, ChainCtl *ctl)
 {
-    cg::cluster_group cluster = cg::this_cluster();
-    const int C = (int)cluster.num_blocks(), rank = (int)cluster.block_rank();
-    extern __shared__ uint32_t s_live[];                         // bit j: cluster j is alive
-    __shared__ Top2 sh[SEQ_THREADS / 32];
-    __shared__ Top2 slotA[2][NNC_MAX_CLUSTER], slotB[2][NNC_MAX_CLUSTER];      // written by every CTA of the cluster
-    __shared__ ChainBc bc[2];                                    // alternating: one __syncthreads per decision
-    const int tid = threadIdx.x, lane = tid & 31;
-    const bool w0 = tid < 32;
-    const int64_t TT = (int64_t)C * SEQ_THREADS, gt = (int64_t)rank * SEQ_THREADS + tid;
-    const bool leader = rank == 0 && tid == 0;
-    // this CTA's copy of the chain, touched by its thread 0 only: element, D[element, previous element], size
-    int32_t *chain = chains + (int64_t)rank * n;
-    unsigned long long *chain_d = chains_d + (int64_t)rank * n;
-    int32_t *chain_s = chains_s + (int64_t)rank * n;
+    cg::grid_group grid = cg::this_grid();
+    __shared__ MinSlot sh[SEQ_THREADS / 32];
+    __shared__ MinSlot bcs[2];                                   // broadcast buffers, alternating
+    __shared__ unsigned long long bcd[2];
+    __shared__ int32_t bci[2][4];
+    const int nblocks = gridDim.x;
+    const int64_t gtid = (int64_t)blockIdx.x * SEQ_THREADS + threadIdx.x;
+    const int64_t gthreads = (int64_t)nblocks * SEQ_THREADS;
+    const bool leader = blockIdx.x == 0 && threadIdx.x == 0;
+    const int lane = threadIdx.x & 31;
+    const bool w0 = threadIdx.x < 32;
+    int32_t *chain = chains + (int64_t)blockIdx.x * n;          // this CTA's copy, touched by its thread 0 only
 
-    const int64_t live_words = (pitch + 31) / 32;
-    for (int64_t w = tid; w < live_words; w += SEQ_THREADS) {
-        const int64_t j = w * 32;
-        s_live[w] = j + 32 <= n ? 0xFFFFFFFFu : (j >= n ? 0u : ((1u << (int)(n - j)) - 1u));
-    }
-    for (int64_t i = gt; i < n; i += TT) nn_store(&nn[i], ~0ull, ~0u, ~0ull, ~0u, 0u);      // nothing known yet
-    __syncthreads();
-    cluster.sync();
+    // replicated scalar state (identical in every thread of the grid)
+    int64_t len = 0, first_live = 0, step = 0, scans = 0, fused = 0, hits = 0;
+    int32_t x = -1, prev = -1;
+    int32_t dead = -1, grown = -1, grown_size = 0;              // last merge, until the next barrier publishes size[]
+    unsigned long long gw = ~0ull; unsigned int gi = ~0u;        // nn of `grown`
+    bool have_tip = false;                                       // nn of the tip is in (tw, ti, tdprev)
+    unsigned long long tw = ~0ull, tdprev = ~0ull; unsigned int ti = ~0u;
+    int q = 0, cur = 0;                                          // broadcast buffer, current nn copy
 
-    // walk state: warp 0 only (uniform over its lanes)
-    int64_t len = 0, first_live = 0, hits = 0, scans = 0, fused = 0;
-    int32_t x = -1, prev = -1, sx = 0, sprev = 0;
-    unsigned long long dprev = ~0ull;                            // D[x, prev]
-    bool need_sx = false;
-    // rows whose entry / size was produced after the last barrier (not yet visible in global memory)
-    int32_t dead = -1, grown = -1, grown_size = 0, known = -1;
-    unsigned long long gw1 = ~0ull, kw1 = ~0ull;
-    unsigned int gi1 = ~0u, ki1 = ~0u;
-    int32_t nx = -1, nprev = -1, nsx = 0, nsprev = 0;            // the chain below the tip, prefetched
-    unsigned long long ndprev = ~0ull;
-    // all threads
-    int64_t step = 0;
-    int q = 0;
-    long long clk[8] = {0, 0, 0, 0, 0, 0, 0, 0}, t0 = clock64();
-#define NNC_LAP(slot_) do { const long long t1_ = clock64(); clk[slot_] += t1_ - t0; t0 = t1_; } while (0)
+#define SIZE_OF(i_) ((i_) == dead ? 0 : ((i_) == grown ? grown_size : __ldcg(&size[(i_)])))
 
     for (int64_t k = 0; k < n - 1;) {
-        if (w0) {
-            for (;;) {
-                if (len == 0) {                                  // lowest live index from the bitmap
-                    int64_t w = first_live >> 5;
-                    for (;;) {
-                        const int64_t ww = w + lane;
-                        const uint32_t bits = ww < live_words ? s_live[ww] : 0u;
-                        const unsigned m = __ballot_sync(0xffffffffu, bits != 0u);
-                        if (m) {
-                            const int src = __ffs(m) - 1;
-                            const uint32_t b0 = __shfl_sync(0xffffffffu, bits, src);
-                            first_live = (w + src) * 32 + (__ffs(b0) - 1);
-                            break;
-                        }
-                        w += 32;
-                    }
-                    x = (int32_t)first_live; prev = -1; len = 1; dprev = ~0ull; need_sx = true;
-                    if (lane == 0) chain[0] = x;
+        MinSlot *nn = nn2 + (int64_t)cur * n;
+        if (len == 0) {
+            if (w0) {                                            // lowest live index, 32 candidates per trip
+                int64_t f = first_live;
+                for (;;) {
+                    const int64_t i = f + lane;
+                    const bool live = i < n && SIZE_OF(i) != 0;
+                    const unsigned m = __ballot_sync(0xffffffffu, live);
+                    if (m) { f += __ffs(m) - 1; break; }
+                    f += 32;
                 }
-                // look-up: independent loads in separate lanes (entry, size, and the chain below the tip in case
-                // this step ends in a merge)
-                // (the chain arrays are private to lane 0, which wrote them: program order keeps them coherent)
-                unsigned long long v = 0, c3d = ~0ull;
-                int32_t c3 = -1, c3s = 0, c4 = -1, c4s = 0;
-                if (lane == 0) {
-                    v = x == grown ? gw1 : (x == known ? kw1 : __ldcg(&nn[x].w1));
-                    if (len >= 3) { c3 = chain[len - 3]; c3s = chain_s[len - 3]; }
-                    if (len >= 4) { c4 = chain[len - 4]; c4s = chain_s[len - 4]; c3d = chain_d[len - 3]; }
-                } else if (lane == 1) {
-                    v = x == grown ? (unsigned long long)gi1 : (x == known ? (unsigned long long)ki1 : (unsigned long long)__ldcg(&nn[x].i1));
-                } else if (lane == 2 && need_sx) {
-                    v = (unsigned long long)(x == dead ? 0 : (x == grown ? grown_size : __ldcg(&size[x])));
-                }
-                const unsigned long long cw = __shfl_sync(0xffffffffu, v, 0);
-                const unsigned int ci = (unsigned int)__shfl_sync(0xffffffffu, v, 1);
-                if (need_sx) {
-                    sx = (int32_t)__shfl_sync(0xffffffffu, v, 2);
-                    if (lane == 0) chain_s[len - 1] = sx;
-                    need_sx = false;
-                }
-                nx = __shfl_sync(0xffffffffu, c3, 0); nsx = __shfl_sync(0xffffffffu, c3s, 0);
-                nprev = __shfl_sync(0xffffffffu, c4, 0); nsprev = __shfl_sync(0xffffffffu, c4s, 0);
-                ndprev = __shfl_sync(0xffffffffu, c3d, 0);
-                RTHC_DEV_ASSERT(x >= 0 && x < n && ((s_live[x >> 5] >> (x & 31)) & 1u));
-                if (ci == ~0u) {                                 // unknown: scan row x over the cluster
-                    if (lane == 0) { bc[q].what = NNC_SCAN; bc[q].x = x; }
-                    break;
-                }
-                ++hits;
-                RTHC_DEV_ASSERT(ci < (unsigned int)n && ci != (unsigned int)x && ((s_live[ci >> 5] >> (ci & 31)) & 1u));
-                RTHC_DEV_ASSERT(sx > 0 && (len == 1 || sprev > 0));
-                int32_t y = (int32_t)ci;
-                unsigned long long dmin = cw;
-                if (len > 1 && dprev <= dmin) { y = prev; dmin = dprev; }      // previous chain element wins ties
-                if (len > 1 && y == prev) {
-                    // ---- reciprocal nearest neighbours: the merge decision -------------------------------
-                    if (lane == 0) {
-                        ChainBc &o = bc[q];
-                        const bool xs = x < y;                   // a dies, b survives (scipy: x < y swap)
-                        o.what = NNC_MERGE;
-                        o.a = xs ? x : y; o.b = xs ? y : x; o.na = xs ? sx : sprev; o.nb = xs ? sprev : sx;
-                        o.dmin = dmin; o.p = nx;
-                    }
-                    break;
-                }
-                // ---- extend the chain -----------------------------------------------------------------
-                RTHC_DEV_ASSERT(len < n);
-                if (lane == 0) { chain[len] = y; chain_d[len] = dmin; }
-                prev = x; sprev = sx; x = y; dprev = dmin; ++len; need_sx = true;
+                if (lane == 0) { bci[q][0] = (int32_t)f; chain[0] = (int32_t)f; }
             }
+            __syncthreads();
+            first_live = bci[q][0]; q ^= 1;
+            x = (int32_t)first_live; prev = -1; len = 1; have_tip = false;
         }
-        __syncthreads();
-        NNC_LAP(0);
-        const int what = bc[q].what;
-        const int par = (int)(step & 1);
-        if (what == NNC_SCAN) {
-            // ---- scan row x: the two smallest (D[x, i], i) over live i != x ---------------------------
-            const int32_t xr = bc[q].x;
-            q ^= 1;
-            const T *row = W + (int64_t)xr * pitch;
-            Top2 t;
-            t.clear();
-            for (int64_t i0 = gt; i0 < n; i0 += TT * 8) {        // up to 8 elements of this thread in flight
-                T d[8];
-                bool ok[8];
-#pragma unroll
-                for (int u = 0; u < 8; ++u) {
-                    const int64_t i = i0 + u * TT;
-                    ok[u] = i < n && i != xr && ((s_live[i >> 5] >> (i & 31)) & 1u);
-                    if (ok[u]) d[u] = __ldcg(&row[i]);
-                }
-#pragma unroll
-                for (int u = 0; u < 8; ++u)
-                    if (ok[u]) t.insert(order_bits(d[u]), (unsigned int)(i0 + u * TT));
+        // ---- nearest neighbour of the tip x -----------------------------------------------------
+        unsigned long long cw, dprev;
+        unsigned int ci;
+        if (have_tip) {
+            cw = tw; ci = ti; dprev = tdprev;
+            have_tip = false;
+        } else {
+            if (threadIdx.x < 3) {                               // three scalars, three lanes: the loads overlap
+                if (threadIdx.x == 0) bcs[q].w = x == grown ? gw : __ldcg(&nn[x].w);
+                else if (threadIdx.x == 1) bcs[q].i = x == grown ? gi : __ldcg(&nn[x].i);
+                else bcd[q] = len > 1 ? order_bits(__ldcg(&W[(int64_t)x * n + prev])) : ~0ull;
             }
-            block_top2(t, sh);
-            if (w0 && lane < C) *cluster.map_shared_rank(&slotA[par][rank], lane) = t;      // lane l publishes to CTA l
-            NNC_LAP(1);
-            cluster.sync();
-            ++step;
-            if (w0) {
-                if (lane < C) t = slotA[par][lane]; else t.clear();
-                warp_top2(t);
-                known = xr; kw1 = t.w1; ki1 = t.i1;
-                if (leader) nn_store(&nn[xr], t.w1, t.i1, t.w2, t.i2, t.i2 != ~0u);
-                dead = -1;                                       // the barrier published the last merge's sizes
-                ++scans;
+            __syncthreads();
+            cw = bcs[q].w; ci = bcs[q].i; dprev = bcd[q]; q ^= 1;
+            if (ci != ~0u) ++hits;
+        }
+        if (ci == ~0u) {
+            // ---- unknown: scan row x over the grid (lowest index of the minimum over live i != x) --
+            unsigned long long bw = ~0ull;
+            unsigned int bi = ~0u;
+            const T *row = W + (int64_t)x * n;
+            for (int64_t i = gtid; i < n; i += gthreads) {
+                if (i == x) continue;
+                const int32_t szi = __ldcg(&size[i]);            // liveness and the element together: one latency
+                const unsigned long long d = order_bits(__ldcg(&row[i]));
+                if ((i == dead ? 0 : (i == grown ? grown_size : szi)) == 0) continue;
+                if (slot_less(d, (unsigned int)i, bw, bi)) { bw = d; bi = (unsigned int)i; }
             }
-            NNC_LAP(2);
+            block_min(bw, bi, sh);
+            MinSlot *cs = slots + (step & 1) * nblocks;
+            if (threadIdx.x == 0) { cs[blockIdx.x].w = bw; cs[blockIdx.x].i = bi; }
+            grid.sync();
+            grid_min(cs, nblocks, cw, ci, sh);
+            ++step; ++scans;
+            dead = -1; grown = -1;
+            if (gtid == x % gthreads) { nn[x].w = cw; nn[x].i = ci; }
+        }
+        int32_t y = (int32_t)ci;
+        unsigned long long dmin = cw;
+        if (len > 1 && dprev <= dmin) { y = prev; dmin = dprev; }  // previous chain element wins ties
+        if (!(len > 1 && y == prev)) {
+            // ---- extend the chain ---------------------------------------------------------------
+            if (threadIdx.x == 0) chain[len] = y;
+            prev = x; x = y; ++len;
             continue;
         }
-        // ---- merge a and b ----------------------------------------------------------------------------
-        const int32_t a = bc[q].a, b = bc[q].b, na = bc[q].na, nb = bc[q].nb, p = bc[q].p;
-        const unsigned long long dminb = bc[q].dmin;
+        // ---- merge x and y (reciprocal nearest neighbours) ---------------------------------------
+        const int32_t a = x < y ? x : y, b = x < y ? y : x;       // a dies, b survives (scipy: x < y swap)
+        if (threadIdx.x == 0) {
+            bci[q][0] = SIZE_OF(a); bci[q][1] = SIZE_OF(b);
+            const int32_t p0 = len >= 3 ? chain[len - 3] : -1, pp0 = len >= 4 ? chain[len - 4] : -1;
+            bci[q][2] = p0; bci[q][3] = pp0;
+            bcd[q] = pp0 >= 0 ? order_bits(__ldcg(&W[(int64_t)p0 * n + pp0])) : ~0ull;
+        }
+        __syncthreads();
+        const int32_t na = bci[q][0], nb = bci[q][1], p = bci[q][2], pp = bci[q][3];
+        const unsigned long long dpp = bcd[q];
         q ^= 1;
-        if (tid == 0) s_live[a >> 5] &= ~(1u << (a & 31));
-        if (leader) { ex[k] = a; ey[k] = b; ew[k] = from_bits(dminb, T()); }
-        cluster.sync();                       // every CTA has left the walk; the leader's earlier stores are visible
-        NNC_LAP(3);
-        const T *ra = W + (int64_t)a * pitch;
-        T *rb = W + (int64_t)b * pitch;
-        const T *rp = W + (int64_t)(p >= 0 ? p : 0) * pitch;
-        const double dab = from_bits(dminb, T());
-        Top2 tb, tp;
-        tb.clear(); tp.clear();
-        constexpr int PB = sizeof(T) == 8 ? 2 : 3;               // elements of this thread in flight (register budget)
-        for (int64_t i0 = gt; i0 < n; i0 += TT * PB) {
-            T da[PB], db[PB], dp[PB];
-            uint4 elo[PB], ehi[PB];
-            int32_t szi[PB];
-            bool ok[PB];
-#pragma unroll
-            for (int u = 0; u < PB; ++u) {
-                const int64_t i = i0 + u * TT;
-                ok[u] = i < n && i != b && ((s_live[i >> 5] >> (i & 31)) & 1u);
-                if (ok[u]) {
-                    da[u] = __ldcg(&ra[i]); db[u] = __ldcg(&rb[i]);
-                    elo[u] = __ldcg(reinterpret_cast<const uint4 *>(&nn[i])); ehi[u] = __ldcg(reinterpret_cast<const uint4 *>(&nn[i]) + 1);
-                    szi[u] = __ldcg(&size[i]);
-                    if (p >= 0) dp[u] = __ldcg(&rp[i]);
-                }
-            }
-#pragma unroll
-            for (int u = 0; u < PB; ++u) {
-                if (!ok[u]) continue;
-                const int64_t i = i0 + u * TT;
-                const T v = lance_williams<T>(method, da[u], db[u], dab, na, nb, szi[u]);
-                rb[i] = v;                       // row b (contiguous)
-                W[i * pitch + b] = v;            // column b (symmetric copy)
-                const unsigned long long ob = order_bits(v);
-                tb.insert(ob, (unsigned int)i);
-                if (i == p) { tp.insert(ob, (unsigned int)b); continue; }       // row p is rescanned as a whole
-                if (p >= 0) tp.insert(order_bits(dp[u]), (unsigned int)i);
-                const unsigned long long w1 = ((unsigned long long)elo[u].y << 32) | elo[u].x;
-                const unsigned long long w2 = ((unsigned long long)elo[u].w << 32) | elo[u].z;
-                const unsigned int i1 = ehi[u].x, i2 = ehi[u].y, act = ehi[u].z;
-                if (i1 == ~0u) continue;                                         // unknown stays unknown
-                // candidates: N = (ob, b), E1 unless it was a or b, E2 if known and not a or b; bound = (w2, i2)
-                const bool h1 = i1 == (unsigned int)a || i1 == (unsigned int)b;
-                const bool k2 = act && !(i2 == (unsigned int)a || i2 == (unsigned int)b);
-                Top2 c;
-                c.clear();
-                c.insert(ob, (unsigned int)b);
-                if (!h1) c.insert(w1, i1);
-                if (k2) c.insert(w2, i2);                                        // only the two smallest matter
-                if (!slot_less(w2, i2, c.w1, c.i1)) {                            // c1 <= bound: exact
-                    const bool second = c.i2 != ~0u && !slot_less(w2, i2, c.w2, c.i2);
-                    nn_store(&nn[i], c.w1, c.i1, second ? c.w2 : w2, second ? c.i2 : i2, second ? 1u : 0u);
-                } else {
-                    nn_store(&nn[i], ~0ull, ~0u, ~0ull, ~0u, 0u);
+        if (leader) { ex[k] = a; ey[k] = b; ew[k] = from_bits(dmin, T()); }
+        const T *ra = W + (int64_t)a * n;
+        T *rb = W + (int64_t)b * n;
+        const T *rp = W + (int64_t)(p >= 0 ? p : 0) * n;
+        MinSlot *nxt = nn2 + (int64_t)(cur ^ 1) * n;
+        const double dab = from_bits(dmin, T());
+        unsigned long long bwb = ~0ull, bwp = ~0ull;
+        unsigned int bib = ~0u, bip = ~0u;
+        for (int64_t i = gtid; i < n; i += gthreads) {
+            if (i == a || i == b) continue;
+            // every load of the element first, liveness included (a dead row costs a few wasted loads; testing size[i]
+            // first would put a second memory latency in front of every live one, and the stores below may alias the
+            // loads as far as the compiler knows)
+            const int32_t szi = __ldcg(&size[i]);
+            const T da = __ldcg(&ra[i]), db = __ldcg(&rb[i]);
+            unsigned long long ow = __ldcg(&nn[i].w);
+            unsigned int oi = __ldcg(&nn[i].i);
+            const T dp = p >= 0 ? __ldcg(&rp[i]) : T(0);
+            const int32_t ni = i == dead ? 0 : (i == grown ? grown_size : szi);
+            if (ni == 0) continue;
+            const T v = lance_williams<T>(method, da, db, dab, na, nb, ni);
+            rb[i] = v;                       // row b (contiguous)
+            W[i * n + b] = v;                // column b (symmetric copy)
+            const unsigned long long ob = order_bits(v);
+            if (slot_less(ob, (unsigned int)i, bwb, bib)) { bwb = ob; bib = (unsigned int)i; }
+            if (i == p) {                    // row p: its only changed entry; the rest is scanned below
+                if (slot_less(ob, (unsigned int)b, bwp, bip)) { bwp = ob; bip = (unsigned int)b; }
+            } else {
+                if (oi == (unsigned int)a || oi == (unsigned int)b) oi = ~0u;
+                else if (oi != ~0u && slot_less(ob, (unsigned int)b, ow, oi)) { ow = ob; oi = (unsigned int)b; }
+                __stcg(&nxt[i].w, ow); __stcg(&nxt[i].i, oi);
+                if (p >= 0) {
+                    const unsigned long long d = order_bits(dp);
+                    if (slot_less(d, (unsigned int)i, bwp, bip)) { bwp = d; bip = (unsigned int)i; }
                 }
             }
         }
-        NNC_LAP(4);
-        block_top2(tb, sh);
-        if (w0 && lane < C) *cluster.map_shared_rank(&slotA[par][rank], lane) = tb;
+        block_min(bwb, bib, sh);
+        MinSlot *sb = slots + (2 + (step & 1)) * nblocks, *sp = slots + (4 + (step & 1)) * nblocks;
+        if (threadIdx.x == 0) { sb[blockIdx.x].w = bwb; sb[blockIdx.x].i = bib; }
         if (p >= 0) {
-            block_top2(tp, sh);
-            if (w0 && lane < C) *cluster.map_shared_rank(&slotB[par][rank], lane) = tp;
+            block_min(bwp, bip, sh);
+            if (threadIdx.x == 0) { sp[blockIdx.x].w = bwp; sp[blockIdx.x].i = bip; }
         }
-        NNC_LAP(5);
-        cluster.sync();                       // row / column b, the cache entries and the slots are visible
-        NNC_LAP(6);
+        grid.sync();                          // row/column b and the other nn copy are visible
         ++step;
-        if (w0) {
-            Top2 t;
-            if (lane < C) t = slotA[par][lane]; else t.clear();
-            warp_top2(t);
-            gw1 = t.w1; gi1 = t.i1;
-            if (leader) { nn_store(&nn[b], t.w1, t.i1, t.w2, t.i2, t.i2 != ~0u); size[a] = 0; size[b] = na + nb; }
-            dead = a; grown = b; grown_size = na + nb;
-            known = -1;
-            if (p >= 0) {
-                if (lane < C) t = slotB[par][lane]; else t.clear();
-                warp_top2(t);
-                known = p; kw1 = t.w1; ki1 = t.i1;
-                if (leader) nn_store(&nn[p], t.w1, t.i1, t.w2, t.i2, t.i2 != ~0u);
-                ++fused;
-            }
-            len -= 2;
-            if (len > 0) { x = nx; prev = nprev; sx = nsx; sprev = nsprev; dprev = ndprev; need_sx = false; }
+        cur ^= 1;
+        grid_min(sb, nblocks, gw, gi, sh);
+        if (gtid == b % gthreads) { __stcg(&nxt[b].w, gw); __stcg(&nxt[b].i, gi); }
+        if (p >= 0) {
+            grid_min(sp, nblocks, tw, ti, sh);
+            tdprev = dpp; have_tip = true; ++fused;
+            if (gtid == p % gthreads) { __stcg(&nxt[p].w, tw); __stcg(&nxt[p].i, ti); }
         }
-        NNC_LAP(7);
+        if (leader) { size[a] = 0; size[b] = na + nb; }
+        dead = a; grown = b; grown_size = na + nb;
         ++k;
+        len -= 2;
+        if (len > 0) { x = p; prev = pp; }
     }
-#undef NNC_LAP
-    if (leader) {
-        ctl->scans = scans; ctl->fused = fused; ctl->hits = hits;
-        for (int c = 0; c < 8; ++c) ctl->clk[c] = clk[c];
-    }
+#undef SIZE_OF
+    if (leader) { ctl->scans = scans; ctl->fused = fused; ctl->hits = hits; }
 }
 
 template <typename T, typename S>
@@ -868,60 +718,37 @@ static int run_nn_chain(rthc_ctx *ctx, const S *d_cond, int method, std::vector<
                         std::vector<int32_t> &ey, std::vector<double> &ew)
 {
     const int64_t n = ctx->n, m = n - 1;
-    const int64_t per16 = 16 / (int64_t)sizeof(T), pitch = (n + per16 - 1) / per16 * per16;
     T *d_W = nullptr;
-    int32_t *d_size = nullptr, *d_chain = nullptr, *d_chain_s = nullptr, *d_ex = nullptr, *d_ey = nullptr;
-    unsigned long long *d_chain_d = nullptr;
+    int32_t *d_size = nullptr, *d_chain = nullptr, *d_ex = nullptr, *d_ey = nullptr;
     double *d_ew = nullptr;
-    NNEntry *d_nn = nullptr;
+    MinSlot *d_slots = nullptr, *d_nn = nullptr;
     ChainCtl *d_ctl = nullptr;
+    int nblocks = ctx->sm_count;
     int rc;
-    const size_t smem = sizeof(uint32_t) * (size_t)((pitch + 31) / 32 + 1);
-    if (smem > 160u * 1024u) return rthc_fail(ctx, RTHC_E_RANGE, "merge loop: %lld samples exceed the liveness bitmap", (long long)n);
-    if ((rc = rthc_dev_alloc(ctx, &d_W, (size_t)(n * pitch)))) return rc;
+    if ((rc = rthc_dev_alloc(ctx, &d_W, (size_t)(n * n)))) return rc;
     if ((rc = rthc_dev_alloc(ctx, &d_size, (size_t)n))) return rc;
-    if ((rc = rthc_dev_alloc(ctx, &d_chain, (size_t)n * NNC_MAX_CLUSTER))) return rc;
-    if ((rc = rthc_dev_alloc(ctx, &d_chain_s, (size_t)n * NNC_MAX_CLUSTER))) return rc;
-    if ((rc = rthc_dev_alloc(ctx, &d_chain_d, (size_t)n * NNC_MAX_CLUSTER))) return rc;
-    if ((rc = rthc_dev_alloc(ctx, &d_nn, (size_t)n))) return rc;
+    if ((rc = rthc_dev_alloc(ctx, &d_chain, (size_t)n * (size_t)nblocks))) return rc;
+    if ((rc = rthc_dev_alloc(ctx, &d_slots, (size_t)6 * nblocks))) return rc;
+    if ((rc = rthc_dev_alloc(ctx, &d_nn, (size_t)2 * (size_t)n))) return rc;
     if ((rc = rthc_dev_alloc(ctx, &d_ex, (size_t)m))) return rc;
     if ((rc = rthc_dev_alloc(ctx, &d_ey, (size_t)m))) return rc;
     if ((rc = rthc_dev_alloc(ctx, &d_ew, (size_t)m))) return rc;
     if ((rc = rthc_dev_alloc(ctx, &d_ctl, 1))) return rc;
     {
-        dim3 grd((unsigned)n, (unsigned)((pitch + 255) / 256));
-        rthc_expand_square<T, S><<<grd, 256, 0, ctx->stream>>>(d_cond, n, pitch, d_W);
+        dim3 grd((unsigned)n, (unsigned)((n + 255) / 256));
+        rthc_expand_square<T, S><<<grd, 256, 0, ctx->stream>>>(d_cond, n, d_W);
+        RTHC_LAUNCH_CHECK(ctx);
+        rthc_nn_init<T><<<(unsigned)n, SEQ_THREADS, 0, ctx->stream>>>(d_W, n, d_nn);
         RTHC_LAUNCH_CHECK(ctx);
         std::vector<int32_t> ones((size_t)n, 1);
         RTHC_CUDA(ctx, cudaMemcpyAsync(d_size, ones.data(), sizeof(int32_t) * (size_t)n, cudaMemcpyHostToDevice, ctx->stream));
-        RTHC_CUDA(ctx, cudaMemsetAsync(d_ctl, 0, sizeof(ChainCtl), ctx->stream));
         RTHC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     }
-    auto kern = rthc_nn_chain_kernel<T>;
-    RTHC_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    cudaError_t ce = cudaErrorInvalidConfiguration;
-    for (int C = NNC_MAX_CLUSTER; C >= 1 && ce != cudaSuccess; C >>= 1) {       // one cluster of 16, 8, ... CTAs
-        if (C > 8 && cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) != cudaSuccess) {
-            cudaGetLastError();
-            continue;
-        }
-        cudaLaunchConfig_t cfg = {};
-        cfg.gridDim = dim3((unsigned)C);
-        cfg.blockDim = dim3(SEQ_THREADS);
-        cfg.dynamicSmemBytes = smem;
-        cfg.stream = ctx->stream;
-        cudaLaunchAttribute attr[1];
-        attr[0].id = cudaLaunchAttributeClusterDimension;
-        attr[0].val.clusterDim.x = (unsigned)C; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
-        cfg.attrs = attr; cfg.numAttrs = 1;
-        int clusters = 0;
-        ce = cudaOccupancyMaxActiveClusters(&clusters, kern, &cfg);
-        if (ce == cudaSuccess && clusters < 1) ce = cudaErrorInvalidConfiguration;
-        if (ce == cudaSuccess)
-            ce = cudaLaunchKernelEx(&cfg, kern, d_W, n, pitch, method, d_size, d_chain, d_chain_d, d_chain_s, d_nn, d_ex, d_ey, d_ew, d_ctl);
-        if (ce != cudaSuccess) cudaGetLastError();
-    }
-    if (ce != cudaSuccess) return rthc_fail(ctx, RTHC_E_CUDA, "merge loop: no thread-block cluster could be launched (%s)", cudaGetErrorString(ce));
+    int64_t nn = n;
+    void *args[] = {(void *)&d_W, (void *)&nn, (void *)&method, (void *)&d_size, (void *)&d_chain, (void *)&d_slots,
+                    (void *)&d_nn, (void *)&d_ex, (void *)&d_ey, (void *)&d_ew, (void *)&d_ctl};
+    RTHC_CUDA(ctx, cudaLaunchCooperativeKernel((void *)rthc_nn_chain_kernel<T>, dim3(nblocks), dim3(SEQ_THREADS), args, 0,
+                                               ctx->stream));
     ctx->launches++;
     ex.resize((size_t)m); ey.resize((size_t)m); ew.resize((size_t)m);
     ChainCtl ctl;
@@ -930,22 +757,12 @@ static int run_nn_chain(rthc_ctx *ctx, const S *d_cond, int method, std::vector<
     RTHC_CUDA(ctx, cudaMemcpyAsync(ew.data(), d_ew, sizeof(double) * (size_t)m, cudaMemcpyDeviceToHost, ctx->stream));
     RTHC_CUDA(ctx, cudaMemcpyAsync(&ctl, d_ctl, sizeof(ChainCtl), cudaMemcpyDeviceToHost, ctx->stream));
     RTHC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-    if (getenv("RTHC_NNC_TIMING")) {                 // section cycles of CTA 0 / thread 0
-        static const char *name[8] = {"walk", "scan: loads + CTA top-2", "scan: barrier + combine", "merge: pre-barrier",
-                                      "merge: pass", "merge: CTA top-2 x2", "merge: barrier", "merge: combine"};
-        long long tot = 0;
-        for (int c = 0; c < 8; ++c) tot += ctl.clk[c];
-        for (int c = 0; c < 8; ++c)
-            fprintf(stderr, "nn_chain %-26s %8.1f Mcycles %5.1f %%\n", name[c], ctl.clk[c] * 1e-6, 100.0 * ctl.clk[c] / (double)(tot ? tot : 1));
-        fprintf(stderr, "nn_chain scans %lld fused %lld merges %lld look-ups %lld\n", (long long)ctl.scans, (long long)ctl.fused,
-                (long long)m, (long long)ctl.hits);
-    }
-    ctx->row_scans = ctl.scans + ctl.fused;         // row scans: own barrier + fused with a merge
-    ctx->chain_full_scans = ctl.scans + 2 * m;      // cluster barriers (info[9]): one per scan, two per merge
+    ctx->row_scans = ctl.scans + ctl.fused;
+    ctx->chain_full_scans = ctl.scans;
     ctx->chain_cache_hits = ctl.hits;
-    rthc_dev_free(ctx, &d_W); rthc_dev_free(ctx, &d_size); rthc_dev_free(ctx, &d_chain);
-    rthc_dev_free(ctx, &d_chain_s); rthc_dev_free(ctx, &d_chain_d); rthc_dev_free(ctx, &d_nn);
-    rthc_dev_free(ctx, &d_ex); rthc_dev_free(ctx, &d_ey); rthc_dev_free(ctx, &d_ew); rthc_dev_free(ctx, &d_ctl);
+    rthc_dev_free(ctx, &d_W); rthc_dev_free(ctx, &d_size); rthc_dev_free(ctx, &d_chain); rthc_dev_free(ctx, &d_slots);
+    rthc_dev_free(ctx, &d_nn); rthc_dev_free(ctx, &d_ex); rthc_dev_free(ctx, &d_ey); rthc_dev_free(ctx, &d_ew);
+    rthc_dev_free(ctx, &d_ctl);
     return 0;
 }
 
