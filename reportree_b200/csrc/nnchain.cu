@@ -758,7 +758,7 @@ static int run_nn_chain(rthc_ctx *ctx, const S *d_cond, int method, std::vector<
     RTHC_CUDA(ctx, cudaMemcpyAsync(&ctl, d_ctl, sizeof(ChainCtl), cudaMemcpyDeviceToHost, ctx->stream));
     RTHC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     ctx->row_scans = ctl.scans + ctl.fused;
-    ctx->chain_full_scans = ctl.scans;
+    ctx->chain_full_scans = ctl.scans + m;          // grid barriers: one per scan of its own, one per merge (info[9])
     ctx->chain_cache_hits = ctl.hits;
     rthc_dev_free(ctx, &d_W); rthc_dev_free(ctx, &d_size); rthc_dev_free(ctx, &d_chain); rthc_dev_free(ctx, &d_slots);
     rthc_dev_free(ctx, &d_nn); rthc_dev_free(ctx, &d_ex); rthc_dev_free(ctx, &d_ey); rthc_dev_free(ctx, &d_ew);
