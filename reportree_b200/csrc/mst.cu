@@ -25,6 +25,27 @@ __global__ void rthc_fill_u64(uint64_t *a, int64_t n, uint64_t val)
     int64_t v = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (v < n) a[v] = val;
 }
+// Round state on the device, so that several Boruvka rounds can be queued without a host round trip each:
+// [0] edges emitted so far, [1] the same at the end of the previous round, [2] done (spanning tree complete, or a
+// round added nothing: the forest of a disconnected edge set is complete), [3] rounds executed.  Every kernel of a
+// round returns at once when done is set.
+#define BST_COUNT 0
+#define BST_PREV 1
+#define BST_DONE 2
+#define BST_ROUNDS 3
+__global__ void rthc_boruvka_round_end(unsigned int *state, int64_t n)
+{
+    if (state[BST_DONE]) return;
+    state[BST_ROUNDS] += 1;
+    if (state[BST_COUNT] == state[BST_PREV] || (int64_t)state[BST_COUNT] >= n - 1) state[BST_DONE] = 1;
+    state[BST_PREV] = state[BST_COUNT];
+}
+__global__ void rthc_fill_u64_round(uint64_t *a, int64_t n, uint64_t val, const unsigned int *state)
+{
+    if (state[BST_DONE]) return;
+    int64_t v = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (v < n) a[v] = val;
+}
 
 // TILE PASS (row and column candidates in ONE sweep over the matrix).  A CTA owns TS_ROWS
 // consecutive rows x TS_COLS columns of the square view; thread t owns the 8 strided columns
@@ -198,8 +219,10 @@ __device__ __forceinline__ void scan_tile_body_vec(const uint16_t *__restrict__ 
 
 __global__ void __launch_bounds__(256)
 rthc_boruvka_scan_tile(const uint16_t *__restrict__ cond, const int64_t *__restrict__ row_base, int64_t n,
-                       const int32_t *__restrict__ comp, uint64_t *best, const int32_t *__restrict__ bands)
+                       const int32_t *__restrict__ comp, uint64_t *best, const int32_t *__restrict__ bands,
+                       const unsigned int *__restrict__ state)
 {
+    if (state[BST_DONE]) return;                            // uniform: a queued round that is not needed
     // bands: the 64-row bands that hold rows of this shard (a sharded context owns 1/world of them)
     const int64_t r0 = (int64_t)bands[blockIdx.y] * TS_ROWS, c0 = (int64_t)blockIdx.x * TS_COLS;
     if (c0 + TS_COLS - 1 <= r0) return;                     // no column j > i in this tile
@@ -276,10 +299,11 @@ rthc_boruvka_scan_tile(const uint16_t *__restrict__ cond, const int64_t *__restr
 
 // same round step over an explicit edge list (merge of the ranks' forests)
 __global__ void rthc_boruvka_scan_edges(const uint64_t *__restrict__ keys, int64_t m,
-                                        const int32_t *__restrict__ comp, uint64_t *best)
+                                        const int32_t *__restrict__ comp, uint64_t *best,
+                                        const unsigned int *__restrict__ state)
 {
     int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (e >= m) return;
+    if (e >= m || state[BST_DONE]) return;
     const uint64_t key = keys[e];
     if (key == RTHC_KEY_INF) return;                // padding of a fixed-size gather
     const int32_t ci = comp[rthc_key_i(key)], cj = comp[rthc_key_j(key)];
@@ -294,7 +318,7 @@ __global__ void rthc_boruvka_hook(const uint64_t *__restrict__ best, const int32
                                   unsigned int *out_count)
 {
     int64_t c = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (c >= n) return;
+    if (c >= n || out_count[BST_DONE]) return;
     if (comp[c] != (int32_t)c) { parent[c] = comp[c]; return; }
     const uint64_t key = best[c];
     if (key == RTHC_KEY_INF) { parent[c] = (int32_t)c; return; }
@@ -308,10 +332,10 @@ __global__ void rthc_boruvka_hook(const uint64_t *__restrict__ best, const int32
     out_keys[atomicAdd(out_count, 1u)] = key;
 }
 
-__global__ void rthc_pointer_jump(int32_t *parent, int64_t n)
+__global__ void rthc_pointer_jump(int32_t *parent, int64_t n, const unsigned int *__restrict__ state)
 {
     int64_t c = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (c >= n) return;
+    if (c >= n || state[BST_DONE]) return;
     const int32_t p = parent[c];
     const int32_t pp = parent[p];
     if (pp != p) parent[c] = pp;
@@ -319,10 +343,10 @@ __global__ void rthc_pointer_jump(int32_t *parent, int64_t n)
 // comp[v] = root of v in the hooked forest.  Every thread chases its own chain (read-only, so no
 // ordering issues); chains are short because each round at least halves the components and a
 // hooked root points straight at a previous root.
-__global__ void rthc_relabel(int32_t *comp, const int32_t *__restrict__ parent, int64_t n)
+__global__ void rthc_relabel(int32_t *comp, const int32_t *__restrict__ parent, int64_t n, const unsigned int *__restrict__ state)
 {
     int64_t v = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (v >= n) return;
+    if (v >= n || state[BST_DONE]) return;
     int32_t r = parent[v];
     for (;;) {
         const int32_t p = parent[r];
@@ -398,47 +422,51 @@ static int sort_keys_device(rthc_ctx *ctx, const uint64_t *d_keys, int64_t m, ui
 // shared round loop: `scan` launches the lightest-edge pass for the current components.  The forest stays on the
 // device: *d_out (caller frees) holds *m_out keys, ascending when `sorted`.
 template <typename ScanFn>
-static int boruvka_rounds(rthc_ctx *ctx, int64_t n, ScanFn scan, bool sorted, uint64_t **d_out, int64_t *m_out)
+static int boruvka_rounds(rthc_ctx *ctx, int64_t n, ScanFn scan, bool sorted, int *hint, uint64_t **d_out, int64_t *m_out)
 {
     int32_t *d_comp = nullptr, *d_parent = nullptr;
     uint64_t *d_best = nullptr, *d_keys = nullptr;
-    unsigned int *d_count = nullptr;
+    unsigned int *d_state = nullptr;
     int rc;
     *d_out = nullptr; *m_out = 0;
     if ((rc = rthc_dev_alloc(ctx, &d_comp, (size_t)n))) return rc;
     if ((rc = rthc_dev_alloc(ctx, &d_parent, (size_t)n))) return rc;
     if ((rc = rthc_dev_alloc(ctx, &d_best, (size_t)n))) return rc;
     if ((rc = rthc_dev_alloc(ctx, &d_keys, (size_t)n))) return rc;
-    if ((rc = rthc_dev_alloc(ctx, &d_count, 1))) return rc;
+    if ((rc = rthc_dev_alloc(ctx, &d_state, 4))) return rc;
     const unsigned nb = (unsigned)((n + 255) / 256);
     rthc_iota_i32<<<nb, 256, 0, ctx->stream>>>(d_comp, n);
     RTHC_LAUNCH_CHECK(ctx);
-    RTHC_CUDA(ctx, cudaMemsetAsync(d_count, 0, sizeof(unsigned int), ctx->stream));
-    unsigned int total = 0;
-    int rounds = 0;
-    while ((int64_t)total < n - 1) {
-        rthc_fill_u64<<<nb, 256, 0, ctx->stream>>>(d_best, n, RTHC_KEY_INF);
-        RTHC_LAUNCH_CHECK(ctx);
-        if ((rc = scan(d_comp, d_best))) return rc;
-        rthc_boruvka_hook<<<nb, 256, 0, ctx->stream>>>(d_best, d_comp, d_parent, n, d_keys, d_count);
-        RTHC_LAUNCH_CHECK(ctx);
-        unsigned int now = 0;
-        RTHC_CUDA(ctx, cudaMemcpyAsync(&now, d_count, sizeof(unsigned int), cudaMemcpyDeviceToHost, ctx->stream));
-        RTHC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-        ++rounds;
-        if (now == total) break;   // forest of a disconnected (sharded) edge set is complete
-        total = now;
-        if ((int64_t)total >= n - 1) break;   // spanning tree complete: the components are not needed again
-        for (int it = 0; it < 4; ++it) {      // 16x path compression bounds the chase below on adversarial chains
-            rthc_pointer_jump<<<nb, 256, 0, ctx->stream>>>(d_parent, n);
+    RTHC_CUDA(ctx, cudaMemsetAsync(d_state, 0, 4 * sizeof(unsigned int), ctx->stream));
+    // Rounds are queued without waiting for each other: as many as the previous call of this kind needed (a queued
+    // round that turns out not to be needed costs nine empty launches), then one by one until the device says done.
+    unsigned int st[4] = {0, 0, 0, 0};
+    int batch = std::max(1, *hint);
+    while (!st[BST_DONE] && (int64_t)st[BST_COUNT] < n - 1) {
+        for (int r = 0; r < batch; ++r) {
+            rthc_fill_u64_round<<<nb, 256, 0, ctx->stream>>>(d_best, n, RTHC_KEY_INF, d_state);
+            RTHC_LAUNCH_CHECK(ctx);
+            if ((rc = scan(d_comp, d_best, d_state))) return rc;
+            rthc_boruvka_hook<<<nb, 256, 0, ctx->stream>>>(d_best, d_comp, d_parent, n, d_keys, d_state);
+            RTHC_LAUNCH_CHECK(ctx);
+            rthc_boruvka_round_end<<<1, 1, 0, ctx->stream>>>(d_state, n);
+            RTHC_LAUNCH_CHECK(ctx);
+            for (int it = 0; it < 4; ++it) {      // 16x path compression bounds the chase below on adversarial chains
+                rthc_pointer_jump<<<nb, 256, 0, ctx->stream>>>(d_parent, n, d_state);
+                RTHC_LAUNCH_CHECK(ctx);
+            }
+            rthc_relabel<<<nb, 256, 0, ctx->stream>>>(d_comp, d_parent, n, d_state);
             RTHC_LAUNCH_CHECK(ctx);
         }
-        rthc_relabel<<<nb, 256, 0, ctx->stream>>>(d_comp, d_parent, n);
-        RTHC_LAUNCH_CHECK(ctx);
+        RTHC_CUDA(ctx, cudaMemcpyAsync(st, d_state, sizeof(st), cudaMemcpyDeviceToHost, ctx->stream));
+        RTHC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+        batch = 1;
     }
-    ctx->boruvka_rounds = rounds;
+    const unsigned int total = st[BST_COUNT];
+    ctx->boruvka_rounds = (int)st[BST_ROUNDS];
+    *hint = (int)st[BST_ROUNDS];
     rthc_dev_free(ctx, &d_comp); rthc_dev_free(ctx, &d_parent); rthc_dev_free(ctx, &d_best);
-    rthc_dev_free(ctx, &d_count);
+    rthc_dev_free(ctx, &d_state);
     if (sorted && total > 0) {
         uint64_t *d_sorted = nullptr;
         if ((rc = sort_keys_device(ctx, d_keys, (int64_t)total, &d_sorted))) return rc;
@@ -473,15 +501,15 @@ int rthc_boruvka_owned(rthc_ctx *ctx, bool sorted, uint64_t **d_keys, int64_t *m
     if (rcb) return rcb;
     if (!bands.empty())
         RTHC_CUDA(ctx, cudaMemcpyAsync(d_bands, bands.data(), sizeof(int32_t) * bands.size(), cudaMemcpyHostToDevice, ctx->stream));
-    auto scan = [&](int32_t *d_comp, uint64_t *d_best) -> int {
+    auto scan = [&](int32_t *d_comp, uint64_t *d_best, const unsigned int *d_state) -> int {
         if (n_owned > 0) {
             dim3 grd((unsigned)((n + TS_COLS - 1) / TS_COLS), (unsigned)bands.size());
-            rthc_boruvka_scan_tile<<<grd, 256, 0, ctx->stream>>>(ctx->d_cond, ctx->d_row_base, n, d_comp, d_best, d_bands);
+            rthc_boruvka_scan_tile<<<grd, 256, 0, ctx->stream>>>(ctx->d_cond, ctx->d_row_base, n, d_comp, d_best, d_bands, d_state);
             RTHC_LAUNCH_CHECK(ctx);
         }
         return 0;
     };
-    const int rc = boruvka_rounds(ctx, n, scan, sorted, d_keys, m);
+    const int rc = boruvka_rounds(ctx, n, scan, sorted, &ctx->boruvka_hint_owned, d_keys, m);
     rthc_dev_free(ctx, &d_bands);
     return rc;
 }
@@ -489,12 +517,12 @@ int rthc_boruvka_owned(rthc_ctx *ctx, bool sorted, uint64_t **d_keys, int64_t *m
 // d_in: m_in packed edges on the device, any order; +inf entries (padding of a fixed-size gather) are skipped
 int rthc_boruvka_edge_list(rthc_ctx *ctx, const uint64_t *d_in, int64_t m_in, int64_t n, uint64_t **d_keys, int64_t *m)
 {
-    auto scan = [&](int32_t *d_comp, uint64_t *d_best) -> int {
+    auto scan = [&](int32_t *d_comp, uint64_t *d_best, const unsigned int *d_state) -> int {
         if (m_in > 0) {
-            rthc_boruvka_scan_edges<<<(unsigned)((m_in + 255) / 256), 256, 0, ctx->stream>>>(d_in, m_in, d_comp, d_best);
+            rthc_boruvka_scan_edges<<<(unsigned)((m_in + 255) / 256), 256, 0, ctx->stream>>>(d_in, m_in, d_comp, d_best, d_state);
             RTHC_LAUNCH_CHECK(ctx);
         }
         return 0;
     };
-    return boruvka_rounds(ctx, n, scan, true, d_keys, m);
+    return boruvka_rounds(ctx, n, scan, true, &ctx->boruvka_hint_edges, d_keys, m);
 }

@@ -87,6 +87,7 @@ struct rthc_ctx {
     size_t h_pin_cap[3] = {0, 0, 0};
     bool have_linkage = false;
     int boruvka_rounds = 0;
+    int boruvka_hint_owned = 1, boruvka_hint_edges = 1;   // rounds the last call of each kind needed: queued without a host round trip
     int64_t row_scans = 0;         // NN-chain: row scans executed (full + fused with a merge)
     int64_t chain_full_scans = 0;  // ... of which paid their own grid barrier
     int64_t chain_cache_hits = 0;  // chain steps answered by the nearest-neighbour cache
