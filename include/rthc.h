@@ -153,6 +153,16 @@ int rthc_cut(rthc_ctx *ctx, const double *t, int T, int32_t *labels_out);
  * (ties can select any number), filled in no particular order; *out_count = how many.           */
 int rthc_closest(rthc_ctx *ctx, int64_t sample, int64_t k, int64_t *out_idx, uint16_t *out_dist,
                  int64_t *out_count, int *out_max_dist);
+/* rthc_closest without any device allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid it).  Same arguments, results and error codes as rthc_closest; the scratch (row copy,
+ * selection lists, 65,536-bin histogram) lives in one file-scope `static __device__` array of the library
+ * (about 3.3 MiB, held by every GPU that loads the library until exit), so n is limited to
+ * RTHC_NOALLOC_MAX_N samples (RTHC_E_RANGE beyond).  The call makes no cudaMalloc / cudaFree / pool
+ * allocation.  All calls on a device share the array: calls that overlap on the GPU race -- serialise them. */
+#define RTHC_NOALLOC_MAX_N 262144
+int rthc_closest_noalloc(rthc_ctx *ctx, int64_t sample, int64_t k, int64_t *out_idx, uint16_t *out_dist,
+                         int64_t *out_count, int *out_max_dist);
 /* Replaces the distance half of a zoom-in re-run (reportree.py:1965-2055 re-invokes
  * partitioning_HC.py with --loci <out>_loci_used.txt on the subset, cgmlst-dists included):
  * `child` (same device, created by rthc_create) receives the m x m sub-matrix of `parent`'s resident

@@ -11,6 +11,7 @@
 //   rthc_subset_from  gather of the m(m-1)/2 sub-matrix into a child context that then runs
 //                     rthc_linkage / rthc_cut as usual
 #include <algorithm>
+#include <mutex>
 
 #include "rthc_internal.cuh"
 
@@ -121,6 +122,91 @@ extern "C" int rthc_closest(rthc_ctx *ctx, int64_t sample, int64_t k, int64_t *o
     RTHC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     rthc_dev_free(ctx, &d_row); rthc_dev_free(ctx, &d_od); rthc_dev_free(ctx, &d_oi);
     rthc_dev_free(ctx, &d_hist); rthc_dev_free(ctx, &d_v);
+    *out_count = cnt;
+    if (out_max_dist) *out_max_dist = vmax;
+    return 0;
+}
+
+// ---- closest samples without any allocation ------------------------------------------------------
+// Same three kernels as rthc_closest, with the scratch (row copy, selected indices / distances, histogram, k-th
+// value) in ONE file-scope device array instead of the context's pool, for callers that may not allocate (CUDA
+// graph capture, serving loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+// Every GPU that loads the library holds the array (about 3.3 MiB) until exit.
+// All calls share it and it keeps the last call's contents: the histogram / counter / cursor words are cleared at
+// the start of every call, everything else is written before it is read.  Calls that overlap on the GPU (two
+// contexts or two host threads on the same device) race on it -- serialise them.
+#define RTHC_NOALLOC_HIST_WORDS (65536 + 2)                     // bins + [65536] count <= v + [65537] cursor
+#define RTHC_NOALLOC_OFF_V      ((size_t)263168)                // hist: 262,152 B, rounded up to 256
+#define RTHC_NOALLOC_OFF_IDX    (RTHC_NOALLOC_OFF_V + 256)
+#define RTHC_NOALLOC_OFF_ROW    (RTHC_NOALLOC_OFF_IDX + 8 * (size_t)RTHC_NOALLOC_MAX_N)
+#define RTHC_NOALLOC_OFF_DIST   (RTHC_NOALLOC_OFF_ROW + 2 * (size_t)RTHC_NOALLOC_MAX_N)
+#define RTHC_NOALLOC_BYTES      (RTHC_NOALLOC_OFF_DIST + 2 * (size_t)RTHC_NOALLOC_MAX_N)
+static_assert(RTHC_NOALLOC_HIST_WORDS * 4 <= RTHC_NOALLOC_OFF_V, "histogram does not fit its slot");
+static __device__ __align__(256) unsigned char rthc_noalloc_scratch[RTHC_NOALLOC_BYTES];
+
+// In host code `rthc_noalloc_scratch` is only a stand-in for the symbol, not a device address: the address is
+// asked for once per device, with that device current, and cached.
+#define RTHC_NOALLOC_MAX_DEVICES 64
+static unsigned char *g_noalloc_ptr[RTHC_NOALLOC_MAX_DEVICES];
+static std::mutex g_noalloc_mutex;
+
+static int noalloc_scratch_for(rthc_ctx *ctx, unsigned char **out)
+{
+    if (ctx->device < 0 || ctx->device >= RTHC_NOALLOC_MAX_DEVICES)
+        return rthc_fail(ctx, RTHC_E_RANGE, "rthc_closest_noalloc: device %d beyond the %d devices it keeps scratch for",
+                         ctx->device, RTHC_NOALLOC_MAX_DEVICES);
+    std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+    if (!g_noalloc_ptr[ctx->device]) {
+        RTHC_CUDA(ctx, cudaSetDevice(ctx->device));
+        void *p = nullptr;
+        RTHC_CUDA(ctx, cudaGetSymbolAddress(&p, rthc_noalloc_scratch));
+        if (!p) return rthc_fail(ctx, RTHC_E_CUDA, "rthc_closest_noalloc: cudaGetSymbolAddress returned NULL");
+        g_noalloc_ptr[ctx->device] = static_cast<unsigned char *>(p);
+    }
+    *out = g_noalloc_ptr[ctx->device];
+    return 0;
+}
+
+extern "C" int rthc_closest_noalloc(rthc_ctx *ctx, int64_t sample, int64_t k, int64_t *out_idx, uint16_t *out_dist,
+                                    int64_t *out_count, int *out_max_dist)
+{
+    if (!ctx || !out_idx || !out_dist || !out_count) return rthc_fail(ctx, RTHC_E_ARG, "rthc_closest_noalloc: NULL argument");
+    if (!ctx->have_dist || !ctx->d_cond)
+        return rthc_fail(ctx, RTHC_E_STATE, "rthc_closest_noalloc needs a resident uint16 distance matrix");
+    if (ctx->world != 1) return rthc_fail(ctx, RTHC_E_STATE, "rthc_closest_noalloc needs a full shard");
+    const int64_t n = ctx->n;
+    if (n > RTHC_NOALLOC_MAX_N)
+        return rthc_fail(ctx, RTHC_E_RANGE, "rthc_closest_noalloc: n = %lld samples exceed the static scratch (at most %d); "
+                         "use rthc_closest", (long long)n, RTHC_NOALLOC_MAX_N);
+    if (sample < 0 || sample >= n || k < 0 || k >= n)
+        return rthc_fail(ctx, RTHC_E_ARG, "rthc_closest_noalloc: sample / k out of range");
+    RTHC_CUDA(ctx, cudaSetDevice(ctx->device));
+    unsigned char *base = nullptr;
+    int rc;
+    if ((rc = noalloc_scratch_for(ctx, &base))) return rc;
+    unsigned int *d_hist = reinterpret_cast<unsigned int *>(base);
+    int *d_v = reinterpret_cast<int *>(base + RTHC_NOALLOC_OFF_V);
+    int64_t *d_oi = reinterpret_cast<int64_t *>(base + RTHC_NOALLOC_OFF_IDX);
+    uint16_t *d_row = reinterpret_cast<uint16_t *>(base + RTHC_NOALLOC_OFF_ROW);
+    uint16_t *d_od = reinterpret_cast<uint16_t *>(base + RTHC_NOALLOC_OFF_DIST);
+    // the array keeps the previous call's contents: histogram, count and cursor start at zero, d_v is always written
+    RTHC_CUDA(ctx, cudaMemsetAsync(d_hist, 0, sizeof(unsigned int) * RTHC_NOALLOC_HIST_WORDS, ctx->stream));
+    const unsigned nb = (unsigned)((n + 255) / 256);
+    rthc_zoom_row_hist<<<nb, 256, 0, ctx->stream>>>(ctx->d_cond, n, sample, d_row, d_hist);
+    RTHC_LAUNCH_CHECK(ctx);
+    rthc_zoom_kth<<<1, 1024, 0, ctx->stream>>>(d_hist, k, d_v, d_hist + 65536);
+    RTHC_LAUNCH_CHECK(ctx);
+    rthc_zoom_select<<<nb, 256, 0, ctx->stream>>>(d_row, n, d_v, d_oi, d_od, d_hist + 65537);
+    RTHC_LAUNCH_CHECK(ctx);
+    unsigned int cnt = 0;
+    int vmax = 0;
+    RTHC_CUDA(ctx, cudaMemcpyAsync(&cnt, d_hist + 65536, sizeof(cnt), cudaMemcpyDeviceToHost, ctx->stream));
+    RTHC_CUDA(ctx, cudaMemcpyAsync(&vmax, d_v, sizeof(vmax), cudaMemcpyDeviceToHost, ctx->stream));
+    RTHC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    if ((int64_t)cnt > n) return rthc_fail(ctx, RTHC_E_STATE, "rthc_closest_noalloc: scratch corrupted (overlapping calls?)");
+    RTHC_CUDA(ctx, cudaMemcpyAsync(out_idx, d_oi, sizeof(int64_t) * cnt, cudaMemcpyDeviceToHost, ctx->stream));
+    RTHC_CUDA(ctx, cudaMemcpyAsync(out_dist, d_od, sizeof(uint16_t) * cnt, cudaMemcpyDeviceToHost, ctx->stream));
+    RTHC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     *out_count = cnt;
     if (out_max_dist) *out_max_dist = vmax;
     return 0;

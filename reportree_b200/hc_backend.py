@@ -74,6 +74,7 @@ def load_library():
         "rthc_alu_peak": (ci, [vp, ctypes.POINTER(ctypes.c_double)]),
         "rthc_alu_peak_block": (ci, [vp, ci, ctypes.POINTER(ctypes.c_double)]),
         "rthc_closest": (ci, [vp, i64, i64, vp, vp, ctypes.POINTER(i64), ctypes.POINTER(ci)]),
+        "rthc_closest_noalloc": (ci, [vp, i64, i64, vp, vp, ctypes.POINTER(i64), ctypes.POINTER(ci)]),
         "rthc_subset_from": (ci, [vp, vp, vp, i64]),
         "rthc_contingency_adjacent": (ci, [vp, vp, ci, i64, vp, vp, vp, vp]),
         "rthc_adjusted_wallace_sums": (ci, [vp, vp, i64, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_double)]),
@@ -94,7 +95,7 @@ EXPORTED_SYMBOLS = [
     "rthc_get_condensed_u16", "rthc_get_owned_condensed_u16", "rthc_get_condensed_range_u16", "rthc_copy_rows_u16", "rthc_direct_pairs",
     "rthc_set_condensed_f64", "rthc_set_single_algo", "rthc_linkage", "rthc_local_forest",
     "rthc_linkage_from_forest", "rthc_local_forest_device", "rthc_linkage_from_forest_device", "rthc_cut", "rthc_info", "rthc_timings", "rthc_mark", "rthc_mark_elapsed_ms", "rthc_alu_peak",
-    "rthc_alu_peak_block", "rthc_closest", "rthc_subset_from",
+    "rthc_alu_peak_block", "rthc_closest", "rthc_closest_noalloc", "rthc_subset_from",
     "rthc_contingency_adjacent", "rthc_adjusted_wallace_sums",
 ]
 
@@ -265,14 +266,16 @@ class HCContext:
         return out
 
     # ---- zoom-in on the resident matrix ----------------------------------
-    def closest(self, sample, k):
+    def closest(self, sample, k, noalloc=False):
         """(indices, distances, max_dist): every sample within the distance found at sorted position
-        k of `sample`'s row (own 0 included), ordered by (distance, index)."""
+        k of `sample`'s row (own 0 included), ordered by (distance, index).  noalloc=True: the variant
+        that works in the library's static device scratch (rthc_closest_noalloc; n <= 262,144, no device
+        allocation, calls on one device must not overlap)."""
         idx = np.empty(self.n, dtype=np.int64)
         d = np.empty(self.n, dtype=np.uint16)
         cnt, vmax = ctypes.c_int64(0), ctypes.c_int(0)
-        self._check(self._L.rthc_closest(self._h, int(sample), int(k), _ptr(idx), _ptr(d), ctypes.byref(cnt),
-                                         ctypes.byref(vmax)))
+        fn = self._L.rthc_closest_noalloc if noalloc else self._L.rthc_closest
+        self._check(fn(self._h, int(sample), int(k), _ptr(idx), _ptr(d), ctypes.byref(cnt), ctypes.byref(vmax)))
         idx, d = idx[: cnt.value], d[: cnt.value]
         order = np.lexsort((idx, d))
         return idx[order].copy(), d[order].copy(), int(vmax.value)
