@@ -6,7 +6,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "libreportree_hc.so")
-SOURCES = ["api.cu", "recode.cu", "distance.cu", "distance_ws.cu", "mst.cu", "cut.cu", "linkage.cu", "nnchain.cu", "probe.cu", "zoom.cu", "stability.cu"]
+SOURCES = ["api.cu", "recode.cu", "collide.cu", "distance.cu", "distance_ws.cu", "mst.cu", "cut.cu", "linkage.cu", "nnchain.cu", "probe.cu", "zoom.cu", "stability.cu"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-O3", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",
          "-Xcompiler", "-fPIC", "-Xcompiler", "-O3", "-fmad=false"]

@@ -112,8 +112,10 @@ extern "C" int rthc_mark_elapsed_ms(rthc_ctx *ctx, double *ms)
 
 void rthc_free_distance_state(rthc_ctx *ctx)
 {
+    if (ctx->d_pcodes == ctx->d_codes) ctx->d_pcodes = nullptr;              // an alias when no locus shares codes
+    rthc_dev_free(ctx, &ctx->d_pcodes);
     rthc_dev_free(ctx, &ctx->d_codes); rthc_dev_free(ctx, &ctx->d_codes32); rthc_dev_free(ctx, &ctx->d_planes);
-    rthc_dev_free(ctx, &ctx->d_esc_code); rthc_dev_free(ctx, &ctx->d_esc_cnt); rthc_dev_free(ctx, &ctx->d_esc_list);
+    rthc_dev_free(ctx, &ctx->d_esc_cnt); rthc_dev_free(ctx, &ctx->d_esc_list); rthc_dev_free(ctx, &ctx->d_esc_pairs);
     rthc_dev_free(ctx, &ctx->d_grp_off); rthc_dev_free(ctx, &ctx->d_grp_np);
     rthc_dev_free(ctx, &ctx->d_cond_f64);
     ctx->have_profiles = ctx->have_dist = false;
@@ -491,7 +493,7 @@ extern "C" int rthc_info(const rthc_ctx *ctx, int64_t *info, int n_info)
     if (!ctx || !info) return RTHC_E_ARG;
     const int64_t v[14] = {ctx->n, ctx->L, ctx->L_kept, ctx->G, ctx->plane_rows, ctx->n_tiles,
                            ctx->boruvka_rounds, ctx->max_alleles, ctx->row_scans, ctx->chain_full_scans,
-                           ctx->chain_cache_hits, ctx->escape_loci, ctx->escape_cells, ctx->escape_pairs};
+                           ctx->chain_cache_hits, ctx->escape_loci, ctx->escape_cells, (int64_t)ctx->escape_pairs_u};
     for (int k = 0; k < n_info && k < 14; ++k) info[k] = v[k];
     return 0;
 }

@@ -21,11 +21,11 @@
 // Independent scalar kernel on the re-coded alleles (uint16, or uint32 when a locus has more than 65,535
 // alleles): one warp per requested pair.  Not on the product path -- the parity tests use it as a second
 // opinion on full-size matrices where the CPU reference only covers a sample.
-// esc: per locus the escape code of recode.cu (two cells that both hold it are DIFFERENT alleles), or nullptr.
+// It reads the dense ranks (ctx->d_codes), not the shared codes the plane packer gets from collide.cu.
 template <typename CT>
 __global__ void rthc_direct_pairs_kernel(const CT *__restrict__ codes, int64_t L, int64_t n_pad,
                                          const int32_t *__restrict__ pi, const int32_t *__restrict__ pj,
-                                         int64_t npairs, const int32_t *__restrict__ esc, int32_t *__restrict__ out)
+                                         int64_t npairs, int32_t *__restrict__ out)
 {
     const int64_t p = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int lane = threadIdx.x & 31;
@@ -34,8 +34,7 @@ __global__ void rthc_direct_pairs_kernel(const CT *__restrict__ codes, int64_t L
     int d = 0;
     for (int64_t l = lane; l < L; l += 32) {
         const CT a = codes[l * n_pad + i], b = codes[l * n_pad + j];
-        const bool both_escaped = esc != nullptr && i != j && a != 0 && (int32_t)a == esc[l] && a == b;
-        d += ((a != b) | both_escaped) & (a != 0) & (b != 0);
+        d += (a != b) & (a != 0) & (b != 0);
     }
 #pragma unroll
     for (int s = 16; s > 0; s >>= 1) d += __shfl_xor_sync(0xffffffffu, d, s);
@@ -50,10 +49,10 @@ int rthc_run_direct_pairs(rthc_ctx *ctx, const int32_t *d_pi, const int32_t *d_p
     const int64_t blocks = (np * 32 + threads - 1) / threads;
     if (ctx->d_codes32)
         rthc_direct_pairs_kernel<uint32_t><<<(unsigned)blocks, threads, 0, ctx->stream>>>(ctx->d_codes32, ctx->L, ctx->n_pad,
-                                                                                          d_pi, d_pj, np, nullptr, d_out);
+                                                                                          d_pi, d_pj, np, d_out);
     else
         rthc_direct_pairs_kernel<uint16_t><<<(unsigned)blocks, threads, 0, ctx->stream>>>(ctx->d_codes, ctx->L, ctx->n_pad,
-                                                                                          d_pi, d_pj, np, ctx->d_esc_code, d_out);
+                                                                                          d_pi, d_pj, np, d_out);
     RTHC_LAUNCH_CHECK(ctx);
     RTHC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     return 0;
@@ -67,7 +66,7 @@ int rthc_run_distance(rthc_ctx *ctx)
     int rc = rthc_launch_distance_ws(ctx, max_np);
     if (rc) return rc;
     RTHC_CUDA(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
-    // escape coding: the plane kernel saw (escape, escape) as equal; add the mismatches back (recode.cu)
+    // shared codes: the plane kernel saw two alleles of one code as equal; add those mismatches back (collide.cu)
     if ((rc = rthc_launch_escape_correct(ctx))) return rc;
     RTHC_CUDA(ctx, cudaEventRecord(ctx->ev_aux, ctx->stream));
     RTHC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));

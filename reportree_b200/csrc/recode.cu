@@ -49,25 +49,13 @@ __global__ void rthc_transpose_i32(const IT *__restrict__ in, int32_t *__restric
 // through a shared tile.  2 reads of the input + 1 write of the codes instead of transpose (read + write) +
 // 2 reads.  Any id >= 2^14 in the matrix sets status bit 1 and the driver repeats with the general path below.
 //
-// ESCAPE CODING (round 2).  The bit planes of a locus cost one LOP3 per pair and plane, and what sets the plane
-// count is the number of DISTINCT alleles -- which in real and synthetic cgMLST data is dominated by singletons
-// (novel alleles seen in one sample): C4 has about 200 of them per locus on top of 5..420 shared alleles.  A second
-// bitmap marks the ids seen at least twice; if coding the singletons of a locus as ONE shared escape code saves a
-// bit plane and the fix-up is cheap, the locus is ranked over the non-singleton alleles only (codes 1..M, escape
-// code M + 1) and its singleton cells are listed.  The plane kernel then counts (escape, escape) as equal where the
-// truth is "different" (two singletons are never the same allele; escape vs. any shared allele already differs), so
-// rthc_escape_correct adds 1 to d(i, j) for every pair of listed samples of the locus: S (S - 1) / 2 scattered
-// uint16 increments per locus, measured at 2.1e10 increments/s on the 10 GB condensed matrix
-// (profiles/r02_dist_probes_a.log).  Rule (per locus, decided on the device): escape iff a plane is saved,
-// S <= RTHC_ESC_CAP and S (S - 1) * RTHC_ESC_COST < planes saved * n (n - 1), i.e. the fix-up costs less than half
-// of the LOP3 time it removes.  Distances stay bit-exact (every GPU parity test runs through this path).
+// Fewer bit planes than the dense rank needs: collide.cu (rthc_collide) re-maps the codes of a locus afterwards.
 #define R32_BITS 16384
 #define R32_WORDS (R32_BITS / 32)
 #define R32_STRIDE (R32_WORDS + 1)       // lane * stride + word: lanes marking the same id hit 32 different banks
 #define R32_CHUNK 512                    // samples per transposed tile
 #define R32_TSTRIDE (R32_CHUNK + 2)      // uint16 row stride of the tile: 257 words, conflict-free both ways
-#define R32_SMEM (2 * 32 * R32_STRIDE * 4 + 32 * R32_STRIDE * 2 + 32 * R32_TSTRIDE * 2)
-#define RTHC_ESC_COST 52480ll            // one increment ~ 820 LOP3 lane-ops; x 32 loci per plane word; x 2 safety
+#define R32_SMEM (32 * R32_STRIDE * 4 + 32 * R32_STRIDE * 2 + 32 * R32_TSTRIDE * 2)
 
 __device__ __forceinline__ int dev_bit_width(int a)   // codes 1..a need this many bits
 {
@@ -77,26 +65,22 @@ __device__ __forceinline__ int dev_bit_width(int a)   // codes 1..a need this ma
 template <typename IT>
 __global__ void __launch_bounds__(RANK_THREADS, 1)
 rthc_rank32(const IT *__restrict__ in, int64_t n, int64_t L, int64_t n_pad, uint16_t *__restrict__ codes,
-            int32_t *__restrict__ n_alleles, int32_t *__restrict__ status, int32_t *__restrict__ esc_code,
-            int32_t *__restrict__ esc_cnt, int32_t *__restrict__ esc_list)
+            int32_t *__restrict__ n_alleles, int32_t *__restrict__ status)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     uint32_t *bm = reinterpret_cast<uint32_t *>(smem_raw);                 // seen
-    uint32_t *bm2 = bm + 32 * R32_STRIDE;                                   // seen at least twice
-    uint16_t *pre = reinterpret_cast<uint16_t *>(bm2 + 32 * R32_STRIDE);
+    uint16_t *pre = reinterpret_cast<uint16_t *>(bm + 32 * R32_STRIDE);
     uint16_t *tile = pre + 32 * R32_STRIDE;
-    __shared__ uint32_t s_tot[32], s_esc[32];
-    __shared__ int s_cnt[32];
+    __shared__ uint32_t s_tot[32];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int64_t l0 = (int64_t)blockIdx.x * 32, l = l0 + lane;
     const bool lv = l < L;
-    for (int w = tid; w < 2 * 32 * R32_STRIDE; w += RANK_THREADS) bm[w] = 0;
-    if (tid < 32) s_cnt[tid] = 0;
+    for (int w = tid; w < 32 * R32_STRIDE; w += RANK_THREADS) bm[w] = 0;
     __syncthreads();
     // ---- mark: 16 row segments in flight per warp; a bit that is already set is not set again --------
     bool big = false;
-    const volatile uint32_t *vbm = bm, *vbm2 = bm2;
-    uint32_t *mybm = bm + lane * R32_STRIDE, *mybm2 = bm2 + lane * R32_STRIDE;
+    const volatile uint32_t *vbm = bm;
+    uint32_t *mybm = bm + lane * R32_STRIDE;
     for (int64_t s0 = warp; s0 < n; s0 += 32 * 16) {
         int32_t v[16];
 #pragma unroll
@@ -111,11 +95,7 @@ rthc_rank32(const IT *__restrict__ in, int64_t n, int64_t L, int64_t n_pad, uint
                 else {
                     const uint32_t bit = 1u << (v[u] & 31);
                     const int w = lane * R32_STRIDE + (v[u] >> 5);
-                    if (!(vbm[w] & bit)) {
-                        if (atomicOr(&mybm[v[u] >> 5], bit) & bit) atomicOr(&mybm2[v[u] >> 5], bit);   // lost the race: a repeat
-                    } else if (!(vbm2[w] & bit)) {
-                        atomicOr(&mybm2[v[u] >> 5], bit);
-                    }
+                    if (!(vbm[w] & bit)) atomicOr(&mybm[v[u] >> 5], bit);
                 }
             }
         }
@@ -124,18 +104,9 @@ rthc_rank32(const IT *__restrict__ in, int64_t n, int64_t L, int64_t n_pad, uint
         if (tid == 0) atomicOr(status, 1);
         return;
     }
-    // ---- rank tables: warp w counts locus l0 + w, decides about escape coding, scans the chosen bitmap ----
+    // ---- rank tables: warp w scans the bitmap of locus l0 + w ----
     {
-        const uint32_t *b1 = bm + warp * R32_STRIDE, *b2 = bm2 + warp * R32_STRIDE;
-        uint32_t d = 0, m = 0;
-        for (int k = 0; k < R32_WORDS / 32; ++k) { d += __popc(b1[k * 32 + lane]); m += __popc(b2[k * 32 + lane]); }
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) { d += __shfl_xor_sync(0xffffffffu, d, o); m += __shfl_xor_sync(0xffffffffu, m, o); }
-        const long long S = (long long)d - (long long)m;
-        const int bits0 = dev_bit_width((int)d), bits1 = dev_bit_width((int)m + 1);
-        const bool esc = esc_list != nullptr && S >= 2 && S <= RTHC_ESC_CAP && bits1 < bits0 && bits0 > RTHC_MIN_BITS &&
-                         S * (S - 1) * RTHC_ESC_COST < (long long)(bits0 - max(bits1, RTHC_MIN_BITS)) * n * (n - 1);
-        const uint32_t *b = esc ? b2 : b1;
+        const uint32_t *b = bm + warp * R32_STRIDE;
         uint16_t *p = pre + warp * R32_STRIDE;
         uint32_t running = 0;
         for (int k = 0; k < R32_WORDS / 32; ++k) {
@@ -151,19 +122,13 @@ rthc_rank32(const IT *__restrict__ in, int64_t n, int64_t L, int64_t n_pad, uint
             running += __shfl_sync(0xffffffffu, inc, 31);
         }
         if (lane == 0) {
-            s_tot[warp] = running + (esc ? 1u : 0u);            // number of codes of the locus
-            s_esc[warp] = esc ? running + 1u : 0u;               // the escape code (0: none)
-            if (l0 + warp < L) {
-                n_alleles[l0 + warp] = (int32_t)s_tot[warp];
-                if (esc_code) { esc_code[l0 + warp] = (int32_t)s_esc[warp]; esc_cnt[l0 + warp] = esc ? (int32_t)S : 0; }
-            }
+            s_tot[warp] = running;                               // number of codes of the locus
+            if (l0 + warp < L) n_alleles[l0 + warp] = (int32_t)running;
         }
     }
     __syncthreads();
     // ---- code + transposed write, 512 samples per tile (16 row segments in flight per warp) ------------
     const uint16_t *mypre = pre + lane * R32_STRIDE;
-    const uint32_t myesc = s_esc[lane];
-    const uint32_t *rankbm = myesc ? mybm2 : mybm;
     for (int64_t c0 = 0; c0 < n_pad; c0 += R32_CHUNK) {
         int32_t v[16];
 #pragma unroll
@@ -177,15 +142,7 @@ rthc_rank32(const IT *__restrict__ in, int64_t n, int64_t L, int64_t n_pad, uint
             if (v[u] > 0) {
                 const uint32_t w = (uint32_t)v[u] >> 5, bit = 1u << (v[u] & 31);
                 RTHC_DEV_ASSERT(mybm[w] & bit);                              // the id was marked in pass 1
-                if (rankbm[w] & bit) {
-                    code = (uint16_t)(1u + mypre[w] + __popc(rankbm[w] & (bit - 1u)));
-                } else {                                                     // a singleton of an escaping locus
-                    RTHC_DEV_ASSERT(myesc != 0);
-                    code = (uint16_t)myesc;
-                    const int pos = atomicAdd(&s_cnt[lane], 1);
-                    RTHC_DEV_ASSERT(pos < RTHC_ESC_CAP);
-                    esc_list[l * RTHC_ESC_CAP + pos] = (int32_t)(c0 + warp + 32 * u);
-                }
+                code = (uint16_t)(1u + mypre[w] + __popc(mybm[w] & (bit - 1u)));
                 RTHC_DEV_ASSERT(code >= 1 && code <= s_tot[lane]);
             }
             tile[lane * R32_TSTRIDE + warp + 32 * u] = code;
@@ -202,40 +159,6 @@ rthc_rank32(const IT *__restrict__ in, int64_t n, int64_t L, int64_t n_pad, uint
         }
         __syncthreads();
     }
-}
-
-// d(i, j) += 1 for every pair of samples listed for an escaping locus (one CTA per locus; see the note above).
-// Only rows this context computed are touched (tile-row ownership as in rthc_setup_geometry); the uint16 entry is
-// incremented through the aligned 32-bit word that holds it (no carry: true distances fit 16 bits).
-__global__ void __launch_bounds__(256) rthc_escape_correct(const int32_t *__restrict__ esc_cnt, const int32_t *__restrict__ esc_list,
-                                                           const int64_t *__restrict__ row_base, int64_t n_tile_rows, int world,
-                                                           int rank, uint16_t *cond)
-{
-    __shared__ int32_t s[RTHC_ESC_CAP];
-    const int64_t l = blockIdx.x;
-    const int S = esc_cnt[l];
-    if (S < 2) return;
-    for (int k = threadIdx.x; k < S; k += 256) s[k] = esc_list[l * RTHC_ESC_CAP + k];
-    __syncthreads();
-    for (int idx = threadIdx.x; idx < S * S; idx += 256) {
-        const int p = idx / S, q = idx - p * S;
-        if (p >= q) continue;
-        const int64_t i = min(s[p], s[q]), j = max(s[p], s[q]);
-        const int64_t r = i / RTHC_TILE;
-        if ((int)(min(r, n_tile_rows - 1 - r) % world) != rank) continue;
-        uint16_t *e = cond + row_base[i] + (j - i - 1);
-        atomicAdd(reinterpret_cast<unsigned int *>(reinterpret_cast<uintptr_t>(e) & ~(uintptr_t)3),
-                  (reinterpret_cast<uintptr_t>(e) & 2) ? 65536u : 1u);
-    }
-}
-
-int rthc_launch_escape_correct(rthc_ctx *ctx)
-{
-    if (!ctx->d_esc_cnt || ctx->escape_pairs == 0) return 0;
-    rthc_escape_correct<<<(unsigned)ctx->L, 256, 0, ctx->stream>>>(ctx->d_esc_cnt, ctx->d_esc_list, ctx->d_row_base, ctx->n_tiles_edge,
-                                                                 ctx->world, ctx->rank, ctx->d_cond);
-    RTHC_LAUNCH_CHECK(ctx);
-    return 0;
 }
 
 // ---- 2. per-locus dense rank through a shared-memory bitmap ---------------------------
@@ -542,31 +465,12 @@ static int rank_fast(rthc_ctx *ctx, const IT *d_rowmajor, int32_t *d_nall, int32
     const int64_t n = ctx->n, L = ctx->L, n_pad = ctx->n_pad;
     RTHC_CUDA(ctx, cudaMemsetAsync(d_status, 0, sizeof(int32_t), ctx->stream));
     RTHC_CUDA(ctx, cudaFuncSetAttribute(rthc_rank32<IT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)R32_SMEM));
-    // escape lists: RTHC_ESC_CAP sample indices per locus, only while that stays small (cg/wgMLST widths; a SNP matrix
-    // with millions of columns has at most a handful of alleles per column and nothing to escape)
-    static const bool esc_off = getenv("RTHC_NO_ESCAPE") != nullptr;          // test hook: plain dense ranking
-    const bool esc = !esc_off && L <= 65536;
-    int rc;
-    if ((rc = rthc_dev_alloc(ctx, &ctx->d_esc_code, (size_t)L))) return rc;
-    if ((rc = rthc_dev_alloc(ctx, &ctx->d_esc_cnt, (size_t)L))) return rc;
-    if (esc && (rc = rthc_dev_alloc(ctx, &ctx->d_esc_list, (size_t)L * RTHC_ESC_CAP))) return rc;
     rthc_rank32<IT><<<(unsigned)((L + 31) / 32), RANK_THREADS, R32_SMEM, ctx->stream>>>(d_rowmajor, n, L, n_pad, ctx->d_codes,
-                                                                                     d_nall, d_status, ctx->d_esc_code,
-                                                                                     ctx->d_esc_cnt, esc ? ctx->d_esc_list : nullptr);
+                                                                                     d_nall, d_status);
     RTHC_LAUNCH_CHECK(ctx);
-    std::vector<int32_t> cnt((size_t)L);
     RTHC_CUDA(ctx, cudaMemcpyAsync(&status, d_status, sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->stream));
     RTHC_CUDA(ctx, cudaMemcpyAsync(nall.data(), d_nall, sizeof(int32_t) * (size_t)L, cudaMemcpyDeviceToHost, ctx->stream));
-    RTHC_CUDA(ctx, cudaMemcpyAsync(cnt.data(), ctx->d_esc_cnt, sizeof(int32_t) * (size_t)L, cudaMemcpyDeviceToHost, ctx->stream));
     RTHC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-    ctx->escape_loci = ctx->escape_cells = ctx->escape_pairs = 0;
-    ctx->max_alleles_raw = 0;
-    if (!(status & 1))
-        for (int64_t l = 0; l < L; ++l) {
-            const int64_t S = cnt[(size_t)l];
-            ctx->max_alleles_raw = std::max<int64_t>(ctx->max_alleles_raw, nall[(size_t)l] + (S > 0 ? S - 1 : 0));
-            if (S > 0) { ctx->escape_loci++; ctx->escape_cells += S; ctx->escape_pairs += S * (S - 1) / 2; }
-        }
     return 0;
 }
 
@@ -579,9 +483,6 @@ static int rank_general(rthc_ctx *ctx, const IT *d_rowmajor, int32_t *d_nall, in
     const int64_t n = ctx->n, L = ctx->L, n_pad = ctx->n_pad;
     int32_t *d_colmajor = nullptr;
     int rc;
-    rthc_dev_free(ctx, &ctx->d_esc_code); rthc_dev_free(ctx, &ctx->d_esc_cnt); rthc_dev_free(ctx, &ctx->d_esc_list);
-    ctx->escape_loci = ctx->escape_cells = ctx->escape_pairs = 0;
-    ctx->max_alleles_raw = -1;
     if ((rc = rthc_dev_alloc(ctx, &d_colmajor, (size_t)(L * n_pad)))) return rc;
     {
         dim3 blk(32, 8), grd((unsigned)((L + 31) / 32), (unsigned)((n_pad + 31) / 32));
@@ -621,13 +522,18 @@ int rthc_recode_and_pack(rthc_ctx *ctx, const void *d_rowmajor, bool in_u16)
         if (rc) return rc;
     }
 
+    int max_all = 0;                                                   // distinct alleles of the widest locus
+    for (int64_t l = 0; l < L; ++l) max_all = std::max(max_all, (int)nall[(size_t)l]);
+    // fast path only: rare alleles of a locus may share codes (fewer bit planes, exact fix-up after the plane kernel);
+    // nall[] becomes the number of codes in use
+    ctx->escape_loci = ctx->escape_cells = 0; ctx->escape_pairs_u = 0;
+    ctx->d_pcodes = ctx->d_codes;
+    if (!ctx->recode_general && (rc = rthc_collide_codes(ctx, d_nall, max_all, nall))) return rc;
+
     // order loci by bit width (widest first), drop loci that cannot mismatch
     std::vector<int32_t> kept;
-    int max_all = 0;
-    for (int64_t l = 0; l < L; ++l) {
-        max_all = std::max(max_all, (int)nall[(size_t)l]);
+    for (int64_t l = 0; l < L; ++l)
         if (nall[(size_t)l] >= 2) kept.push_back((int32_t)l);
-    }
     std::stable_sort(kept.begin(), kept.end(), [&](int32_t a, int32_t b) {
         return bit_width(nall[(size_t)a]) > bit_width(nall[(size_t)b]);
     });
@@ -637,7 +543,7 @@ int rthc_recode_and_pack(rthc_ctx *ctx, const void *d_rowmajor, bool in_u16)
                          "stored as uint16, so at most 65,535 such loci are supported",
                          (long long)kept.size(), (long long)L);
     }
-    ctx->max_alleles = ctx->max_alleles_raw >= 0 ? (int)ctx->max_alleles_raw : max_all;      // distinct alleles, not codes
+    ctx->max_alleles = max_all;                                        // distinct alleles, not codes
     ctx->L_kept = (int64_t)kept.size();
     const int G = (int)((kept.size() + 31) / 32);
     std::vector<int32_t> perm((size_t)G * 32, -1), goff((size_t)std::max(G, 1)), gnp((size_t)std::max(G, 1));
@@ -676,7 +582,7 @@ int rthc_recode_and_pack(rthc_ctx *ctx, const void *d_rowmajor, bool in_u16)
             rthc_pack_planes<uint32_t><<<grd, 256, 0, ctx->stream>>>(ctx->d_codes32, d_perm, ctx->d_grp_off, ctx->d_grp_np,
                                                                      ctx->d_planes, n_pad, rows);
         else
-            rthc_pack_planes<uint16_t><<<grd, 256, 0, ctx->stream>>>(ctx->d_codes, d_perm, ctx->d_grp_off, ctx->d_grp_np,
+            rthc_pack_planes<uint16_t><<<grd, 256, 0, ctx->stream>>>(ctx->d_pcodes, d_perm, ctx->d_grp_off, ctx->d_grp_np,
                                                                      ctx->d_planes, n_pad, rows);
         RTHC_LAUNCH_CHECK(ctx);
     }

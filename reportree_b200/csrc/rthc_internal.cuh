@@ -11,7 +11,7 @@
 #define RTHC_TILE 128            // samples per tile-row (ownership granularity) of the distance kernel
 #define RTHC_BLK 64              // samples per plane block in HBM / per bulk copy
 #define RTHC_MIN_BITS 3          // every locus group carries at least 3 bit planes (zero-padded)
-#define RTHC_ESC_CAP 1024        // escape coding: at most this many singleton cells per locus are listed
+#define RTHC_ESC_CAP 4096        // shared codes (collide.cu): at most this many cells of a locus hold a shared code and are listed
 #define RTHC_KEY_INF 0xFFFFFFFFFFFFFFFFull
 #define RTHC_COND_PAD 64         // spare uint16 entries behind d_cond: 16-byte row loads may run 15 entries past a segment
 
@@ -48,9 +48,14 @@ struct rthc_ctx {
 
     // device buffers (distance half)
     uint16_t *d_codes = nullptr;   // [L][n_pad] dense-ranked codes, column-major per locus
-    // escape coding (recode.cu): per locus the escape code (0: none), the number of escaped cells and their samples
-    int32_t *d_esc_code = nullptr, *d_esc_cnt = nullptr, *d_esc_list = nullptr;
-    int64_t escape_loci = 0, escape_cells = 0, escape_pairs = 0, max_alleles_raw = -1;
+    // shared codes (collide.cu): what the plane packer reads (d_codes itself when no locus shares codes), per locus the
+    // number of listed cells, the cells (sample | code << 24 | dense rank << 40), pairs incremented by the last fix-up
+    uint16_t *d_pcodes = nullptr;
+    int32_t *d_esc_cnt = nullptr;
+    uint64_t *d_esc_list = nullptr;
+    unsigned long long *d_esc_pairs = nullptr;
+    unsigned long long escape_pairs_u = 0;
+    int64_t escape_loci = 0, escape_cells = 0;
     int64_t geom_n = -1; int geom_rank = -1, geom_world = -1; bool geom_full = false;      // what d_tiles / d_row_base were built for
     bool recode_general = false;   // last re-code left the fast path (an allele id >= 2^14 somewhere)
     uint32_t *d_codes32 = nullptr; // same, used INSTEAD of d_codes when a locus has more than 65,535 called alleles
@@ -173,7 +178,8 @@ int rthc_setup_geometry(rthc_ctx *ctx, int64_t n);
 int rthc_recode_and_pack(rthc_ctx *ctx, const void *d_rowmajor, bool in_u16);   // recode.cu
 int rthc_run_distance(rthc_ctx *ctx);                                 // distance.cu
 int rthc_launch_distance_ws(rthc_ctx *ctx, int max_np);                // distance_ws.cu
-int rthc_launch_escape_correct(rthc_ctx *ctx);                           // recode.cu
+int rthc_launch_escape_correct(rthc_ctx *ctx);                           // collide.cu
+int rthc_collide_codes(rthc_ctx *ctx, int32_t *d_nall, int max_alleles, std::vector<int32_t> &nall);   // collide.cu
 int rthc_run_direct_pairs(rthc_ctx *ctx, const int32_t *d_pi, const int32_t *d_pj, int64_t np,
                           int32_t *d_out);                            // distance.cu
 // Boruvka results stay on the device: *d_keys (pool allocation, caller frees with rthc_dev_free) holds *m packed

@@ -154,35 +154,65 @@ def test_uint16_input_and_both_recoder_paths_agree(hc, oracle, n, L):
         assert np.array_equal(ctx.condensed(), ref)
 
 
-@pytest.mark.parametrize("world", [1, 3])
-def test_escape_coded_singletons_are_fixed_up_exactly(hc, oracle, world):
-    """Loci whose allele count is dominated by singletons are re-coded with one shared escape code (fewer bit
-    planes) and the pairs of escaped cells get their mismatch back from rthc_escape_correct.  n = 3,000 so that the
-    device's cost rule accepts the escape; mixtures: no singletons, a few, hundreds, only singletons + one shared
-    allele, singletons next to missing cells, and a locus the rule must refuse (more singletons than the cap)."""
+def _shared_code_matrix(kind):
     rng = np.random.default_rng(77)
-    n, L = 3000, 40
-    X = rng.integers(1, 6, size=(n, L)).astype(np.int32)
+    if kind == "singletons":
+        # mixtures: no singletons, a few, hundreds, only singletons + one shared allele, singletons next to missing cells
+        n, L = 3000, 40
+        X = rng.integers(1, 6, size=(n, L)).astype(np.int32)
+        for l in range(L):
+            k = [0, 2, 3, 17, 60, 250, 700, 1500][l % 8]                    # singletons of this locus
+            rows = rng.choice(n, k, replace=False)
+            X[rows, l] = 1000 + np.arange(k)
+            if l % 5 == 0:
+                X[rng.choice(n, 40, replace=False), l] = 0
+        X[:, 7] = 1
+        X[rng.choice(n, 300, replace=False), 7] = 2000 + np.arange(300)      # one shared allele + 300 singletons
+        return X
+    if kind == "zipf":
+        # founder alleles with a long tail of rare ones (the shape of the C3 / C4 / C5 workloads), 3 % missing
+        from reportree_b200 import synth
+        return synth.allele_matrix(2500, 96, seed=5, missing=0.03, p_mut=0.02, founders=60)
+    # "flat": many alleles of similar, small counts -- every code of a locus receives (k = C), ties everywhere
+    n, L = 2000, 64
+    X = np.empty((n, L), dtype=np.int32)
     for l in range(L):
-        k = [0, 2, 3, 17, 60, 250, 700, 1500][l % 8]                    # singletons of this locus
-        rows = rng.choice(n, k, replace=False)
-        X[rows, l] = 1000 + np.arange(k)
-        if l % 5 == 0:
-            X[rng.choice(n, 40, replace=False), l] = 0
-    X[:, 7] = 1
-    X[rng.choice(n, 300, replace=False), 7] = 2000 + np.arange(300)      # one shared allele + 300 singletons
+        A = [9, 20, 64, 130, 300, 700, 1500, 1999][l % 8]
+        X[:, l] = 1 + rng.integers(0, A, n) * 3
+    X[rng.random((n, L)) < 0.02] = 0
+    return X
+
+
+@pytest.mark.parametrize("kind,div,world", [("singletons", None, 1), ("singletons", None, 3), ("singletons", "1", 1),
+                                            ("zipf", None, 1), ("zipf", "1", 3), ("zipf", "64", 1),
+                                            ("flat", "1", 1), ("flat", "300", 1), ("flat", None, 2)])
+def test_shared_codes_are_fixed_up_exactly(hc, oracle, monkeypatch, kind, div, world):
+    """Rare alleles of a locus share codes (fewer bit planes, collide.cu) and the pairs of cells that hold two
+    different alleles of one code get their mismatch back from rthc_collide_fixup.  RTHC_COLLIDE_DIV moves the
+    device's cost rule: 1 = share wherever the per-locus cell cap allows (every branch of the plan: all codes
+    receiving, level search, cap refusals), default = what production does at this size."""
+    if div is None:
+        monkeypatch.delenv("RTHC_COLLIDE_DIV", raising=False)
+    else:
+        monkeypatch.setenv("RTHC_COLLIDE_DIV", div)
+    X = _shared_code_matrix(kind)
+    n = X.shape[0]
+    rng = np.random.default_rng(1)
     ref = oracle.dist_condensed(X)
     ctxs = [hc.HCContext(rank=r, world=world) for r in range(world)]
     try:
         got = np.zeros_like(ref)
         seen = np.zeros(ref.size, dtype=bool)
         from reportree_b200 import sharded
+        pairs = 0
         for r, ctx in enumerate(ctxs):
             ctx.set_profiles(X)
             info = ctx.info()
-            assert info["escape_loci"] >= 10 and info["escape_pairs"] > 0, info
-            assert info["max_alleles"] >= 1500                            # distinct alleles, not codes
+            if div is not None or kind == "singletons":
+                assert info["escape_loci"] >= 5 and info["escape_cells"] > 0, info
+            assert info["max_alleles"] == max(np.unique(c[c > 0]).size for c in X.T)      # distinct alleles, not codes
             ctx.distance()
+            pairs += ctx.info()["escape_pairs"]
             rows = sharded.owned_rows(n, r, world)
             own = ctx.owned_condensed()
             p = 0
@@ -192,12 +222,14 @@ def test_escape_coded_singletons_are_fixed_up_exactly(hc, oracle, world):
                 got[base:base + cnt] = own[p:p + cnt]
                 seen[base:base + cnt] = True
                 p += cnt
-            if world == 1:                                                # the scalar check kernel knows the escape codes
+            if world == 1:                                                # the scalar check kernel reads the dense ranks
                 pi = rng.integers(0, n, 4000).astype(np.int32)
                 pj = rng.integers(0, n, 4000).astype(np.int32)
                 sq = (X[pi] != X[pj]) & (X[pi] != 0) & (X[pj] != 0)
                 assert np.array_equal(ctx.direct_pairs(pi, pj), sq.sum(1))
         assert seen.all() and np.array_equal(got, ref)
+        if div is not None or kind == "singletons":
+            assert pairs > 0
     finally:
         for c in ctxs:
             c.close()
