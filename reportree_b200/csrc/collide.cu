@@ -22,6 +22,7 @@
 #include "rthc_internal.cuh"
 
 #define COL_THREADS 512
+#define COL_PROBE 4096                    // samples counted before the two most frequent codes are singled out
 #define COL_CLAMP ((1u << 18) - 1u)       // sort key: min(count, COL_CLAMP) << 14 | (16383 - code)
 
 __device__ __forceinline__ int col_bit_width(int a) { return a <= 0 ? 0 : 32 - __clz(a); }
@@ -53,7 +54,7 @@ rthc_collide(const uint16_t *__restrict__ codes, uint16_t *__restrict__ pcodes, 
     uint32_t *psort = keys + N2;                                       // [N2 + 1] prefix sums of the sorted counts
     __shared__ unsigned long long s_red[COL_THREADS / 32];
     __shared__ int s_k, s_best_b, s_best_k, s_cnt;
-    __shared__ unsigned long long s_best_cost;
+    __shared__ unsigned long long s_best_cost, s_top;
     const int tid = threadIdx.x;
     const int64_t l = blockIdx.x;
     const uint16_t *col = codes + l * n_pad;
@@ -69,8 +70,12 @@ rthc_collide(const uint16_t *__restrict__ codes, uint16_t *__restrict__ pcodes, 
     for (int w = tid; w < N2; w += COL_THREADS) hist[w] = 0;
     if (tid == 0) s_cnt = 0;
     __syncthreads();
-    // ---- pass 1: count per code (equal codes of a warp are merged before the shared atomic) -----------------
-    for (int64_t s = 2 * tid; s < n_pad; s += 2 * COL_THREADS) {        // n_pad % 128 == 0: a warp is in or out as a whole
+    // ---- pass 1: count per code.  Lanes of a warp that hold the same code would serialise on one shared counter
+    // (the most frequent allele of a cgMLST locus covers 10..90 % of the samples), and __match_any_sync costs more than
+    // the rest of the loop.  So: the first COL_PROBE samples are counted with match_any, the two most frequent codes
+    // so far are then counted by ballot in registers, everything else goes straight to its counter. -------------------
+    const int64_t probe_end = min((int64_t)COL_PROBE, n_pad);
+    for (int64_t s = 2 * tid; s < probe_end; s += 2 * COL_THREADS) {    // n_pad % 128 == 0: a warp is in or out as a whole
         const uint32_t w = *reinterpret_cast<const uint32_t *>(col + s);
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
@@ -78,6 +83,38 @@ rthc_collide(const uint16_t *__restrict__ codes, uint16_t *__restrict__ pcodes, 
             const uint32_t m = __match_any_sync(0xffffffffu, c);
             if ((tid & 31) == __ffs(m) - 1) atomicAdd(&hist[c], (uint32_t)__popc(m));
         }
+    }
+    __syncthreads();
+    if (probe_end < n_pad) {
+        uint32_t top[2];
+#pragma unroll
+        for (int round = 0; round < 2; ++round) {
+            if (tid == 0) s_top = 0ull;
+            __syncthreads();
+            unsigned long long best = 0;
+            for (int c = 1 + tid; c <= A; c += COL_THREADS)
+                if (round == 0 || (uint32_t)c != top[0]) best = max(best, ((unsigned long long)hist[c] << 32) | (unsigned)c);
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) best = max(best, __shfl_xor_sync(0xffffffffu, best, o));
+            if ((tid & 31) == 0 && best) atomicMax(&s_top, best);
+            __syncthreads();
+            top[round] = (uint32_t)(s_top & 0xFFFFFFFFull);            // 0 (the missing code) if there is none
+            __syncthreads();
+        }
+        const uint32_t t1 = top[0], t2 = top[1];
+        uint32_t n1 = 0, n2 = 0;                                       // lane 0 of every warp
+        for (int64_t s = probe_end + 2 * tid; s < n_pad; s += 2 * COL_THREADS) {
+            const uint32_t w = *reinterpret_cast<const uint32_t *>(col + s);
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                const uint32_t c = h ? (w >> 16) : (w & 0xFFFFu);
+                const bool is1 = c == t1, is2 = c == t2;
+                n1 += __popc(__ballot_sync(0xffffffffu, is1));
+                n2 += __popc(__ballot_sync(0xffffffffu, is2));
+                if (!is1 && !is2) atomicAdd(&hist[c], 1u);
+            }
+        }
+        if ((tid & 31) == 0) { if (n1) atomicAdd(&hist[t1], n1); if (n2 && t2 != t1) atomicAdd(&hist[t2], n2); }
     }
     __syncthreads();
     // ---- sort the alleles by count, descending (bitonic, keys padded with 0) ---------------------------------
