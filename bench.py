@@ -196,6 +196,7 @@ def run_ours(args):
     state = {"dist_ms": [], "link_ms": [], "cut_ms": [], "recode_ms": [], "h2d_ms": [], "d2h_bytes": 0, "Z": None}
     exch = sharded.ForestExchange(n, dist) if world > 1 else None                 # device-resident forest gather
     loader = sharded.ShardedProfileLoader(n, L, dist) if world > 1 else None      # 1/world of the rows per rank + all_gather
+    planes_x = sharded.PlaneExchange(n, L, dist) if sharded.PlaneExchange.usable(L, world) else None   # re-coder sharded by loci
 
     seg = {}
 
@@ -207,10 +208,16 @@ def run_ours(args):
     def step(resident):
         t = time.perf_counter()
         if resident:
-            ctx.set_profiles_device(dX.data_ptr(), n, L)
+            if planes_x is not None:
+                planes_x.set_profiles(ctx, dX.data_ptr(), np.int32)
+            else:
+                ctx.set_profiles_device(dX.data_ptr(), n, L)
         elif world > 1:
             ptr = loader.load(host_codes)
-            ctx.set_profiles_device(ptr, n, L, loader.dtype)
+            if planes_x is not None:
+                planes_x.set_profiles(ctx, ptr, loader.dtype)
+            else:
+                ctx.set_profiles_device(ptr, n, L, loader.dtype)
         else:
             ctx.set_profiles(host_codes)
         t = lap("set_profiles", t)
@@ -286,6 +293,11 @@ def run_ours(args):
     kern = {k: float(np.mean(v)) for k, v in state.items() if isinstance(v, list) and v}
     kern_steps = {k: [round(float(x), 3) for x in v] for k, v in state.items() if isinstance(v, list) and v}
     host_seg = {k: round(float(np.mean(v)), 3) for k, v in seg.items()}
+    host_seg_all = None
+    if world > 1:                                   # where each rank spends its step (a slow rank shows up as waiting time of the others)
+        host_seg_all = [None] * world
+        dist.all_gather_object(host_seg_all, dict(host_seg, dist_kernel=round(float(np.mean(state["dist_ms"])), 3),
+                                                  recode=round(float(np.mean(state["recode_ms"])), 3)))
     info = ctx.info()
     owned_pairs = ctx.owned_pairs()
     clocks = sampler.stop() if rank == 0 else None
@@ -355,12 +367,13 @@ def run_ours(args):
             "config": {"workload": WORKLOAD["name"], "n": n, "L": L, "pairs": P, "thresholds": WORKLOAD["thresholds"],
                        "l2": "inputs larger than L2 (bit planes %.0f MB + condensed output %.1f GB per step)" % (
                            info["plane_rows"] * ctx_npad(n) * 4 / 1e6, 2.0 * owned_pairs / 1e9),
-                       "sharding": "tile-rows of the upper triangle over %d rank(s)" % world,
+                       "sharding": "tile-rows of the upper triangle over %d rank(s)" % world + (
+                           "; re-coder sharded by locus ranges, planes gathered over NCCL" if planes_x is not None else ""),
                        "single_linkage": "Boruvka MST (north_star; same partitions as scipy, cluster ids may differ on ties); "
                                          "exact_names_mode times the CLI-default scipy-order Prim"},
             "stage_ms": kern,
             "stage_ms_per_step": kern_steps,
-            "host_wall_ms_rank0": host_seg,
+            "host_wall_ms_rank0": host_seg, "host_wall_ms_all_ranks": host_seg_all,
             "e2e_stage_ms_per_step": {k: [round(float(x), 3) for x in v] for k, v in state.items() if isinstance(v, list) and v},
             "roofline": roofline,
             "e2e": {"value": e2e_value, "unit": "comparisons/s", "ms_per_step": 1e3 * dt_e2e / args.steps,

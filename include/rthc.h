@@ -142,6 +142,37 @@ int rthc_local_forest_device(rthc_ctx *ctx, uint64_t *d_keys_out, int64_t capaci
  * must have synchronised whatever produced them.                                                       */
 int rthc_linkage_from_forest_device(rthc_ctx *ctx, const uint64_t *d_keys, int64_t m, int64_t n,
                                     double *Z_out);
+/* ---- re-coder sharded by locus ranges ------------------------------------------------------
+ * Replaces, for world > 1, the replicated call of rthc_set_profiles_*_device: the per-locus work of the
+ * reference's input stage (the cell parse / allele identity of cgmlst-dists behind
+ * scripts/partitioning_HC.py:502, cleaning :293-298) is independent per locus, so rank q of the context's shard
+ * (rthc_set_shard) re-codes and bit-slices only the loci [q * chunk, (q + 1) * chunk), chunk =
+ * rthc_shard_chunk(L, world) (a multiple of 32), and the caller gathers the ranks' products with its own
+ * collective (torch.distributed all_gather_into_tensor over NCCL in reportree_b200/sharded.py):
+ *   1. rthc_recode_shard(ctx, dev_codes, in_u16, n, L, hdr, hdr_len): dev_codes = the WHOLE n x L row-major
+ *      matrix in device memory (int32, or uint16 when in_u16); hdr (host, hdr_len >= RTHC_SHARD_HDR + chunk / 32
+ *      int32) receives [0] groups of 32 loci, [1] plane rows, [2] most planes in a group, [3] loci kept,
+ *      [4] most alleles in a locus, [5] loci with shared codes, [6] cells listed for the fix-up, [7] loci of
+ *      this rank, [RTHC_SHARD_HDR + g] planes of group g.
+ *   2. the caller gathers the headers (host or device), takes rows_max = max over ranks of hdr[1] and provides
+ *      three DEVICE buffers: planes uint32[world][n_pad / 64][rows_max][64] (n_pad = n rounded up to 128),
+ *      counts int32[world][chunk], cells uint64[world][chunk][4096].
+ *   3. rthc_export_shard(ctx, planes slot of this rank, rows_max, counts slot, cells slot): fills this rank's
+ *      slots (synchronous on return); the caller runs one all_gather per buffer.
+ *   4. rthc_import_planes(ctx, planes, rows_max, hdr_all (host, world x hdr_len), hdr_len, counts, cells):
+ *      the context is then in the state rthc_set_profiles_* leaves (ready for rthc_distance).  The three
+ *      gathered buffers are BORROWED: they must stay allocated and unchanged until the next
+ *      rthc_set_profiles_* / rthc_recode_shard / rthc_destroy of this context.
+ * Distances are identical to the unsharded path (the loci are the same, their grouping differs);
+ * rthc_direct_pairs is not available in this state.                                                     */
+#define RTHC_SHARD_HDR 8
+int64_t rthc_shard_chunk(int64_t L, int world);
+int rthc_recode_shard(rthc_ctx *ctx, const void *dev_codes, int in_u16, int64_t n, int64_t L, int32_t *hdr,
+                      int64_t hdr_len);
+int rthc_export_shard(rthc_ctx *ctx, void *d_planes_slot, int64_t rows_max, int32_t *d_cnt_slot,
+                      uint64_t *d_list_slot);
+int rthc_import_planes(rthc_ctx *ctx, const void *d_planes_all, int64_t rows_max, const int32_t *hdr_all,
+                       int64_t hdr_len, const int32_t *d_cnt_all, const uint64_t *d_list_all);
 /* labels_out: T x n int32, row k = fcluster(Z, t[k], "distance") of the last linkage. */
 int rthc_cut(rthc_ctx *ctx, const double *t, int T, int32_t *labels_out);
 

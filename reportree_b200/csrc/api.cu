@@ -112,11 +112,16 @@ extern "C" int rthc_mark_elapsed_ms(rthc_ctx *ctx, double *ms)
 
 void rthc_free_distance_state(rthc_ctx *ctx)
 {
+    if (ctx->planes_borrowed) {                                             // the caller's gathered buffers (rthc_import_planes)
+        ctx->d_planes = nullptr; ctx->d_esc_cnt = nullptr; ctx->d_esc_list = nullptr;
+        ctx->planes_borrowed = false;
+    }
+    ctx->L_stride = 0;
     if (ctx->d_pcodes == ctx->d_codes) ctx->d_pcodes = nullptr;              // an alias when no locus shares codes
     rthc_dev_free(ctx, &ctx->d_pcodes);
     rthc_dev_free(ctx, &ctx->d_codes); rthc_dev_free(ctx, &ctx->d_codes32); rthc_dev_free(ctx, &ctx->d_planes);
     rthc_dev_free(ctx, &ctx->d_esc_cnt); rthc_dev_free(ctx, &ctx->d_esc_list); rthc_dev_free(ctx, &ctx->d_esc_pairs);
-    rthc_dev_free(ctx, &ctx->d_grp_off); rthc_dev_free(ctx, &ctx->d_grp_np);
+    rthc_dev_free(ctx, &ctx->d_grp_off); rthc_dev_free(ctx, &ctx->d_grp_np); rthc_dev_free(ctx, &ctx->d_grp_base);
     rthc_dev_free(ctx, &ctx->d_cond_f64);
     ctx->have_profiles = ctx->have_dist = false;
 }
@@ -142,6 +147,7 @@ extern "C" void rthc_destroy(rthc_ctx *ctx)
     rthc_free_distance_state(ctx);
     rthc_free_geometry(ctx);
     rthc_dev_free(ctx, &ctx->d_cond);
+    rthc_dev_free(ctx, &ctx->d_gbm);
     rthc_free_linkage_state(ctx);
     if (ctx->ev0) cudaEventDestroy(ctx->ev0);
     if (ctx->ev1) cudaEventDestroy(ctx->ev1);
@@ -384,6 +390,152 @@ extern "C" int rthc_set_profiles_u16(rthc_ctx *ctx, const uint16_t *codes, int64
 extern "C" int rthc_set_profiles_u16_device(rthc_ctx *ctx, const void *dev_codes, int64_t n, int64_t L)
 {
     return set_profiles_device(ctx, dev_codes, n, L, true);
+}
+
+// ---- re-coder sharded by locus ranges (everything that does not shard caps the scaling) ----------------
+// With several ranks the distance tiles shard but the re-coder would run in full on every rank (C4: 3.6 ms of a
+// 39 ms step on 8 GPUs).  The loci are independent until the planes are built, so rank q re-codes and packs only the
+// loci [q * chunk, (q + 1) * chunk) -- the SAME code path as a whole matrix, applied to a column range -- and the
+// ranks then gather three buffers (planes, listed-cell counts, listed cells) with the caller's collective:
+//     rthc_recode_shard   ->  header (groups, plane rows, plane count per group, ...) of this rank
+//     (caller: all_gather of the headers, rows_max = widest rank, allocates the gathered buffers)
+//     rthc_export_shard   ->  this rank's slot of the gathered buffers filled
+//     (caller: all_gather_into_tensor x 3)
+//     rthc_import_planes  ->  context ready for rthc_distance, planes = [rank][64-sample block][rows_max][64]
+// The groups of a rank never mix with another rank's, so the result is the same set of loci in another order: the
+// distances are identical (tests: every cell against the CPU restatement).
+static inline int64_t shard_chunk(int64_t L, int world)
+{
+    return ((L + world - 1) / world + 31) / 32 * 32;
+}
+extern "C" int64_t rthc_shard_chunk(int64_t L, int world) { return world < 1 ? 0 : shard_chunk(L, world); }
+
+extern "C" int rthc_recode_shard(rthc_ctx *ctx, const void *dev_codes, int in_u16, int64_t n, int64_t L, int32_t *hdr,
+                                 int64_t hdr_len)
+{
+    if (!ctx || !dev_codes || !hdr) return rthc_fail(ctx, RTHC_E_ARG, "rthc_recode_shard: NULL argument");
+    int rc = check_shape(ctx, n, L);
+    if (rc) return rc;
+    const int64_t chunk = shard_chunk(L, ctx->world);
+    if (hdr_len < RTHC_SHARD_HDR + chunk / 32) return rthc_fail(ctx, RTHC_E_ARG, "rthc_recode_shard: header too short");
+    RTHC_CUDA(ctx, cudaSetDevice(ctx->device));
+    rthc_free_distance_state(ctx);
+    rthc_free_linkage_state(ctx);
+    ctx->t_ms[0] = 0;
+    RTHC_CUDA(ctx, cudaDeviceSynchronize());   // the caller's producer stream is unknown
+    const int64_t l0 = std::min(L, ctx->rank * chunk), l1 = std::min(L, l0 + chunk), Lloc = l1 - l0;
+    for (int64_t k = 0; k < hdr_len; ++k) hdr[k] = 0;
+    ctx->L_global = L;
+    if (Lloc == 0) {                           // more ranks than 32-locus blocks: this one contributes nothing
+        ctx->L = 0; ctx->G = 0; ctx->plane_rows = 0; ctx->max_np = 0; ctx->L_kept = 0; ctx->max_alleles = 0;
+        ctx->escape_loci = ctx->escape_cells = 0; ctx->h_grp_np.clear(); ctx->t_ms[1] = 0;
+        return rthc_setup_geometry(ctx, n);
+    }
+    ctx->L_stride = L;
+    const size_t elem = in_u16 ? sizeof(uint16_t) : sizeof(int32_t);
+    rc = set_profiles_common(ctx, (const unsigned char *)dev_codes + (size_t)l0 * elem, n, Lloc, in_u16 != 0);
+    ctx->L_stride = 0;
+    ctx->have_profiles = false;                // not before rthc_import_planes
+    if (rc) return rc;
+    hdr[0] = ctx->G; hdr[1] = ctx->plane_rows; hdr[2] = ctx->max_np; hdr[3] = (int32_t)ctx->L_kept;
+    hdr[4] = ctx->max_alleles; hdr[5] = (int32_t)ctx->escape_loci;
+    hdr[6] = (int32_t)std::min<int64_t>(ctx->escape_cells, INT32_MAX); hdr[7] = (int32_t)Lloc;
+    for (int g = 0; g < ctx->G; ++g) hdr[RTHC_SHARD_HDR + g] = ctx->h_grp_np[(size_t)g];
+    return 0;
+}
+
+extern "C" int rthc_export_shard(rthc_ctx *ctx, void *d_planes_slot, int64_t rows_max, int32_t *d_cnt_slot,
+                                 uint64_t *d_list_slot)
+{
+    if (!ctx || !d_planes_slot || !d_cnt_slot || !d_list_slot) return rthc_fail(ctx, RTHC_E_ARG, "rthc_export_shard: NULL argument");
+    if (ctx->L_global <= 0 || ctx->planes_borrowed) return rthc_fail(ctx, RTHC_E_STATE, "rthc_export_shard before rthc_recode_shard");
+    if (rows_max < ctx->plane_rows) return rthc_fail(ctx, RTHC_E_ARG, "rthc_export_shard: rows_max below this rank's plane rows");
+    RTHC_CUDA(ctx, cudaSetDevice(ctx->device));
+    RTHC_CUDA(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
+    const int64_t chunk = shard_chunk(ctx->L_global, ctx->world), nblk = ctx->n_pad / RTHC_BLK, Lloc = ctx->L;
+    if (ctx->plane_rows > 0)
+        RTHC_CUDA(ctx, cudaMemcpy2DAsync(d_planes_slot, (size_t)rows_max * RTHC_BLK * 4, ctx->d_planes,
+                                         (size_t)ctx->plane_rows * RTHC_BLK * 4, (size_t)ctx->plane_rows * RTHC_BLK * 4,
+                                         (size_t)nblk, cudaMemcpyDeviceToDevice, ctx->stream));
+    RTHC_CUDA(ctx, cudaMemsetAsync(d_cnt_slot, 0, sizeof(int32_t) * (size_t)chunk, ctx->stream));
+    if (ctx->d_esc_cnt && ctx->d_esc_list && ctx->escape_cells > 0 && Lloc > 0) {
+        RTHC_CUDA(ctx, cudaMemcpyAsync(d_cnt_slot, ctx->d_esc_cnt, sizeof(int32_t) * (size_t)Lloc, cudaMemcpyDeviceToDevice, ctx->stream));
+        RTHC_CUDA(ctx, cudaMemcpyAsync(d_list_slot, ctx->d_esc_list, sizeof(uint64_t) * (size_t)Lloc * RTHC_ESC_CAP,
+                                       cudaMemcpyDeviceToDevice, ctx->stream));
+    }
+    RTHC_CUDA(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
+    RTHC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));        // the collective runs on the caller's stream
+    float ms = 0;
+    RTHC_CUDA(ctx, cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1));
+    ctx->t_ms[1] += ms;
+    return 0;
+}
+
+extern "C" int rthc_import_planes(rthc_ctx *ctx, const void *d_planes_all, int64_t rows_max, const int32_t *hdr_all,
+                                  int64_t hdr_len, const int32_t *d_cnt_all, const uint64_t *d_list_all)
+{
+    if (!ctx || !d_planes_all || !hdr_all || !d_cnt_all || !d_list_all)
+        return rthc_fail(ctx, RTHC_E_ARG, "rthc_import_planes: NULL argument");
+    if (ctx->L_global <= 0 || ctx->planes_borrowed) return rthc_fail(ctx, RTHC_E_STATE, "rthc_import_planes before rthc_recode_shard");
+    RTHC_CUDA(ctx, cudaSetDevice(ctx->device));
+    const int64_t L = ctx->L_global, chunk = shard_chunk(L, ctx->world), nblk = ctx->n_pad / RTHC_BLK;
+    // this rank's own re-code products are in the gathered buffers now
+    if (ctx->d_pcodes == ctx->d_codes) ctx->d_pcodes = nullptr;
+    rthc_dev_free(ctx, &ctx->d_pcodes); rthc_dev_free(ctx, &ctx->d_codes); rthc_dev_free(ctx, &ctx->d_codes32);
+    rthc_dev_free(ctx, &ctx->d_planes); rthc_dev_free(ctx, &ctx->d_esc_cnt); rthc_dev_free(ctx, &ctx->d_esc_list);
+    rthc_dev_free(ctx, &ctx->d_grp_off); rthc_dev_free(ctx, &ctx->d_grp_np); rthc_dev_free(ctx, &ctx->d_grp_base);
+    std::vector<int64_t> gbase;
+    std::vector<int32_t> gnp;
+    int64_t rows = 0, kept = 0, cells = 0, loci = 0;
+    int max_np = 0, max_all = 0;
+    for (int q = 0; q < ctx->world; ++q) {
+        const int32_t *h = hdr_all + (size_t)q * (size_t)hdr_len;
+        if (h[0] < 0 || RTHC_SHARD_HDR + (int64_t)h[0] > hdr_len || h[1] > rows_max)
+            return rthc_fail(ctx, RTHC_E_ARG, "rthc_import_planes: header of rank %d is inconsistent", q);
+        int64_t off = 0;
+        for (int g = 0; g < h[0]; ++g) {
+            const int np = h[RTHC_SHARD_HDR + g];
+            gbase.push_back((int64_t)q * nblk * rows_max + off);
+            gnp.push_back(np);
+            off += np;
+        }
+        if (off != h[1]) return rthc_fail(ctx, RTHC_E_ARG, "rthc_import_planes: plane rows of rank %d do not add up", q);
+        rows += h[1]; max_np = std::max(max_np, (int)h[2]); kept += h[3]; max_all = std::max(max_all, (int)h[4]);
+        loci += h[5]; cells += h[6];
+    }
+    if (kept > 65535)
+        return rthc_fail(ctx, RTHC_E_RANGE, "%lld of the %lld loci have two or more called alleles; distances are "
+                         "stored as uint16, so at most 65,535 such loci are supported", (long long)kept, (long long)L);
+    const int G = (int)gnp.size();
+    {   // the distance kernel runs one unrolled body per plane count: keep groups of equal width together, widest first,
+        // as the unsharded re-coder does (every change of body is an instruction-cache refill)
+        std::vector<int> order((size_t)G);
+        for (int g = 0; g < G; ++g) order[(size_t)g] = g;
+        std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return gnp[(size_t)a] > gnp[(size_t)b]; });
+        std::vector<int64_t> b2((size_t)G);
+        std::vector<int32_t> n2((size_t)G);
+        for (int g = 0; g < G; ++g) { b2[(size_t)g] = gbase[(size_t)order[(size_t)g]]; n2[(size_t)g] = gnp[(size_t)order[(size_t)g]]; }
+        gbase.swap(b2); gnp.swap(n2);
+    }
+    int rc;
+    if ((rc = rthc_dev_alloc(ctx, &ctx->d_grp_base, (size_t)std::max(G, 1)))) return rc;
+    if ((rc = rthc_dev_alloc(ctx, &ctx->d_grp_np, (size_t)std::max(G, 1)))) return rc;
+    if (!ctx->d_esc_pairs && (rc = rthc_dev_alloc(ctx, &ctx->d_esc_pairs, 1))) return rc;
+    if (G > 0) {
+        RTHC_CUDA(ctx, cudaMemcpyAsync(ctx->d_grp_base, gbase.data(), sizeof(int64_t) * (size_t)G, cudaMemcpyHostToDevice, ctx->stream));
+        RTHC_CUDA(ctx, cudaMemcpyAsync(ctx->d_grp_np, gnp.data(), sizeof(int32_t) * (size_t)G, cudaMemcpyHostToDevice, ctx->stream));
+    }
+    RTHC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    ctx->d_planes = const_cast<uint32_t *>(static_cast<const uint32_t *>(d_planes_all));
+    ctx->d_esc_cnt = const_cast<int32_t *>(d_cnt_all);
+    ctx->d_esc_list = const_cast<uint64_t *>(d_list_all);
+    ctx->planes_borrowed = true;
+    ctx->blk_stride_rows = rows_max;
+    ctx->esc_L = (int64_t)ctx->world * chunk;
+    ctx->L = L; ctx->G = G; ctx->plane_rows = (int)rows; ctx->max_np = max_np; ctx->L_kept = kept; ctx->max_alleles = max_all;
+    ctx->escape_loci = loci; ctx->escape_cells = cells; ctx->escape_pairs_u = 0;
+    ctx->have_profiles = true;
+    return 0;
 }
 
 extern "C" int rthc_distance(rthc_ctx *ctx)

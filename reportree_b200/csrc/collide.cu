@@ -351,7 +351,7 @@ int rthc_launch_escape_correct(rthc_ctx *ctx)
     if (!ctx->d_esc_cnt || !ctx->d_esc_list || ctx->escape_cells == 0) return 0;
     RTHC_CUDA(ctx, cudaMemsetAsync(ctx->d_esc_pairs, 0, sizeof(unsigned long long), ctx->stream));
     RTHC_CUDA(ctx, cudaFuncSetAttribute(rthc_collide_fixup, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FIX_SMEM));
-    rthc_collide_fixup<<<(unsigned)ctx->L, FIX_THREADS, FIX_SMEM, ctx->stream>>>(ctx->d_esc_cnt, ctx->d_esc_list, ctx->d_row_base, ctx->n_tiles_edge,
+    rthc_collide_fixup<<<(unsigned)ctx->esc_L, FIX_THREADS, FIX_SMEM, ctx->stream>>>(ctx->d_esc_cnt, ctx->d_esc_list, ctx->d_row_base, ctx->n_tiles_edge,
                                                                 ctx->world, ctx->rank, ctx->d_cond, ctx->d_esc_pairs);
     RTHC_LAUNCH_CHECK(ctx);
     RTHC_CUDA(ctx, cudaMemcpyAsync(&ctx->escape_pairs_u, ctx->d_esc_pairs, sizeof(unsigned long long), cudaMemcpyDeviceToHost,
@@ -369,6 +369,7 @@ int rthc_collide_codes(rthc_ctx *ctx, int32_t *d_nall, int max_alleles, std::vec
     // columns has a handful of alleles per column and nothing to share)
     const bool on = !off && L <= 65536 && max_alleles >= (1 << RTHC_MIN_BITS);
     ctx->escape_loci = ctx->escape_cells = 0; ctx->escape_pairs_u = 0;
+    ctx->esc_L = L;
     if (!on) { ctx->d_pcodes = ctx->d_codes; return 0; }
     int rc;
     int32_t *d_nall2 = nullptr;

@@ -193,8 +193,8 @@ __device__ __forceinline__ void ws_run(WsRing &R, WsAcc &A, WsOps &cur, int coun
 }
 
 __global__ void __launch_bounds__(WS_THREADS, 1)
-rthc_distance_ws(const uint32_t *__restrict__ planes, const int32_t *__restrict__ grp_off,
-                 const int32_t *__restrict__ grp_np, int G, int max_np, int plane_rows,
+rthc_distance_ws(const uint32_t *__restrict__ planes, const int64_t *__restrict__ grp_base,
+                 const int32_t *__restrict__ grp_np, int G, int max_np, int64_t blk_stride_rows,
                  const int2 *__restrict__ tiles, int n_tiles, const int64_t *__restrict__ row_base,
                  int64_t n, uint16_t *__restrict__ cond)
 {
@@ -206,8 +206,8 @@ rthc_distance_ws(const uint32_t *__restrict__ planes, const int32_t *__restrict_
     const int blk_words = max_np * RTHC_BLK;
     const uint32_t stage_words = (uint32_t)blk_words * 4;
     uint32_t *stage_base = reinterpret_cast<uint32_t *>(smem_raw);
-    uint32_t *gtab = stage_base + (size_t)RTHC_STAGES * stage_words;     // (offset << 8) | np per group
-    for (int g = tid; g < G; g += WS_THREADS) gtab[g] = ((uint32_t)grp_off[g] << 8) | (uint32_t)grp_np[g];
+    uint64_t *gtab = reinterpret_cast<uint64_t *>(stage_base + (size_t)RTHC_STAGES * stage_words);     // (row offset << 8) | np per group
+    for (int g = tid; g < G; g += WS_THREADS) gtab[g] = ((uint64_t)grp_base[g] << 8) | (uint64_t)grp_np[g];
     if (tid == 0) {
 #pragma unroll
         for (int s = 0; s < RTHC_STAGES; ++s) {
@@ -224,7 +224,7 @@ rthc_distance_ws(const uint32_t *__restrict__ planes, const int32_t *__restrict_
         // ------------------------------ producer warp ------------------------------------------
         asm volatile("setmaxnreg.dec.sync.aligned.u32 24;");
         if (tid == WS_CONSUMERS) {
-            const size_t blk_stride = (size_t)plane_rows * RTHC_BLK;      // words per 64-sample block in HBM
+            const size_t blk_stride = (size_t)blk_stride_rows * RTHC_BLK; // words per 64-sample block in HBM
             uint32_t it = 0;
             // one padding group (group 0 of the last tile again) closes the ring: consumers fetch
             // plane 0 of "the next group" unconditionally
@@ -238,14 +238,15 @@ rthc_distance_ws(const uint32_t *__restrict__ planes, const int32_t *__restrict_
                 for (int g = 0; g < (pad ? 1 : G); ++g, ++it) {
                     const uint32_t s = it % RTHC_STAGES;
                     if (it >= RTHC_STAGES) mbar_wait(&empty_bar[s], ((it / RTHC_STAGES) - 1u) & 1u);
-                    const uint32_t e = gtab[g];
-                    const uint32_t np = e & 0xFFu, off = e >> 8;
+                    const uint64_t e = gtab[g];
+                    const uint32_t np = (uint32_t)(e & 0xFFu);
+                    const size_t off = (size_t)(e >> 8);
                     const uint32_t bytes = np * RTHC_BLK * 4u;
                     uint32_t *dst = stage_base + (size_t)s * stage_words;
                     mbar_expect_tx(&full_bar[s], 4 * bytes);
 #pragma unroll
                     for (int h = 0; h < 4; ++h)
-                        tma_bulk_g2s(dst + h * blk_words, srcs[h] + (size_t)off * RTHC_BLK, bytes, &full_bar[s]);
+                        tma_bulk_g2s(dst + h * blk_words, srcs[h] + off * RTHC_BLK, bytes, &full_bar[s]);
                 }
             }
         }
@@ -324,13 +325,13 @@ rthc_distance_ws(const uint32_t *__restrict__ planes, const int32_t *__restrict_
 int rthc_launch_distance_ws(rthc_ctx *ctx, int max_np)
 {
     const size_t smem = (size_t)RTHC_STAGES * (size_t)max_np * 4 * RTHC_BLK * sizeof(uint32_t) +
-                        (size_t)(ctx->G + 1) * sizeof(uint32_t);
+                        (size_t)(ctx->G + 1) * sizeof(uint64_t);
     if (smem > 200u * 1024u)
         return rthc_fail(ctx, RTHC_E_RANGE, "plane stage does not fit shared memory (max_np=%d)", max_np);
     RTHC_CUDA(ctx, cudaFuncSetAttribute(rthc_distance_ws, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const int64_t grid = ctx->n_tiles < ctx->sm_count ? ctx->n_tiles : ctx->sm_count;
     rthc_distance_ws<<<(unsigned)grid, WS_THREADS, smem, ctx->stream>>>(
-        ctx->d_planes, ctx->d_grp_off, ctx->d_grp_np, ctx->G, max_np, ctx->plane_rows, ctx->d_tiles,
+        ctx->d_planes, ctx->d_grp_base, ctx->d_grp_np, ctx->G, max_np, ctx->blk_stride_rows, ctx->d_tiles,
         (int)ctx->n_tiles, ctx->d_row_base, ctx->n, ctx->d_cond);
     RTHC_LAUNCH_CHECK(ctx);
     return 0;

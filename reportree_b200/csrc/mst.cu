@@ -422,8 +422,13 @@ static int sort_keys_device(rthc_ctx *ctx, const uint64_t *d_keys, int64_t m, ui
 // shared round loop: `scan` launches the lightest-edge pass for the current components.  The forest stays on the
 // device: *d_out (caller frees) holds *m_out keys, ascending when `sorted`.
 template <typename ScanFn>
-static int boruvka_rounds(rthc_ctx *ctx, int64_t n, ScanFn scan, bool sorted, int *hint, uint64_t **d_out, int64_t *m_out)
+static int boruvka_rounds(rthc_ctx *ctx, int64_t n, ScanFn scan, bool sorted, int *hint, uint64_t **d_out, int64_t *m_out,
+                          int64_t full_count = -1)
 {
+    // full_count: edges of the complete forest when the caller knows it (n - 1 for a connected edge set; fewer for a
+    // shard whose first rows belong to other ranks: their samples are isolated here).  Without it a disconnected
+    // edge set needs one more round -- one more pass over the matrix -- just to see that nothing is added.
+    const int64_t stop_n = full_count >= 0 ? full_count + 1 : n;
     int32_t *d_comp = nullptr, *d_parent = nullptr;
     uint64_t *d_best = nullptr, *d_keys = nullptr;
     unsigned int *d_state = nullptr;
@@ -442,14 +447,14 @@ static int boruvka_rounds(rthc_ctx *ctx, int64_t n, ScanFn scan, bool sorted, in
     // round that turns out not to be needed costs nine empty launches), then one by one until the device says done.
     unsigned int st[4] = {0, 0, 0, 0};
     int batch = std::max(1, *hint);
-    while (!st[BST_DONE] && (int64_t)st[BST_COUNT] < n - 1) {
+    while (!st[BST_DONE] && (int64_t)st[BST_COUNT] < stop_n - 1) {
         for (int r = 0; r < batch; ++r) {
             rthc_fill_u64_round<<<nb, 256, 0, ctx->stream>>>(d_best, n, RTHC_KEY_INF, d_state);
             RTHC_LAUNCH_CHECK(ctx);
             if ((rc = scan(d_comp, d_best, d_state))) return rc;
             rthc_boruvka_hook<<<nb, 256, 0, ctx->stream>>>(d_best, d_comp, d_parent, n, d_keys, d_state);
             RTHC_LAUNCH_CHECK(ctx);
-            rthc_boruvka_round_end<<<1, 1, 0, ctx->stream>>>(d_state, n);
+            rthc_boruvka_round_end<<<1, 1, 0, ctx->stream>>>(d_state, stop_n);
             RTHC_LAUNCH_CHECK(ctx);
             for (int it = 0; it < 4; ++it) {      // 16x path compression bounds the chase below on adversarial chains
                 rthc_pointer_jump<<<nb, 256, 0, ctx->stream>>>(d_parent, n, d_state);
@@ -509,7 +514,9 @@ int rthc_boruvka_owned(rthc_ctx *ctx, bool sorted, uint64_t **d_keys, int64_t *m
         }
         return 0;
     };
-    const int rc = boruvka_rounds(ctx, n, scan, sorted, &ctx->boruvka_hint_owned, d_keys, m);
+    // the owned rows i reach every sample j > i, so the shard's forest spans exactly the samples from its first row on
+    const int64_t full_count = n_owned > 0 ? n - 1 - (int64_t)ctx->h_owned_rows.front() : 0;
+    const int rc = boruvka_rounds(ctx, n, scan, sorted, &ctx->boruvka_hint_owned, d_keys, m, full_count);
     rthc_dev_free(ctx, &d_bands);
     return rc;
 }

@@ -26,13 +26,13 @@
 // ---- 1. transpose n x L (row-major int32 / uint16) -> L x n_pad int32 (general path only) ----
 template <typename IT>
 __global__ void rthc_transpose_i32(const IT *__restrict__ in, int32_t *__restrict__ out,
-                                   int64_t n, int64_t L, int64_t n_pad)
+                                   int64_t n, int64_t L, int64_t n_pad, int64_t Ls)
 {
-    __shared__ int32_t tile[32][33];
+    __shared__ int32_t tile[32][33];                       // Ls: row stride of `in` (L, or more when `in` is a column range)
     int64_t l0 = (int64_t)blockIdx.x * 32, s0 = (int64_t)blockIdx.y * 32;
     for (int r = threadIdx.y; r < 32; r += blockDim.y) {
         int64_t s = s0 + r, l = l0 + threadIdx.x;
-        tile[r][threadIdx.x] = (s < n && l < L) ? (int32_t)in[s * L + l] : 0;
+        tile[r][threadIdx.x] = (s < n && l < L) ? (int32_t)in[s * Ls + l] : 0;
     }
     __syncthreads();
     for (int r = threadIdx.y; r < 32; r += blockDim.y) {
@@ -62,31 +62,34 @@ __device__ __forceinline__ int dev_bit_width(int a)   // codes 1..a need this ma
     return a <= 0 ? 0 : 32 - __clz(a);
 }
 
+// Two kernels, both with grid (32-locus blocks, row splits), so that a matrix with few loci per device (a locus
+// range of the sharded re-coder: 12 blocks per rank for C4 on 8 GPUs) still fills the machine:
+//   rthc_rank32_mark  marks the ids of its rows in shared bitmaps and ORs the non-empty words into the
+//                     global bitmap gbm[locus][512 words] (zeroed by the caller);
+//   rthc_rank32_code  loads the 32 finished bitmaps, builds the popcount prefix tables and codes its rows.
 template <typename IT>
 __global__ void __launch_bounds__(RANK_THREADS, 1)
-rthc_rank32(const IT *__restrict__ in, int64_t n, int64_t L, int64_t n_pad, uint16_t *__restrict__ codes,
-            int32_t *__restrict__ n_alleles, int32_t *__restrict__ status)
+rthc_rank32_mark(const IT *__restrict__ in, int64_t n, int64_t L, int64_t Ls, int64_t rows_per_split,
+                 uint32_t *__restrict__ gbm, int32_t *__restrict__ status)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     uint32_t *bm = reinterpret_cast<uint32_t *>(smem_raw);                 // seen
-    uint16_t *pre = reinterpret_cast<uint16_t *>(bm + 32 * R32_STRIDE);
-    uint16_t *tile = pre + 32 * R32_STRIDE;
-    __shared__ uint32_t s_tot[32];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int64_t l0 = (int64_t)blockIdx.x * 32, l = l0 + lane;
     const bool lv = l < L;
+    const int64_t r_begin = (int64_t)blockIdx.y * rows_per_split, r_end = min(n, r_begin + rows_per_split);
     for (int w = tid; w < 32 * R32_STRIDE; w += RANK_THREADS) bm[w] = 0;
     __syncthreads();
     // ---- mark: 16 row segments in flight per warp; a bit that is already set is not set again --------
     bool big = false;
     const volatile uint32_t *vbm = bm;
     uint32_t *mybm = bm + lane * R32_STRIDE;
-    for (int64_t s0 = warp; s0 < n; s0 += 32 * 16) {
+    for (int64_t s0 = r_begin + warp; s0 < r_end; s0 += 32 * 16) {
         int32_t v[16];
 #pragma unroll
         for (int u = 0; u < 16; ++u) {
             const int64_t r = s0 + 32 * u;
-            v[u] = (lv && r < n) ? (int32_t)__ldg(in + r * L + l) : 0;
+            v[u] = (lv && r < r_end) ? (int32_t)__ldg(in + r * Ls + l) : 0;
         }
 #pragma unroll
         for (int u = 0; u < 16; ++u) {
@@ -104,6 +107,34 @@ rthc_rank32(const IT *__restrict__ in, int64_t n, int64_t L, int64_t n_pad, uint
         if (tid == 0) atomicOr(status, 1);
         return;
     }
+    for (int w = tid; w < 32 * R32_WORDS; w += RANK_THREADS) {
+        const int loc = w / R32_WORDS, k = w % R32_WORDS;
+        const uint32_t x = bm[loc * R32_STRIDE + k];
+        if (x && l0 + loc < L) atomicOr(&gbm[(l0 + loc) * R32_WORDS + k], x);
+    }
+}
+
+template <typename IT>
+__global__ void __launch_bounds__(RANK_THREADS, 1)
+rthc_rank32_code(const IT *__restrict__ in, int64_t n, int64_t L, int64_t Ls, int64_t n_pad, int64_t rows_per_split,
+                 const uint32_t *__restrict__ gbm, uint16_t *__restrict__ codes, int32_t *__restrict__ n_alleles,
+                 const int32_t *__restrict__ status)
+{
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    uint32_t *bm = reinterpret_cast<uint32_t *>(smem_raw);                 // seen
+    uint16_t *pre = reinterpret_cast<uint16_t *>(bm + 32 * R32_STRIDE);
+    uint16_t *tile = pre + 32 * R32_STRIDE;
+    __shared__ uint32_t s_tot[32];
+    if (*status & 1) return;                       // an id >= 2^14 somewhere: the general path redoes everything
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int64_t l0 = (int64_t)blockIdx.x * 32, l = l0 + lane;
+    const bool lv = l < L;
+    for (int w = tid; w < 32 * R32_WORDS; w += RANK_THREADS) {
+        const int loc = w / R32_WORDS, k = w % R32_WORDS;
+        bm[loc * R32_STRIDE + k] = l0 + loc < L ? gbm[(l0 + loc) * R32_WORDS + k] : 0u;
+    }
+    __syncthreads();
+    const uint32_t *mybm = bm + lane * R32_STRIDE;
     // ---- rank tables: warp w scans the bitmap of locus l0 + w ----
     {
         const uint32_t *b = bm + warp * R32_STRIDE;
@@ -123,18 +154,19 @@ rthc_rank32(const IT *__restrict__ in, int64_t n, int64_t L, int64_t n_pad, uint
         }
         if (lane == 0) {
             s_tot[warp] = running;                               // number of codes of the locus
-            if (l0 + warp < L) n_alleles[l0 + warp] = (int32_t)running;
+            if (blockIdx.y == 0 && l0 + warp < L) n_alleles[l0 + warp] = (int32_t)running;
         }
     }
     __syncthreads();
     // ---- code + transposed write, 512 samples per tile (16 row segments in flight per warp) ------------
     const uint16_t *mypre = pre + lane * R32_STRIDE;
-    for (int64_t c0 = 0; c0 < n_pad; c0 += R32_CHUNK) {
+    const int64_t c_begin = (int64_t)blockIdx.y * rows_per_split, c_end = min(n_pad, c_begin + rows_per_split);
+    for (int64_t c0 = c_begin; c0 < c_end; c0 += R32_CHUNK) {      // rows_per_split % R32_CHUNK == 0
         int32_t v[16];
 #pragma unroll
         for (int u = 0; u < 16; ++u) {
             const int64_t r = c0 + warp + 32 * u;
-            v[u] = (lv && r < n) ? (int32_t)__ldg(in + r * L + l) : 0;
+            v[u] = (lv && r < n) ? (int32_t)__ldg(in + r * Ls + l) : 0;
         }
 #pragma unroll
         for (int u = 0; u < 16; ++u) {
@@ -462,11 +494,32 @@ template <typename IT>
 static int rank_fast(rthc_ctx *ctx, const IT *d_rowmajor, int32_t *d_nall, int32_t *d_status, std::vector<int32_t> &nall,
                      int32_t &status)
 {
-    const int64_t n = ctx->n, L = ctx->L, n_pad = ctx->n_pad;
+    const int64_t n = ctx->n, L = ctx->L, n_pad = ctx->n_pad, Ls = ctx->L_stride ? ctx->L_stride : L;
     RTHC_CUDA(ctx, cudaMemsetAsync(d_status, 0, sizeof(int32_t), ctx->stream));
-    RTHC_CUDA(ctx, cudaFuncSetAttribute(rthc_rank32<IT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)R32_SMEM));
-    rthc_rank32<IT><<<(unsigned)((L + 31) / 32), RANK_THREADS, R32_SMEM, ctx->stream>>>(d_rowmajor, n, L, n_pad, ctx->d_codes,
-                                                                                     d_nall, d_status);
+    const unsigned nblocks = (unsigned)((L + 31) / 32);
+    // row splits: enough CTAs for about four waves of the code kernel (one CTA per SM), rows per split a multiple of
+    // the 512-sample tile
+    int64_t splits = std::max<int64_t>(1, (4 * (int64_t)ctx->sm_count + nblocks - 1) / nblocks);
+    int64_t rows_per_split = ((n_pad + splits - 1) / splits + R32_CHUNK - 1) / R32_CHUNK * R32_CHUNK;
+    splits = (n_pad + rows_per_split - 1) / rows_per_split;
+    // the global bitmaps stay with the context (grow only): a 6 MB block that comes and goes between the GB-sized ones
+    // made the pool split and re-grow its large blocks for several calls
+    int rc;
+    if (ctx->gbm_cap < (size_t)L * R32_WORDS) {
+        ctx->gbm_cap = 0;
+        if ((rc = rthc_dev_alloc(ctx, &ctx->d_gbm, (size_t)L * R32_WORDS))) return rc;
+        ctx->gbm_cap = (size_t)L * R32_WORDS;
+    }
+    uint32_t *d_gbm = ctx->d_gbm;
+    RTHC_CUDA(ctx, cudaMemsetAsync(d_gbm, 0, sizeof(uint32_t) * (size_t)L * R32_WORDS, ctx->stream));
+    const int mark_smem = 32 * R32_STRIDE * 4;
+    RTHC_CUDA(ctx, cudaFuncSetAttribute(rthc_rank32_mark<IT>, cudaFuncAttributeMaxDynamicSharedMemorySize, mark_smem));
+    RTHC_CUDA(ctx, cudaFuncSetAttribute(rthc_rank32_code<IT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)R32_SMEM));
+    const dim3 grid(nblocks, (unsigned)splits);
+    rthc_rank32_mark<IT><<<grid, RANK_THREADS, mark_smem, ctx->stream>>>(d_rowmajor, n, L, Ls, rows_per_split, d_gbm, d_status);
+    RTHC_LAUNCH_CHECK(ctx);
+    rthc_rank32_code<IT><<<grid, RANK_THREADS, R32_SMEM, ctx->stream>>>(d_rowmajor, n, L, Ls, n_pad, rows_per_split, d_gbm,
+                                                                       ctx->d_codes, d_nall, d_status);
     RTHC_LAUNCH_CHECK(ctx);
     RTHC_CUDA(ctx, cudaMemcpyAsync(&status, d_status, sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->stream));
     RTHC_CUDA(ctx, cudaMemcpyAsync(nall.data(), d_nall, sizeof(int32_t) * (size_t)L, cudaMemcpyDeviceToHost, ctx->stream));
@@ -486,7 +539,7 @@ static int rank_general(rthc_ctx *ctx, const IT *d_rowmajor, int32_t *d_nall, in
     if ((rc = rthc_dev_alloc(ctx, &d_colmajor, (size_t)(L * n_pad)))) return rc;
     {
         dim3 blk(32, 8), grd((unsigned)((L + 31) / 32), (unsigned)((n_pad + 31) / 32));
-        rthc_transpose_i32<IT><<<grd, blk, 0, ctx->stream>>>(d_rowmajor, d_colmajor, n, L, n_pad);
+        rthc_transpose_i32<IT><<<grd, blk, 0, ctx->stream>>>(d_rowmajor, d_colmajor, n, L, n_pad, ctx->L_stride ? ctx->L_stride : L);
         RTHC_LAUNCH_CHECK(ctx);
     }
     if ((rc = rank_all<uint16_t>(ctx, d_colmajor, ctx->d_codes, d_nall, d_status, nall, status))) return rc;
@@ -564,12 +617,19 @@ int rthc_recode_and_pack(rthc_ctx *ctx, const void *d_rowmajor, bool in_u16)
     }
     ctx->G = G;
     ctx->plane_rows = rows;
+    ctx->blk_stride_rows = rows;
     ctx->max_np = max_np;
+    ctx->h_grp_np.assign(gnp.begin(), gnp.begin() + G);
+    std::vector<int64_t> gbase((size_t)std::max(G, 1));
+    for (int g = 0; g < G; ++g) gbase[(size_t)g] = goff[(size_t)g];
 
     if ((rc = rthc_dev_alloc(ctx, &ctx->d_planes, (size_t)std::max(rows, 1) * (size_t)n_pad))) return rc;
     if ((rc = rthc_dev_alloc(ctx, &ctx->d_grp_off, (size_t)std::max(G, 1)))) return rc;
+    if ((rc = rthc_dev_alloc(ctx, &ctx->d_grp_base, (size_t)std::max(G, 1)))) return rc;
     if ((rc = rthc_dev_alloc(ctx, &ctx->d_grp_np, (size_t)std::max(G, 1)))) return rc;
     if (G > 0) {
+        RTHC_CUDA(ctx, cudaMemcpyAsync(ctx->d_grp_base, gbase.data(), (size_t)G * sizeof(int64_t), cudaMemcpyHostToDevice,
+                                       ctx->stream));
         if ((rc = rthc_dev_alloc(ctx, &d_perm, perm.size()))) return rc;
         RTHC_CUDA(ctx, cudaMemcpyAsync(d_perm, perm.data(), perm.size() * sizeof(int32_t),
                                        cudaMemcpyHostToDevice, ctx->stream));

@@ -59,9 +59,18 @@ struct rthc_ctx {
     int64_t geom_n = -1; int geom_rank = -1, geom_world = -1; bool geom_full = false;      // what d_tiles / d_row_base were built for
     bool recode_general = false;   // last re-code left the fast path (an allele id >= 2^14 somewhere)
     uint32_t *d_codes32 = nullptr; // same, used INSTEAD of d_codes when a locus has more than 65,535 called alleles
-    uint32_t *d_planes = nullptr;  // [plane_rows][n_pad]
-    int32_t *d_grp_off = nullptr;  // [G]
+    uint32_t *d_planes = nullptr;  // [n_pad / 64][blk_stride_rows][64]: plane row `base` of a group, 64-sample block b, lives at row b * blk_stride_rows + base
+    int32_t *d_grp_off = nullptr;  // [G] first plane row of a group inside its block (what the packer writes)
+    int64_t *d_grp_base = nullptr; // [G] the same as the distance kernel wants it: row offset inside block 0 of the WHOLE buffer
     int32_t *d_grp_np = nullptr;   // [G]
+    int64_t blk_stride_rows = 0;   // plane_rows for a matrix re-coded here; rows_max of the widest rank for gathered planes
+    // planes re-coded by locus ranges on several ranks and gathered (rthc_recode_shard / rthc_export_shard / rthc_import_planes):
+    // d_planes, d_esc_cnt and d_esc_list then point into the CALLER's gathered buffers and are not freed here
+    uint32_t *d_gbm = nullptr; size_t gbm_cap = 0;     // allele-id bitmaps of the fast re-coder path (recode.cu), kept across calls
+    bool planes_borrowed = false;
+    int64_t L_stride = 0;          // row stride of the caller's matrix while a column range is re-coded (0: L)
+    int64_t L_global = 0, esc_L = 0;      // loci of the whole matrix; entries of d_esc_cnt
+    std::vector<int32_t> h_grp_np; // plane counts of the groups built by the last re-code (header of rthc_recode_shard)
     int2 *d_tiles = nullptr;       // tile list (I, J), J >= I, owned tile rows only
     int64_t n_tiles = 0;
     int64_t *d_row_base = nullptr; // [n_pad] offset of (i, i+1) in d_cond, -1 if row not owned

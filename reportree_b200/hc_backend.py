@@ -52,6 +52,10 @@ def load_library():
         "rthc_set_profiles_i32_device": (ci, [vp, vp, i64, i64]),
         "rthc_set_profiles_u16": (ci, [vp, vp, i64, i64]),
         "rthc_set_profiles_u16_device": (ci, [vp, vp, i64, i64]),
+        "rthc_shard_chunk": (i64, [i64, ci]),
+        "rthc_recode_shard": (ci, [vp, vp, ci, i64, i64, vp, i64]),
+        "rthc_export_shard": (ci, [vp, vp, i64, vp, vp]),
+        "rthc_import_planes": (ci, [vp, vp, i64, vp, i64, vp, vp]),
         "rthc_distance": (ci, [vp]),
         "rthc_owned_pairs": (i64, [vp]),
         "rthc_get_condensed_u16": (ci, [vp, vp]),
@@ -91,6 +95,7 @@ EXPORTED_SYMBOLS = [
     "rthc_create", "rthc_prewarm", "rthc_destroy", "rthc_last_error", "rthc_version", "rthc_set_shard",
     "rthc_set_shard_full_storage", "rthc_import_shard", "rthc_finish_import",
     "rthc_set_profiles_i32", "rthc_set_profiles_i32_device", "rthc_set_profiles_u16", "rthc_set_profiles_u16_device",
+    "rthc_shard_chunk", "rthc_recode_shard", "rthc_export_shard", "rthc_import_planes",
     "rthc_distance", "rthc_owned_pairs",
     "rthc_get_condensed_u16", "rthc_get_owned_condensed_u16", "rthc_get_condensed_range_u16", "rthc_copy_rows_u16", "rthc_direct_pairs",
     "rthc_set_condensed_f64", "rthc_set_single_algo", "rthc_linkage", "rthc_local_forest",
@@ -164,6 +169,22 @@ class HCContext:
         self.n, self.L = int(n), int(L)
         fn = self._L.rthc_set_profiles_u16_device if np.dtype(dtype) == np.uint16 else self._L.rthc_set_profiles_i32_device
         self._check(fn(self._h, ctypes.c_void_p(int(dev_ptr)), self.n, self.L))
+
+    # ---- re-coder sharded by locus ranges (world > 1; driven by sharded.PlaneExchange) ----
+    def recode_shard(self, dev_ptr, n, L, dtype, hdr):
+        """This rank's loci of the device-resident n x L matrix -> planes; fills hdr (int32 numpy, see rthc.h)."""
+        self.n, self.L = int(n), int(L)
+        self._check(self._L.rthc_recode_shard(self._h, ctypes.c_void_p(int(dev_ptr)), int(np.dtype(dtype) == np.uint16),
+                                              self.n, self.L, _ptr(hdr), hdr.size))
+
+    def export_shard(self, planes_slot_ptr, rows_max, cnt_slot_ptr, list_slot_ptr):
+        self._check(self._L.rthc_export_shard(self._h, ctypes.c_void_p(int(planes_slot_ptr)), int(rows_max),
+                                              ctypes.c_void_p(int(cnt_slot_ptr)), ctypes.c_void_p(int(list_slot_ptr))))
+
+    def import_planes(self, planes_ptr, rows_max, hdr_all, cnt_ptr, list_ptr):
+        hdr_all = np.ascontiguousarray(hdr_all, dtype=np.int32)
+        self._check(self._L.rthc_import_planes(self._h, ctypes.c_void_p(int(planes_ptr)), int(rows_max), _ptr(hdr_all),
+                                               hdr_all.shape[1], ctypes.c_void_p(int(cnt_ptr)), ctypes.c_void_p(int(list_ptr))))
 
     def distance(self):
         self._check(self._L.rthc_distance(self._h))

@@ -153,3 +153,65 @@ class ShardedProfileLoader:
     def replica(self):
         """The replicated matrix of the last load() as a tensor (tests)."""
         return self.full16 if self.dtype == np.uint16 else self.full
+
+
+SHARD_HDR = 8          # RTHC_SHARD_HDR
+LIST_CAP = 4096        # RTHC_ESC_CAP: listed cells per locus
+
+
+def shard_chunk(L, world):
+    """Loci per rank of the sharded re-coder (rthc_shard_chunk): ceil(L / world) rounded up to 32."""
+    return ((int(L) + world - 1) // world + 31) // 32 * 32
+
+
+class PlaneExchange:
+    """Re-coder sharded by locus ranges for world > 1 (include/rthc.h, "re-coder sharded by locus ranges"): every
+    rank dense-ranks, re-maps and bit-slices only its chunk of the loci, then ONE small all_gather of the headers
+    and three all_gather_into_tensor calls (planes, listed-cell counts, listed cells) give every rank the plane
+    matrix of the whole matrix.  Replaces ctx.set_profiles_device(ptr, n, L, dtype) on every rank; the gathered
+    buffers belong to this object and stay alive with it (the context borrows them)."""
+
+    MAX_LIST_BYTES = 1 << 30
+
+    def __init__(self, n, L, dist, device="cuda"):
+        import torch
+        self.n, self.L, self.dist, self.torch, self.device = int(n), int(L), dist, torch, device
+        self.world, self.rank = dist.get_world_size(), dist.get_rank()
+        self.chunk = shard_chunk(self.L, self.world)
+        self.hdr_len = SHARD_HDR + self.chunk // 32
+        self.n_blk = (self.n + 127) // 128 * 2
+        self.hdr = np.zeros(self.hdr_len, dtype=np.int32)
+        self.hdr_dev = torch.zeros(self.hdr_len, dtype=torch.int32, device=device)
+        self.hdr_all_dev = torch.zeros((self.world, self.hdr_len), dtype=torch.int32, device=device)
+        self.cnt_all = torch.zeros((self.world, self.chunk), dtype=torch.int32, device=device)
+        self.list_all = torch.zeros((self.world, self.chunk, LIST_CAP), dtype=torch.int64, device=device)
+        self.cnt_mine = torch.zeros(self.chunk, dtype=torch.int32, device=device)
+        self.list_mine = torch.zeros((self.chunk, LIST_CAP), dtype=torch.int64, device=device)
+        self.planes_all = self.planes_mine = None
+        self.rows_max = 0
+
+    @staticmethod
+    def usable(L, world):
+        """False for matrices so wide that the gathered cell lists would not be small (SNP matrices): the caller
+        then re-codes the whole matrix on every rank as before."""
+        return world > 1 and world * shard_chunk(L, world) * LIST_CAP * 8 <= PlaneExchange.MAX_LIST_BYTES
+
+    def set_profiles(self, ctx, dev_ptr, dtype=np.int32):
+        t = self.torch
+        ctx.recode_shard(dev_ptr, self.n, self.L, dtype, self.hdr)
+        self.hdr_dev.copy_(t.from_numpy(self.hdr))
+        self.dist.all_gather_into_tensor(self.hdr_all_dev, self.hdr_dev)
+        hdr_all = self.hdr_all_dev.cpu().numpy()
+        rows_max = max(1, int(hdr_all[:, 1].max()))
+        if self.planes_all is None or rows_max > self.rows_max:
+            self.rows_max = rows_max
+            self.planes_all = t.empty((self.world, self.n_blk, rows_max, 64), dtype=t.int32, device=self.device)
+            self.planes_mine = t.empty((self.n_blk, rows_max, 64), dtype=t.int32, device=self.device)
+        ctx.export_shard(self.planes_mine.data_ptr(), self.rows_max, self.cnt_mine.data_ptr(), self.list_mine.data_ptr())
+        self.dist.all_gather_into_tensor(self.planes_all, self.planes_mine)
+        self.dist.all_gather_into_tensor(self.cnt_all, self.cnt_mine)
+        self.dist.all_gather_into_tensor(self.list_all, self.list_mine)
+        if self.planes_all.is_cuda:
+            t.cuda.current_stream().synchronize()
+        ctx.import_planes(self.planes_all.data_ptr(), self.rows_max, hdr_all, self.cnt_all.data_ptr(), self.list_all.data_ptr())
+        return hdr_all

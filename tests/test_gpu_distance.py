@@ -316,3 +316,83 @@ def test_sharded_rows_cover_matrix(hc, oracle, world):
             pos += ln
         assert pos == part.size
     assert seen.all()
+
+
+def _sharded_recode_distances(hc, X, world, dtype=np.int32):
+    """rthc_recode_shard / rthc_export_shard / rthc_import_planes with `world` contexts on ONE device: the gathered
+    buffers of sharded.PlaneExchange are then simply shared, no collective needed.  Returns the assembled matrix."""
+    import torch
+    from reportree_b200 import sharded
+    n, L = X.shape
+    chunk = sharded.shard_chunk(L, world)
+    assert chunk == hc.load_library().rthc_shard_chunk(L, world)
+    hdr_len = sharded.SHARD_HDR + chunk // 32
+    dX = torch.from_numpy(np.ascontiguousarray(X.astype(dtype))).cuda() if dtype != np.uint16 else \
+        torch.from_numpy(np.ascontiguousarray(X.astype(np.uint16)).view(np.int16)).cuda()
+    ctxs = [hc.HCContext(rank=r, world=world) for r in range(world)]
+    try:
+        hdr_all = np.zeros((world, hdr_len), dtype=np.int32)
+        for r, ctx in enumerate(ctxs):
+            ctx.recode_shard(dX.data_ptr(), n, L, dtype, hdr_all[r])
+        rows_max = max(1, int(hdr_all[:, 1].max()))
+        n_blk = (n + 127) // 128 * 2
+        planes = torch.zeros((world, n_blk, rows_max, 64), dtype=torch.int32, device="cuda")
+        cnt = torch.zeros((world, chunk), dtype=torch.int32, device="cuda")
+        cells = torch.zeros((world, chunk, sharded.LIST_CAP), dtype=torch.int64, device="cuda")
+        for r, ctx in enumerate(ctxs):
+            ctx.export_shard(planes[r].data_ptr(), rows_max, cnt[r].data_ptr(), cells[r].data_ptr())
+        torch.cuda.synchronize()
+        P = n * (n - 1) // 2
+        got = np.zeros(P, dtype=np.uint16)
+        seen = np.zeros(P, dtype=bool)
+        infos = []
+        for r, ctx in enumerate(ctxs):
+            ctx.import_planes(planes.data_ptr(), rows_max, hdr_all, cnt.data_ptr(), cells.data_ptr())
+            ctx.distance()
+            infos.append(ctx.info())
+            own = ctx.owned_condensed()
+            p = 0
+            for i in sharded.owned_rows(n, r, world):
+                base = n * i - i * (i + 1) // 2
+                c = n - 1 - i
+                got[base:base + c] = own[p:p + c]
+                seen[base:base + c] = True
+                p += c
+        assert seen.all()
+        return got, infos, hdr_all
+    finally:
+        for c in ctxs:
+            c.close()
+
+
+@pytest.mark.parametrize("kind,world,div", [("zipf", 2, None), ("zipf", 3, "1"), ("singletons", 8, None),
+                                            ("flat", 4, "300"), ("narrow", 3, None), ("wideids", 2, None)])
+def test_recoder_sharded_by_loci_gives_the_same_distances(hc, oracle, monkeypatch, kind, world, div):
+    """world > 1: every rank re-codes only its range of loci and the plane matrix is assembled from the ranks'
+    parts (rthc_recode_shard / rthc_export_shard / rthc_import_planes).  Cases: rare alleles with shared codes and
+    their fix-up lists crossing ranks, more ranks than 32-locus blocks (ranks without loci), uint16 input, a range
+    that needs the general path (ids >= 2^14) next to ranges that do not."""
+    if div is None:
+        monkeypatch.delenv("RTHC_COLLIDE_DIV", raising=False)
+    else:
+        monkeypatch.setenv("RTHC_COLLIDE_DIV", div)
+    dtype = np.int32
+    if kind == "narrow":
+        rng = np.random.default_rng(3)
+        X = _rand_codes(rng, 300, 40, 9, 0.05)              # 40 loci over 3 ranks: chunk 32 -> 32 + 8 + 0
+        dtype = np.uint16
+    elif kind == "wideids":
+        rng = np.random.default_rng(4)
+        X = _rand_codes(rng, 500, 150, 30, 0.03)
+        X[:, 100:] = np.where(X[:, 100:] > 0, X[:, 100:] * 40000, 0)     # second rank only: ids up to 1.2e6
+    else:
+        X = _shared_code_matrix(kind)
+    ref = oracle.dist_condensed(X)
+    got, infos, hdr_all = _sharded_recode_distances(hc, X, world, dtype)
+    assert np.array_equal(got, ref)
+    assert all(i["L"] == X.shape[1] for i in infos)
+    assert infos[0]["plane_rows"] == int(hdr_all[:, 1].sum()) and infos[0]["groups"] == int(hdr_all[:, 0].sum())
+    if kind == "narrow":
+        assert hdr_all[2, 0] == 0 and hdr_all[2, 7] == 0            # the third rank had no loci
+    if div is not None or kind == "singletons":
+        assert infos[0]["escape_cells"] > 0

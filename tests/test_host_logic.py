@@ -138,3 +138,14 @@ def test_square_to_condensed_checks():
         phc.square_to_condensed(np.array([[0, 1], [2, 0.0]]))
     with pytest.raises(ValueError):
         phc.square_to_condensed(np.array([[1, 1], [1, 0.0]]))
+
+
+def test_shard_chunk_matches_the_library():
+    """Loci per rank of the sharded re-coder: the Python helper and the C entry point agree (no GPU call)."""
+    from reportree_b200 import hc_backend, sharded
+    L = hc_backend.load_library()
+    for loci in (1, 31, 32, 33, 40, 3000, 3002, 7600, 65535, 70001):
+        for world in (1, 2, 3, 4, 8):
+            c = sharded.shard_chunk(loci, world)
+            assert c == L.rthc_shard_chunk(loci, world)
+            assert c % 32 == 0 and c * world >= loci and (c - 32) * world < loci + 32 * world
