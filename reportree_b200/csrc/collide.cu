@@ -328,13 +328,22 @@ __global__ void __launch_bounds__(FIX_THREADS) rthc_collide_fixup(const int32_t 
         const uint32_t bin = ((uint32_t)(ep >> 24) & 0x7FFFu) - base;
         const int end = (int)start[bin + 1];
         const int64_t sp = (int64_t)(ep & 0xFFFFFFu);
-        for (int q = p + 1; q < end; ++q) {
+        // one rank: every cell pairs with the cells behind it in its code's run.  Several ranks: a pair belongs to the
+        // rank that owns the row of its SMALLER sample, so a cell whose row is someone else's is skipped as a whole and
+        // an owned one walks its whole run for the larger samples -- the walk shards with the rows instead of being
+        // repeated on every rank.
+        int q0 = p + 1;
+        if (world > 1) {
+            const int64_t r = sp / RTHC_TILE;
+            if ((int)(min(r, n_tile_rows - 1 - r) % world) != rank) continue;
+            q0 = (int)start[bin];
+        }
+        for (int q = q0; q < end; ++q) {
             const uint64_t eq = srt[q];
             if (((ep ^ eq) >> 40) == 0) continue;                      // the same allele: the planes were right
             const int64_t sq = (int64_t)(eq & 0xFFFFFFu);
+            if (world > 1 && sq < sp) continue;                        // counted from the other side
             const int64_t i = min(sp, sq), j = max(sp, sq);
-            const int64_t r = i / RTHC_TILE;
-            if ((int)(min(r, n_tile_rows - 1 - r) % world) != rank) continue;
             uint16_t *e = cond + row_base[i] + (j - i - 1);
             atomicAdd(reinterpret_cast<unsigned int *>(reinterpret_cast<uintptr_t>(e) & ~(uintptr_t)3),
                       (reinterpret_cast<uintptr_t>(e) & 2) ? 65536u : 1u);
