@@ -200,7 +200,7 @@ class PlaneExchange:
         t = self.torch
         ctx.recode_shard(dev_ptr, self.n, self.L, dtype, self.hdr)
         self.hdr_dev.copy_(t.from_numpy(self.hdr))
-        self.dist.all_gather_into_tensor(self.hdr_all_dev, self.hdr_dev)
+        self.dist.all_gather_into_tensor(self.hdr_all_dev.view(-1), self.hdr_dev)
         hdr_all = self.hdr_all_dev.cpu().numpy()
         rows_max = max(1, int(hdr_all[:, 1].max()))
         if self.planes_all is None or rows_max > self.rows_max:
@@ -208,9 +208,9 @@ class PlaneExchange:
             self.planes_all = t.empty((self.world, self.n_blk, rows_max, 64), dtype=t.int32, device=self.device)
             self.planes_mine = t.empty((self.n_blk, rows_max, 64), dtype=t.int32, device=self.device)
         ctx.export_shard(self.planes_mine.data_ptr(), self.rows_max, self.cnt_mine.data_ptr(), self.list_mine.data_ptr())
-        self.dist.all_gather_into_tensor(self.planes_all, self.planes_mine)
-        self.dist.all_gather_into_tensor(self.cnt_all, self.cnt_mine)
-        self.dist.all_gather_into_tensor(self.list_all, self.list_mine)
+        self.dist.all_gather_into_tensor(self.planes_all.view(-1), self.planes_mine.view(-1))      # flat: gloo and NCCL agree on that
+        self.dist.all_gather_into_tensor(self.cnt_all.view(-1), self.cnt_mine)
+        self.dist.all_gather_into_tensor(self.list_all.view(-1), self.list_mine.view(-1))
         if self.planes_all.is_cuda:
             t.cuda.current_stream().synchronize()
         ctx.import_planes(self.planes_all.data_ptr(), self.rows_max, hdr_all, self.cnt_all.data_ptr(), self.list_all.data_ptr())

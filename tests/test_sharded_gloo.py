@@ -208,3 +208,89 @@ def test_device_resident_exchange_helpers_over_gloo(world):
         assert np.array_equal(np.sort(real), expect)         # every rank sees every forest, padding dropped
         assert np.array_equal(full, X)
     assert sum(g[5] for g in got) == n * L * 4               # the H2D bytes add up to one copy of the matrix
+
+
+# ---- re-coder sharded by locus ranges: the exchange of sharded.PlaneExchange over gloo ------------------------------
+class _StandInContext:
+    """What PlaneExchange needs from hc_backend.HCContext, without a GPU: recode_shard reports a header for this
+    rank's locus range, export_shard writes a recognisable pattern into the rank's slots, import_planes keeps what
+    it was given.  (The kernels behind the real calls are covered by
+    tests/test_gpu_distance.py::test_recoder_sharded_by_loci_gives_the_same_distances.)"""
+
+    def __init__(self, rank, world):
+        self.rank, self.world = rank, world
+        self.imported = None
+
+    def recode_shard(self, dev_ptr, n, L, dtype, hdr):
+        from reportree_b200 import sharded
+        chunk = sharded.shard_chunk(L, self.world)
+        l0 = min(L, self.rank * chunk)
+        loci = min(L, l0 + chunk) - l0
+        groups = (loci + 31) // 32
+        hdr[:] = 0
+        hdr[0], hdr[7] = groups, loci
+        for g in range(groups):
+            hdr[sharded.SHARD_HDR + g] = 4 + (self.rank + g) % 5            # planes of group g
+        hdr[1] = int(hdr[sharded.SHARD_HDR:sharded.SHARD_HDR + groups].sum())
+        hdr[2] = int(hdr[sharded.SHARD_HDR:sharded.SHARD_HDR + groups].max()) if groups else 0
+        hdr[3], hdr[4], hdr[5], hdr[6] = loci, 100 + self.rank, groups, 7 * self.rank
+        self.rows = int(hdr[1])
+
+    def export_shard(self, planes_ptr, rows_max, cnt_ptr, list_ptr):
+        import ctypes
+        assert rows_max >= self.rows
+        self.rows_max = rows_max
+        ctypes.memset(planes_ptr, 0x10 + self.rank, self.n_blk * rows_max * 64 * 4)
+        ctypes.memset(cnt_ptr, 0x20 + self.rank, self.chunk * 4)
+        ctypes.memset(list_ptr, 0x30 + self.rank, self.chunk * 4096 * 8)
+
+    def import_planes(self, planes_ptr, rows_max, hdr_all, cnt_ptr, list_ptr):
+        self.imported = (planes_ptr, rows_max, np.array(hdr_all), cnt_ptr, list_ptr)
+
+
+def _plane_worker(rank, world, port, n, L, q):
+    sys.path.insert(0, ROOT)
+    import torch.distributed as dist
+    from reportree_b200 import sharded
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    ex = sharded.PlaneExchange(n, L, dist, device="cpu")
+    ctx = _StandInContext(rank, world)
+    ctx.n_blk, ctx.chunk = ex.n_blk, ex.chunk
+    ok = True
+    for rep in range(2):                                     # the buffers are reused by a second matrix of the same shape
+        hdr_all = ex.set_profiles(ctx, 0, np.int32)
+        ok &= ctx.imported is not None and ctx.imported[0] == ex.planes_all.data_ptr() and ctx.imported[1] == ex.rows_max
+        ok &= ex.rows_max == int(hdr_all[:, 1].max())
+        for r in range(world):
+            ok &= bool((ex.planes_all[r].view(-1).numpy().view(np.uint8) == 0x10 + r).all())
+            ok &= bool((ex.cnt_all[r].numpy().view(np.uint8) == 0x20 + r).all())
+            ok &= bool((ex.list_all[r].view(-1).numpy().view(np.uint8) == 0x30 + r).all())
+            ok &= int(hdr_all[r, 4]) == 100 + r and int(hdr_all[r, 6]) == 7 * r
+    q.put((rank, ok, hdr_all.tolist(), ex.chunk))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,L", [(2, 3000), (3, 40)])
+def test_plane_exchange_over_gloo(world, L):
+    from reportree_b200 import sharded
+    n = 300
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_plane_worker, args=(r, world, port, n, L, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    got = [q.get(timeout=120) for _ in range(world)]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    chunk = sharded.shard_chunk(L, world)
+    for rank, ok, hdr_all, ch in got:
+        assert ok and ch == chunk
+        assert hdr_all == got[0][2]                           # every rank holds the same gathered headers
+        assert sum(h[7] for h in hdr_all) == L                # the ranks' locus ranges tile the matrix
+    if world == 3:
+        assert [h[7] for h in got[0][2]] == [32, 8, 0]        # more ranks than 32-locus blocks
