@@ -495,12 +495,15 @@ extern "C" int rthc_import_planes(rthc_ctx *ctx, const void *d_planes_all, int64
         int64_t off = 0;
         for (int g = 0; g < h[0]; ++g) {
             const int np = h[RTHC_SHARD_HDR + g];
+            if (np < RTHC_MIN_BITS + 1 || np > 25)
+                return rthc_fail(ctx, RTHC_E_ARG, "rthc_import_planes: group %d of rank %d claims %d planes", g, q, np);
+            max_np = std::max(max_np, np);                   // (not the header's own maximum: it sizes shared memory)
             gbase.push_back((int64_t)q * nblk * rows_max + off);
             gnp.push_back(np);
             off += np;
         }
         if (off != h[1]) return rthc_fail(ctx, RTHC_E_ARG, "rthc_import_planes: plane rows of rank %d do not add up", q);
-        rows += h[1]; max_np = std::max(max_np, (int)h[2]); kept += h[3]; max_all = std::max(max_all, (int)h[4]);
+        rows += h[1]; kept += h[3]; max_all = std::max(max_all, (int)h[4]);
         loci += h[5]; cells += h[6];
     }
     if (kept > 65535)
