@@ -396,3 +396,28 @@ def test_recoder_sharded_by_loci_gives_the_same_distances(hc, oracle, monkeypatc
         assert hdr_all[2, 0] == 0 and hdr_all[2, 7] == 0            # the third rank had no loci
     if div is not None or kind == "singletons":
         assert infos[0]["escape_cells"] > 0
+
+
+@pytest.mark.parametrize("div", [None, "1"])
+def test_shared_codes_at_the_fast_path_limit_of_alleles(hc, oracle, monkeypatch, div):
+    """A locus with 16,383 distinct allele ids (the most the fast re-coder path takes: ids < 2^14) next to ordinary
+    loci: the shared-code plan then sorts 16,384 keys in shared memory and works with 14-bit dense codes."""
+    if div is None:
+        monkeypatch.delenv("RTHC_COLLIDE_DIV", raising=False)
+    else:
+        monkeypatch.setenv("RTHC_COLLIDE_DIV", div)
+    rng = np.random.default_rng(99)
+    n, L = 17000, 6
+    X = rng.integers(1, 40, size=(n, L)).astype(np.int32)
+    X[:, 2] = 1 + (np.arange(n) % 16383)                       # ids up to 16,383, 617 of them twice
+    X[:, 4] = 1 + (rng.zipf(1.3, n) % 9000)                    # long tail
+    X[rng.random((n, L)) < 0.01] = 0
+    ref = oracle.dist_condensed(X)
+    with hc.HCContext() as ctx:
+        ctx.set_profiles(X)
+        info = ctx.info()
+        assert info["max_alleles"] == max(np.unique(c[c > 0]).size for c in X.T) > 16000     # (missing cells took a few)
+        ctx.distance()
+        assert np.array_equal(ctx.condensed(), ref)
+        if div == "1":
+            assert ctx.info()["escape_pairs"] > 0
