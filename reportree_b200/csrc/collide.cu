@@ -103,15 +103,21 @@ rthc_collide(const uint16_t *__restrict__ codes, uint16_t *__restrict__ pcodes, 
         }
         const uint32_t t1 = top[0], t2 = top[1];
         uint32_t n1 = 0, n2 = 0;                                       // lane 0 of every warp
-        for (int64_t s = probe_end + 2 * tid; s < n_pad; s += 2 * COL_THREADS) {
-            const uint32_t w = *reinterpret_cast<const uint32_t *>(col + s);
+        // 8 samples (one 16-byte load) per lane and trip; the trip count is uniform per warp (ballots), lanes past the
+        // end carry a code that matches nothing
+        for (int64_t base = probe_end + (int64_t)(tid >> 5) * 256; base < n_pad; base += (COL_THREADS / 32) * 256) {
+            const int64_t s = base + 8 * (tid & 31);
+            const bool in = s < n_pad;                                  // n_pad % 8 == 0: all 8 or none
+            uint4 w4 = make_uint4(0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu);
+            if (in) w4 = *reinterpret_cast<const uint4 *>(col + s);
+            const uint32_t ws[4] = {w4.x, w4.y, w4.z, w4.w};
 #pragma unroll
-            for (int h = 0; h < 2; ++h) {
-                const uint32_t c = h ? (w >> 16) : (w & 0xFFFFu);
+            for (int h = 0; h < 8; ++h) {
+                const uint32_t c = (h & 1) ? (ws[h >> 1] >> 16) : (ws[h >> 1] & 0xFFFFu);
                 const bool is1 = c == t1, is2 = c == t2;
                 n1 += __popc(__ballot_sync(0xffffffffu, is1));
                 n2 += __popc(__ballot_sync(0xffffffffu, is2));
-                if (!is1 && !is2) atomicAdd(&hist[c], 1u);
+                if (in && !is1 && !is2) atomicAdd(&hist[c], 1u);
             }
         }
         if ((tid & 31) == 0) { if (n1) atomicAdd(&hist[t1], n1); if (n2 && t2 != t1) atomicAdd(&hist[t2], n2); }
@@ -231,12 +237,13 @@ rthc_collide(const uint16_t *__restrict__ codes, uint16_t *__restrict__ pcodes, 
     __syncthreads();
     // ---- pass 2: re-map the column, list the cells whose code is shared -------------------------------------------
     uint64_t *mylist = list + l * RTHC_ESC_CAP;
-    for (int64_t s = 2 * tid; s < n_pad; s += 2 * COL_THREADS) {
-        const uint32_t w = *reinterpret_cast<const uint32_t *>(col + s);
-        uint32_t out = 0;
+    for (int64_t s = 8 * tid; s < n_pad; s += 8 * COL_THREADS) {       // n_pad % 8 == 0; 16 bytes in, 16 bytes out
+        const uint4 w4 = *reinterpret_cast<const uint4 *>(col + s);
+        const uint32_t ws[4] = {w4.x, w4.y, w4.z, w4.w};
+        uint32_t os[4] = {0, 0, 0, 0};
 #pragma unroll
-        for (int h = 0; h < 2; ++h) {
-            const uint32_t c = h ? (w >> 16) : (w & 0xFFFFu);
+        for (int h = 0; h < 8; ++h) {
+            const uint32_t c = (h & 1) ? (ws[h >> 1] >> 16) : (ws[h >> 1] & 0xFFFFu);
             const uint32_t m = map[c];
             if (m & 0x8000u) {
                 const int pos = atomicAdd(&s_cnt, 1);
@@ -244,9 +251,9 @@ rthc_collide(const uint16_t *__restrict__ codes, uint16_t *__restrict__ pcodes, 
                 if (pos < RTHC_ESC_CAP)
                     mylist[pos] = (uint64_t)(s + h) | ((uint64_t)(m & 0x7FFFu) << 24) | ((uint64_t)c << 40);
             }
-            out |= (m & 0x7FFFu) << (16 * h);
+            os[h >> 1] |= (m & 0x7FFFu) << (16 * (h & 1));
         }
-        *reinterpret_cast<uint32_t *>(pcol + s) = out;
+        *reinterpret_cast<uint4 *>(pcol + s) = make_uint4(os[0], os[1], os[2], os[3]);
     }
     __syncthreads();
     if (tid == 0) {
