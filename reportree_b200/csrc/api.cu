@@ -148,6 +148,7 @@ extern "C" void rthc_destroy(rthc_ctx *ctx)
     rthc_free_geometry(ctx);
     rthc_dev_free(ctx, &ctx->d_cond);
     rthc_dev_free(ctx, &ctx->d_gbm);
+    rthc_dev_free(ctx, &ctx->d_pm);
     rthc_free_linkage_state(ctx);
     if (ctx->ev0) cudaEventDestroy(ctx->ev0);
     if (ctx->ev1) cudaEventDestroy(ctx->ev1);

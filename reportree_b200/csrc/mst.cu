@@ -419,12 +419,247 @@ static int sort_keys_device(rthc_ctx *ctx, const uint64_t *d_keys, int64_t m, ui
     return 0;
 }
 
+// ---- contraction after the first round ------------------------------------------------------------------------------
+// Round 1 (every sample hooks to its nearest neighbour) leaves a few thousand components where there were n samples
+// (C4: 100,000 -> about 3,000), yet every further round would stream the whole matrix again just to find the lightest
+// edge between those few components.  Instead ONE more pass reduces the matrix to the lightest edge of every PAIR of
+// components (K x K keys under the same (w, i, j) order), and the remaining rounds scan that edge list (tens of MB
+// instead of 10 GB each).  Borůvka's later rounds only ever pick, for a merged component, the lightest edge to another
+// one, and that edge is the lightest edge of some pair of round-1 components -- so the forest is the same, edge for edge.
+//   rows are grouped by component (counting sort) so that a CTA keeps the K candidate keys of "its" component in
+//   shared memory and writes them to the K x K table once per run of rows.
+#define PM_ROWS 64
+#define PM_KMAX 8192
+
+// dense[r] = rank of root r among the roots (single CTA), *k_out = number of roots
+__global__ void __launch_bounds__(1024) rthc_pm_dense_roots(const int32_t *__restrict__ comp, int64_t n, int32_t *__restrict__ dense,
+                                                            int32_t *__restrict__ k_out)
+{
+    __shared__ uint32_t s_w[32];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int64_t per = (n + 1023) / 1024, v0 = min(n, (int64_t)tid * per), v1 = min(n, v0 + per);
+    uint32_t cnt = 0;
+    for (int64_t v = v0; v < v1; ++v) cnt += comp[v] == (int32_t)v;
+    uint32_t inc = cnt;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += t;
+    }
+    if (lane == 31) s_w[warp] = inc;
+    __syncthreads();
+    uint32_t run = inc - cnt;
+    for (int w = 0; w < warp; ++w) run += s_w[w];
+    for (int64_t v = v0; v < v1; ++v)
+        if (comp[v] == (int32_t)v) dense[v] = (int32_t)run++;
+    if (tid == 1023) *k_out = (int32_t)run;
+}
+__global__ void rthc_pm_comp16(const int32_t *__restrict__ comp, const int32_t *__restrict__ dense, int64_t n,
+                               uint16_t *__restrict__ comp16)
+{
+    const int64_t v = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (v < n) comp16[v] = (uint16_t)dense[comp[v]];
+}
+// rows with storage (owned, i < n - 1) counted per component, then placed (two launches around a scan)
+__global__ void rthc_pm_count(const int32_t *__restrict__ rows, int64_t n_rows, int64_t n, const uint16_t *__restrict__ comp16,
+                              uint32_t *__restrict__ hist)
+{
+    const int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (q < n_rows && rows[q] < n - 1) atomicAdd(&hist[comp16[rows[q]]], 1u);
+}
+__global__ void __launch_bounds__(1024) rthc_pm_scan(uint32_t *hist, int K, uint32_t *total)      // exclusive, in place, K <= PM_KMAX
+{
+    __shared__ uint32_t s_w[32];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    constexpr int PER = PM_KMAX / 1024;
+    uint32_t v[PER], sum = 0;
+#pragma unroll
+    for (int u = 0; u < PER; ++u) { const int e = tid * PER + u; v[u] = e < K ? hist[e] : 0u; sum += v[u]; }
+    uint32_t inc = sum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += t;
+    }
+    if (lane == 31) s_w[warp] = inc;
+    __syncthreads();
+    uint32_t run = inc - sum;
+    for (int w = 0; w < warp; ++w) run += s_w[w];
+#pragma unroll
+    for (int u = 0; u < PER; ++u) { const int e = tid * PER + u; if (e < K) hist[e] = run; run += v[u]; }
+    if (tid == 1023) *total = run;
+}
+__global__ void rthc_pm_place(const int32_t *__restrict__ rows, int64_t n_rows, int64_t n, const uint16_t *__restrict__ comp16,
+                              uint32_t *__restrict__ cursor, int32_t *__restrict__ order)
+{
+    const int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (q < n_rows && rows[q] < n - 1) order[atomicAdd(&cursor[comp16[rows[q]]], 1u)] = rows[q];
+}
+
+// lightest edge from the component of a run of rows to every other component.  A CTA takes PM_ROWS grouped rows; for
+// every run of rows of one component it first reduces over the ROWS in registers (per column the smallest
+// (w, row) -- the column-minimum half of the tile scan, no shared memory in the inner loop), then merges the columns
+// of equal component through the K-entry table in shared memory, and writes the table to M[ci][*] once per run.
+__global__ void __launch_bounds__(256)
+rthc_pm_pair_min(const uint16_t *__restrict__ cond, const int64_t *__restrict__ row_base, int64_t n,
+                 const uint16_t *__restrict__ comp16, const int32_t *__restrict__ order, const uint32_t *__restrict__ n_rows_p,
+                 int K, unsigned long long *__restrict__ M)
+{
+    extern __shared__ unsigned long long pm_tab[];
+    __shared__ int32_t s_row[PM_ROWS];
+    __shared__ int64_t s_base[PM_ROWS];
+    const int tid = threadIdx.x;
+    const int64_t n_rows = *n_rows_p;
+    const int64_t q0 = (int64_t)blockIdx.x * PM_ROWS, q1 = min(n_rows, q0 + PM_ROWS);
+    if (q0 >= n_rows) return;
+    for (int e = tid; e < K; e += 256) pm_tab[e] = RTHC_KEY_INF;
+    int64_t q = q0;
+    while (q < q1) {                                           // one run of rows of the same component (uniform)
+        const int ci = comp16[order[q]];
+        int64_t qe = q + 1;
+        while (qe < q1 && (int)comp16[order[qe]] == ci) ++qe;
+        const int nr = (int)(qe - q);
+        __syncthreads();                                       // table reset / previous run's rows no longer in use
+        if (tid < nr) {                                        // rows in ascending order: ties in w go to the smaller row
+            const int32_t my = order[q + tid];
+            int rank = 0;
+            for (int t = 0; t < nr; ++t) rank += order[q + t] < my;
+            s_row[rank] = my;
+            s_base[rank] = row_base[my] - my - 1;              // (cond + base)[j] = d(my, j) for j > my
+        }
+        __syncthreads();
+        const int64_t i_lo = s_row[0];
+        int r_full = 0;                                        // rows entirely left of the current column block (rows ascend)
+        for (int64_t jb = i_lo + 1; jb < n; jb += 8 * 256) {
+            uint32_t colmin[8];
+#pragma unroll
+            for (int e = 0; e < 8; ++e) colmin[e] = 0xFFFFFFFFu;
+            const int64_t j0 = jb + tid;
+            const bool whole = jb + 8 * 256 <= n;              // no column of the block is past the end
+            while (r_full < nr && s_row[r_full] < jb) ++r_full;
+            int r = 0;
+            if (whole) {                                       // rows left of the block: plain streaming, 16 loads in flight
+#pragma unroll 2
+                for (; r < r_full; ++r) {
+                    const uint16_t *row = cond + s_base[r] + j0;
+                    uint32_t w[8];
+#pragma unroll
+                    for (int e = 0; e < 8; ++e) w[e] = row[256 * e];
+#pragma unroll
+                    for (int e = 0; e < 8; ++e) colmin[e] = min(colmin[e], (w[e] << 16) | (uint32_t)r);
+                }
+            }
+            for (; r < nr; ++r) {                              // rows that start inside the block (or the last block): checked
+                const int64_t i = s_row[r];
+                if (i >= jb + 8 * 256 - 1) break;              // this row and the following ones start right of the block
+                const uint16_t *row = cond + s_base[r] + j0;
+#pragma unroll
+                for (int e = 0; e < 8; ++e) {
+                    const int64_t j = j0 + 256 * e;
+                    if (j > i && j < n) colmin[e] = min(colmin[e], ((uint32_t)row[256 * e] << 16) | (uint32_t)r);
+                }
+            }
+#pragma unroll
+            for (int e = 0; e < 8; ++e) {
+                if (colmin[e] == 0xFFFFFFFFu) continue;
+                const int64_t j = j0 + 256 * e;
+                const int cj = comp16[j];
+                if (cj == ci) continue;
+                const unsigned long long key = rthc_pack_key(colmin[e] >> 16, (uint32_t)s_row[colmin[e] & 0xFFFFu], (uint32_t)j);
+                if (key < pm_tab[cj]) atomicMin(&pm_tab[cj], key);
+            }
+        }
+        __syncthreads();
+        for (int e = tid; e < K; e += 256) {
+            const unsigned long long k = pm_tab[e];
+            if (k != RTHC_KEY_INF) { atomicMin(&M[(size_t)ci * K + e], k); pm_tab[e] = RTHC_KEY_INF; }
+        }
+        q = qe;
+    }
+}
+// M is filled from the side of the row's component only: the lightest edge of the pair {a, b} is the smaller of
+// M[a][b] and M[b][a]; pairs without an edge (a shard sees only its rows) are skipped
+__global__ void rthc_pm_extract(const unsigned long long *__restrict__ M, int K, unsigned long long *__restrict__ edges,
+                                unsigned long long *__restrict__ n_edges)
+{
+    const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= (int64_t)K * K) return;
+    const int a = (int)(t / K), b = (int)(t % K);
+    if (a >= b) return;
+    const unsigned long long k = min(M[t], M[(size_t)b * K + a]);
+    if (k != RTHC_KEY_INF) edges[atomicAdd(n_edges, 1ull)] = k;
+}
+
+// after round 1: returns 0 and sets *d_edges / *m_edges (inside the context's scratch block) when the contraction applies,
+// 1 when it does not
+static int pair_min_contract(rthc_ctx *ctx, int64_t n, const int32_t *d_comp, int64_t comps, uint64_t **d_edges, int64_t *m_edges)
+{
+    const char *env = getenv("RTHC_PAIRMIN_MIN_N");                      // test hook: contraction for small matrices too
+    const int64_t min_n = env ? atoll(env) : 30000;
+    const int64_t n_owned = (int64_t)ctx->h_owned_rows.size();
+    if (n < min_n || comps < 2 || comps > PM_KMAX || n_owned == 0 || !ctx->d_cond) return 1;
+    const int K = (int)comps;
+    // one scratch block that stays with the context (grow only): blocks of tens of MB that come and go between the
+    // GB-sized ones make the stream-ordered pool split and re-grow its large blocks (6 ms per call measured here)
+    auto up = [](size_t b) { return (b + 255) / 256 * 256; };
+    const size_t o_dense = 0, o_comp16 = o_dense + up(4 * (size_t)n), o_hist = o_comp16 + up(2 * (size_t)n),
+                 o_cursor = o_hist + up(4 * ((size_t)K + 1)), o_order = o_cursor + up(4 * ((size_t)K + 1)),
+                 o_k = o_order + up(4 * (size_t)n_owned), o_ne = o_k + 256, o_M = o_ne + 256,
+                 o_e = o_M + up(8 * (size_t)K * K), total = o_e + up(8 * ((size_t)K * (K - 1) / 2 + 1));
+    if (ctx->pm_cap < total) {
+        ctx->pm_cap = 0;
+        if (rthc_dev_alloc(ctx, &ctx->d_pm, total + total / 4)) { ctx->err.clear(); return 1; }     // no room: plain rounds
+        ctx->pm_cap = total + total / 4;
+    }
+    unsigned char *base = ctx->d_pm;
+    int32_t *d_dense = reinterpret_cast<int32_t *>(base + o_dense), *d_k = reinterpret_cast<int32_t *>(base + o_k);
+    int32_t *d_order = reinterpret_cast<int32_t *>(base + o_order);
+    uint16_t *d_comp16 = reinterpret_cast<uint16_t *>(base + o_comp16);
+    uint32_t *d_hist = reinterpret_cast<uint32_t *>(base + o_hist), *d_cursor = reinterpret_cast<uint32_t *>(base + o_cursor);
+    unsigned long long *d_M = reinterpret_cast<unsigned long long *>(base + o_M);
+    unsigned long long *d_e = reinterpret_cast<unsigned long long *>(base + o_e);
+    unsigned long long *d_ne = reinterpret_cast<unsigned long long *>(base + o_ne);
+    const unsigned nb = (unsigned)((n + 255) / 256), nbo = (unsigned)((n_owned + 255) / 256);
+    rthc_pm_dense_roots<<<1, 1024, 0, ctx->stream>>>(d_comp, n, d_dense, d_k);
+    RTHC_LAUNCH_CHECK(ctx);
+    rthc_pm_comp16<<<nb, 256, 0, ctx->stream>>>(d_comp, d_dense, n, d_comp16);
+    RTHC_LAUNCH_CHECK(ctx);
+    RTHC_CUDA(ctx, cudaMemsetAsync(d_hist, 0, sizeof(uint32_t) * ((size_t)K + 1), ctx->stream));
+    rthc_pm_count<<<nbo, 256, 0, ctx->stream>>>(ctx->d_owned_rows, n_owned, n, d_comp16, d_hist);
+    RTHC_LAUNCH_CHECK(ctx);
+    rthc_pm_scan<<<1, 1024, 0, ctx->stream>>>(d_hist, K, d_hist + K);          // hist[K] = rows in all
+    RTHC_LAUNCH_CHECK(ctx);
+    RTHC_CUDA(ctx, cudaMemcpyAsync(d_cursor, d_hist, sizeof(uint32_t) * ((size_t)K + 1), cudaMemcpyDeviceToDevice, ctx->stream));
+    rthc_pm_place<<<nbo, 256, 0, ctx->stream>>>(ctx->d_owned_rows, n_owned, n, d_comp16, d_cursor, d_order);
+    RTHC_LAUNCH_CHECK(ctx);
+    RTHC_CUDA(ctx, cudaMemsetAsync(d_M, 0xFF, sizeof(unsigned long long) * (size_t)K * K, ctx->stream));
+    RTHC_CUDA(ctx, cudaMemsetAsync(d_ne, 0, sizeof(unsigned long long), ctx->stream));
+    const size_t smem = sizeof(unsigned long long) * (size_t)K;
+    RTHC_CUDA(ctx, cudaFuncSetAttribute(rthc_pm_pair_min, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    rthc_pm_pair_min<<<(unsigned)((n_owned + PM_ROWS - 1) / PM_ROWS), 256, smem, ctx->stream>>>(
+        ctx->d_cond, ctx->d_row_base, n, d_comp16, d_order, d_hist + K, K, d_M);
+    RTHC_LAUNCH_CHECK(ctx);
+    rthc_pm_extract<<<(unsigned)(((int64_t)K * K + 255) / 256), 256, 0, ctx->stream>>>(d_M, K, d_e, d_ne);
+    RTHC_LAUNCH_CHECK(ctx);
+    unsigned long long ne = 0;
+    int32_t k_dev = 0;
+    RTHC_CUDA(ctx, cudaMemcpyAsync(&ne, d_ne, sizeof(ne), cudaMemcpyDeviceToHost, ctx->stream));
+    RTHC_CUDA(ctx, cudaMemcpyAsync(&k_dev, d_k, sizeof(k_dev), cudaMemcpyDeviceToHost, ctx->stream));
+    RTHC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    if (k_dev != K) return rthc_fail(ctx, RTHC_E_STATE, "contraction: %d components on the device, %d expected", (int)k_dev, K);
+    *d_edges = reinterpret_cast<uint64_t *>(d_e);
+    *m_edges = (int64_t)ne;
+    return 0;
+}
+
 // shared round loop: `scan` launches the lightest-edge pass for the current components.  The forest stays on the
 // device: *d_out (caller frees) holds *m_out keys, ascending when `sorted`.
 template <typename ScanFn>
 static int boruvka_rounds(rthc_ctx *ctx, int64_t n, ScanFn scan, bool sorted, int *hint, uint64_t **d_out, int64_t *m_out,
-                          int64_t full_count = -1)
+                          int64_t full_count = -1, bool contract = false)
 {
+    // contract: after the first round the matrix may be reduced to the lightest edge per pair of components
+    // (pair_min_contract), which the remaining rounds scan instead of calling `scan`
     // full_count: edges of the complete forest when the caller knows it (n - 1 for a connected edge set; fewer for a
     // shard whose first rows belong to other ranks: their samples are isolated here).  Without it a disconnected
     // edge set needs one more round -- one more pass over the matrix -- just to see that nothing is added.
@@ -446,12 +681,20 @@ static int boruvka_rounds(rthc_ctx *ctx, int64_t n, ScanFn scan, bool sorted, in
     // Rounds are queued without waiting for each other: as many as the previous call of this kind needed (a queued
     // round that turns out not to be needed costs nine empty launches), then one by one until the device says done.
     unsigned int st[4] = {0, 0, 0, 0};
-    int batch = std::max(1, *hint);
+    int batch = contract ? 1 : std::max(1, *hint);
+    bool contraction_tried = !contract;
+    uint64_t *d_pair = nullptr;
+    int64_t m_pair = 0;
     while (!st[BST_DONE] && (int64_t)st[BST_COUNT] < stop_n - 1) {
         for (int r = 0; r < batch; ++r) {
             rthc_fill_u64_round<<<nb, 256, 0, ctx->stream>>>(d_best, n, RTHC_KEY_INF, d_state);
             RTHC_LAUNCH_CHECK(ctx);
-            if ((rc = scan(d_comp, d_best, d_state))) return rc;
+            if (d_pair) {
+                if (m_pair > 0) {
+                    rthc_boruvka_scan_edges<<<(unsigned)((m_pair + 255) / 256), 256, 0, ctx->stream>>>(d_pair, m_pair, d_comp, d_best, d_state);
+                    RTHC_LAUNCH_CHECK(ctx);
+                }
+            } else if ((rc = scan(d_comp, d_best, d_state))) return rc;
             rthc_boruvka_hook<<<nb, 256, 0, ctx->stream>>>(d_best, d_comp, d_parent, n, d_keys, d_state);
             RTHC_LAUNCH_CHECK(ctx);
             rthc_boruvka_round_end<<<1, 1, 0, ctx->stream>>>(d_state, stop_n);
@@ -466,6 +709,12 @@ static int boruvka_rounds(rthc_ctx *ctx, int64_t n, ScanFn scan, bool sorted, in
         RTHC_CUDA(ctx, cudaMemcpyAsync(st, d_state, sizeof(st), cudaMemcpyDeviceToHost, ctx->stream));
         RTHC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
         batch = 1;
+        if (!contraction_tried && !st[BST_DONE] && (int64_t)st[BST_COUNT] < stop_n - 1) {
+            contraction_tried = true;
+            rc = pair_min_contract(ctx, n, d_comp, n - (int64_t)st[BST_COUNT], &d_pair, &m_pair);
+            if (rc < 0) return rc;
+            batch = std::max(1, *hint - 1);                   // the rounds the previous call needed after its first
+        }
     }
     const unsigned int total = st[BST_COUNT];
     ctx->boruvka_rounds = (int)st[BST_ROUNDS];
@@ -516,7 +765,7 @@ int rthc_boruvka_owned(rthc_ctx *ctx, bool sorted, uint64_t **d_keys, int64_t *m
     };
     // the owned rows i reach every sample j > i, so the shard's forest spans exactly the samples from its first row on
     const int64_t full_count = n_owned > 0 ? n - 1 - (int64_t)ctx->h_owned_rows.front() : 0;
-    const int rc = boruvka_rounds(ctx, n, scan, sorted, &ctx->boruvka_hint_owned, d_keys, m, full_count);
+    const int rc = boruvka_rounds(ctx, n, scan, sorted, &ctx->boruvka_hint_owned, d_keys, m, full_count, true);
     rthc_dev_free(ctx, &d_bands);
     return rc;
 }

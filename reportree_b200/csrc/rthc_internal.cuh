@@ -66,6 +66,7 @@ struct rthc_ctx {
     int64_t blk_stride_rows = 0;   // plane_rows for a matrix re-coded here; rows_max of the widest rank for gathered planes
     // planes re-coded by locus ranges on several ranks and gathered (rthc_recode_shard / rthc_export_shard / rthc_import_planes):
     // d_planes, d_esc_cnt and d_esc_list then point into the CALLER's gathered buffers and are not freed here
+    unsigned char *d_pm = nullptr; size_t pm_cap = 0;   // scratch of the Boruvka contraction (mst.cu), kept across calls
     uint32_t *d_gbm = nullptr; size_t gbm_cap = 0;     // allele-id bitmaps of the fast re-coder path (recode.cu), kept across calls
     bool planes_borrowed = false;
     int64_t L_stride = 0;          // row stride of the caller's matrix while a column range is re-coded (0: L)

@@ -163,3 +163,47 @@ def test_event_marks_and_stage_timings(hc):
         assert total > 0
         assert 0 < tm["distance_ms"] < total and 0 < tm["linkage_ms"] < total and tm["launches"] > 5
         assert tm["recode_ms"] + tm["distance_ms"] + tm["linkage_ms"] + tm["cut_ms"] <= total * 1.05
+
+
+@pytest.mark.parametrize("kind", ["ties", "clusters"])
+def test_contraction_after_the_first_round_gives_the_same_forest(hc, oracle, monkeypatch, kind):
+    """After Boruvka's first round the matrix is reduced to the lightest edge per pair of components and the remaining
+    rounds scan that list (mst.cu, pair_min_contract; production: n >= 30,000, here forced for small n).  The strict
+    (w, i, j) order makes the forest unique, so Z and every per-shard forest must be IDENTICAL with and without."""
+    rng = np.random.default_rng(12)
+    if kind == "ties":
+        n = 1100
+        X = _rand_codes(rng, n, 25, 3, 0.05)                       # few distinct distances: ties everywhere
+    else:
+        from reportree_b200 import synth
+        n = 2600
+        X = synth.allele_matrix(n, 120, seed=3, missing=0.02, p_mut=0.01, founders=40)
+
+    def run():
+        out = {}
+        with hc.HCContext() as ctx:
+            ctx.set_profiles(X)
+            ctx.distance()
+            out["Z"] = ctx.linkage("single")
+            out["rounds"] = ctx.info()["boruvka_rounds"]
+        for world in (2, 3):
+            for rank in range(world):
+                with hc.HCContext(rank=rank, world=world) as ctx:
+                    ctx.set_profiles(X)
+                    ctx.distance()
+                    out[(world, rank)] = np.sort(ctx.local_forest())
+        return out
+
+    monkeypatch.setenv("RTHC_PAIRMIN_MIN_N", "1000000000")          # never
+    plain = run()
+    monkeypatch.setenv("RTHC_PAIRMIN_MIN_N", "0")                   # always (when at least 2 components are left)
+    contracted = run()
+    assert plain["rounds"] >= 2
+    for k in plain:
+        assert np.array_equal(plain[k], contracted[k]), k
+    y = None
+    with hc.HCContext() as ctx:
+        ctx.set_profiles(X)
+        ctx.distance()
+        y = ctx.condensed().astype(np.float64)
+    assert np.array_equal(contracted["Z"][:, 2], linkage(y, "single")[:, 2])
