@@ -594,10 +594,8 @@ __global__ void rthc_pm_extract(const unsigned long long *__restrict__ M, int K,
 // 1 when it does not
 static int pair_min_contract(rthc_ctx *ctx, int64_t n, const int32_t *d_comp, int64_t comps, uint64_t **d_edges, int64_t *m_edges)
 {
-    const char *env = getenv("RTHC_PAIRMIN_MIN_N");                      // test hook: contraction for small matrices too
-    const int64_t min_n = env ? atoll(env) : 30000;
     const int64_t n_owned = (int64_t)ctx->h_owned_rows.size();
-    if (n < min_n || comps < 2 || comps > PM_KMAX || n_owned == 0 || !ctx->d_cond) return 1;
+    if (comps < 2 || comps > PM_KMAX || n_owned == 0 || !ctx->d_cond) return 1;
     const int K = (int)comps;
     // one scratch block that stays with the context (grow only): blocks of tens of MB that come and go between the
     // GB-sized ones make the stream-ordered pool split and re-grow its large blocks (6 ms per call measured here)
@@ -765,7 +763,13 @@ int rthc_boruvka_owned(rthc_ctx *ctx, bool sorted, uint64_t **d_keys, int64_t *m
     };
     // the owned rows i reach every sample j > i, so the shard's forest spans exactly the samples from its first row on
     const int64_t full_count = n_owned > 0 ? n - 1 - (int64_t)ctx->h_owned_rows.front() : 0;
-    const int rc = boruvka_rounds(ctx, n, scan, sorted, &ctx->boruvka_hint_owned, d_keys, m, full_count, true);
+    // The contraction pays when a pass over the owned rows is long against its own fixed costs (eight small launches,
+    // one more host round trip, and K table entries written per run of rows, which does not shrink with the shard):
+    // C4 measured 16.4 -> 7.8 ms on one GPU, 6.8 -> 4.6 on two, 4.5 -> 3.4 on four, but 2.5 -> 3.3 ms on eight
+    // (6.2e8 owned pairs).  RTHC_PAIRMIN_MIN_N (test hook) replaces the rule by "n at least this".
+    const char *env = getenv("RTHC_PAIRMIN_MIN_N");
+    const bool contract = env ? n >= atoll(env) : ctx->owned_pairs >= 1000000000ll;
+    const int rc = boruvka_rounds(ctx, n, scan, sorted, &ctx->boruvka_hint_owned, d_keys, m, full_count, contract);
     rthc_dev_free(ctx, &d_bands);
     return rc;
 }

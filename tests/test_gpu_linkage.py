@@ -168,7 +168,7 @@ def test_event_marks_and_stage_timings(hc):
 @pytest.mark.parametrize("kind", ["ties", "clusters"])
 def test_contraction_after_the_first_round_gives_the_same_forest(hc, oracle, monkeypatch, kind):
     """After Boruvka's first round the matrix is reduced to the lightest edge per pair of components and the remaining
-    rounds scan that list (mst.cu, pair_min_contract; production: n >= 30,000, here forced for small n).  The strict
+    rounds scan that list (mst.cu, pair_min_contract; production: shards of 1e9 pairs and more, here forced for small n).  The strict
     (w, i, j) order makes the forest unique, so Z and every per-shard forest must be IDENTICAL with and without."""
     rng = np.random.default_rng(12)
     if kind == "ties":
